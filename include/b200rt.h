@@ -1,0 +1,236 @@
+/* b200rt.h - C ABI of the B200-native ray-intersection + shading path.
+ *
+ * Drop-in boundary for the hot path of SpacewaIker/python-raytracer
+ * (citations are file:line under the reference's `provided/`):
+ *
+ *   reference caller           main.py:25-30      load_scene(infile) ; full_scene.render([subimage, tasks])
+ *   reference entry point      scene.py:35-79     Scene.render(subimage, tasks) -> ndarray (W_sub, H, 3)
+ *   reference inner path       scene.py:81-209    cast_ray / _compute_regular_lighting / _compute_refraction
+ *                              geometry/ *.py     intersect / shadow_intersect / is_inside / get_material / get_diffuse
+ *   reference fan-in           glue.py:17-26      concatenate strips, rot90, *255 truncation
+ *
+ * The reference has no FFI of its own (pure Python); the binding a maintainer adds is the
+ * ctypes stub shown in INTEGRATION.md.  Every entry point returns 0 on success or a
+ * non-zero RtStatus; nothing throws across the ABI; there is no hidden global state besides
+ * a thread-local last-error string.  `stream` arguments are `cudaStream_t` passed as void*.
+ *
+ * The SAME scene description (`RtSceneDesc`, host pointers) is consumed by the CPU oracle
+ * (`oracle/rt_oracle.c`, test infrastructure) so that both sides see identical inputs.
+ */
+#ifndef B200RT_H
+#define B200RT_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_ABI_VERSION 1
+
+/* ---- enums ------------------------------------------------------------------------- */
+enum RtKind { RT_KIND_SPHERE = 0, RT_KIND_PLANE = 1, RT_KIND_BOX = 2, RT_KIND_MESH = 3, RT_KIND_NODE = 4 };
+enum RtMatType { RT_MAT_DIFFUSE = 0, RT_MAT_MIRROR = 1, RT_MAT_REFRACTIVE = 2 };      /* scene.py:97,105 */
+enum RtLightType { RT_LIGHT_POINT = 0, RT_LIGHT_DIRECTIONAL = 1 };                   /* scene.py:153,156 */
+enum RtCsg { RT_CSG_UNION = 0, RT_CSG_INTERSECTION = 1, RT_CSG_DIFFERENCE = 2, RT_CSG_NONE = 3 }; /* hierarchy.py:49-58 */
+enum RtGate { RT_GATE_AABB = 0, RT_GATE_SPHERE = 1 };                                 /* mesh.py:48-51 */
+
+enum RtStatus {
+    RT_OK = 0,
+    RT_ERR_INVALID = 1,      /* bad argument / inconsistent description */
+    RT_ERR_CUDA = 2,         /* a CUDA runtime call failed; see rt_last_error() */
+    RT_ERR_NOMEM = 3,
+    RT_ERR_NO_MATERIAL = 4,  /* a shaded hit had no material (reference: IndexError, geometry/__init__.py:57) */
+    RT_ERR_LIMIT = 5         /* scene exceeds a compiled limit (CSG nesting depth, lights) */
+};
+
+/* ---- scene records (plain data, host pointers) ------------------------------------- */
+
+/* helperclasses.py:28-37 ; scene_parser.py:129-142 */
+typedef struct RtMaterial {
+    float diffuse[3];
+    float specular[3];
+    int32_t type;       /* RtMatType */
+    int32_t _pad;
+    double hardness;    /* exponent of scene.py:181 (Python number) */
+    double tint;        /* scene.py:104,108 (Python float) */
+    double refr_index;  /* scene.py:191,194 (Python float) */
+} RtMaterial;           /* 56 bytes */
+
+/* helperclasses.py:50-56 ; scene_parser.py:107-122 */
+typedef struct RtLight {
+    int32_t type;       /* RtLightType */
+    float colour[3];
+    float vector[3];    /* point: position ; directional: direction */
+    float power;
+} RtLight;              /* 32 bytes */
+
+/* One geometry object (leaf primitive or CSG/transform node).  Top-level objects come
+ * first, in scene order (scene.py:87 iterates them in that order); the children of a node
+ * are contiguous at [first_child, first_child + n_children).
+ *   sphere  simple_geometry.py:12-83    a = center, radius
+ *   plane   simple_geometry.py:86-176   a = point, b = normal, ax_w/ax_h = texture/checker axes, tex, tex_scale
+ *   box     simple_geometry.py:179-355  a = minpos, b = maxpos, tex
+ *   mesh    mesh.py:16-156              mesh = index into meshes[]
+ *   node    hierarchy.py:11-146         csg, xform = index into xforms[], children
+ */
+typedef struct RtObject {
+    int32_t kind;        /* RtKind */
+    int32_t n_mats;      /* len(materials) after set_fallback_material (hierarchy.py:21-28) */
+    int32_t mat0, mat1;  /* materials[0], materials[1] as indices into materials[] (-1 = absent) */
+    int32_t tex;         /* texture index or -1 */
+    int32_t mesh;        /* mesh index or -1 */
+    int32_t first_child; /* node */
+    int32_t n_children;  /* node */
+    int32_t csg;         /* RtCsg (node) */
+    int32_t xform;       /* index into xforms[] (node) */
+    float radius;        /* sphere */
+    float _pad0;
+    float a[3];
+    float b[3];
+    float speed[3];      /* (0,0,0) when the reference's speed is None */
+    float ax_w[3];       /* plane width_axis  simple_geometry.py:93-102 */
+    float ax_h[3];       /* plane height_axis simple_geometry.py:103 */
+    float _pad1;
+    double tex_scale;    /* plane texture_scale (simple_geometry.py:158-160), 1.0 default */
+    double radius_d;     /* sphere radius as the Python float the parser read (used by the oracle) */
+} RtObject;              /* 128 bytes */
+
+/* hierarchy.py:30-37: M = T*Rx*Ry*Rz*S, Minv = inverse(M); column-major (m[col*4+row]) like GLM */
+typedef struct RtXform {
+    float M[16];
+    float Minv[16];
+} RtXform;
+
+/* mesh.py:17-51: vertices already (v + translate) * scale; per-vertex normals already
+ * area-weighted and normalised (NULL when flat shaded); gate = the bounding volume chosen at mesh.py:48-51 */
+typedef struct RtMesh {
+    int32_t n_verts;
+    int32_t n_faces;
+    const float* verts;      /* n_verts * 3 */
+    const int32_t* faces;    /* n_faces * 3 */
+    const float* vnormals;   /* n_verts * 3 or NULL */
+    int32_t flat_shaded;
+    int32_t gate;            /* RtGate */
+    float gate_min[3];
+    float gate_max[3];
+    float gate_center[3];
+    float gate_radius;
+    float _pad[2];
+} RtMesh;
+
+/* PIL image as the reference samples it: getpixel((i, j)) = rgb[(j*width + i)*3 ...] */
+typedef struct RtTexture {
+    int32_t width, height;
+    const uint8_t* rgb;
+} RtTexture;
+
+/* The whole scene: what scene_parser.load_scene() hands to scene.Scene (scene_parser.py:158) */
+typedef struct RtSceneDesc {
+    int32_t abi_version;     /* RT_ABI_VERSION */
+    int32_t width, height;   /* helperclasses.py:75-79 */
+    /* camera basis and frustum, helperclasses.py:81-94 */
+    float cam_pos[3], cam_u[3], cam_v[3], cam_w[3];
+    double cam_d, left, right, bottom, top;
+    /* lens and sampling, helperclasses.py:96-108 ; scene.py:28-29 */
+    double focal_length, aperture;
+    int32_t dof_samples, aa_samples, jitter;
+    int32_t n_times;
+    const double* motion_times;
+    float ambient[3];
+    int32_t max_depth;       /* cast_ray's max_recursion default, scene.py:81 (10) */
+    uint64_t jitter_seed;    /* Philox4x32-10 key; counter = ((col*H+row)*D+dof)*S+aa */
+    int32_t n_lights;
+    int32_t n_materials;
+    int32_t n_objects;       /* all objects, top-level first */
+    int32_t n_top;           /* len(scene.objects) */
+    int32_t n_xforms;
+    int32_t n_meshes;
+    int32_t n_textures;
+    int32_t _pad;
+    const RtLight* lights;
+    const RtMaterial* materials;
+    const RtObject* objects;
+    const RtXform* xforms;
+    const RtMesh* meshes;
+    const RtTexture* textures;
+} RtSceneDesc;
+
+/* Which pixels one call renders.  The region [col0,col0+ncols) x [row0,row0+nrows) is cut
+ * into tile_w x tile_h tiles numbered column-major (tile = tcol * n_tile_rows + trow);
+ * this call renders the tiles with tile % world == rank (scene.py:36-37 strips generalised
+ * to interleaved tiles for load balance; glue.py:19-22 is the gather).  With world == 1 and
+ * direct != 0 the output is written straight in the reference layout (ncols, nrows, 3);
+ * otherwise it is the compact tile buffer (n_local_tiles, tile_w, tile_h, 3) that
+ * rt_assemble_tiles() scatters into the reference layout. */
+typedef struct RtRenderJob {
+    int32_t col0, ncols, row0, nrows;
+    int32_t tile_w, tile_h;
+    int32_t rank, world;
+    int32_t direct;
+    int32_t mesh_mode;       /* 0 = LBVH traversal, 1 = brute force over all faces (test aid, mesh.py:77) */
+    int64_t max_batch_rays;  /* 0 = default */
+} RtRenderJob;
+
+/* Device-side tallies of one rt_render call */
+typedef struct RtCounters {
+    uint64_t rays_primary;
+    uint64_t rays_shadow;
+    uint64_t rays_reflect;
+    uint64_t rays_refract;
+    uint64_t bvh_nodes;      /* BVH nodes fetched */
+    uint64_t tri_tests;      /* triangles tested */
+    uint64_t prim_tests;     /* analytic primitive tests */
+    uint64_t shaded_hits;
+    uint64_t mesh_hits_smooth;
+    uint64_t queued_rays;    /* secondary rays written to / read from the compacted queues */
+    uint64_t kernel_launches;/* launches issued by this call */
+    uint64_t error_flags;    /* bit (RtStatus) set by kernels */
+} RtCounters;
+
+typedef struct RtScene RtScene;  /* opaque, device-resident */
+
+/* ---- entry points -------------------------------------------------------------------- */
+
+/* Replaces scene.Scene.__init__ + the per-object state built by scene_parser.load_scene
+ * (scene_parser.py:158-161): copies the description to HBM in SoA form and precomputes the
+ * pixel-centre and sunflower tables of scene.py:41-43,118-138. */
+int rt_scene_create(const RtSceneDesc* desc, RtScene** out);
+
+/* Replaces the per-ray brute-force face loop set-up (mesh.py:72-77): builds one LBVH per
+ * mesh on the GPU (Morton codes, radix sort, Karras hierarchy, bottom-up refit). */
+int rt_scene_build_bvh(RtScene* scene, void* stream);
+
+/* Replaces Scene.render(subimage, tasks) (scene.py:35-79).  d_out is DEVICE memory:
+ * job->direct ? (ncols, nrows, 3) : (n_local_tiles, tile_w, tile_h, 3), float32.
+ * counters may be NULL; when given, the call synchronises the stream before returning. */
+int rt_render(RtScene* scene, const RtRenderJob* job, float* d_out, RtCounters* counters, void* stream);
+
+/* Same, HOST output buffer (pageable or pinned): device staging + D2H copy inside the call;
+ * synchronous.  This is the end-to-end call Scene.render() uses. */
+int rt_render_host(RtScene* scene, const RtRenderJob* job, float* h_out, RtCounters* counters, void* stream);
+
+/* Number of pixels / tiles a job writes for (rank, world): sizes the compact buffer. */
+int rt_job_extent(const RtRenderJob* job, int64_t* n_local_tiles, int64_t* n_floats);
+
+/* Replaces glue.py:19-22: scatter `world` compact tile buffers (concatenated in rank order,
+ * each rank's buffer starting at rank_offsets_floats[r]) into the reference layout (ncols, nrows, 3). */
+int rt_assemble_tiles(const RtRenderJob* job, const float* d_gathered, const int64_t* rank_offsets_floats,
+                      float* d_out, void* stream);
+
+/* Replaces main.py:31-33 / glue.py:23-25: rot90 + (image*255) truncation, (ncols,nrows,3) f32 -> (nrows,ncols,3) u8 */
+int rt_finalize_u8(const float* d_image, int32_t ncols, int32_t nrows, uint8_t* d_out_u8, void* stream);
+
+int rt_scene_destroy(RtScene* scene);
+
+/* Introspection used by tests and the bench */
+int rt_scene_bvh_stats(const RtScene* scene, int32_t mesh, int64_t* n_nodes, int64_t* n_leaf_tris, int64_t* bytes);
+/* Copies the LBVH of `mesh` back to host buffers for validation: nodes (n_nodes*16 floats), leaf order (n_faces int32) */
+int rt_scene_bvh_download(const RtScene* scene, int32_t mesh, float* h_nodes, int32_t* h_order);
+const char* rt_last_error(void);
+int rt_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200RT_H */

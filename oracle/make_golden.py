@@ -1,0 +1,139 @@
+"""Generate tests/golden/ from the UNMODIFIED reference (tier-0 oracle).  Dev container only.
+
+    python oracle/make_golden.py [--only NAME ...]
+
+Inputs are read from /root/reference (scenes, torus.obj, textures) and re-serialised into
+tests/golden/{scenes,meshes,textures}/ so that the GPU box (which has no /root/reference) can
+load the same scenes; outputs are the reference's own renders of those inputs, executed
+through oracle/shims by oracle/ref_runner.py:
+
+    tests/golden/renders/<case>.png       (H,W,3) uint8, exactly main.py:31-33's PNG
+    tests/golden/renders/<case>_f32.npz   every 4th column/row of the float image (values are
+                                          float32-exact: scene.py:73 divides a float32 vec3)
+    tests/golden/MANIFEST.json            per case: scene file, overrides, seed, and whether the
+                                          render is bit-identical to the author's renders/*.png
+
+Jittered cases draw from Philox4x32-10 (oracle/philox.py) instead of the unseeded global
+numpy RNG (scene.py:64), so they are reproducible; the author's jittered PNGs are only
+statistically comparable and are not used.
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+from PIL import Image
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE)
+import ref_runner  # noqa: E402
+
+REF = ref_runner.REFERENCE
+OUT = os.path.join(HERE, "..", "tests", "golden")
+
+SCENES = {  # golden scene name -> reference file
+    "TwoSpheresPlane": "scenes/TwoSpheresPlane.json",
+    "MirrorRefraction": "scenes/MirrorRefraction.json",
+    "MotionBlur": "scenes/MotionBlur.json",
+    "TorusMesh": "test_scenes/TorusMesh.json",   # scenes/TorusMesh.json points at a bunny.obj that is not shipped
+    "DepthOfField": "scenes/DepthOfField.json",
+    "NovelScene1": "scenes/NovelScene1.json",
+    "NovelScene2": "scenes/NovelScene2.json",
+}
+
+
+def _torus_smooth():
+    with open(os.path.join(REF, SCENES["TorusMesh"])) as fh:
+        objs = json.load(fh)["objects"]
+    for o in objs:
+        if o["type"] == "mesh":
+            o["flat_shaded"] = False
+    return {"objects": objs}
+
+
+CASES = [  # (case, scene, overrides, author's render to cross-check or None)
+    ("TwoSpheresPlane", "TwoSpheresPlane", None, "renders/TwoSpheresPlane.png"),
+    ("MirrorRefraction", "MirrorRefraction", None, "renders/MirrorRefraction.png"),
+    ("MotionBlur", "MotionBlur", None, "renders/MotionBlur.png"),
+    ("TorusMesh_flat", "TorusMesh", None, "renders/TorusMesh_flat.png"),
+    ("TorusMesh_smooth", "TorusMesh", "torus_smooth", "renders/TorusMesh.png"),
+    ("DepthOfField", "DepthOfField", None, None),
+    ("NovelScene1_small", "NovelScene1", {"resolution": [256, 128], "AA": {"jitter": True, "samples": 2}}, None),
+    ("NovelScene2_small", "NovelScene2", {"resolution": [128, 64], "AA": {"jitter": True, "samples": 2},
+                                          "DOF": {"samples": 3}, "motion": {"samples": 3, "final": 1}}, None),
+]
+
+
+def export_inputs():
+    os.makedirs(os.path.join(OUT, "scenes"), exist_ok=True)
+    os.makedirs(os.path.join(OUT, "meshes"), exist_ok=True)
+    os.makedirs(os.path.join(OUT, "textures"), exist_ok=True)
+    textures = set()
+
+    def walk(objs):
+        for o in objs:
+            if "texture" in o:
+                textures.add(o["texture"])
+            walk(o.get("children", []))
+
+    for name, rel in SCENES.items():
+        with open(os.path.join(REF, rel)) as fh:
+            data = json.load(fh)
+        walk(data["objects"])
+        with open(os.path.join(OUT, "scenes", name + ".json"), "w") as fh:
+            json.dump(data, fh, separators=(",", ":"))
+    for t in sorted(textures):
+        im = Image.open(os.path.join(REF, t))
+        assert t.endswith(".png")
+        im.save(os.path.join(OUT, t), optimize=True)   # same pixels and mode, re-encoded
+    # torus: keep only v / f rows
+    with open(os.path.join(REF, "meshes/torus.obj")) as fh, open(os.path.join(OUT, "meshes", "torus.obj"), "w") as out:
+        out.write("# tests/golden fixture: v/f rows of the reference's meshes/torus.obj\n")
+        for line in fh:
+            p = line.split()
+            if p and p[0] in ("v", "f"):
+                out.write(" ".join(p) + "\n")
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--only", nargs="*", default=None)
+    ap.add_argument("--seed", type=lambda s: int(s, 0), default=0x5EED)
+    a = ap.parse_args()
+    export_inputs()
+    os.makedirs(os.path.join(OUT, "renders"), exist_ok=True)
+    man_path = os.path.join(OUT, "MANIFEST.json")
+    manifest = json.load(open(man_path)) if os.path.exists(man_path) else {}
+    for case, scene, ov, author in CASES:
+        if a.only and case not in a.only:
+            continue
+        overrides = _torus_smooth() if ov == "torus_smooth" else ov
+        t0 = time.time()
+        img, cpu = ref_runner.render_reference(SCENES[scene], overrides=overrides, seed=a.seed)
+        png = ref_runner.to_png_array(img)
+        assert np.array_equal(img.astype(np.float32).astype(np.float64), img)
+        Image.fromarray(png).save(os.path.join(OUT, "renders", case + ".png"), optimize=True)
+        cols = np.arange(0, img.shape[0], 4)
+        rows = np.arange(0, img.shape[1], 4)
+        np.savez_compressed(os.path.join(OUT, "renders", case + "_f32.npz"), cols=cols, rows=rows,
+                            rgb=img[np.ix_(cols, rows)].astype(np.float32))
+        entry = {"scene": scene + ".json", "overrides": overrides, "seed": a.seed,
+                 "width": int(img.shape[0]), "height": int(img.shape[1]),
+                 "reference_cpu_seconds": round(cpu, 1), "generator": "oracle/make_golden.py"}
+        if author:
+            ref_png = np.array(Image.open(os.path.join(REF, author)).convert("RGB"))
+            diff = np.abs(ref_png.astype(int) - png.astype(int)).max(axis=2)
+            entry["author_render"] = author
+            entry["author_render_max_abs_diff_u8"] = int(diff.max())
+            entry["author_render_pixels_differing"] = int((diff > 0).sum())
+        manifest[case] = entry
+        print(f"{case}: {img.shape} {time.time()-t0:.1f}s wall {cpu:.1f}s cpu "
+              f"author-diff={entry.get('author_render_max_abs_diff_u8')}", flush=True)
+        with open(man_path, "w") as fh:
+            json.dump(manifest, fh, indent=1, sort_keys=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,727 @@
+// rt_core.cuh - per-ray device functions of the render path: primitive intersection, LBVH
+// traversal, CSG/transform nodes, closest hit, any-hit shadow test, Blinn-Phong shading.
+//
+// Written from scratch for the GPU; each function cites the reference lines whose RESULTS it
+// must reproduce (file:line under the reference's provided/).  fp32 throughout.
+#pragma once
+#include "rt_types.cuh"
+
+#define RT_EPS 1e-4f                 // geometry/__init__.py:12
+#define RT_SHADOW_EPS 1e-4f          // geometry/__init__.py:39
+#define RT_SHADOW_EPS_SPHERE 1e-3f   // simple_geometry.py:13
+
+#if defined(__CUDA_ARCH__)
+#define RT_RSQRT(x) rsqrtf(x)
+#else
+#define RT_RSQRT(x) (1.0f / sqrtf(x))
+#endif
+
+RT_HD float4 ld4(const float4* p) { return RT_LDG(p); }
+RT_HD int as_int(float f) { union { float f; int i; } u; u.f = f; return u.i; }
+RT_HD float as_float(int i) { union { float f; int i; } u; u.i = i; return u.f; }
+
+struct TraceCtx {
+    const SceneView& S;
+    float time;          // scene.current_time of this ray (scene.py:68), carried per ray
+    Tally& tally;
+    int* stack;          // BVH traversal stack of this thread: entry k at stack[k * stack_stride]
+    int stack_stride;
+};
+
+// `center + speed * current_time` (simple_geometry.py:21-24,106-109,189-194)
+RT_HD float3 moved(const DevObject* o, float3 base, float time) { return base + f3(ld4(&o->speed)) * time; }
+
+// ------------------------------------------------------------------------------------------------
+// Sphere (simple_geometry.py:20-80).  A = d.d is ray-constant and passed in.
+RT_HD bool sphere_roots(float3 center, float radius, const Ray& r, float A, float& t1, float& t2) {
+    float3 oc = r.o - center;
+    float B = 2.0f * dot(r.d, oc);
+    float Cc = dot(oc, oc) - radius * radius;
+    float disc = B * B - 4.0f * A * Cc;
+    if (disc < 0.0f) return false;
+    float sq = sqrtf(disc);
+    float inv2a = 1.0f / (2.0f * A);
+    t1 = (-B - sq) * inv2a;
+    t2 = (-B + sq) * inv2a;
+    return true;
+}
+
+// Plane (simple_geometry.py:105-131): |d.n| > eps, t = (point - o).n / d.n (caller applies the t window)
+RT_HD bool plane_t(float3 point, float3 n, const Ray& r, float& t) {
+    float denom = dot(r.d, n);
+    if (!(fabsf(denom) > RT_EPS)) return false;
+    t = dot(point - r.o, n) / denom;
+    return true;
+}
+
+// Checkerboard material choice (simple_geometry.py:133-148)
+RT_HD int plane_material(const DevObject* o, float3 p, float time) {
+    if (o->n_mats == 1) return o->mat0;
+    if (o->n_mats == 0) return -2;
+    float3 position = moved(o, f3(ld4(&o->a)), time);
+    float3 n = f3(ld4(&o->b));
+    float3 pp = p - n * dot(p - position, n);
+    float x = dot(pp - position, f3(ld4(&o->ax_w)));
+    float z = dot(pp - position, f3(ld4(&o->ax_h)));
+    double s = floor((double)position.x - (double)x) + floor((double)position.z - (double)z);
+    double parity = s - 2.0 * floor(s * 0.5);       // Python (dx + dz) % 2
+    return parity == 0.0 ? o->mat0 : o->mat1;
+}
+
+// Box slab test with labelled entry interval (simple_geometry.py:196-226, helperclasses.py:62-66).
+// Returns false on the reference's early `return []` (zero direction component with the origin outside).
+RT_HD bool box_slabs(float3 mn, float3 mx, const Ray& r, float& entry, float& exit_, int& label) {
+    float st[3], en[3];
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int k = 0; k < 3; k++) {
+        float o = comp(r.o, k), d = comp(r.d, k), lo = comp(mn, k), hi = comp(mx, k);
+        if (d == 0.0f) {
+            if (!(lo < o && o < hi)) return false;
+            st[k] = -RT_INF; en[k] = RT_INF;
+        } else {
+            float t1 = (lo - o) / d, t2 = (hi - o) / d;
+            st[k] = fminf(t1, t2); en[k] = fmaxf(t1, t2);
+        }
+    }
+    entry = st[0]; label = 0;                           // max(..., key=start): first maximal wins
+    if (st[1] > entry) { entry = st[1]; label = 1; }
+    if (st[2] > entry) { entry = st[2]; label = 2; }
+    exit_ = en[0];                                      // min(..., key=end)
+    if (en[1] < exit_) exit_ = en[1];
+    if (en[2] < exit_) exit_ = en[2];
+    return true;
+}
+RT_HD float3 box_normal(const Ray& r, int label) {     // simple_geometry.py:231-242
+    float d = comp(r.d, label);
+    float s = d < 0.0f ? 1.0f : (d > 0.0f ? -1.0f : 0.0f);
+    return f3(label == 0 ? s : 0.0f, label == 1 ? s : 0.0f, label == 2 ? s : 0.0f);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Mesh gate (bounding_volumes.py:18-37,49-83; SURVEY Q11: a ray starting inside the AABB never hits the mesh)
+RT_HD bool mesh_gate(const DevMesh* m, const Ray& r) {
+    if (m->gate == RT_GATE_SPHERE) {
+        float t1, t2;
+        if (!sphere_roots(f3(ld4(&m->gate_center)), m->gate_radius, r, dot(r.d, r.d), t1, t2)) return false;
+        return t1 > 0.0f || t2 > 0.0f;
+    }
+    float en, ex; int label;
+    if (!box_slabs(f3(ld4(&m->gate_min)), f3(ld4(&m->gate_max)), r, en, ex, label)) return false;
+    return !(en > ex || en < 0.0f);
+}
+
+// Triangle tests.  Closest-hit form (mesh.py:82-102): plane hit with the NORMALISED face normal,
+// |d.n| < 1e-4 rejected, t < 0 rejected, three inclusive edge tests.
+RT_HD bool tri_hit(float3 v0, float3 v1, float3 v2, const Ray& r, float& t) {
+    float3 c = cross(v1 - v0, v2 - v0);
+    float3 n = c * RT_RSQRT(dot(c, c));
+    float denom = dot(r.d, n);
+    if (fabsf(denom) < RT_EPS) return false;
+    t = dot(v0 - r.o, n) / denom;
+    if (t < 0.0f) return false;
+    float3 p = r.o + r.d * t;
+    float b0 = dot(cross(v1 - v0, p - v0), n);
+    float b1 = dot(cross(v2 - v1, p - v1), n);
+    float b2 = dot(cross(v0 - v2, p - v2), n);
+    return b0 >= 0.0f && b1 >= 0.0f && b2 >= 0.0f;
+}
+// Shadow form (mesh.py:125-151): UN-normalised normal with the same 1e-4 cut-off, t < shadow_epsilon skipped,
+// no upper bound on t.
+RT_HD bool tri_shadow(float3 v0, float3 v1, float3 v2, const Ray& r) {
+    float3 n = cross(v1 - v0, v2 - v0);
+    float denom = dot(r.d, n);
+    if (fabsf(denom) < RT_EPS) return false;
+    float t = dot(v0 - r.o, n) / denom;
+    if (t < RT_SHADOW_EPS) return false;
+    float3 p = r.o + r.d * t;
+    return dot(cross(v1 - v0, p - v0), n) >= 0.0f && dot(cross(v2 - v1, p - v1), n) >= 0.0f &&
+           dot(cross(v0 - v2, p - v2), n) >= 0.0f;
+}
+
+// Ray / two-child-box node test.  Conservative: NaNs from 0*inf drop out of fminf/fmaxf.
+RT_HD void node_slabs(const BvhNode& nd, float3 o, float3 inv, float tmin, float tmax, bool& h0, bool& h1, float& n0, float& n1) {
+    float ax = (nd.q0.x - o.x) * inv.x, bx = (nd.q0.w - o.x) * inv.x;
+    float ay = (nd.q0.y - o.y) * inv.y, by = (nd.q1.x - o.y) * inv.y;
+    float az = (nd.q0.z - o.z) * inv.z, bz = (nd.q1.y - o.z) * inv.z;
+    n0 = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), tmin));
+    float f0 = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), tmax));
+    h0 = n0 <= f0;
+    ax = (nd.q1.z - o.x) * inv.x; bx = (nd.q2.y - o.x) * inv.x;
+    ay = (nd.q1.w - o.y) * inv.y; by = (nd.q2.z - o.y) * inv.y;
+    az = (nd.q2.x - o.z) * inv.z; bz = (nd.q2.w - o.z) * inv.z;
+    n1 = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), tmin));
+    float f1 = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), tmax));
+    h1 = n1 <= f1;
+}
+
+// LBVH traversal.  `onTri(slot, tmax)` tests triangle `slot`, may shrink tmax, returns true to stop.
+// Replaces the face loops of mesh.py:77 and :125 (brute force kept as mesh_mode 1 for the equivalence test).
+template <class OnTri>
+RT_HD void mesh_visit(TraceCtx& cx, const DevMesh* m, const Ray& r, float tmin, float& tmax, OnTri&& onTri) {
+    const int n = m->n_tris;
+    if (n <= 0) return;
+    if (cx.S.mesh_mode == 1 || n == 1) {
+        for (int s = 0; s < n; s++) { cx.tally.tris++; if (onTri(s, tmax)) return; }
+        return;
+    }
+    const BvhNode* nodes = m->nodes;
+    float3 inv = f3(1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z);
+    int* stk = cx.stack; const int stride = cx.stack_stride;
+    int sp = 0, node = 0;
+    for (;;) {
+        BvhNode nd;
+        nd.q0 = ld4(&nodes[node].q0); nd.q1 = ld4(&nodes[node].q1);
+        nd.q2 = ld4(&nodes[node].q2); nd.q3 = ld4(&nodes[node].q3);
+        cx.tally.nodes++;
+        bool h0, h1; float n0, n1;
+        node_slabs(nd, r.o, inv, tmin, tmax, h0, h1, n0, n1);
+        int c0 = as_int(nd.q3.x), c1 = as_int(nd.q3.y);
+        if (h0 && c0 < 0) { cx.tally.tris++; if (onTri(~c0, tmax)) return; h0 = false; }
+        if (h1 && c1 < 0) { if (n1 <= tmax) { cx.tally.tris++; if (onTri(~c1, tmax)) return; } h1 = false; }
+        if (h0 && n0 > tmax) h0 = false;
+        if (h1 && n1 > tmax) h1 = false;
+        if (h0 && h1) {
+            int nearc = c0, farc = c1;
+            if (n1 < n0) { nearc = c1; farc = c0; }
+            if (sp < RT_STACK_DEPTH) stk[(sp++) * stride] = farc;
+            else cx.tally.err |= 1u << RT_ERR_LIMIT;
+            node = nearc;
+        } else if (h0) node = c0;
+        else if (h1) node = c1;
+        else {
+            if (sp == 0) return;
+            node = stk[(--sp) * stride];
+        }
+    }
+}
+
+RT_HD void tri_load(const DevMesh* m, int slot, float3& v0, float3& v1, float3& v2, int& face) {
+    float4 a = ld4(m->tri + 3 * (size_t)slot), b = ld4(m->tri + 3 * (size_t)slot + 1), c = ld4(m->tri + 3 * (size_t)slot + 2);
+    v0 = f3(a); v1 = f3(b); v2 = f3(c); face = as_int(a.w);
+}
+
+// Shading normal of an accepted triangle hit (mesh.py:84,103-113); barycentrics as libigl computes them
+RT_HD float3 tri_normal(TraceCtx& cx, const DevMesh* m, int slot, float3 p) {
+    float3 v0, v1, v2; int face;
+    tri_load(m, slot, v0, v1, v2, face);
+    if (m->flat_shaded || m->vnormals == nullptr) return normalize(cross(v1 - v0, v2 - v0));
+    cx.tally.smooth++;
+    float3 e0 = v1 - v0, e1 = v2 - v0, e2 = p - v0;
+    float d00 = dot(e0, e0), d01 = dot(e0, e1), d11 = dot(e1, e1), d20 = dot(e2, e0), d21 = dot(e2, e1);
+    float denom = d00 * d11 - d01 * d01;
+    float l1 = (d11 * d20 - d01 * d21) / denom;
+    float l2 = (d00 * d21 - d01 * d20) / denom;
+    float l0 = 1.0f - (l1 + l2);
+    int4 vi = RT_LDG(m->face_vidx + slot);
+    float3 n0 = f3(ld4(m->vnormals + vi.x)), n1 = f3(ld4(m->vnormals + vi.y)), n2 = f3(ld4(m->vnormals + vi.z));
+    return normalize((n0 * l0 + n1 * l1) + n2 * l2);
+}
+
+// Mesh.shadow_intersect (mesh.py:121-153): gate, then any accepted face; t_max is ignored by the reference
+RT_HD bool mesh_shadow(TraceCtx& cx, const DevMesh* m, const Ray& r) {
+    if (!mesh_gate(m, r)) return false;
+    bool occ = false;
+    float tmax = RT_INF;
+    mesh_visit(cx, m, r, RT_SHADOW_EPS * 0.5f, tmax, [&](int slot, float&) {
+        float3 v0, v1, v2; int face;
+        tri_load(m, slot, v0, v1, v2, face);
+        if (tri_shadow(v0, v1, v2, r)) { occ = true; return true; }
+        return false;
+    });
+    return occ;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Texture / diffuse lookups (scene.py:143-146)
+RT_HD float3 texel(const DevTexture* t, long long i, long long j) {
+    i = i < 0 ? 0 : (i >= t->width ? t->width - 1 : i);     // the reference would raise IndexError; clamp
+    j = j < 0 ? 0 : (j >= t->height ? t->height - 1 : j);
+    const uint8_t* px = t->rgb + ((size_t)j * (size_t)t->width + (size_t)i) * 3;
+    return f3((float)(RT_LDG(px) / 255.0), (float)(RT_LDG(px + 1) / 255.0), (float)(RT_LDG(px + 2) / 255.0));
+}
+RT_HD double py_mod(double a, double m) { double r = fmod(a, m); return (r != 0.0 && r < 0.0) ? r + m : r; }
+
+// Plane.get_diffuse (simple_geometry.py:150-173): tiled nearest texel, or the checker material's diffuse
+RT_HD float3 plane_diffuse(const SceneView& S, const DevObject* o, float3 p, float time, Tally& tally) {
+    if (o->tex >= 0) {
+        const DevTexture* tx = S.textures + o->tex;
+        float3 n = f3(ld4(&o->b));
+        float3 base = f3(ld4(&o->a));
+        float3 position = moved(o, base, time);
+        float3 pp = p - n * dot(p - base, n);                 // projection uses the UN-moved point (:163)
+        double u = (double)dot(pp - position, f3(ld4(&o->ax_w))) * 1000.0 / o->tex_scale;
+        double v = (double)dot(pp - position, f3(ld4(&o->ax_h))) * 1000.0 / o->tex_scale;
+        return texel(tx, (long long)py_mod(u, (double)tx->width), (long long)py_mod(v, (double)tx->height));
+    }
+    int m = plane_material(o, p, time);
+    if (m < 0) { tally.err |= 1u << RT_ERR_NO_MATERIAL; return f3(0, 0, 0); }
+    return f3(ld4(&S.materials[m].diffuse));
+}
+// AABB.get_diffuse (simple_geometry.py:312-355): cube-face mapping (PIL truncates the float indices)
+RT_HD float3 box_diffuse(const SceneView& S, const DevObject* o, float3 p, float time, Tally& tally) {
+    if (o->tex >= 0) {
+        const DevTexture* tx = S.textures + o->tex;
+        float3 mn = moved(o, f3(ld4(&o->a)), time), mx = moved(o, f3(ld4(&o->b)), time);
+        double W = tx->width, H = tx->height;
+        double x = ((double)p.x - mn.x) / ((double)mx.x - mn.x);
+        double y = ((double)p.y - mn.y) / ((double)mx.y - mn.y);
+        double z = ((double)p.z - mn.z) / ((double)mx.z - mn.z);
+        double i, j;
+        if (fabs((double)p.x - mn.x) < 1e-4) { i = z * W; j = (1 - y) * H; }
+        else if (fabs((double)p.x - mx.x) < 1e-4) { i = (1 - z) * W; j = (1 - y) * H; }
+        else if (fabs((double)p.y - mn.y) < 1e-4) { i = x * W; j = (1 - z) * H; }
+        else if (fabs((double)p.y - mx.y) < 1e-4) { i = x * W; j = z * H; }
+        else if (fabs((double)p.z - mn.z) < 1e-4) { i = (1 - x) * W; j = (1 - y) * H; }
+        else if (fabs((double)p.z - mx.z) < 1e-4) { i = x * W; j = (1 - y) * H; }
+        else { i = 0; j = 0; }
+        i = fmin(fmax(0.0, i), W - 1);
+        j = fmin(fmax(0.0, j), H - 1);
+        return texel(tx, (long long)i, (long long)j);
+    }
+    if (o->n_mats < 1) { tally.err |= 1u << RT_ERR_NO_MATERIAL; return f3(0, 0, 0); }
+    return f3(ld4(&S.materials[o->mat0].diffuse));
+}
+
+// ------------------------------------------------------------------------------------------------
+// CSG / transform nodes (hierarchy.py:42-138).  Recursion is unrolled at compile time to
+// RT_MAX_NEST levels (template depth), no device call stack.
+
+RT_HD bool difference_shadow(TraceCtx& cx, int c0, const Ray& mr);
+
+template <int D> struct Nest {
+    // is_inside (hierarchy.py:111-129; Sphere :74-80, AABB :296-307; Plane/Mesh: base class False)
+    static RT_HD bool inside(TraceCtx& cx, int oi, float3 p) {
+        const DevObject* o = cx.S.objects + oi;
+        switch (o->kind) {
+            case RT_KIND_SPHERE: {
+                float4 a = ld4(&o->a);
+                float3 q = p - moved(o, f3(a), cx.time);
+                return sqrtf(dot(q, q)) < a.w;
+            }
+            case RT_KIND_BOX: {
+                float3 mn = moved(o, f3(ld4(&o->a)), cx.time), mx = moved(o, f3(ld4(&o->b)), cx.time);
+                return mn.x < p.x && p.x < mx.x && mn.y < p.y && p.y < mx.y && mn.z < p.z && p.z < mx.z;
+            }
+            case RT_KIND_NODE: {
+                float3 q = xform_point(cx.S.xforms[o->xform].Minv, p);
+                const int c0 = o->first_child, nc = o->n_children;
+                if (o->csg == RT_CSG_UNION) {
+                    for (int k = 0; k < nc; k++) if (Nest<D - 1>::inside(cx, c0 + k, q)) return true;
+                    return false;
+                } else if (o->csg == RT_CSG_INTERSECTION) {
+                    for (int k = 0; k < nc; k++) if (!Nest<D - 1>::inside(cx, c0 + k, q)) return false;
+                    return true;
+                } else if (o->csg == RT_CSG_DIFFERENCE && nc >= 2) {
+                    return Nest<D - 1>::inside(cx, c0, q) && !Nest<D - 1>::inside(cx, c0 + 1, q);
+                }
+                return false;
+            }
+            default: return false;
+        }
+    }
+    // get_material (hierarchy.py:131-138; Plane :133; others materials[0])
+    static RT_HD int material(TraceCtx& cx, int oi, float3 p) {
+        const DevObject* o = cx.S.objects + oi;
+        if (o->kind == RT_KIND_PLANE) return plane_material(o, p, cx.time);
+        if (o->kind == RT_KIND_NODE) {
+            float3 q = xform_point(cx.S.xforms[o->xform].Minv, p);
+            for (int k = 0; k < o->n_children; k++)
+                if (Nest<D - 1>::inside(cx, o->first_child + k, q)) return Nest<D - 1>::material(cx, o->first_child + k, q);
+            return -1;   // None
+        }
+        return o->n_mats > 0 ? o->mat0 : -2;
+    }
+
+    // shadow_intersect (hierarchy.py:80-109 and the leaf versions)
+    static RT_HD bool shadow(TraceCtx& cx, int oi, const Ray& r, float tmax) {
+        const DevObject* o = cx.S.objects + oi;
+        cx.tally.prims++;
+        switch (o->kind) {
+            case RT_KIND_SPHERE: {                                     // simple_geometry.py:48-72
+                float4 a = ld4(&o->a);
+                float t1, t2;
+                if (!sphere_roots(moved(o, f3(a), cx.time), a.w, r, dot(r.d, r.d), t1, t2)) return false;
+                return (RT_SHADOW_EPS_SPHERE < t1 && t1 < tmax) || (RT_SHADOW_EPS_SPHERE < t2 && t2 < tmax);
+            }
+            case RT_KIND_PLANE: {                                      // simple_geometry.py:122-131
+                float t;
+                if (!plane_t(moved(o, f3(ld4(&o->a)), cx.time), f3(ld4(&o->b)), r, t)) return false;
+                return RT_SHADOW_EPS < t && t < tmax;
+            }
+            case RT_KIND_BOX: {                                        // simple_geometry.py:251-294 (entry t only, may be < 0)
+                float en, ex; int label;
+                if (!box_slabs(moved(o, f3(ld4(&o->a)), cx.time), moved(o, f3(ld4(&o->b)), cx.time), r, en, ex, label)) return false;
+                if (en > ex) return false;
+                return RT_SHADOW_EPS < en && en < tmax;
+            }
+            case RT_KIND_MESH: return mesh_shadow(cx, cx.S.meshes + o->mesh, r);
+            case RT_KIND_NODE: {
+                const DevXform* xf = cx.S.xforms + o->xform;
+                Ray mr; mr.o = xform_point(xf->Minv, r.o); mr.d = xform_dir(xf->Minv, r.d);
+                const int c0 = o->first_child, nc = o->n_children;
+                if (o->csg == RT_CSG_UNION) {
+                    for (int k = 0; k < nc; k++) if (Nest<D - 1>::shadow(cx, c0 + k, mr, tmax)) return true;
+                    return false;
+                } else if (o->csg == RT_CSG_INTERSECTION) {            // ALL children must report shadow
+                    for (int k = 0; k < nc; k++) if (!Nest<D - 1>::shadow(cx, c0 + k, mr, tmax)) return false;
+                    return true;
+                } else if (o->csg == RT_CSG_DIFFERENCE && nc >= 2) {   // via intersect(); t_max ignored
+                    return difference_shadow(cx, c0, mr);
+                }
+                return false;
+            }
+        }
+        return false;
+    }
+};
+
+// nesting deeper than RT_MAX_NEST: flagged, treated as empty
+template <> struct Nest<0> {
+    static RT_HD bool inside(TraceCtx& cx, int, float3) { cx.tally.err |= 1u << RT_ERR_LIMIT; return false; }
+    static RT_HD int material(TraceCtx& cx, int, float3) { cx.tally.err |= 1u << RT_ERR_LIMIT; return -1; }
+    static RT_HD bool shadow(TraceCtx& cx, int, const Ray&, float) { cx.tally.err |= 1u << RT_ERR_LIMIT; return false; }
+};
+
+// Candidate hits of ONE leaf primitive for `r`, in the reference's list order; `want(t)` prunes early.
+template <class Want, class Cand>
+RT_HD void leaf_hits(TraceCtx& cx, int oi, const Ray& r, Want&& want, Cand&& cand) {
+    const DevObject* o = cx.S.objects + oi;
+    cx.tally.prims++;
+    switch (o->kind) {
+        case RT_KIND_SPHERE: {                                     // simple_geometry.py:20-46: both roots with t > 0
+            float4 a = ld4(&o->a);
+            float3 center = moved(o, f3(a), cx.time);
+            float t1, t2;
+            if (!sphere_roots(center, a.w, r, dot(r.d, r.d), t1, t2)) return;
+            float ts[2] = {t1, t2};
+            for (int k = 0; k < 2; k++) {
+                float t = ts[k];
+                if (t > 0.0f && want(t)) {
+                    Hit h; h.t = t; h.p = r.o + r.d * t; h.n = normalize(h.p - center);
+                    h.mat = o->n_mats > 0 ? o->mat0 : -2; h.geom = oi;
+                    cand(h);
+                }
+            }
+            return;
+        }
+        case RT_KIND_PLANE: {                                      // simple_geometry.py:105-120
+            float3 n = f3(ld4(&o->b)); float t;
+            if (!plane_t(moved(o, f3(ld4(&o->a)), cx.time), n, r, t)) return;
+            if (t >= 0.0f && want(t)) {
+                Hit h; h.t = t; h.p = r.o + r.d * t; h.n = n;
+                h.mat = plane_material(o, h.p, cx.time); h.geom = oi;
+                cand(h);
+            }
+            return;
+        }
+        case RT_KIND_BOX: {                                        // simple_geometry.py:188-249: entry AND exit, both with the entry normal
+            float en, ex; int label;
+            if (!box_slabs(moved(o, f3(ld4(&o->a)), cx.time), moved(o, f3(ld4(&o->b)), cx.time), r, en, ex, label)) return;
+            if (en > ex || en < 0.0f) return;
+            float3 n = box_normal(r, label);
+            float ts[2] = {en, ex};
+            for (int k = 0; k < 2; k++)
+                if (want(ts[k])) {
+                    Hit h; h.t = ts[k]; h.p = r.o + r.d * ts[k]; h.n = n;
+                    h.mat = o->n_mats > 0 ? o->mat0 : -2; h.geom = oi;
+                    cand(h);
+                }
+            return;
+        }
+        case RT_KIND_MESH: {                                       // mesh.py:72-119 (every accepted face)
+            const DevMesh* m = cx.S.meshes + o->mesh;
+            if (!mesh_gate(m, r)) return;
+            float tmax = RT_INF;
+            const int mat = o->n_mats > 0 ? o->mat0 : -2;
+            mesh_visit(cx, m, r, 0.0f, tmax, [&](int slot, float&) {
+                float3 v0, v1, v2; int face; float t;
+                tri_load(m, slot, v0, v1, v2, face);
+                if (tri_hit(v0, v1, v2, r, t) && want(t)) {
+                    Hit h; h.t = t; h.p = r.o + r.d * t; h.n = tri_normal(cx, m, slot, h.p); h.mat = mat; h.geom = oi;
+                    cand(h);
+                }
+                return false;
+            });
+            return;
+        }
+        default: return;
+    }
+}
+
+// intersect() of an arbitrary object (hierarchy.py:42-78 for nodes): every hit of `root` for `r`,
+// positions/normals in the space `r` lives in.  Depth-first over the node tree with an explicit frame
+// stack; a candidate from a leaf is carried UP through its ancestors' CSG filters and transforms
+// (times never change on the way up, so `want(t)` prunes before any of that work).  The reference
+// enumerates hits in list order; consumers here are order-free (strict-< running minimum in DFS
+// order == list order; boolean any).
+struct NodeFrame { int obj; int cursor; Ray ray; };
+
+template <class Want, class Emit>
+RT_HD void object_hits(TraceCtx& cx, int root, const Ray& r, Want&& want, Emit&& emit) {
+    const DevObject* objs = cx.S.objects;
+    NodeFrame fr[RT_MAX_NEST];
+    int depth = -1;
+    int leaf = root;
+    auto cand = [&](Hit h) {
+        int child = leaf;
+        for (int lv = depth; lv >= 0; lv--) {
+            const DevObject* nd = objs + fr[lv].obj;
+            const int c0 = nd->first_child, nc = nd->n_children;
+            if (nd->csg == RT_CSG_INTERSECTION) {                  // hierarchy.py:52-57: every OTHER child contains it
+                for (int j = 0; j < nc; j++)
+                    if (c0 + j != child && !Nest<RT_MAX_NEST>::inside(cx, c0 + j, h.p)) return;
+            } else if (nd->csg == RT_CSG_DIFFERENCE) {             // hierarchy.py:58-70
+                if (child == c0) { if (Nest<RT_MAX_NEST>::inside(cx, c0 + 1, h.p)) return; }
+                else {
+                    if (!Nest<RT_MAX_NEST>::inside(cx, c0, h.p)) return;
+                    h.mat = Nest<RT_MAX_NEST>::material(cx, c0, h.p);
+                    h.n = -h.n;
+                }
+            }
+            if (h.mat == -1) h.mat = nd->n_mats > 0 ? nd->mat0 : -2;    // hierarchy.py:73-74
+            const DevXform* xf = cx.S.xforms + nd->xform;
+            h.p = xform_point(xf->M, h.p);                          // hierarchy.py:75
+            h.n = xform_normal(xf->Minv, h.n);                      // hierarchy.py:76
+            child = fr[lv].obj;
+        }
+        emit(h);
+    };
+    if (objs[root].kind != RT_KIND_NODE) { leaf_hits(cx, root, r, want, cand); return; }
+    auto push = [&](int oi, const Ray& pr) {
+        const DevXform* xf = cx.S.xforms + objs[oi].xform;
+        depth++;
+        fr[depth].obj = oi; fr[depth].cursor = 0;
+        fr[depth].ray.o = xform_point(xf->Minv, pr.o);              // hierarchy.py:43-45 (direction NOT renormalised)
+        fr[depth].ray.d = xform_dir(xf->Minv, pr.d);
+        cx.tally.prims++;
+    };
+    push(root, r);
+    while (depth >= 0) {
+        const DevObject* nd = objs + fr[depth].obj;
+        const int csg = nd->csg, nc = nd->n_children;
+        const int limit = (csg == RT_CSG_UNION || csg == RT_CSG_INTERSECTION) ? nc : ((csg == RT_CSG_DIFFERENCE && nc >= 2) ? 2 : 0);
+        if (fr[depth].cursor >= limit) { depth--; continue; }
+        const int child = nd->first_child + fr[depth].cursor++;
+        if (objs[child].kind == RT_KIND_NODE) {
+            if (depth + 1 >= RT_MAX_NEST) { cx.tally.err |= 1u << RT_ERR_LIMIT; continue; }
+            Ray pr = fr[depth].ray;
+            push(child, pr);
+        } else {
+            leaf = child;
+            leaf_hits(cx, child, fr[depth].ray, want, cand);
+        }
+    }
+}
+
+// Hierarchy.shadow_intersect, difference case (hierarchy.py:94-107): goes through intersect() of both
+// children, `time > shadow_epsilon`, and ignores t_max.
+RT_HD bool difference_shadow(TraceCtx& cx, int c0, const Ray& mr) {
+    bool occ = false;
+    auto want = [&](float t) { return !occ && t > RT_SHADOW_EPS; };
+    object_hits(cx, c0, mr, want, [&](const Hit& h) {
+        if (!occ && !Nest<RT_MAX_NEST>::inside(cx, c0 + 1, h.p)) occ = true;
+    });
+    if (occ) return true;
+    object_hits(cx, c0 + 1, mr, want, [&](const Hit& h) {
+        if (!occ && Nest<RT_MAX_NEST>::inside(cx, c0, h.p)) occ = true;
+    });
+    return occ;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Closest hit over the top-level objects (scene.py:85-94): min by time, ties -> first in list order.
+// Leaves are resolved lazily (only t while scanning; position/normal/material for the winner).
+template <bool HAS_NODES>
+RT_HD bool closest_hit(TraceCtx& cx, const Ray& r, Hit& out) {
+    const SceneView& S = cx.S;
+    float best = RT_INF;
+    int best_obj = -1, best_aux = 0;
+    Hit node_hit; node_hit.t = RT_INF; node_hit.mat = -1; node_hit.geom = -1; node_hit.n = f3(0, 0, 0); node_hit.p = f3(0, 0, 0);
+    const float A = dot(r.d, r.d);
+    for (int oi = 0; oi < S.n_top; oi++) {
+        const DevObject* o = S.objects + oi;
+        const int kind = o->kind;
+        if (kind == RT_KIND_SPHERE) {
+            cx.tally.prims++;
+            float4 a = ld4(&o->a);
+            float t1, t2;
+            if (sphere_roots(moved(o, f3(a), cx.time), a.w, r, A, t1, t2)) {
+                float t = t1 > 0.0f ? t1 : t2;                       // t1 <= t2: first positive root is the list minimum
+                if (t > 0.0f && t < best) { best = t; best_obj = oi; }
+            }
+        } else if (kind == RT_KIND_PLANE) {
+            cx.tally.prims++;
+            float t;
+            if (plane_t(moved(o, f3(ld4(&o->a)), cx.time), f3(ld4(&o->b)), r, t) && t >= 0.0f && t < best) { best = t; best_obj = oi; }
+        } else if (kind == RT_KIND_BOX) {
+            cx.tally.prims++;
+            float en, ex; int label;
+            if (box_slabs(moved(o, f3(ld4(&o->a)), cx.time), moved(o, f3(ld4(&o->b)), cx.time), r, en, ex, label) &&
+                !(en > ex || en < 0.0f) && en < best) { best = en; best_obj = oi; best_aux = label; }
+        } else if (kind == RT_KIND_MESH) {
+            cx.tally.prims++;
+            const DevMesh* m = S.meshes + o->mesh;
+            if (mesh_gate(m, r)) {
+                // strict '<' against earlier objects; among this mesh's own faces an equal t goes to the lower face index (list order)
+                float tmax = best;
+                int best_face = 0x7fffffff, best_slot = -1;
+                mesh_visit(cx, m, r, 0.0f, tmax, [&](int slot, float& tm) {
+                    float3 v0, v1, v2; int face; float t;
+                    tri_load(m, slot, v0, v1, v2, face);
+                    if (tri_hit(v0, v1, v2, r, t)) {
+                        if ((best_slot < 0 && t < best) || (best_slot >= 0 && (t < tm || (t == tm && face < best_face)))) {
+                            tm = t; best_face = face; best_slot = slot;
+                        }
+                    }
+                    return false;
+                });
+                if (best_slot >= 0) { best = tmax; best_obj = oi; best_aux = best_slot; }
+            }
+        } else if (HAS_NODES && kind == RT_KIND_NODE) {
+            object_hits(cx, oi, r, [&](float t) { return t < best; },
+                        [&](const Hit& h) { if (h.t < best) { best = h.t; best_obj = oi; node_hit = h; } });
+        }
+    }
+    if (best_obj < 0) return false;
+    const DevObject* o = S.objects + best_obj;
+    if (HAS_NODES && o->kind == RT_KIND_NODE) { out = node_hit; return true; }
+    out.t = best; out.geom = best_obj;
+    out.p = r.o + r.d * best;                                          // Ray.getPoint, helperclasses.py:21
+    out.mat = o->n_mats > 0 ? o->mat0 : -2;
+    switch (o->kind) {
+        case RT_KIND_SPHERE: out.n = normalize(out.p - moved(o, f3(ld4(&o->a)), cx.time)); break;
+        case RT_KIND_PLANE: out.n = f3(ld4(&o->b)); out.mat = plane_material(o, out.p, cx.time); break;
+        case RT_KIND_BOX: out.n = box_normal(r, best_aux); break;
+        default: out.n = tri_normal(cx, S.meshes + o->mesh, best_aux, out.p); break;
+    }
+    return true;
+}
+
+// Any-hit over the top-level objects (scene.py:160-164)
+template <bool HAS_NODES>
+RT_HD bool occluded(TraceCtx& cx, const Ray& r, float tmax) {
+    const SceneView& S = cx.S;
+    const float A = dot(r.d, r.d);
+    for (int oi = 0; oi < S.n_top; oi++) {
+        const DevObject* o = S.objects + oi;
+        const int kind = o->kind;
+        if (kind == RT_KIND_SPHERE) {
+            cx.tally.prims++;
+            float4 a = ld4(&o->a);
+            float t1, t2;
+            if (sphere_roots(moved(o, f3(a), cx.time), a.w, r, A, t1, t2) &&
+                ((RT_SHADOW_EPS_SPHERE < t1 && t1 < tmax) || (RT_SHADOW_EPS_SPHERE < t2 && t2 < tmax))) return true;
+        } else if (HAS_NODES || kind != RT_KIND_NODE) {
+            if (Nest<HAS_NODES ? RT_MAX_NEST : 1>::shadow(cx, oi, r, tmax)) return true;
+        }
+    }
+    return false;
+}
+
+// ------------------------------------------------------------------------------------------------
+// _compute_regular_lighting (scene.py:140-187): Blinn-Phong + shadow rays + ambient
+template <bool HAS_NODES>
+RT_HD float3 shade_local(TraceCtx& cx, const Ray& ray, const Hit& hit) {
+    const SceneView& S = cx.S;
+    const DevMaterial* mat = S.materials + hit.mat;
+    float4 md = ld4(&mat->diffuse), ms = ld4(&mat->specular);
+    const DevObject* g = S.objects + hit.geom;
+    float3 diffuse;
+    if (g->kind == RT_KIND_BOX) diffuse = box_diffuse(S, g, hit.p, cx.time, cx.tally);
+    else if (g->kind == RT_KIND_PLANE) diffuse = plane_diffuse(S, g, hit.p, cx.time, cx.tally);
+    else diffuse = f3(md);
+    cx.tally.shaded++;
+    float3 colour = f3(0, 0, 0);
+    for (int li = 0; li < S.n_lights; li++) {
+        const DevLight* L = S.lights + li;
+        float4 lv = ld4(&L->vector);
+        const bool point = as_int(lv.w) == RT_LIGHT_POINT;
+        Ray sr; sr.o = hit.p;                                          // un-offset origin, un-normalised direction (Q12)
+        sr.d = point ? f3(lv) - hit.p : -f3(lv);
+        cx.tally.shadow++;
+        if (occluded<HAS_NODES>(cx, sr, point ? 1.0f : RT_INF)) continue;
+        float3 light_dir = point ? normalize(sr.d) : f3(ld4(&L->dir_norm));
+        float3 lambert = diffuse * fmaxf(0.0f, dot(hit.n, light_dir));
+        float3 half_vect = normalize(light_dir - ray.d);
+        float3 specular = f3(ms) * powf(fmaxf(0.0f, dot(hit.n, half_vect)), md.w);   // 0**0 == 1 both sides
+        colour = colour + f3(ld4(&L->colour_power)) * (lambert + specular);
+    }
+    return colour + S.ambient * diffuse;
+}
+
+// The clamped-affine fold of the per-level clamp (scene.py:104,108,113-116).  A path carries
+// F(c) = clamp(a + w*c, lo, hi): the map from "colour returned by the next cast_ray" to the sample
+// value.  Composing with one more level g(c) = clamp(A + W*c, 0, 1) stays in the same family.
+struct PathFold { float3 a; float w; float3 lo, hi; };
+RT_HD PathFold fold_identity() { PathFold f; f.a = f3(0, 0, 0); f.w = 1.0f; f.lo = f3(0, 0, 0); f.hi = f3(1, 1, 1); return f; }
+RT_HD float3 fold_eval(const PathFold& f, float3 c) { return clamp3(f.a + c * f.w, f.lo, f.hi); }
+RT_HD PathFold fold_compose(const PathFold& f, float3 A, float W) {
+    PathFold g;
+    float3 e0 = f.a, e1 = f.a + f3(f.w, f.w, f.w);                     // F's pre-clamp value at g = 0 and g = 1
+    g.lo = clamp3(f3(fminf(e0.x, e1.x), fminf(e0.y, e1.y), fminf(e0.z, e1.z)), f.lo, f.hi);
+    g.hi = clamp3(f3(fmaxf(e0.x, e1.x), fmaxf(e0.y, e1.y), fmaxf(e0.z, e1.z)), f.lo, f.hi);
+    g.a = f.a + A * f.w;
+    g.w = f.w * W;
+    return g;
+}
+
+// One level of cast_ray (scene.py:81-116) for one path.  Returns true when the path continues with
+// `next` (reflection / refraction ray); otherwise `sample` holds the finished sample value.
+struct PathState { Ray ray; PathFold fold; int depth_left; int in_shape; };
+
+template <bool HAS_NODES>
+RT_HD bool trace_level(TraceCtx& cx, PathState& ps, float3& sample) {
+    Hit hit;
+    if (ps.depth_left <= 0 || !closest_hit<HAS_NODES>(cx, ps.ray, hit)) { sample = fold_eval(ps.fold, f3(0, 0, 0)); return false; }
+    if (hit.mat < 0) { cx.tally.err |= 1u << RT_ERR_NO_MATERIAL; sample = fold_eval(ps.fold, f3(0, 0, 0)); return false; }
+    const DevMaterial* mat = cx.S.materials + hit.mat;
+    const int type = mat->type;
+    if (type == RT_MAT_MIRROR) {                                       // scene.py:97-104
+        float3 rd = reflect3(ps.ray.d, hit.n);
+        float3 ro = hit.p + rd * 0.01f;
+        float3 local = shade_local<HAS_NODES>(cx, ps.ray, hit);
+        ps.fold = fold_compose(ps.fold, local * ld4(&mat->specular).w, mat->one_minus_tint);
+        if (ps.depth_left - 1 <= 0) { sample = fold_eval(ps.fold, f3(0, 0, 0)); return false; }
+        cx.tally.reflect++;
+        ps.ray.o = ro; ps.ray.d = rd; ps.depth_left -= 1; ps.in_shape = 0;
+        return true;
+    }
+    if (type == RT_MAT_REFRACTIVE) {                                   // scene.py:105-108,189-209
+        float eta;
+        if (ps.in_shape) { eta = mat->refr_index; hit.n = -hit.n; }    // normal flipped BEFORE local lighting (Q19)
+        else eta = mat->inv_refr;
+        bool tir;
+        float3 rd = refract3(ps.ray.d, hit.n, eta, tir);
+        if (!tir && rd.x == 0.0f && rd.y == 0.0f && rd.z == 0.0f) tir = true;   // `refract_dir == vec3(0)`
+        float3 ro = hit.p + rd * 0.0001f;
+        float3 local = shade_local<HAS_NODES>(cx, ps.ray, hit);
+        ps.fold = fold_compose(ps.fold, local * ld4(&mat->specular).w, mat->one_minus_tint);
+        if (tir || ps.depth_left - 1 <= 0) { sample = fold_eval(ps.fold, f3(0, 0, 0)); return false; }
+        cx.tally.refract++;
+        ps.ray.o = ro; ps.ray.d = rd; ps.depth_left -= 1; ps.in_shape = !ps.in_shape;
+        return true;
+    }
+    sample = fold_eval(ps.fold, clamp01(shade_local<HAS_NODES>(cx, ps.ray, hit)));   // scene.py:109-116
+    return false;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Sample generation (scene.py:47-69): primary ray of (col, row, dof d, aa s)
+RT_HD Ray generate_ray(const SceneView& S, int col, int row, int d, int s) {
+    float x = RT_LDG(S.col_x + col), y = RT_LDG(S.row_y + row);
+    float3 base_dir = normalize((S.cam_u * x + S.cam_v * y) - S.cam_w);          // d = 1: d*w == w
+    float3 focal_point = S.cam_pos + base_dir * S.focal_length;
+    Ray r;
+    r.d = normalize(focal_point - f3(ld4(S.dof_origin + d)));
+    r.o = f3(ld4(S.ray_origin + d * S.S + s));
+    if (S.jitter) {
+        uint64_t idx = (((uint64_t)col * (uint64_t)S.height + (uint64_t)row) * (uint64_t)S.D + (uint64_t)d) * (uint64_t)S.S + (uint64_t)s;
+        uint32_t c0 = (uint32_t)idx, c1 = (uint32_t)(idx >> 32), c2 = 0, c3 = 0;
+        philox4x32_10(c0, c1, c2, c3, S.seed_lo, S.seed_hi);
+        float3 rnd = f3((float)c0 * 2.3283064365386963e-10f, (float)c1 * 2.3283064365386963e-10f, (float)c2 * 2.3283064365386963e-10f);
+        r.o = r.o + normalize(rnd) * S.noise_scale;
+    }
+    return r;
+}

@@ -1,0 +1,95 @@
+// rt_types.cuh - device-resident scene layout (what rt_scene_create builds in HBM).
+#pragma once
+#include "rt_math.cuh"
+#include "../../include/b200rt.h"
+
+#define RT_MAX_NEST 8        // CSG / transform nesting depth supported (NovelScene uses 5)
+#define RT_STACK_DEPTH 64    // BVH traversal stack entries per ray
+
+// One geometry object, 16-byte aligned so fields load as 128-bit vectors (warp-uniform index
+// -> one broadcast transaction).  Meaning of a/b per kind as in RtObject (include/b200rt.h).
+struct __attribute__((aligned(16))) DevObject {
+    float4 a;        // sphere: centre, w = radius | plane: point | box: minpos
+    float4 b;        // plane: normal | box: maxpos
+    float4 speed;    // xyz
+    int kind, n_mats, mat0, mat1;
+    int tex, mesh, first_child, n_children;
+    int csg, xform, pad0, pad1;
+    float4 ax_w;     // plane width axis
+    float4 ax_h;     // plane height axis
+    double tex_scale;
+    double pad2;
+};
+
+struct __attribute__((aligned(16))) DevMaterial {
+    float4 diffuse;   // w = hardness
+    float4 specular;  // w = tint
+    float refr_index; // eta inside
+    float inv_refr;   // (float)(1.0 / refr_index)
+    float one_minus_tint;
+    int type;
+};
+
+struct __attribute__((aligned(16))) DevLight {
+    float4 vector;    // w = type
+    float4 colour_power;  // colour * (float)power, scene.py:183
+    float4 dir_norm;  // directional: normalize(-vector) (scene.py:173), precomputed
+};
+
+struct DevXform { float M[16]; float Minv[16]; };
+
+// LBVH node, 64 B = 4 x float4, both children's boxes in the parent so one fetch decides both:
+//   q0 = (c0.min.xyz, c0.max.x)  q1 = (c0.max.yz, c1.min.xy)  q2 = (c1.min.z, c1.max.xyz)
+//   q3 = (bits child0, bits child1, -, -)   child >= 0: node index ; child < 0: ~child = triangle slot
+struct __attribute__((aligned(16))) BvhNode { float4 q0, q1, q2, q3; };
+
+struct DevMesh {
+    const float4* tri;       // 3 float4 per triangle slot (Morton order): v0|v1|v2, w of v0 = bits(original face index)
+    const BvhNode* nodes;    // n_tris - 1 nodes (root = 0); NULL when n_tris < 2
+    const int4* face_vidx;   // per triangle slot: vertex indices (for smooth normals) + original face
+    const float4* vnormals;  // per vertex, NULL when flat shaded
+    int n_tris;
+    int flat_shaded;
+    int gate;
+    float gate_radius;
+    float4 gate_min, gate_max, gate_center;
+};
+
+struct DevTexture { const uint8_t* rgb; int width, height; };
+
+struct SceneView {
+    const DevObject* objects; int n_objects, n_top;
+    const DevMaterial* materials; int n_materials;
+    const DevLight* lights; int n_lights;
+    const DevXform* xforms;
+    const DevMesh* meshes;
+    const DevTexture* textures;
+    float3 ambient;
+    int max_depth;
+    int mesh_mode;    // 0 = LBVH, 1 = brute force (test aid)
+    // sampling tables (scene.py:41-43,118-138 precomputed once per scene)
+    const float* col_x;          // [W]  (float)x of pixel-centre column
+    const float* row_y;          // [H]
+    const float4* dof_origin;    // [D]
+    const float4* ray_origin;    // [D*S] AA point around each DOF point
+    const float* times;          // [T] (float)motion_times
+    float3 cam_pos, cam_u, cam_v, cam_w;
+    float focal_length, noise_scale;
+    int width, height, D, S, T, jitter;
+    uint32_t seed_lo, seed_hi;
+};
+
+struct Ray { float3 o, d; };
+
+// geometry/__init__.py:15-22
+struct Hit {
+    float t;
+    float3 n, p;
+    int mat;    // material index; -1 = None (hierarchy.py:73), -2 = reference would raise IndexError
+    int geom;   // leaf object index (scene.py:143 dispatches on the hit's geometry)
+};
+
+// per-thread tallies, reduced per block into RtCounters
+struct Tally {
+    unsigned shadow, reflect, refract, nodes, tris, prims, shaded, smooth, err;
+};
