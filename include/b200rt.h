@@ -161,7 +161,7 @@ typedef struct RtSceneDesc {
  * this call renders the tiles with tile % world == rank (scene.py:36-37 strips generalised
  * to interleaved tiles for load balance; glue.py:19-22 is the gather).  With world == 1 and
  * direct != 0 the output is written straight in the reference layout (ncols, nrows, 3);
- * otherwise it is the compact tile buffer (n_local_tiles, tile_w, tile_h, 3) that
+ * otherwise it is the compact tile buffer (n_local_tiles, tile_h, tile_w, 3) that
  * rt_assemble_tiles() scatters into the reference layout. */
 typedef struct RtRenderJob {
     int32_t col0, ncols, row0, nrows;
@@ -188,6 +188,15 @@ typedef struct RtCounters {
     uint64_t error_flags;    /* bit (RtStatus) set by kernels */
 } RtCounters;
 
+/* Per-kernel-class device timing (CUDA events on the launch stream) + the tallies of each class for the
+ * last rt_render call; used by bench.py for the roofline of the dominant kernel. */
+typedef struct RtProfile {
+    double ms_primary, ms_secondary, ms_resolve;   /* summed event time since profiling was enabled */
+    uint64_t n_primary, n_secondary, n_resolve;    /* launches timed */
+    RtCounters primary;                            /* tallies of k_primary launches of the last rt_render */
+    RtCounters secondary;                          /* tallies of k_secondary launches of the last rt_render */
+} RtProfile;
+
 typedef struct RtScene RtScene;  /* opaque, device-resident */
 
 /* ---- entry points -------------------------------------------------------------------- */
@@ -202,7 +211,7 @@ int rt_scene_create(const RtSceneDesc* desc, RtScene** out);
 int rt_scene_build_bvh(RtScene* scene, void* stream);
 
 /* Replaces Scene.render(subimage, tasks) (scene.py:35-79).  d_out is DEVICE memory:
- * job->direct ? (ncols, nrows, 3) : (n_local_tiles, tile_w, tile_h, 3), float32.
+ * job->direct ? (ncols, nrows, 3) : (n_local_tiles, tile_h, tile_w, 3), float32.
  * counters may be NULL; when given, the call synchronises the stream before returning. */
 int rt_render(RtScene* scene, const RtRenderJob* job, float* d_out, RtCounters* counters, void* stream);
 
@@ -227,6 +236,18 @@ int rt_scene_destroy(RtScene* scene);
 int rt_scene_bvh_stats(const RtScene* scene, int32_t mesh, int64_t* n_nodes, int64_t* n_leaf_tris, int64_t* bytes);
 /* Copies the LBVH of `mesh` back to host buffers for validation: nodes (n_nodes*16 floats), leaf order (n_faces int32) */
 int rt_scene_bvh_download(const RtScene* scene, int32_t mesh, float* h_nodes, int32_t* h_order);
+/* Unit-test aids: cast_ray (scene.py:81-116) and the any-hit loop (scene.py:160-164) for explicit rays.
+ * All pointers are HOST buffers: origins/dirs (n,3) f32, times (n) f32; outputs rgb (n,3), first-hit t (n, inf = miss),
+ * normal/position (n,3), leaf object index and material index (n).  Outputs may be NULL. */
+int rt_trace_rays(RtScene* scene, int64_t n, const float* h_origins, const float* h_dirs, const float* h_times,
+                  float* h_rgb, float* h_hit_t, float* h_hit_n, float* h_hit_p, int32_t* h_hit_geom, int32_t* h_hit_mat,
+                  int32_t mesh_mode, void* stream);
+int rt_occluded(RtScene* scene, int64_t n, const float* h_origins, const float* h_dirs, const float* h_times,
+                const float* h_tmax, int32_t* h_occluded, int32_t mesh_mode, void* stream);
+/* enable != 0: start recording an event pair around every kernel of rt_render (and reset the sums); 0: stop */
+int rt_scene_profile(RtScene* scene, int32_t enable);
+/* synchronises the recorded events and returns the sums */
+int rt_scene_profile_read(RtScene* scene, RtProfile* out);
 const char* rt_last_error(void);
 int rt_abi_version(void);
 

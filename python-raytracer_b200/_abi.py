@@ -88,6 +88,12 @@ class RtCounters(C.Structure):
         return {n: int(getattr(self, n)) for n, _ in self._fields_}
 
 
+class RtProfile(C.Structure):
+    _fields_ = [("ms_primary", C.c_double), ("ms_secondary", C.c_double), ("ms_resolve", C.c_double),
+                ("n_primary", C.c_uint64), ("n_secondary", C.c_uint64), ("n_resolve", C.c_uint64),
+                ("primary", RtCounters), ("secondary", RtCounters)]
+
+
 DEFAULT_JITTER_SEED = 0x5EED
 DEFAULT_MAX_DEPTH = 10  # scene.py:81
 
@@ -264,7 +270,8 @@ LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "lib
 
 ENTRY_POINTS = ["rt_scene_create", "rt_scene_build_bvh", "rt_render", "rt_render_host", "rt_job_extent",
                 "rt_assemble_tiles", "rt_finalize_u8", "rt_scene_destroy", "rt_scene_bvh_stats",
-                "rt_scene_bvh_download", "rt_last_error", "rt_abi_version", "rt_trace_rays", "rt_occluded"]
+                "rt_scene_bvh_download", "rt_last_error", "rt_abi_version", "rt_trace_rays", "rt_occluded",
+                "rt_scene_profile", "rt_scene_profile_read"]
 
 
 class B200RTError(RuntimeError):
@@ -295,6 +302,8 @@ def load_library(path=None):
     lib.rt_scene_bvh_download.argtypes = [vp, i32, vp, vp]
     lib.rt_trace_rays.argtypes = [vp, C.c_int64, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, vp]
     lib.rt_occluded.argtypes = [vp, C.c_int64, vp, vp, vp, vp, vp, i32, vp]
+    lib.rt_scene_profile.argtypes = [vp, i32]
+    lib.rt_scene_profile_read.argtypes = [vp, C.POINTER(RtProfile)]
     lib.rt_last_error.restype = C.c_char_p
     lib.rt_last_error.argtypes = []
     lib.rt_abi_version.argtypes = []

@@ -1,0 +1,511 @@
+// b200rt.cu - C ABI of the render path (include/b200rt.h): scene upload, LBVH build, wavefront
+// render orchestration on a CUDA stream.  Single translation unit: kernels live in the .cuh files.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "rt_bvh.cuh"
+#include "rt_kernels.cuh"
+#include "rt_scene_build.hpp"
+
+static thread_local std::string g_last_error;
+
+static int fail(int code, const std::string& msg) { g_last_error = msg; return code; }
+
+#define CU(expr)                                                                                          \
+    do {                                                                                                  \
+        cudaError_t e_ = (expr);                                                                          \
+        if (e_ != cudaSuccess)                                                                            \
+            return fail(e_ == cudaErrorMemoryAllocation ? RT_ERR_NOMEM : RT_ERR_CUDA,                      \
+                        std::string(#expr) + ": " + cudaGetErrorString(e_));                              \
+    } while (0)
+
+struct MeshBuild {
+    int n_verts = 0, n_faces = 0;
+    float* d_verts = nullptr;       // n_verts*3
+    int* d_faces = nullptr;         // n_faces*3
+    float4* d_vnormals = nullptr;   // n_verts
+    float4* d_tri = nullptr;        // 3*n_faces
+    int4* d_face_vidx = nullptr;    // n_faces
+    BvhNode* d_nodes = nullptr;     // n_faces-1
+    int* d_order = nullptr;         // n_faces: slot -> original face
+    float3 lo, hi;
+    float pad = 0.0f;
+    bool built = false;
+};
+
+struct RtScene {
+    SceneView view{};
+    std::vector<void*> allocs;
+    std::vector<MeshBuild> meshes;
+    std::vector<DevMesh> h_meshes;
+    DevMesh* d_meshes = nullptr;
+    bool has_nodes = false, has_specular = false, has_mesh = false;
+    int samples_per_pixel = 1;
+    // work buffers of rt_render, grown on demand
+    float4* d_samples = nullptr; long long samples_cap = 0;
+    float4* d_queue[2] = {nullptr, nullptr}; long long queue_cap = 0;
+    unsigned long long* d_qcount = nullptr;   // [max_depth + 1]
+    RtCounters* d_counters = nullptr;
+    float* d_stage = nullptr; long long stage_cap = 0;   // rt_render_host staging
+    int device = 0;
+    int sm_count = 148;
+    unsigned long long last_launches = 0;
+    bool profiling = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev[3];   // primary / secondary / resolve
+    double prof_ms[3] = {0, 0, 0};
+    unsigned long long prof_n[3] = {0, 0, 0};
+};
+
+struct ProfScope {   // event pair around one launch when profiling is on
+    RtScene* sc; int cls; cudaStream_t st; cudaEvent_t a = nullptr, b = nullptr;
+    ProfScope(RtScene* s, int c, cudaStream_t t) : sc(s), cls(c), st(t) {
+        if (sc->profiling) { cudaEventCreate(&a); cudaEventCreate(&b); cudaEventRecord(a, st); }
+    }
+    ~ProfScope() { if (a) { cudaEventRecord(b, st); sc->ev[cls].push_back({a, b}); } }
+};
+
+template <class T>
+static int upload(RtScene* sc, const T* host, size_t n, T** out) {
+    *out = nullptr;
+    const size_t alloc_n = n == 0 ? 1 : n;
+    void* p = nullptr;
+    CU(cudaMalloc(&p, alloc_n * sizeof(T)));
+    sc->allocs.push_back(p);
+    if (host && n) CU(cudaMemcpy(p, host, n * sizeof(T), cudaMemcpyHostToDevice));
+    else CU(cudaMemset(p, 0, alloc_n * sizeof(T)));
+    *out = (T*)p;
+    return RT_OK;
+}
+#define UP(call) do { int rc_ = (call); if (rc_ != RT_OK) return rc_; } while (0)
+
+using rtb::h3;
+using rtb::h4;
+
+extern "C" int rt_abi_version(void) { return RT_ABI_VERSION; }
+extern "C" const char* rt_last_error(void) { return g_last_error.c_str(); }
+
+static int scene_create_impl(const RtSceneDesc* d, RtScene* sc) {
+    CU(cudaGetDevice(&sc->device));
+    CU(cudaDeviceGetAttribute(&sc->sm_count, cudaDevAttrMultiProcessorCount, sc->device));
+    HostScene hs;
+    std::string err;
+    int rc = rtb::convert_scene(d, hs, err);
+    if (rc != RT_OK) return fail(rc, err);
+    sc->has_nodes = hs.has_nodes; sc->has_specular = hs.has_specular; sc->has_mesh = hs.has_mesh;
+    sc->view = hs.view;
+    SceneView& V = sc->view;
+    DevObject* d_objs; UP(upload(sc, hs.objs.data(), hs.objs.size(), &d_objs));
+    DevMaterial* d_mats; UP(upload(sc, hs.mats.data(), hs.mats.size(), &d_mats));
+    DevLight* d_lights; UP(upload(sc, hs.lights.data(), hs.lights.size(), &d_lights));
+    static_assert(sizeof(DevXform) == sizeof(RtXform), "xform layout");
+    DevXform* d_xf; UP(upload(sc, (const DevXform*)d->xforms, (size_t)d->n_xforms, &d_xf));
+    V.objects = d_objs; V.materials = d_mats; V.lights = d_lights; V.xforms = d_xf;
+    // ---- textures
+    std::vector<DevTexture> texs(d->n_textures);
+    for (int i = 0; i < d->n_textures; i++) {
+        uint8_t* px; UP(upload(sc, d->textures[i].rgb, (size_t)d->textures[i].width * d->textures[i].height * 3, &px));
+        texs[i].rgb = px; texs[i].width = d->textures[i].width; texs[i].height = d->textures[i].height;
+    }
+    DevTexture* d_tex; UP(upload(sc, texs.data(), texs.size(), &d_tex));
+    V.textures = d_tex;
+    // ---- meshes (raw arrays now; LBVH in rt_scene_build_bvh)
+    sc->meshes.resize(d->n_meshes);
+    sc->h_meshes.resize(d->n_meshes);
+    for (int i = 0; i < d->n_meshes; i++) {
+        const RtMesh& m = d->meshes[i];
+        MeshBuild& b = sc->meshes[i];
+        b.n_verts = m.n_verts; b.n_faces = m.n_faces;
+        for (size_t k = 0; k < (size_t)m.n_faces * 3; k++)
+            if (m.faces[k] < 0 || m.faces[k] >= m.n_verts) return fail(RT_ERR_INVALID, "mesh face index out of range");
+        UP(upload(sc, m.verts, (size_t)m.n_verts * 3, &b.d_verts));
+        UP(upload(sc, m.faces, (size_t)m.n_faces * 3, &b.d_faces));
+        if (m.vnormals && !m.flat_shaded) {
+            std::vector<float4> vn(m.n_verts);
+            for (int k = 0; k < m.n_verts; k++) vn[k] = h4(m.vnormals + 3 * (size_t)k);
+            UP(upload(sc, vn.data(), vn.size(), &b.d_vnormals));
+        }
+        rtb::mesh_bounds(m, b.lo, b.hi, b.pad);
+        rtb::mesh_header(m, sc->h_meshes[i]);
+        sc->h_meshes[i].vnormals = b.d_vnormals;
+    }
+    UP(upload(sc, (const DevMesh*)nullptr, (size_t)d->n_meshes, &sc->d_meshes));
+    V.meshes = sc->d_meshes;
+    // ---- sampling tables
+    float *d_colx, *d_rowy, *d_times; float4 *d_dof, *d_org;
+    UP(upload(sc, hs.col_x.data(), hs.col_x.size(), &d_colx)); UP(upload(sc, hs.row_y.data(), hs.row_y.size(), &d_rowy));
+    UP(upload(sc, hs.dof_origin.data(), hs.dof_origin.size(), &d_dof)); UP(upload(sc, hs.ray_origin.data(), hs.ray_origin.size(), &d_org));
+    UP(upload(sc, hs.times.data(), hs.times.size(), &d_times));
+    V.col_x = d_colx; V.row_y = d_rowy; V.dof_origin = d_dof; V.ray_origin = d_org; V.times = d_times;
+    sc->samples_per_pixel = d->dof_samples * d->aa_samples * d->n_times;
+    UP(upload(sc, (const unsigned long long*)nullptr, (size_t)d->max_depth + 2, &sc->d_qcount));
+    UP(upload(sc, (const RtCounters*)nullptr, 2, &sc->d_counters));
+    return RT_OK;
+}
+
+static void drain_events(RtScene* sc);
+
+extern "C" int rt_scene_destroy(RtScene* sc) {
+    if (!sc) return RT_OK;
+    for (void* p : sc->allocs) cudaFree(p);
+    if (sc->d_samples) cudaFree(sc->d_samples);
+    for (int k = 0; k < 2; k++) if (sc->d_queue[k]) cudaFree(sc->d_queue[k]);
+    if (sc->d_stage) cudaFree(sc->d_stage);
+    drain_events(sc);
+    delete sc;
+    return RT_OK;
+}
+
+extern "C" int rt_scene_create(const RtSceneDesc* d, RtScene** out) {
+    if (!d || !out) return fail(RT_ERR_INVALID, "null argument");
+    if (d->abi_version != RT_ABI_VERSION) return fail(RT_ERR_INVALID, "RtSceneDesc.abi_version mismatch");
+    RtScene* sc = new RtScene();
+    int rc = scene_create_impl(d, sc);
+    if (rc != RT_OK) { std::string keep = g_last_error; rt_scene_destroy(sc); g_last_error = keep; *out = nullptr; return rc; }
+    *out = sc;
+    return RT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// LBVH build
+static int build_mesh_bvh(RtScene* sc, int mi, cudaStream_t st) {
+    MeshBuild& b = sc->meshes[mi];
+    DevMesh& g = sc->h_meshes[mi];
+    const int n = b.n_faces;
+    g.n_tris = n;
+    if (n == 0) { b.built = true; return RT_OK; }
+    UP(upload(sc, (const float4*)nullptr, (size_t)n * 3, &b.d_tri));
+    UP(upload(sc, (const int4*)nullptr, (size_t)n, &b.d_face_vidx));
+    UP(upload(sc, (const int*)nullptr, (size_t)n, &b.d_order));
+    UP(upload(sc, (const BvhNode*)nullptr, (size_t)std::max(1, n - 1), &b.d_nodes));
+    // temporaries
+    uint64_t *keys[2]; int* vals[2]; unsigned* hist; int2* children; int *parent_node, *parent_leaf; unsigned* arrive;
+    float4 *leaf_lo, *leaf_hi, *node_lo, *node_hi;
+    const int n_tiles = (n + RS_TILE - 1) / RS_TILE;
+    std::vector<void*> tmp;
+    auto talloc = [&](void** p, size_t bytes) { cudaError_t e = cudaMalloc(p, std::max<size_t>(bytes, 16)); if (e == cudaSuccess) tmp.push_back(*p); return e; };
+    auto tfree = [&]() { for (void* p : tmp) cudaFree(p); };
+#define TA(ptr, bytes) do { cudaError_t e_ = talloc((void**)&(ptr), (bytes)); if (e_ != cudaSuccess) { tfree(); return fail(RT_ERR_NOMEM, cudaGetErrorString(e_)); } } while (0)
+    TA(keys[0], sizeof(uint64_t) * n); TA(keys[1], sizeof(uint64_t) * n);
+    TA(vals[0], sizeof(int) * n); TA(vals[1], sizeof(int) * n);
+    TA(hist, sizeof(unsigned) * 256 * n_tiles);
+    TA(children, sizeof(int2) * n); TA(parent_node, sizeof(int) * n); TA(parent_leaf, sizeof(int) * n);
+    TA(arrive, sizeof(unsigned) * n);
+    TA(leaf_lo, sizeof(float4) * n); TA(leaf_hi, sizeof(float4) * n); TA(node_lo, sizeof(float4) * n); TA(node_hi, sizeof(float4) * n);
+#undef TA
+    float3 ext = b.hi - b.lo;
+    float3 inv_ext = f3(ext.x > 0 ? 1.0f / ext.x : 0.0f, ext.y > 0 ? 1.0f / ext.y : 0.0f, ext.z > 0 ? 1.0f / ext.z : 0.0f);
+    const int T = 256, G = (n + T - 1) / T;
+    k_morton<<<G, T, 0, st>>>(b.d_verts, b.d_faces, n, b.lo, inv_ext, keys[0], vals[0]);
+    int cur = 0;
+    for (int pass = 0; pass < 8; pass++) {           // 63-bit keys: 8 digits of 8 bits, least significant first
+        const int shift = pass * 8;
+        k_rs_hist<<<n_tiles, RS_THREADS, 0, st>>>(keys[cur], n, shift, n_tiles, hist);
+        k_rs_scan<<<1, 1024, 0, st>>>(hist, 256 * n_tiles);
+        k_rs_scatter<<<n_tiles, RS_THREADS, 0, st>>>(keys[cur], vals[cur], n, shift, n_tiles, hist, keys[cur ^ 1], vals[cur ^ 1]);
+        cur ^= 1;
+    }
+    cudaMemcpyAsync(b.d_order, vals[cur], sizeof(int) * n, cudaMemcpyDeviceToDevice, st);
+    cudaMemsetAsync(arrive, 0, sizeof(unsigned) * n, st);
+    if (n >= 2) k_lbvh_hierarchy<<<G, T, 0, st>>>(keys[cur], n, children, parent_node, parent_leaf);
+    k_lbvh_leaves_refit<<<G, T, 0, st>>>(b.d_verts, b.d_faces, vals[cur], n, children, parent_node, parent_leaf, b.d_tri, b.d_face_vidx,
+                                        leaf_lo, leaf_hi, node_lo, node_hi, arrive);
+    if (n >= 2) k_lbvh_emit<<<G, T, 0, st>>>(n, children, leaf_lo, leaf_hi, node_lo, node_hi, b.pad, b.d_nodes);
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    tfree();
+    if (e != cudaSuccess) return fail(RT_ERR_CUDA, std::string("LBVH build: ") + cudaGetErrorString(e));
+    g.tri = b.d_tri; g.nodes = n >= 2 ? b.d_nodes : nullptr; g.face_vidx = b.d_face_vidx;
+    b.built = true;
+    return RT_OK;
+}
+
+extern "C" int rt_scene_build_bvh(RtScene* sc, void* stream) {
+    if (!sc) return fail(RT_ERR_INVALID, "null scene");
+    CU(cudaSetDevice(sc->device));
+    for (size_t i = 0; i < sc->meshes.size(); i++)
+        if (!sc->meshes[i].built) UP(build_mesh_bvh(sc, (int)i, (cudaStream_t)stream));
+    if (!sc->h_meshes.empty())
+        CU(cudaMemcpy(sc->d_meshes, sc->h_meshes.data(), sizeof(DevMesh) * sc->h_meshes.size(), cudaMemcpyHostToDevice));
+    return RT_OK;
+}
+
+extern "C" int rt_scene_bvh_stats(const RtScene* sc, int32_t mesh, int64_t* n_nodes, int64_t* n_leaf_tris, int64_t* bytes) {
+    if (!sc || mesh < 0 || mesh >= (int)sc->meshes.size()) return fail(RT_ERR_INVALID, "mesh index");
+    const MeshBuild& b = sc->meshes[mesh];
+    if (n_nodes) *n_nodes = std::max(0, b.n_faces - 1);
+    if (n_leaf_tris) *n_leaf_tris = b.n_faces;
+    if (bytes) *bytes = (int64_t)std::max(0, b.n_faces - 1) * 64 + (int64_t)b.n_faces * (48 + 16) + (b.d_vnormals ? (int64_t)b.n_verts * 16 : 0);
+    return RT_OK;
+}
+
+extern "C" int rt_scene_bvh_download(const RtScene* sc, int32_t mesh, float* h_nodes, int32_t* h_order) {
+    if (!sc || mesh < 0 || mesh >= (int)sc->meshes.size()) return fail(RT_ERR_INVALID, "mesh index");
+    const MeshBuild& b = sc->meshes[mesh];
+    if (!b.built) return fail(RT_ERR_INVALID, "BVH not built");
+    if (h_nodes && b.n_faces >= 2) CU(cudaMemcpy(h_nodes, b.d_nodes, sizeof(BvhNode) * (size_t)(b.n_faces - 1), cudaMemcpyDeviceToHost));
+    if (h_order && b.n_faces >= 1) CU(cudaMemcpy(h_order, b.d_order, sizeof(int) * (size_t)b.n_faces, cudaMemcpyDeviceToHost));
+    return RT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// render
+static int make_pixel_map(const RtRenderJob* job, PixelMap& pm, long long& n_local_tiles) {
+    if (!rtb::make_pixel_map(job, pm, n_local_tiles)) return fail(RT_ERR_INVALID, "bad RtRenderJob");
+    return RT_OK;
+}
+
+extern "C" int rt_job_extent(const RtRenderJob* job, int64_t* n_local_tiles, int64_t* n_floats) {
+    PixelMap pm; long long nt;
+    UP(make_pixel_map(job, pm, nt));
+    if (n_local_tiles) *n_local_tiles = nt;
+    if (n_floats) *n_floats = (job->direct && job->world == 1) ? (int64_t)job->ncols * job->nrows * 3 : pm.n_local_pixels * 3;
+    return RT_OK;
+}
+
+template <class T>
+static int grow(T** buf, long long* cap, long long need, size_t elems_per_unit = 1) {
+    if (need <= *cap) return RT_OK;
+    if (*buf) { cudaFree(*buf); *buf = nullptr; *cap = 0; }
+    void* p = nullptr;
+    CU(cudaMalloc(&p, (size_t)need * elems_per_unit * sizeof(T)));
+    *buf = (T*)p; *cap = need;
+    return RT_OK;
+}
+
+static void sum_counters(const RtCounters* two, RtCounters* out) {
+    const uint64_t* a = (const uint64_t*)&two[0]; const uint64_t* b = (const uint64_t*)&two[1];
+    uint64_t* o = (uint64_t*)out;
+    for (size_t k = 0; k < sizeof(RtCounters) / sizeof(uint64_t); k++) o[k] = a[k] + b[k];
+    out->error_flags = two[0].error_flags | two[1].error_flags;
+}
+
+template <bool HAS_NODES>
+static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, float* d_out, cudaStream_t st, unsigned long long* launches) {
+    SceneView V = sc->view;
+    V.mesh_mode = job->mesh_mode;
+    const int N = sc->samples_per_pixel;
+    long long max_rays = job->max_batch_rays > 0 ? job->max_batch_rays : (16ll << 20);
+    max_rays = std::min(max_rays, 1ll << 30);
+    const long long px_per_batch = std::max(1ll, max_rays / N);
+    const long long batch_cap = std::min(px_per_batch, std::max(1ll, pm.n_local_pixels)) * N;
+    UP(grow(&sc->d_samples, &sc->samples_cap, batch_cap));
+    const bool secondary = sc->has_specular && V.max_depth > 1;
+    if (secondary && batch_cap > sc->queue_cap) {
+        for (int k = 0; k < 2; k++) {
+            if (sc->d_queue[k]) { cudaFree(sc->d_queue[k]); sc->d_queue[k] = nullptr; }
+            sc->queue_cap = 0;
+            CU(cudaMalloc((void**)&sc->d_queue[k], sizeof(float4) * RT_QUEUE_PLANES * (size_t)batch_cap));
+        }
+        sc->queue_cap = batch_cap;
+    }
+    const size_t smem = sc->has_mesh ? sizeof(int) * RT_STACK_DEPTH * RT_BLOCK : 0;
+    if (smem) {
+        CU(cudaFuncSetAttribute(k_primary<HAS_NODES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CU(cudaFuncSetAttribute(k_secondary<HAS_NODES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    }
+    const int direct = (job->direct && job->world == 1) ? 1 : 0;
+    const int max_grid = sc->sm_count * 16;
+    for (long long p0 = 0; p0 < pm.n_local_pixels; p0 += px_per_batch) {
+        const long long npx = std::min(px_per_batch, pm.n_local_pixels - p0);
+        const long long n_rays = npx * N;
+        CU(cudaMemsetAsync(sc->d_qcount, 0, sizeof(unsigned long long) * (size_t)(V.max_depth + 2), st));
+        RayQueue q0{sc->d_queue[0], sc->queue_cap}, q1{sc->d_queue[1], sc->queue_cap};
+        const int grid = (int)std::min<long long>((n_rays + RT_BLOCK - 1) / RT_BLOCK, max_grid);
+        {
+            ProfScope ps_(sc, 0, st);
+            k_primary<HAS_NODES><<<grid, RT_BLOCK, smem, st>>>(V, pm, p0, n_rays, sc->d_samples, q0, sc->d_qcount, sc->d_counters);
+        }
+        (*launches)++;
+        if (secondary) {
+            for (int level = 1; level < V.max_depth; level++) {       // level L consumes the rays spawned by level L-1
+                RayQueue& qin = (level & 1) ? q0 : q1;
+                RayQueue& qout = (level & 1) ? q1 : q0;
+                ProfScope ps_(sc, 1, st);
+                k_secondary<HAS_NODES><<<max_grid, RT_BLOCK, smem, st>>>(V, qin, sc->d_qcount + (level - 1), sc->d_samples, qout,
+                                                                         sc->d_qcount + level, sc->d_counters + 1);
+                (*launches)++;
+            }
+        }
+        {
+            ProfScope ps_(sc, 2, st);
+            k_resolve<<<(int)((npx + 127) / 128), 128, 0, st>>>(pm, p0, (int)npx, N, sc->d_samples, d_out, direct);
+        }
+        (*launches)++;
+    }
+    CU(cudaGetLastError());
+    return RT_OK;
+}
+
+extern "C" int rt_render(RtScene* sc, const RtRenderJob* job, float* d_out, RtCounters* counters, void* stream) {
+    if (!sc || !d_out) return fail(RT_ERR_INVALID, "null argument");
+    for (auto& m : sc->meshes) if (!m.built) return fail(RT_ERR_INVALID, "rt_scene_build_bvh has not been called");
+    PixelMap pm; long long nt;
+    UP(make_pixel_map(job, pm, nt));
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaSetDevice(sc->device));
+    CU(cudaMemsetAsync(sc->d_counters, 0, 2 * sizeof(RtCounters), st));
+    unsigned long long launches = 0;
+    int rc = sc->has_nodes ? render_impl<true>(sc, job, pm, d_out, st, &launches) : render_impl<false>(sc, job, pm, d_out, st, &launches);
+    if (rc != RT_OK) return rc;
+    sc->last_launches = launches;
+    if (counters) {
+        RtCounters two[2];
+        CU(cudaMemcpyAsync(two, sc->d_counters, 2 * sizeof(RtCounters), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        sum_counters(two, counters);
+        counters->kernel_launches = launches;
+    }
+    return RT_OK;
+}
+
+extern "C" int rt_render_host(RtScene* sc, const RtRenderJob* job, float* h_out, RtCounters* counters, void* stream) {
+    if (!sc || !h_out) return fail(RT_ERR_INVALID, "null argument");
+    int64_t n_floats = 0;
+    UP(rt_job_extent(job, nullptr, &n_floats));
+    UP(grow(&sc->d_stage, &sc->stage_cap, std::max<long long>(n_floats, 1)));
+    cudaStream_t st = (cudaStream_t)stream;
+    UP(rt_render(sc, job, sc->d_stage, nullptr, stream));
+    CU(cudaMemcpyAsync(h_out, sc->d_stage, sizeof(float) * (size_t)n_floats, cudaMemcpyDeviceToHost, st));
+    RtCounters two[2];
+    if (counters) CU(cudaMemcpyAsync(two, sc->d_counters, 2 * sizeof(RtCounters), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (counters) { sum_counters(two, counters); counters->kernel_launches = sc->last_launches; }
+    return RT_OK;
+}
+
+extern "C" int rt_assemble_tiles(const RtRenderJob* job, const float* d_gathered, const int64_t* rank_offsets_floats, float* d_out, void* stream) {
+    PixelMap pm; long long nt;
+    UP(make_pixel_map(job, pm, nt));
+    if (job->world > 64) return fail(RT_ERR_LIMIT, "world > 64");
+    cudaStream_t st = (cudaStream_t)stream;
+    long long* d_off = nullptr;
+    CU(cudaMallocAsync((void**)&d_off, sizeof(long long) * job->world, st));
+    CU(cudaMemcpyAsync(d_off, rank_offsets_floats, sizeof(long long) * job->world, cudaMemcpyHostToDevice, st));
+    const long long n = (long long)job->ncols * job->nrows;
+    if (n > 0) k_assemble<<<(int)((n + 255) / 256), 256, 0, st>>>(pm, d_gathered, d_off, d_out);
+    CU(cudaFreeAsync(d_off, st));
+    CU(cudaGetLastError());
+    return RT_OK;
+}
+
+extern "C" int rt_finalize_u8(const float* d_image, int32_t ncols, int32_t nrows, uint8_t* d_out_u8, void* stream) {
+    const long long n = (long long)ncols * nrows;
+    if (n > 0) k_finalize_u8<<<(int)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(d_image, ncols, nrows, d_out_u8);
+    CU(cudaGetLastError());
+    return RT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// unit-test aids: explicit rays (host buffers in, host buffers out)
+struct DevTmp {
+    std::vector<void*> p;
+    ~DevTmp() { for (void* q : p) cudaFree(q); }
+    template <class T> int get(T** out, size_t n, const T* src = nullptr) {
+        void* q = nullptr;
+        CU(cudaMalloc(&q, std::max<size_t>(n, 1) * sizeof(T)));
+        p.push_back(q);
+        if (src && n) CU(cudaMemcpy(q, src, n * sizeof(T), cudaMemcpyHostToDevice));
+        *out = (T*)q;
+        return RT_OK;
+    }
+};
+
+extern "C" int rt_trace_rays(RtScene* sc, int64_t n, const float* h_org, const float* h_dir, const float* h_times, float* h_rgb,
+                             float* h_t, float* h_n, float* h_p, int32_t* h_geom, int32_t* h_mat, int32_t mesh_mode, void* stream) {
+    if (!sc || n < 0) return fail(RT_ERR_INVALID, "bad argument");
+    for (auto& m : sc->meshes) if (!m.built) return fail(RT_ERR_INVALID, "rt_scene_build_bvh has not been called");
+    if (n == 0) return RT_OK;
+    CU(cudaSetDevice(sc->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    DevTmp tmp;
+    float *org, *dir, *times, *rgb, *t, *nn, *pp; int *geom, *mat;
+    UP(tmp.get(&org, 3 * n, h_org)); UP(tmp.get(&dir, 3 * n, h_dir)); UP(tmp.get(&times, n, h_times));
+    UP(tmp.get(&rgb, 3 * n)); UP(tmp.get(&t, n)); UP(tmp.get(&nn, 3 * n)); UP(tmp.get(&pp, 3 * n));
+    UP(tmp.get(&geom, n)); UP(tmp.get(&mat, n));
+    SceneView V = sc->view; V.mesh_mode = mesh_mode;
+    const size_t smem = sc->has_mesh ? sizeof(int) * RT_STACK_DEPTH * RT_BLOCK : 0;
+    const int grid = (int)((n + RT_BLOCK - 1) / RT_BLOCK);
+    CU(cudaMemsetAsync(sc->d_counters, 0, sizeof(RtCounters), st));
+    if (sc->has_nodes) {
+        if (smem) CU(cudaFuncSetAttribute(k_trace<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_trace<true><<<grid, RT_BLOCK, smem, st>>>(V, n, org, dir, times, rgb, t, nn, pp, geom, mat, sc->d_counters);
+    } else {
+        if (smem) CU(cudaFuncSetAttribute(k_trace<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_trace<false><<<grid, RT_BLOCK, smem, st>>>(V, n, org, dir, times, rgb, t, nn, pp, geom, mat, sc->d_counters);
+    }
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(st));
+    if (h_rgb) CU(cudaMemcpy(h_rgb, rgb, sizeof(float) * 3 * n, cudaMemcpyDeviceToHost));
+    if (h_t) CU(cudaMemcpy(h_t, t, sizeof(float) * n, cudaMemcpyDeviceToHost));
+    if (h_n) CU(cudaMemcpy(h_n, nn, sizeof(float) * 3 * n, cudaMemcpyDeviceToHost));
+    if (h_p) CU(cudaMemcpy(h_p, pp, sizeof(float) * 3 * n, cudaMemcpyDeviceToHost));
+    if (h_geom) CU(cudaMemcpy(h_geom, geom, sizeof(int) * n, cudaMemcpyDeviceToHost));
+    if (h_mat) CU(cudaMemcpy(h_mat, mat, sizeof(int) * n, cudaMemcpyDeviceToHost));
+    return RT_OK;
+}
+
+extern "C" int rt_occluded(RtScene* sc, int64_t n, const float* h_org, const float* h_dir, const float* h_times, const float* h_tmax,
+                           int32_t* h_occ, int32_t mesh_mode, void* stream) {
+    if (!sc || n < 0) return fail(RT_ERR_INVALID, "bad argument");
+    for (auto& m : sc->meshes) if (!m.built) return fail(RT_ERR_INVALID, "rt_scene_build_bvh has not been called");
+    if (n == 0) return RT_OK;
+    CU(cudaSetDevice(sc->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    DevTmp tmp;
+    float *org, *dir, *times, *tmax; int* occ;
+    UP(tmp.get(&org, 3 * n, h_org)); UP(tmp.get(&dir, 3 * n, h_dir)); UP(tmp.get(&times, n, h_times)); UP(tmp.get(&tmax, n, h_tmax));
+    UP(tmp.get(&occ, n));
+    SceneView V = sc->view; V.mesh_mode = mesh_mode;
+    const size_t smem = sc->has_mesh ? sizeof(int) * RT_STACK_DEPTH * RT_BLOCK : 0;
+    const int grid = (int)((n + RT_BLOCK - 1) / RT_BLOCK);
+    if (sc->has_nodes) {
+        if (smem) CU(cudaFuncSetAttribute(k_occluded<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_occluded<true><<<grid, RT_BLOCK, smem, st>>>(V, n, org, dir, times, tmax, occ, sc->d_counters);
+    } else {
+        if (smem) CU(cudaFuncSetAttribute(k_occluded<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_occluded<false><<<grid, RT_BLOCK, smem, st>>>(V, n, org, dir, times, tmax, occ, sc->d_counters);
+    }
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(st));
+    CU(cudaMemcpy(h_occ, occ, sizeof(int) * n, cudaMemcpyDeviceToHost));
+    return RT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// profiling
+static void drain_events(RtScene* sc) {
+    for (int c = 0; c < 3; c++) {
+        for (auto& pr : sc->ev[c]) {
+            cudaEventSynchronize(pr.second);
+            float ms = 0.0f;
+            if (cudaEventElapsedTime(&ms, pr.first, pr.second) == cudaSuccess) { sc->prof_ms[c] += ms; sc->prof_n[c]++; }
+            cudaEventDestroy(pr.first); cudaEventDestroy(pr.second);
+        }
+        sc->ev[c].clear();
+    }
+}
+
+extern "C" int rt_scene_profile(RtScene* sc, int32_t enable) {
+    if (!sc) return fail(RT_ERR_INVALID, "null scene");
+    drain_events(sc);
+    sc->profiling = enable != 0;
+    if (enable) for (int c = 0; c < 3; c++) { sc->prof_ms[c] = 0; sc->prof_n[c] = 0; }
+    return RT_OK;
+}
+
+extern "C" int rt_scene_profile_read(RtScene* sc, RtProfile* out) {
+    if (!sc || !out) return fail(RT_ERR_INVALID, "null argument");
+    drain_events(sc);
+    out->ms_primary = sc->prof_ms[0]; out->ms_secondary = sc->prof_ms[1]; out->ms_resolve = sc->prof_ms[2];
+    out->n_primary = sc->prof_n[0]; out->n_secondary = sc->prof_n[1]; out->n_resolve = sc->prof_n[2];
+    RtCounters two[2];
+    CU(cudaMemcpy(two, sc->d_counters, 2 * sizeof(RtCounters), cudaMemcpyDeviceToHost));
+    out->primary = two[0]; out->secondary = two[1];
+    return RT_OK;
+}

@@ -1,0 +1,31 @@
+"""Build csrc/libb200rt.so for sm_100a with nvcc (cross-compiles without a GPU)."""
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+OUT = os.path.join(HERE, "libb200rt.so")
+SRCS = ["b200rt.cu"]
+DEPS = ["b200rt.cu", "rt_kernels.cuh", "rt_core.cuh", "rt_bvh.cuh", "rt_types.cuh", "rt_math.cuh", "../../include/b200rt.h"]
+FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-shared",
+         "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr"]
+
+
+def build(force=False, verbose=False):
+    newest = max(os.path.getmtime(os.path.join(HERE, d)) for d in DEPS)
+    if not force and os.path.exists(OUT) and os.path.getmtime(OUT) >= newest:
+        return OUT
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    cmd = [nvcc] + FLAGS + ["-o", OUT] + [os.path.join(HERE, s) for s in SRCS]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    with open(os.path.join(HERE, "build.log"), "w") as fh:
+        fh.write(" ".join(cmd) + "\n" + r.stdout + r.stderr)
+    if verbose or r.returncode != 0:
+        sys.stderr.write(r.stdout + r.stderr)
+    if r.returncode != 0:
+        raise RuntimeError("nvcc failed, see csrc/build.log")
+    return OUT
+
+
+if __name__ == "__main__":
+    build(force="--force" in sys.argv, verbose=True)

@@ -1,0 +1,223 @@
+// rt_bvh.cuh - LBVH construction on the GPU (replaces the per-ray brute-force face loop set-up of
+// mesh.py:72-77): 63-bit Morton codes of triangle centroids -> LSD radix sort (8 x 8 bits, hand
+// written: per-tile histograms, one scan, stable scatter by warp match + per-round block offsets)
+// -> Karras 2012 radix-tree hierarchy -> bottom-up AABB refit with atomic arrival counters ->
+// 64-byte traversal nodes holding both children's boxes + triangles re-laid in Morton order.
+#pragma once
+#include "rt_types.cuh"
+
+// ---- Morton codes -------------------------------------------------------------------------------
+RT_HD uint64_t expand21(uint64_t v) {   // spread the low 21 bits to every third bit
+    v &= 0x1fffffull;
+    v = (v | v << 32) & 0x1f00000000ffffull;
+    v = (v | v << 16) & 0x1f0000ff0000ffull;
+    v = (v | v << 8) & 0x100f00f00f00f00full;
+    v = (v | v << 4) & 0x10c30c30c30c30c3ull;
+    v = (v | v << 2) & 0x1249249249249249ull;
+    return v;
+}
+RT_HD uint64_t morton63(float3 c, float3 lo, float3 inv_ext) {
+    float x = fminf(fmaxf((c.x - lo.x) * inv_ext.x, 0.0f), 1.0f);
+    float y = fminf(fmaxf((c.y - lo.y) * inv_ext.y, 0.0f), 1.0f);
+    float z = fminf(fmaxf((c.z - lo.z) * inv_ext.z, 0.0f), 1.0f);
+    uint64_t xi = (uint64_t)fminf(x * 2097152.0f, 2097151.0f);
+    uint64_t yi = (uint64_t)fminf(y * 2097152.0f, 2097151.0f);
+    uint64_t zi = (uint64_t)fminf(z * 2097152.0f, 2097151.0f);
+    return (expand21(xi) << 2) | (expand21(yi) << 1) | expand21(zi);
+}
+
+RT_HD float3 vert_at(const float* verts, int i) { return f3(verts[3 * (size_t)i], verts[3 * (size_t)i + 1], verts[3 * (size_t)i + 2]); }
+
+// ---- Karras 2012: node i of the binary radix tree over n sorted keys ------------------------------------
+RT_HD int clz64(uint64_t x) {
+#if defined(__CUDA_ARCH__)
+    return __clzll((long long)x);
+#else
+    return x ? __builtin_clzll(x) : 64;
+#endif
+}
+RT_HD int clz32(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+    return __clz((int)x);
+#else
+    return x ? __builtin_clz(x) : 32;
+#endif
+}
+// common-prefix length of keys i and j; identical keys fall back to the index (unique) so the tree stays binary
+RT_HD int lbvh_delta(const uint64_t* keys, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    uint64_t a = keys[i], b = keys[j];
+    if (a == b) return 64 + clz32((uint32_t)i ^ (uint32_t)j);
+    return clz64(a ^ b);
+}
+// children: >= 0 internal node index, < 0 leaf ~slot
+RT_HD void lbvh_node(const uint64_t* keys, int n, int i, int& left, int& right) {
+    int d = (lbvh_delta(keys, n, i, i + 1) - lbvh_delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    int dmin = lbvh_delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (lbvh_delta(keys, n, i, i + lmax * d) > dmin) lmax *= 2;
+    int l = 0;
+    for (int t = lmax / 2; t >= 1; t /= 2)
+        if (lbvh_delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    int j = i + l * d;
+    int dnode = lbvh_delta(keys, n, i, j);
+    int s = 0;
+    for (int t = (l + 1) / 2;; t = (t + 1) / 2) {
+        if (lbvh_delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+        if (t <= 1) break;
+    }
+    int gamma = i + s * d + (d < 0 ? d : 0);
+    int lo = i < j ? i : j, hi = i < j ? j : i;
+    left = (lo == gamma) ? ~gamma : gamma;
+    right = (hi == gamma + 1) ? ~(gamma + 1) : gamma + 1;
+}
+
+#if defined(__CUDACC__)
+// ---- kernels ------------------------------------------------------------------------------------------
+__global__ void k_morton(const float* __restrict__ verts, const int* __restrict__ faces, int n, float3 lo, float3 inv_ext,
+                         uint64_t* __restrict__ keys, int* __restrict__ vals) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float3 a = vert_at(verts, faces[3 * i]), b = vert_at(verts, faces[3 * i + 1]), c = vert_at(verts, faces[3 * i + 2]);
+    float3 cen = (a + b + c) * (1.0f / 3.0f);
+    keys[i] = morton63(cen, lo, inv_ext);
+    vals[i] = i;
+}
+
+#define RS_THREADS 256
+#define RS_ROUNDS 16
+#define RS_TILE (RS_THREADS * RS_ROUNDS)
+
+// per-tile digit histogram, hist[digit * n_tiles + tile]
+__global__ void __launch_bounds__(RS_THREADS) k_rs_hist(const uint64_t* __restrict__ keys, int n, int shift, int n_tiles, unsigned* __restrict__ hist) {
+    __shared__ unsigned h[256];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    const int base = blockIdx.x * RS_TILE;
+    for (int r = 0; r < RS_ROUNDS; r++) {
+        int i = base + r * RS_THREADS + threadIdx.x;
+        if (i < n) atomicAdd(&h[(unsigned)(keys[i] >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    hist[threadIdx.x * n_tiles + blockIdx.x] = h[threadIdx.x];
+}
+
+// exclusive scan of `m` counters in place, single block
+__global__ void __launch_bounds__(1024) k_rs_scan(unsigned* __restrict__ data, int m) {
+    __shared__ unsigned part[1024];
+    const int per = (m + 1023) / 1024;
+    const int b = threadIdx.x * per, e = min(b + per, m);
+    unsigned s = 0;
+    for (int i = b; i < e; i++) s += data[i];
+    part[threadIdx.x] = s;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {     // Hillis-Steele inclusive scan of the partials
+        unsigned v = threadIdx.x >= o ? part[threadIdx.x - o] : 0;
+        __syncthreads();
+        part[threadIdx.x] += v;
+        __syncthreads();
+    }
+    unsigned run = threadIdx.x ? part[threadIdx.x - 1] : 0;
+    for (int i = b; i < e; i++) { unsigned v = data[i]; data[i] = run; run += v; }
+}
+
+// stable scatter: rounds walk the tile in key order; inside a round, rank = (#equal digits in lower warps
+// of this round) + (#equal digits in lower lanes), on top of the per-digit count of earlier rounds
+__global__ void __launch_bounds__(RS_THREADS) k_rs_scatter(const uint64_t* __restrict__ keys, const int* __restrict__ vals, int n, int shift,
+                                                           int n_tiles, const unsigned* __restrict__ offs,
+                                                           uint64_t* __restrict__ keys_out, int* __restrict__ vals_out) {
+    __shared__ unsigned warp_cnt[RS_THREADS / 32][256];
+    __shared__ unsigned digit_base[256];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    digit_base[threadIdx.x] = offs[threadIdx.x * n_tiles + blockIdx.x];
+    const int base = blockIdx.x * RS_TILE;
+    for (int r = 0; r < RS_ROUNDS; r++) {
+        for (int w = 0; w < RS_THREADS / 32; w++) warp_cnt[w][threadIdx.x] = 0;
+        __syncthreads();
+        const int i = base + r * RS_THREADS + threadIdx.x;
+        const bool valid = i < n;
+        uint64_t key = valid ? keys[i] : 0;
+        const unsigned digit = valid ? ((unsigned)(key >> shift) & 255u) : 256u + (unsigned)lane;   // invalid lanes match nobody
+        const unsigned peers = __match_any_sync(0xffffffffu, digit);
+        const unsigned rank = __popc(peers & ((1u << lane) - 1));
+        if (valid && rank == 0) warp_cnt[warp][digit] = __popc(peers);
+        __syncthreads();
+        {   // thread d turns the per-warp counts of digit d into exclusive offsets and advances the digit base
+            unsigned run = digit_base[threadIdx.x];
+            for (int w = 0; w < RS_THREADS / 32; w++) { unsigned c = warp_cnt[w][threadIdx.x]; warp_cnt[w][threadIdx.x] = run; run += c; }
+            digit_base[threadIdx.x] = run;
+        }
+        __syncthreads();
+        if (valid) {
+            const unsigned dst = warp_cnt[warp][digit] + rank;
+            keys_out[dst] = key;
+            vals_out[dst] = vals[i];
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void k_lbvh_hierarchy(const uint64_t* __restrict__ keys, int n, int2* __restrict__ children, int* __restrict__ parent_node,
+                                 int* __restrict__ parent_leaf) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int l, r;
+    lbvh_node(keys, n, i, l, r);
+    children[i] = make_int2(l, r);
+    if (l < 0) parent_leaf[~l] = i; else parent_node[l] = i;
+    if (r < 0) parent_leaf[~r] = i; else parent_node[r] = i;
+    if (i == 0) parent_node[0] = -1;
+}
+
+// leaves: triangles in Morton order + their boxes; then walk up, second arrival merges the children
+__global__ void k_lbvh_leaves_refit(const float* __restrict__ verts, const int* __restrict__ faces, const int* __restrict__ order, int n,
+                                    const int2* __restrict__ children, const int* __restrict__ parent_node, const int* __restrict__ parent_leaf,
+                                    float4* __restrict__ tri, int4* __restrict__ face_vidx,
+                                    float4* __restrict__ leaf_lo, float4* __restrict__ leaf_hi,
+                                    float4* __restrict__ node_lo, float4* __restrict__ node_hi, unsigned* __restrict__ arrive) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    const int f = order[s];
+    const int i0 = faces[3 * f], i1 = faces[3 * f + 1], i2 = faces[3 * f + 2];
+    float3 a = vert_at(verts, i0), b = vert_at(verts, i1), c = vert_at(verts, i2);
+    tri[3 * (size_t)s] = f4(a.x, a.y, a.z, as_float(f));
+    tri[3 * (size_t)s + 1] = f4(b.x, b.y, b.z, 0.0f);
+    tri[3 * (size_t)s + 2] = f4(c.x, c.y, c.z, 0.0f);
+    face_vidx[s] = make_int4(i0, i1, i2, f);
+    float3 lo = f3(fminf(a.x, fminf(b.x, c.x)), fminf(a.y, fminf(b.y, c.y)), fminf(a.z, fminf(b.z, c.z)));
+    float3 hi = f3(fmaxf(a.x, fmaxf(b.x, c.x)), fmaxf(a.y, fmaxf(b.y, c.y)), fmaxf(a.z, fmaxf(b.z, c.z)));
+    leaf_lo[s] = f4(lo.x, lo.y, lo.z, 0.0f);
+    leaf_hi[s] = f4(hi.x, hi.y, hi.z, 0.0f);
+    if (n < 2) return;
+    __threadfence();
+    int node = parent_leaf[s];
+    while (node >= 0) {
+        if (atomicAdd(&arrive[node], 1u) == 0) return;     // first child to arrive stops; the second merges
+        __threadfence();
+        int2 ch = children[node];
+        float4 l0, h0, l1, h1;                             // L1 is not coherent: read the siblings' boxes from L2
+        if (ch.x < 0) { l0 = __ldcg(leaf_lo + ~ch.x); h0 = __ldcg(leaf_hi + ~ch.x); } else { l0 = __ldcg(node_lo + ch.x); h0 = __ldcg(node_hi + ch.x); }
+        if (ch.y < 0) { l1 = __ldcg(leaf_lo + ~ch.y); h1 = __ldcg(leaf_hi + ~ch.y); } else { l1 = __ldcg(node_lo + ch.y); h1 = __ldcg(node_hi + ch.y); }
+        node_lo[node] = f4(fminf(l0.x, l1.x), fminf(l0.y, l1.y), fminf(l0.z, l1.z), 0.0f);
+        node_hi[node] = f4(fmaxf(h0.x, h1.x), fmaxf(h0.y, h1.y), fmaxf(h0.z, h1.z), 0.0f);
+        __threadfence();
+        node = parent_node[node];
+    }
+}
+
+// final 64-byte traversal nodes: both children's (padded) boxes in the parent
+__global__ void k_lbvh_emit(int n, const int2* __restrict__ children, const float4* __restrict__ leaf_lo, const float4* __restrict__ leaf_hi,
+                            const float4* __restrict__ node_lo, const float4* __restrict__ node_hi, float pad, BvhNode* __restrict__ out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int2 ch = children[i];
+    float4 l0 = ch.x < 0 ? leaf_lo[~ch.x] : node_lo[ch.x], h0 = ch.x < 0 ? leaf_hi[~ch.x] : node_hi[ch.x];
+    float4 l1 = ch.y < 0 ? leaf_lo[~ch.y] : node_lo[ch.y], h1 = ch.y < 0 ? leaf_hi[~ch.y] : node_hi[ch.y];
+    BvhNode nd;
+    nd.q0 = f4(l0.x - pad, l0.y - pad, l0.z - pad, h0.x + pad);
+    nd.q1 = f4(h0.y + pad, h0.z + pad, l1.x - pad, l1.y - pad);
+    nd.q2 = f4(l1.z - pad, h1.x + pad, h1.y + pad, h1.z + pad);
+    nd.q3 = f4(as_float(ch.x), as_float(ch.y), 0.0f, 0.0f);
+    out[i] = nd;
+}
+#endif  // __CUDACC__

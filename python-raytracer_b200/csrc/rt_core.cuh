@@ -17,8 +17,6 @@
 #endif
 
 RT_HD float4 ld4(const float4* p) { return RT_LDG(p); }
-RT_HD int as_int(float f) { union { float f; int i; } u; u.f = f; return u.i; }
-RT_HD float as_float(int i) { union { float f; int i; } u; u.i = i; return u.f; }
 
 struct TraceCtx {
     const SceneView& S;
@@ -288,11 +286,38 @@ RT_HD float3 box_diffuse(const SceneView& S, const DevObject* o, float3 p, float
 // CSG / transform nodes (hierarchy.py:42-138).  Recursion is unrolled at compile time to
 // RT_MAX_NEST levels (template depth), no device call stack.
 
-RT_HD bool difference_shadow(TraceCtx& cx, int c0, const Ray& mr);
+// shadow_intersect of a leaf primitive (simple_geometry.py:48-72,122-131,251-294; mesh.py:121-153)
+RT_HD bool leaf_shadow(TraceCtx& cx, int oi, const Ray& r, float tmax) {
+    const DevObject* o = cx.S.objects + oi;
+    cx.tally.prims++;
+    switch (o->kind) {
+    case RT_KIND_SPHERE: {                                     // simple_geometry.py:48-72
+        float4 a = ld4(&o->a);
+        float t1, t2;
+        if (!sphere_roots(moved(o, f3(a), cx.time), a.w, r, dot(r.d, r.d), t1, t2)) return false;
+        return (RT_SHADOW_EPS_SPHERE < t1 && t1 < tmax) || (RT_SHADOW_EPS_SPHERE < t2 && t2 < tmax);
+    }
+    case RT_KIND_PLANE: {                                      // simple_geometry.py:122-131
+        float t;
+        if (!plane_t(moved(o, f3(ld4(&o->a)), cx.time), f3(ld4(&o->b)), r, t)) return false;
+        return RT_SHADOW_EPS < t && t < tmax;
+    }
+    case RT_KIND_BOX: {                                        // simple_geometry.py:251-294 (entry t only, may be < 0)
+        float en, ex; int label;
+        if (!box_slabs(moved(o, f3(ld4(&o->a)), cx.time), moved(o, f3(ld4(&o->b)), cx.time), r, en, ex, label)) return false;
+        if (en > ex) return false;
+        return RT_SHADOW_EPS < en && en < tmax;
+    }
+    case RT_KIND_MESH: return mesh_shadow(cx, cx.S.meshes + o->mesh, r);
+            default: return false;
+    }
+}
+
+RT_HD_NOINLINE bool difference_shadow(TraceCtx& cx, int c0, const Ray& mr);
 
 template <int D> struct Nest {
     // is_inside (hierarchy.py:111-129; Sphere :74-80, AABB :296-307; Plane/Mesh: base class False)
-    static RT_HD bool inside(TraceCtx& cx, int oi, float3 p) {
+    static RT_HD_NOINLINE bool inside(TraceCtx& cx, int oi, float3 p) {
         const DevObject* o = cx.S.objects + oi;
         switch (o->kind) {
             case RT_KIND_SPHERE: {
@@ -322,7 +347,7 @@ template <int D> struct Nest {
         }
     }
     // get_material (hierarchy.py:131-138; Plane :133; others materials[0])
-    static RT_HD int material(TraceCtx& cx, int oi, float3 p) {
+    static RT_HD_NOINLINE int material(TraceCtx& cx, int oi, float3 p) {
         const DevObject* o = cx.S.objects + oi;
         if (o->kind == RT_KIND_PLANE) return plane_material(o, p, cx.time);
         if (o->kind == RT_KIND_NODE) {
@@ -335,28 +360,11 @@ template <int D> struct Nest {
     }
 
     // shadow_intersect (hierarchy.py:80-109 and the leaf versions)
-    static RT_HD bool shadow(TraceCtx& cx, int oi, const Ray& r, float tmax) {
+    static RT_HD_NOINLINE bool shadow(TraceCtx& cx, int oi, const Ray& r, float tmax) {
         const DevObject* o = cx.S.objects + oi;
+        if (o->kind != RT_KIND_NODE) return leaf_shadow(cx, oi, r, tmax);
         cx.tally.prims++;
         switch (o->kind) {
-            case RT_KIND_SPHERE: {                                     // simple_geometry.py:48-72
-                float4 a = ld4(&o->a);
-                float t1, t2;
-                if (!sphere_roots(moved(o, f3(a), cx.time), a.w, r, dot(r.d, r.d), t1, t2)) return false;
-                return (RT_SHADOW_EPS_SPHERE < t1 && t1 < tmax) || (RT_SHADOW_EPS_SPHERE < t2 && t2 < tmax);
-            }
-            case RT_KIND_PLANE: {                                      // simple_geometry.py:122-131
-                float t;
-                if (!plane_t(moved(o, f3(ld4(&o->a)), cx.time), f3(ld4(&o->b)), r, t)) return false;
-                return RT_SHADOW_EPS < t && t < tmax;
-            }
-            case RT_KIND_BOX: {                                        // simple_geometry.py:251-294 (entry t only, may be < 0)
-                float en, ex; int label;
-                if (!box_slabs(moved(o, f3(ld4(&o->a)), cx.time), moved(o, f3(ld4(&o->b)), cx.time), r, en, ex, label)) return false;
-                if (en > ex) return false;
-                return RT_SHADOW_EPS < en && en < tmax;
-            }
-            case RT_KIND_MESH: return mesh_shadow(cx, cx.S.meshes + o->mesh, r);
             case RT_KIND_NODE: {
                 const DevXform* xf = cx.S.xforms + o->xform;
                 Ray mr; mr.o = xform_point(xf->Minv, r.o); mr.d = xform_dir(xf->Minv, r.d);
@@ -517,7 +525,7 @@ RT_HD void object_hits(TraceCtx& cx, int root, const Ray& r, Want&& want, Emit&&
 
 // Hierarchy.shadow_intersect, difference case (hierarchy.py:94-107): goes through intersect() of both
 // children, `time > shadow_epsilon`, and ignores t_max.
-RT_HD bool difference_shadow(TraceCtx& cx, int c0, const Ray& mr) {
+RT_HD_NOINLINE bool difference_shadow(TraceCtx& cx, int c0, const Ray& mr) {
     bool occ = false;
     auto want = [&](float t) { return !occ && t > RT_SHADOW_EPS; };
     object_hits(cx, c0, mr, want, [&](const Hit& h) {
@@ -613,8 +621,10 @@ RT_HD bool occluded(TraceCtx& cx, const Ray& r, float tmax) {
             float t1, t2;
             if (sphere_roots(moved(o, f3(a), cx.time), a.w, r, A, t1, t2) &&
                 ((RT_SHADOW_EPS_SPHERE < t1 && t1 < tmax) || (RT_SHADOW_EPS_SPHERE < t2 && t2 < tmax))) return true;
-        } else if (HAS_NODES || kind != RT_KIND_NODE) {
-            if (Nest<HAS_NODES ? RT_MAX_NEST : 1>::shadow(cx, oi, r, tmax)) return true;
+        } else if (kind != RT_KIND_NODE) {
+            if (leaf_shadow(cx, oi, r, tmax)) return true;
+        } else if (HAS_NODES) {
+            if (Nest<RT_MAX_NEST>::shadow(cx, oi, r, tmax)) return true;
         }
     }
     return false;
@@ -725,3 +735,24 @@ RT_HD Ray generate_ray(const SceneView& S, int col, int row, int d, int s) {
     }
     return r;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Which pixels a launch covers (see RtRenderJob in include/b200rt.h)
+struct PixelMap {
+    int col0, ncols, row0, nrows;
+    int tile_w, tile_h, rank, world;
+    int n_tile_rows;            // tiles per tile-column
+    int tile_px;                // tile_w * tile_h
+    long long n_local_pixels;   // n_local_tiles * tile_px (partial tiles padded)
+};
+
+RT_HD bool pixel_of(const PixelMap& pm, long long lp, int& col, int& row) {
+    long long lt = lp / pm.tile_px;
+    int q = (int)(lp - lt * pm.tile_px);
+    long long gt = lt * pm.world + pm.rank;
+    int tcol = (int)(gt / pm.n_tile_rows), trow = (int)(gt - (long long)tcol * pm.n_tile_rows);
+    col = pm.col0 + tcol * pm.tile_w + q % pm.tile_w;
+    row = pm.row0 + trow * pm.tile_h + q / pm.tile_w;
+    return col < pm.col0 + pm.ncols && row < pm.row0 + pm.nrows;
+}
+

@@ -1,0 +1,239 @@
+// rt_kernels.cuh - the wavefront kernels of the render path (one thread per (pixel, sample) ray).
+//
+//   k_primary   : raygen + closest hit + shading (inline shadow rays) for every primary ray of a batch;
+//                 finished samples go to the sample buffer, reflection/refraction rays are compacted
+//                 (warp ballot + prefix popcount + one atomic per warp) into the next ray queue
+//   k_secondary : one recursion level of cast_ray for a compacted queue (replaces scene.py:102,203,208)
+//   k_resolve   : per-pixel sum in the reference's loop order and division (scene.py:69,73)
+//   k_assemble  : scatter gathered tile buffers into the reference layout (glue.py:19-22)
+//   k_finalize  : rot90 + *255 truncation (main.py:31-33)
+#pragma once
+#include "rt_core.cuh"
+
+#define RT_BLOCK 128
+
+// Compacted ray queue, SoA of float4 planes (coalesced 128-bit accesses):
+//   plane 0: origin.xyz, time           plane 1: dir.xyz, bits(sample slot)
+//   plane 2: fold.a.xyz, fold.w         plane 3: fold.lo.xyz, bits(depth_left | in_shape << 8)
+//   plane 4: fold.hi.xyz, -
+struct RayQueue { float4* planes; long long cap; };
+#define RT_QUEUE_PLANES 5
+
+__device__ __forceinline__ void queue_store(const RayQueue& q, long long i, const PathState& ps, float time, unsigned slot) {
+    q.planes[0 * q.cap + i] = f4(ps.ray.o.x, ps.ray.o.y, ps.ray.o.z, time);
+    q.planes[1 * q.cap + i] = f4(ps.ray.d.x, ps.ray.d.y, ps.ray.d.z, as_float((int)slot));
+    q.planes[2 * q.cap + i] = f4(ps.fold.a.x, ps.fold.a.y, ps.fold.a.z, ps.fold.w);
+    q.planes[3 * q.cap + i] = f4(ps.fold.lo.x, ps.fold.lo.y, ps.fold.lo.z, as_float(ps.depth_left | (ps.in_shape << 8)));
+    q.planes[4 * q.cap + i] = f4(ps.fold.hi.x, ps.fold.hi.y, ps.fold.hi.z, 0.0f);
+}
+__device__ __forceinline__ void queue_load(const RayQueue& q, long long i, PathState& ps, float& time, unsigned& slot) {
+    float4 p0 = q.planes[0 * q.cap + i], p1 = q.planes[1 * q.cap + i], p2 = q.planes[2 * q.cap + i];
+    float4 p3 = q.planes[3 * q.cap + i], p4 = q.planes[4 * q.cap + i];
+    ps.ray.o = f3(p0); time = p0.w;
+    ps.ray.d = f3(p1); slot = (unsigned)as_int(p1.w);
+    ps.fold.a = f3(p2); ps.fold.w = p2.w;
+    ps.fold.lo = f3(p3); int fl = as_int(p3.w); ps.depth_left = fl & 0xff; ps.in_shape = (fl >> 8) & 1;
+    ps.fold.hi = f3(p4);
+}
+
+// Warp-aggregated append: ballot -> exclusive prefix by popcount -> one atomicAdd per warp.
+// Must be reached by all 32 lanes of the warp.
+__device__ __forceinline__ long long queue_reserve(unsigned long long* count, bool want) {
+    unsigned mask = __ballot_sync(0xffffffffu, want);
+    if (mask == 0) return -1;
+    unsigned lane = threadIdx.x & 31;
+    int leader = __ffs(mask) - 1;
+    unsigned long long base = 0;
+    if ((int)lane == leader) base = atomicAdd(count, (unsigned long long)__popc(mask));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return want ? (long long)(base + __popc(mask & ((1u << lane) - 1))) : -1;
+}
+
+__device__ __forceinline__ void tally_flush(const Tally& t, unsigned long long primary, unsigned long long queued, RtCounters* c) {
+    unsigned v[9] = {t.shadow, t.reflect, t.refract, t.nodes, t.tris, t.prims, t.shaded, t.smooth, t.err};
+    unsigned long long w[9];
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        unsigned long long x = v[k];
+        if (k == 8) {   // error bits: OR
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) x |= __shfl_xor_sync(0xffffffffu, x, o);
+        } else {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+        }
+        w[k] = x;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { primary += __shfl_xor_sync(0xffffffffu, primary, o); queued += __shfl_xor_sync(0xffffffffu, queued, o); }
+    if ((threadIdx.x & 31) == 0) {
+        if (primary) atomicAdd((unsigned long long*)&c->rays_primary, primary);
+        if (w[0]) atomicAdd((unsigned long long*)&c->rays_shadow, w[0]);
+        if (w[1]) atomicAdd((unsigned long long*)&c->rays_reflect, w[1]);
+        if (w[2]) atomicAdd((unsigned long long*)&c->rays_refract, w[2]);
+        if (w[3]) atomicAdd((unsigned long long*)&c->bvh_nodes, w[3]);
+        if (w[4]) atomicAdd((unsigned long long*)&c->tri_tests, w[4]);
+        if (w[5]) atomicAdd((unsigned long long*)&c->prim_tests, w[5]);
+        if (w[6]) atomicAdd((unsigned long long*)&c->shaded_hits, w[6]);
+        if (w[7]) atomicAdd((unsigned long long*)&c->mesh_hits_smooth, w[7]);
+        if (queued) atomicAdd((unsigned long long*)&c->queued_rays, queued);
+        if (w[8]) atomicOr((unsigned long long*)&c->error_flags, w[8]);
+    }
+}
+
+__device__ __forceinline__ Tally tally_zero() { Tally t; t.shadow = t.reflect = t.refract = t.nodes = t.tris = t.prims = t.shaded = t.smooth = t.err = 0; return t; }
+
+extern __shared__ int rt_smem_stack[];   // RT_STACK_DEPTH * blockDim.x ints when the scene has a mesh
+
+// ---- primary rays ---------------------------------------------------------------------------------
+// ray i of the batch: pixel = pixel_begin + i / N, slot = i % N = (d*S + s)*T + t  (loop order of scene.py:57-67)
+template <bool HAS_NODES>
+__global__ void __launch_bounds__(RT_BLOCK) k_primary(SceneView S, PixelMap pm, long long pixel_begin, long long n_rays,
+                                                       float4* __restrict__ samples, RayQueue qout, unsigned long long* qcount,
+                                                       RtCounters* counters) {
+    Tally tally = tally_zero();
+    unsigned long long n_primary = 0, n_queued = 0;
+    const int N = S.D * S.S * S.T;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long base = (long long)blockIdx.x * blockDim.x; base < n_rays; base += stride) {
+        const long long i = base + threadIdx.x;
+        bool cont = false;
+        PathState ps; float time = 0.0f;
+        if (i < n_rays) {
+            const long long lp = pixel_begin + i / N;
+            const int slot = (int)(i % N);
+            int col, row;
+            float3 sample = f3(0, 0, 0);
+            if (pixel_of(pm, lp, col, row)) {
+                const int t = slot % S.T, ds = slot / S.T;
+                const int s = ds % S.S, d = ds / S.S;
+                ps.ray = generate_ray(S, col, row, d, s);
+                ps.fold = fold_identity(); ps.depth_left = S.max_depth; ps.in_shape = 0;
+                time = RT_LDG(S.times + t);
+                TraceCtx cx{S, time, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x};
+                n_primary++;
+                cont = trace_level<HAS_NODES>(cx, ps, sample);
+            }
+            if (!cont) samples[i] = f4(sample.x, sample.y, sample.z, 0.0f);
+        }
+        long long qi = queue_reserve(qcount, cont);
+        if (cont) { queue_store(qout, qi, ps, time, (unsigned)i); n_queued++; }
+    }
+    tally_flush(tally, n_primary, n_queued, counters);
+}
+
+// ---- one recursion level over a compacted queue -----------------------------------------------------
+template <bool HAS_NODES>
+__global__ void __launch_bounds__(RT_BLOCK) k_secondary(SceneView S, RayQueue qin, const unsigned long long* qin_count,
+                                                         float4* __restrict__ samples, RayQueue qout, unsigned long long* qout_count,
+                                                         RtCounters* counters) {
+    Tally tally = tally_zero();
+    unsigned long long n_queued = 0;
+    const long long n = (long long)*qin_count;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long base = (long long)blockIdx.x * blockDim.x; base < n; base += stride) {
+        const long long i = base + threadIdx.x;
+        bool cont = false;
+        PathState ps; float time = 0.0f; unsigned slot = 0;
+        if (i < n) {
+            queue_load(qin, i, ps, time, slot);
+            TraceCtx cx{S, time, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x};
+            float3 sample;
+            cont = trace_level<HAS_NODES>(cx, ps, sample);
+            if (!cont) samples[slot] = f4(sample.x, sample.y, sample.z, 0.0f);
+        }
+        long long qi = queue_reserve(qout_count, cont);
+        if (cont) { queue_store(qout, qi, ps, time, slot); n_queued++; }
+    }
+    tally_flush(tally, 0, n_queued, counters);
+}
+
+// ---- per-pixel average -------------------------------------------------------------------------------
+// colour accumulates in float32 in loop order (scene.py:69), then one float32 division (scene.py:73)
+__global__ void k_resolve(PixelMap pm, long long pixel_begin, int n_pixels, int N, const float4* __restrict__ samples,
+                          float* __restrict__ out, int direct) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_pixels) return;
+    const long long lp = pixel_begin + p;
+    int col, row;
+    const bool valid = pixel_of(pm, lp, col, row);
+    float3 c = f3(0, 0, 0);
+    if (valid) {
+        const float4* sp = samples + (long long)p * N;
+        for (int k = 0; k < N; k++) { float4 v = sp[k]; c = c + f3(v); }
+        const float n = (float)N;
+        c = f3(c.x / n, c.y / n, c.z / n);
+    }
+    long long o;
+    if (direct) { if (!valid) return; o = ((long long)(col - pm.col0) * pm.nrows + (row - pm.row0)) * 3; }
+    else o = lp * 3;
+    out[o] = c.x; out[o + 1] = c.y; out[o + 2] = c.z;
+}
+
+// ---- fan-in (glue.py:19-22) ----------------------------------------------------------------------------
+__global__ void k_assemble(PixelMap pm, const float* __restrict__ gathered, const long long* __restrict__ rank_off,
+                           float* __restrict__ out) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)pm.ncols * pm.nrows) return;
+    const int c = (int)(i / pm.nrows), r = (int)(i - (long long)c * pm.nrows);
+    const int tcol = c / pm.tile_w, trow = r / pm.tile_h;
+    const long long gt = (long long)tcol * pm.n_tile_rows + trow;
+    const int rank = (int)(gt % pm.world);
+    const long long lt = gt / pm.world;
+    const int q = (r - trow * pm.tile_h) * pm.tile_w + (c - tcol * pm.tile_w);
+    const float* src = gathered + rank_off[rank] + (lt * pm.tile_px + q) * 3;
+    out[i * 3] = src[0]; out[i * 3 + 1] = src[1]; out[i * 3 + 2] = src[2];
+}
+
+// ---- main.py:31-33: rot90 + (image * 255).astype(uint8) (double product, truncation) --------------------
+__global__ void k_finalize_u8(const float* __restrict__ img, int ncols, int nrows, uint8_t* __restrict__ out) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)ncols * nrows) return;
+    const int line = (int)(i / ncols), j = (int)(i - (long long)line * ncols);
+    const float* src = img + ((long long)j * nrows + (nrows - 1 - line)) * 3;
+#pragma unroll
+    for (int k = 0; k < 3; k++) out[i * 3 + k] = (uint8_t)(int)((double)src[k] * 255.0);
+}
+
+// ---- unit-test aids: explicit rays through the same device functions ---------------------------------------
+template <bool HAS_NODES>
+__global__ void __launch_bounds__(RT_BLOCK) k_trace(SceneView S, long long n, const float* __restrict__ org, const float* __restrict__ dir,
+                                                     const float* __restrict__ times, float* rgb, float* hit_t, float* hit_n, float* hit_p,
+                                                     int* hit_geom, int* hit_mat, RtCounters* counters) {
+    Tally tally = tally_zero();
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        PathState ps;
+        ps.ray.o = f3(org[3 * i], org[3 * i + 1], org[3 * i + 2]);
+        ps.ray.d = f3(dir[3 * i], dir[3 * i + 1], dir[3 * i + 2]);
+        TraceCtx cx{S, times[i], tally, rt_smem_stack + threadIdx.x, (int)blockDim.x};
+        Hit h;
+        if (closest_hit<HAS_NODES>(cx, ps.ray, h)) {
+            hit_t[i] = h.t; hit_geom[i] = h.geom; hit_mat[i] = h.mat;
+            hit_n[3 * i] = h.n.x; hit_n[3 * i + 1] = h.n.y; hit_n[3 * i + 2] = h.n.z;
+            hit_p[3 * i] = h.p.x; hit_p[3 * i + 1] = h.p.y; hit_p[3 * i + 2] = h.p.z;
+        } else {
+            hit_t[i] = RT_INF; hit_geom[i] = -1; hit_mat[i] = -1;
+            for (int k = 0; k < 3; k++) { hit_n[3 * i + k] = 0.0f; hit_p[3 * i + k] = 0.0f; }
+        }
+        ps.fold = fold_identity(); ps.depth_left = S.max_depth; ps.in_shape = 0;
+        float3 sample;
+        while (trace_level<HAS_NODES>(cx, ps, sample)) {}
+        rgb[3 * i] = sample.x; rgb[3 * i + 1] = sample.y; rgb[3 * i + 2] = sample.z;
+    }
+    tally_flush(tally, 0, 0, counters);
+}
+
+template <bool HAS_NODES>
+__global__ void __launch_bounds__(RT_BLOCK) k_occluded(SceneView S, long long n, const float* __restrict__ org, const float* __restrict__ dir,
+                                                        const float* __restrict__ times, const float* __restrict__ tmax, int* occ,
+                                                        RtCounters* counters) {
+    Tally tally = tally_zero();
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        Ray r; r.o = f3(org[3 * i], org[3 * i + 1], org[3 * i + 2]); r.d = f3(dir[3 * i], dir[3 * i + 1], dir[3 * i + 2]);
+        TraceCtx cx{S, times[i], tally, rt_smem_stack + threadIdx.x, (int)blockDim.x};
+        occ[i] = occluded<HAS_NODES>(cx, r, tmax[i]) ? 1 : 0;
+    }
+    tally_flush(tally, 0, 0, counters);
+}

@@ -25,6 +25,8 @@
 
 #define RT_INF __builtin_huge_valf()
 
+RT_HD int as_int(float f) { union { float f; int i; } u; u.f = f; return u.i; }
+RT_HD float as_float(int i) { union { float f; int i; } u; u.i = i; return u.f; }
 RT_HD float3 f3(float x, float y, float z) { float3 r; r.x = x; r.y = y; r.z = z; return r; }
 RT_HD float3 f3(const float4& v) { return f3(v.x, v.y, v.z); }
 RT_HD float4 f4(float x, float y, float z, float w) { float4 r; r.x = x; r.y = y; r.z = z; r.w = w; return r; }

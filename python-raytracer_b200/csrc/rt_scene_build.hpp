@@ -1,0 +1,153 @@
+// rt_scene_build.hpp - host-side conversion RtSceneDesc -> device record arrays and sampling tables.
+// Pure host C++ (no CUDA calls): b200rt.cu uploads the vectors to HBM; tests/hostsim points a SceneView
+// at them directly to exercise the same per-ray functions on the CPU.
+#pragma once
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "rt_core.cuh"
+
+struct HostScene {
+    std::vector<DevObject> objs;
+    std::vector<DevMaterial> mats;
+    std::vector<DevLight> lights;
+    std::vector<float> col_x, row_y, times;
+    std::vector<float4> dof_origin, ray_origin;
+    bool has_nodes = false, has_specular = false, has_mesh = false;
+    SceneView view{};          // scalars filled; pointers are the caller's business
+};
+
+namespace rtb {
+inline float3 h3(const float* p) { return f3(p[0], p[1], p[2]); }
+inline float4 h4(const float* p, float w = 0.0f) { return f4(p[0], p[1], p[2], w); }
+
+// scene.py:118-138: golden-angle disc points in WORLD x/y around `origin` (float32 results)
+inline void sunflower(int n, float3 origin, double radius, std::vector<float4>& out) {
+    const double phi = (1.0 + std::sqrt(5.0)) / 2.0;
+    const double stride = 2.0 * 3.14159265358979323846 / phi;
+    for (int k = 1; k <= n; k++) {
+        double r = radius * std::sqrt(k - 0.5) / std::sqrt(n - 0.5);
+        double th = k * stride;
+        out.push_back(f4((float)(r * std::cos(th) + (double)origin.x), (float)(r * std::sin(th) + (double)origin.y), origin.z, 0.0f));
+    }
+}
+
+inline int nest_depth(const RtSceneDesc* d, int oi, int depth) {
+    const RtObject& o = d->objects[oi];
+    if (o.kind != RT_KIND_NODE) return depth;
+    int m = depth + 1;
+    for (int k = 0; k < o.n_children; k++) m = std::max(m, nest_depth(d, o.first_child + k, depth + 1));
+    return m;
+}
+
+// returns RT_OK or an RtStatus with `err` set
+inline int convert_scene(const RtSceneDesc* d, HostScene& hs, std::string& err) {
+    auto bad = [&](int code, const char* m) { err = m; return code; };
+    if (d->width <= 0 || d->height <= 0 || d->dof_samples <= 0 || d->aa_samples <= 0 || d->n_times <= 0)
+        return bad(RT_ERR_INVALID, "resolution and sample counts must be positive");
+    if (d->max_depth < 0 || d->max_depth > 255) return bad(RT_ERR_LIMIT, "max_depth must be in [0, 255]");
+    hs.objs.resize(d->n_objects);
+    for (int i = 0; i < d->n_objects; i++) {
+        const RtObject& o = d->objects[i];
+        DevObject& g = hs.objs[i];
+        memset(&g, 0, sizeof g);
+        if (o.kind < 0 || o.kind > RT_KIND_NODE) return bad(RT_ERR_INVALID, "object kind out of range");
+        if (o.kind == RT_KIND_NODE && (o.xform < 0 || o.xform >= d->n_xforms || o.first_child < 0 || o.n_children < 0 ||
+                                       o.first_child + o.n_children > d->n_objects))
+            return bad(RT_ERR_INVALID, "node child range / xform index out of range");
+        if (o.kind == RT_KIND_MESH && (o.mesh < 0 || o.mesh >= d->n_meshes)) return bad(RT_ERR_INVALID, "mesh index out of range");
+        if (o.tex >= d->n_textures) return bad(RT_ERR_INVALID, "texture index out of range");
+        if ((o.n_mats > 0 && (o.mat0 < 0 || o.mat0 >= d->n_materials)) || (o.n_mats > 1 && (o.mat1 < 0 || o.mat1 >= d->n_materials)))
+            return bad(RT_ERR_INVALID, "material index out of range");
+        g.a = h4(o.a, o.radius); g.b = h4(o.b); g.speed = h4(o.speed);
+        g.kind = o.kind; g.n_mats = o.n_mats; g.mat0 = o.mat0; g.mat1 = o.mat1;
+        g.tex = o.tex; g.mesh = o.mesh; g.first_child = o.first_child; g.n_children = o.n_children;
+        g.csg = o.csg; g.xform = o.xform;
+        g.ax_w = h4(o.ax_w); g.ax_h = h4(o.ax_h);
+        g.tex_scale = o.tex_scale;
+        if (o.kind == RT_KIND_NODE) hs.has_nodes = true;
+        if (o.kind == RT_KIND_MESH) hs.has_mesh = true;
+    }
+    if (d->n_top < 0 || d->n_top > d->n_objects) return bad(RT_ERR_INVALID, "n_top out of range");
+    for (int i = 0; i < d->n_top; i++)
+        if (nest_depth(d, i, 0) > RT_MAX_NEST) return bad(RT_ERR_LIMIT, "CSG/transform nesting deeper than RT_MAX_NEST");
+    hs.mats.resize(d->n_materials);
+    for (int i = 0; i < d->n_materials; i++) {
+        const RtMaterial& m = d->materials[i];
+        hs.mats[i].diffuse = h4(m.diffuse, (float)m.hardness);
+        hs.mats[i].specular = h4(m.specular, (float)m.tint);
+        hs.mats[i].refr_index = (float)m.refr_index;
+        hs.mats[i].inv_refr = (float)(1.0 / m.refr_index);          // scene.py:194
+        hs.mats[i].one_minus_tint = (float)(1.0 - m.tint);          // scene.py:104
+        hs.mats[i].type = m.type;
+        if (m.type != RT_MAT_DIFFUSE) hs.has_specular = true;
+    }
+    hs.lights.resize(d->n_lights);
+    for (int i = 0; i < d->n_lights; i++) {
+        const RtLight& l = d->lights[i];
+        hs.lights[i].vector = h4(l.vector, as_float(l.type));
+        hs.lights[i].colour_power = f4(l.colour[0] * l.power, l.colour[1] * l.power, l.colour[2] * l.power, 0.0f);   // scene.py:183
+        float3 nd = normalize(-h3(l.vector));                        // scene.py:173
+        hs.lights[i].dir_norm = f4(nd.x, nd.y, nd.z, 0.0f);
+    }
+    // sampling tables (scene.py:41-43,57,60,64), accumulated in float64 exactly like the reference's loops
+    const double dx = (d->right - d->left) / d->width, dy = (d->top - d->bottom) / d->height;
+    hs.col_x.resize(d->width); hs.row_y.resize(d->height);
+    { double x = d->left + 0.5 * dx; for (int c = 0; c < d->width; c++) { hs.col_x[c] = (float)x; x += dx; } }
+    { double y = d->bottom + 0.5 * dy; for (int r = 0; r < d->height; r++) { hs.row_y[r] = (float)y; y += dy; } }
+    sunflower(d->dof_samples, h3(d->cam_pos), d->aperture, hs.dof_origin);
+    for (int k = 0; k < d->dof_samples; k++) sunflower(d->aa_samples, f3(hs.dof_origin[k]), 2 * (dx + dy), hs.ray_origin);
+    hs.times.resize(d->n_times);
+    for (int t = 0; t < d->n_times; t++) hs.times[t] = (float)d->motion_times[t];
+    SceneView& V = hs.view;
+    V.n_objects = d->n_objects; V.n_top = d->n_top; V.n_materials = d->n_materials; V.n_lights = d->n_lights;
+    V.cam_pos = h3(d->cam_pos); V.cam_u = h3(d->cam_u); V.cam_v = h3(d->cam_v); V.cam_w = h3(d->cam_w);
+    V.focal_length = (float)d->focal_length;
+    V.noise_scale = (float)(0.1 * (dx + dy));
+    V.width = d->width; V.height = d->height; V.D = d->dof_samples; V.S = d->aa_samples; V.T = d->n_times;
+    V.jitter = d->jitter;
+    V.seed_lo = (uint32_t)d->jitter_seed; V.seed_hi = (uint32_t)(d->jitter_seed >> 32);
+    V.ambient = h3(d->ambient);
+    V.max_depth = d->max_depth;
+    V.mesh_mode = 0;
+    return RT_OK;
+}
+
+// mesh bounds + the padding used for the conservative LBVH boxes
+inline void mesh_bounds(const RtMesh& m, float3& lo, float3& hi, float& pad) {
+    lo = f3(INFINITY, INFINITY, INFINITY); hi = f3(-INFINITY, -INFINITY, -INFINITY);
+    float maxabs = 0.0f;
+    for (int k = 0; k < m.n_verts; k++) {
+        float3 v = h3(m.verts + 3 * (size_t)k);
+        lo = f3(fminf(lo.x, v.x), fminf(lo.y, v.y), fminf(lo.z, v.z));
+        hi = f3(fmaxf(hi.x, v.x), fmaxf(hi.y, v.y), fmaxf(hi.z, v.z));
+        maxabs = fmaxf(maxabs, fmaxf(fabsf(v.x), fmaxf(fabsf(v.y), fabsf(v.z))));
+    }
+    // the reference's inclusive edge tests accept points a few ulp outside the triangle: keep node boxes conservative
+    pad = 1e-5f * maxabs + 1e-7f;
+}
+inline void mesh_header(const RtMesh& m, DevMesh& g) {
+    memset(&g, 0, sizeof g);
+    g.n_tris = m.n_faces; g.flat_shaded = m.flat_shaded; g.gate = m.gate; g.gate_radius = m.gate_radius;
+    g.gate_min = h4(m.gate_min); g.gate_max = h4(m.gate_max); g.gate_center = h4(m.gate_center);
+}
+
+// RtRenderJob -> PixelMap (tile interleave across ranks, include/b200rt.h); false on a malformed job
+inline bool make_pixel_map(const RtRenderJob* job, PixelMap& pm, long long& n_local_tiles) {
+    if (!job || job->ncols < 0 || job->nrows < 0 || job->tile_w <= 0 || job->tile_h <= 0 || job->world <= 0 ||
+        job->rank < 0 || job->rank >= job->world)
+        return false;
+    pm.col0 = job->col0; pm.ncols = job->ncols; pm.row0 = job->row0; pm.nrows = job->nrows;
+    pm.tile_w = job->tile_w; pm.tile_h = job->tile_h; pm.rank = job->rank; pm.world = job->world;
+    pm.n_tile_rows = std::max(1, (job->nrows + job->tile_h - 1) / job->tile_h);
+    pm.tile_px = job->tile_w * job->tile_h;
+    const long long n_tile_cols = (job->ncols + job->tile_w - 1) / job->tile_w;
+    const long long n_tiles = (job->ncols == 0 || job->nrows == 0) ? 0 : n_tile_cols * pm.n_tile_rows;
+    n_local_tiles = n_tiles > job->rank ? (n_tiles - job->rank + job->world - 1) / job->world : 0;
+    pm.n_local_pixels = n_local_tiles * pm.tile_px;
+    return true;
+}
+}  // namespace rtb

@@ -1,0 +1,84 @@
+import json
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests", "hostsim")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+
+
+def pytest_collection_modifyitems(config, items):
+    try:
+        import torch
+        has_gpu = torch.cuda.is_available()
+    except Exception:
+        has_gpu = False
+    if has_gpu:
+        return
+    skip = pytest.mark.skip(reason="no CUDA device")
+    for item in items:
+        if "gpu" in item.keywords:
+            item.add_marker(skip)
+
+
+def _merge(data, overrides):
+    for k, v in (overrides or {}).items():
+        if isinstance(v, dict) and isinstance(data.get(k), dict):
+            data[k] = {**data[k], **v}
+        else:
+            data[k] = v
+    return data
+
+
+def manifest():
+    with open(os.path.join(GOLDEN, "MANIFEST.json")) as fh:
+        return json.load(fh)
+
+
+def load_case(case, extra_overrides=None):
+    """Scene of a golden case (tests/golden/MANIFEST.json), through the package's own parser."""
+    import python_raytracer_b200 as rt
+    rt.scene_parser.VERBOSE = False
+    e = manifest()[case]
+    with open(os.path.join(GOLDEN, "scenes", e["scene"])) as fh:
+        data = _merge(json.load(fh), e["overrides"])
+    data = _merge(data, extra_overrides)
+    sc = rt.scene_parser.load_scene_dict(data, os.path.join(GOLDEN, "scenes"))
+    sc.jitter_seed = e["seed"]
+    return sc
+
+
+def golden_png(case):
+    from PIL import Image
+    return np.array(Image.open(os.path.join(GOLDEN, "renders", case + ".png")).convert("RGB"))
+
+
+def golden_f32(case):
+    z = np.load(os.path.join(GOLDEN, "renders", case + "_f32.npz"))
+    return z["cols"], z["rows"], z["rgb"]
+
+
+def to_png_array(image):
+    return (np.rot90(np.asarray(image, dtype=np.float64), k=1, axes=(0, 1)) * 255).astype(np.uint8)
+
+
+def parity_stats(a_u8, b_u8):
+    d = np.abs(a_u8.astype(int) - b_u8.astype(int)).max(axis=2)
+    return float((d <= 1).mean()), int(d.max()), d
+
+
+# BASELINE.json north_star: per-channel |delta| <= 1/255 on >= 99.9 % of pixels
+PARITY_FRACTION = 0.999
+
+ALL_CASES = ["TwoSpheresPlane", "MirrorRefraction", "MotionBlur", "TorusMesh_flat", "TorusMesh_smooth",
+             "DepthOfField", "NovelScene1_small", "NovelScene2_small"]

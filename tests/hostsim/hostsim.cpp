@@ -1,0 +1,185 @@
+// hostsim.cpp - TEST INFRASTRUCTURE ONLY: compiles the per-ray device functions of
+// python-raytracer_b200/csrc (rt_core.cuh, rt_bvh.cuh: the RT_HD functions) with the HOST compiler so
+// their logic can be checked against the oracle in the GPU-less dev container.  Never loaded by the
+// product package; the kernels (rt_kernels.cuh) and the GPU LBVH builder kernels are not part of it.
+#include <algorithm>
+#include <cstdint>
+#include <numeric>
+#include <string>
+#include <vector>
+
+#include "../../python-raytracer_b200/csrc/rt_bvh.cuh"
+#include "../../python-raytracer_b200/csrc/rt_core.cuh"
+#include "../../python-raytracer_b200/csrc/rt_scene_build.hpp"
+
+struct HostMesh {
+    std::vector<float4> tri, vn;
+    std::vector<int4> vidx;
+    std::vector<BvhNode> nodes;
+    std::vector<int> order;
+};
+
+struct Sim {
+    HostScene hs;
+    std::vector<HostMesh> meshes;
+    std::vector<DevMesh> mesh_hdr;
+    std::vector<DevTexture> texs;
+    SceneView V;
+};
+
+static void box_of(const HostMesh& hm, const std::vector<int2>& ch, int c, std::vector<float3>& nlo, std::vector<float3>& nhi, float3& lo, float3& hi) {
+    if (c < 0) {
+        int s = ~c;
+        float3 a = f3(hm.tri[3 * s]), b = f3(hm.tri[3 * s + 1]), d = f3(hm.tri[3 * s + 2]);
+        lo = f3(fminf(a.x, fminf(b.x, d.x)), fminf(a.y, fminf(b.y, d.y)), fminf(a.z, fminf(b.z, d.z)));
+        hi = f3(fmaxf(a.x, fmaxf(b.x, d.x)), fmaxf(a.y, fmaxf(b.y, d.y)), fmaxf(a.z, fmaxf(b.z, d.z)));
+        return;
+    }
+    float3 l0, h0, l1, h1;
+    box_of(hm, ch, ch[c].x, nlo, nhi, l0, h0);
+    box_of(hm, ch, ch[c].y, nlo, nhi, l1, h1);
+    lo = f3(fminf(l0.x, l1.x), fminf(l0.y, l1.y), fminf(l0.z, l1.z));
+    hi = f3(fmaxf(h0.x, h1.x), fmaxf(h0.y, h1.y), fmaxf(h0.z, h1.z));
+    nlo[c] = lo; nhi[c] = hi;
+}
+
+static void build_mesh(const RtMesh& m, HostMesh& hm, DevMesh& g) {
+    const int n = m.n_faces;
+    float3 lo, hi; float pad;
+    rtb::mesh_bounds(m, lo, hi, pad);
+    rtb::mesh_header(m, g);
+    float3 ext = hi - lo;
+    float3 inv_ext = f3(ext.x > 0 ? 1.0f / ext.x : 0.0f, ext.y > 0 ? 1.0f / ext.y : 0.0f, ext.z > 0 ? 1.0f / ext.z : 0.0f);
+    std::vector<uint64_t> keys(n);
+    hm.order.resize(n);
+    for (int i = 0; i < n; i++) {
+        float3 a = vert_at(m.verts, m.faces[3 * i]), b = vert_at(m.verts, m.faces[3 * i + 1]), c = vert_at(m.verts, m.faces[3 * i + 2]);
+        keys[i] = morton63((a + b + c) * (1.0f / 3.0f), lo, inv_ext);
+        hm.order[i] = i;
+    }
+    std::stable_sort(hm.order.begin(), hm.order.end(), [&](int a, int b) { return keys[a] < keys[b]; });
+    std::vector<uint64_t> sk(n);
+    hm.tri.resize(3 * (size_t)n); hm.vidx.resize(n);
+    for (int s = 0; s < n; s++) {
+        int f = hm.order[s];
+        sk[s] = keys[f];
+        int i0 = m.faces[3 * f], i1 = m.faces[3 * f + 1], i2 = m.faces[3 * f + 2];
+        float3 a = vert_at(m.verts, i0), b = vert_at(m.verts, i1), c = vert_at(m.verts, i2);
+        hm.tri[3 * s] = f4(a.x, a.y, a.z, as_float(f));
+        hm.tri[3 * s + 1] = f4(b.x, b.y, b.z, 0);
+        hm.tri[3 * s + 2] = f4(c.x, c.y, c.z, 0);
+        hm.vidx[s].x = i0; hm.vidx[s].y = i1; hm.vidx[s].z = i2; hm.vidx[s].w = f;
+    }
+    if (m.vnormals && !m.flat_shaded) {
+        hm.vn.resize(m.n_verts);
+        for (int k = 0; k < m.n_verts; k++) hm.vn[k] = rtb::h4(m.vnormals + 3 * (size_t)k);
+    }
+    if (n >= 2) {
+        std::vector<int2> ch(n - 1);
+        for (int i = 0; i < n - 1; i++) lbvh_node(sk.data(), n, i, ch[i].x, ch[i].y);
+        std::vector<float3> nlo(n - 1), nhi(n - 1);
+        float3 rl, rh;
+        box_of(hm, ch, 0, nlo, nhi, rl, rh);
+        hm.nodes.resize(n - 1);
+        for (int i = 0; i < n - 1; i++) {
+            float3 l0, h0, l1, h1;
+            box_of(hm, ch, ch[i].x, nlo, nhi, l0, h0);   // (recomputes subtrees; fine at test sizes) 
+            box_of(hm, ch, ch[i].y, nlo, nhi, l1, h1);
+            BvhNode nd;
+            nd.q0 = f4(l0.x - pad, l0.y - pad, l0.z - pad, h0.x + pad);
+            nd.q1 = f4(h0.y + pad, h0.z + pad, l1.x - pad, l1.y - pad);
+            nd.q2 = f4(l1.z - pad, h1.x + pad, h1.y + pad, h1.z + pad);
+            nd.q3 = f4(as_float(ch[i].x), as_float(ch[i].y), 0, 0);
+            hm.nodes[i] = nd;
+        }
+    }
+    g.tri = hm.tri.data(); g.nodes = n >= 2 ? hm.nodes.data() : nullptr; g.face_vidx = hm.vidx.data();
+    g.vnormals = hm.vn.empty() ? nullptr : hm.vn.data();
+}
+
+static int make_sim(const RtSceneDesc* d, Sim& sim) {
+    std::string err;
+    int rc = rtb::convert_scene(d, sim.hs, err);
+    if (rc) return rc;
+    sim.meshes.resize(d->n_meshes); sim.mesh_hdr.resize(d->n_meshes);
+    for (int i = 0; i < d->n_meshes; i++) build_mesh(d->meshes[i], sim.meshes[i], sim.mesh_hdr[i]);
+    sim.texs.resize(d->n_textures);
+    for (int i = 0; i < d->n_textures; i++) { sim.texs[i].rgb = d->textures[i].rgb; sim.texs[i].width = d->textures[i].width; sim.texs[i].height = d->textures[i].height; }
+    SceneView& V = sim.V;
+    V = sim.hs.view;
+    V.objects = sim.hs.objs.data(); V.materials = sim.hs.mats.data(); V.lights = sim.hs.lights.data();
+    V.xforms = (const DevXform*)d->xforms; V.meshes = sim.mesh_hdr.data(); V.textures = sim.texs.data();
+    V.col_x = sim.hs.col_x.data(); V.row_y = sim.hs.row_y.data(); V.dof_origin = sim.hs.dof_origin.data();
+    V.ray_origin = sim.hs.ray_origin.data(); V.times = sim.hs.times.data();
+    return 0;
+}
+
+static void add_tally(RtCounters* c, const Tally& t, uint64_t primary) {
+    if (!c) return;
+    c->rays_primary += primary; c->rays_shadow += t.shadow; c->rays_reflect += t.reflect; c->rays_refract += t.refract;
+    c->bvh_nodes += t.nodes; c->tri_tests += t.tris; c->prim_tests += t.prims; c->shaded_hits += t.shaded;
+    c->mesh_hits_smooth += t.smooth; c->error_flags |= t.err;
+}
+
+template <bool HN>
+static void render_px(const Sim& sim, const SceneView& V, const int32_t* cols, const int32_t* rows, int64_t n, float* out, RtCounters* ctr) {
+#pragma omp parallel
+    {
+        Tally tally{}; uint64_t primary = 0;
+        int stack[RT_STACK_DEPTH];
+#pragma omp for schedule(dynamic, 16)
+        for (int64_t i = 0; i < n; i++) {
+            float3 colour = f3(0, 0, 0);
+            for (int d = 0; d < V.D; d++)
+                for (int s = 0; s < V.S; s++) {
+                    Ray ray = generate_ray(V, cols[i], rows[i], d, s);
+                    for (int t = 0; t < V.T; t++) {
+                        PathState ps; ps.ray = ray; ps.fold = fold_identity(); ps.depth_left = V.max_depth; ps.in_shape = 0;
+                        TraceCtx cx{V, V.times[t], tally, stack, 1};
+                        float3 sample;
+                        primary++;
+                        while (trace_level<HN>(cx, ps, sample)) {}
+                        colour = colour + sample;
+                    }
+                }
+            float nn = (float)(V.D * V.S * V.T);
+            out[3 * i] = colour.x / nn; out[3 * i + 1] = colour.y / nn; out[3 * i + 2] = colour.z / nn;
+        }
+#pragma omp critical
+        add_tally(ctr, tally, primary);
+    }
+}
+
+extern "C" int hostsim_render_pixels(const RtSceneDesc* d, const int32_t* cols, const int32_t* rows, int64_t n, float* out,
+                                     int mesh_mode, RtCounters* ctr) {
+    Sim sim;
+    int rc = make_sim(d, sim);
+    if (rc) return rc;
+    if (ctr) *ctr = RtCounters{};
+    SceneView V = sim.V; V.mesh_mode = mesh_mode;
+    if (sim.hs.has_nodes) render_px<true>(sim, V, cols, rows, n, out, ctr); else render_px<false>(sim, V, cols, rows, n, out, ctr);
+    return 0;
+}
+
+extern "C" int hostsim_bvh(const RtSceneDesc* d, int mesh, float* nodes_out, int32_t* order_out) {
+    Sim sim;
+    int rc = make_sim(d, sim);
+    if (rc) return rc;
+    const HostMesh& hm = sim.meshes[mesh];
+    if (nodes_out && !hm.nodes.empty()) memcpy(nodes_out, hm.nodes.data(), sizeof(BvhNode) * hm.nodes.size());
+    if (order_out) memcpy(order_out, hm.order.data(), sizeof(int) * hm.order.size());
+    return 0;
+}
+
+// pixel mapping of a render job: (col,row,valid) of every local pixel slot, in compact-buffer order
+extern "C" long long hostsim_job_pixels(const RtRenderJob* job, int32_t* cols, int32_t* rows, int32_t* valid) {
+    PixelMap pm; long long nt;
+    if (!rtb::make_pixel_map(job, pm, nt)) return -1;
+    if (cols)
+        for (long long lp = 0; lp < pm.n_local_pixels; lp++) {
+            int c, r;
+            valid[lp] = pixel_of(pm, lp, c, r) ? 1 : 0;
+            cols[lp] = c; rows[lp] = r;
+        }
+    return pm.n_local_pixels;
+}

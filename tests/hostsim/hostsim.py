@@ -1,0 +1,71 @@
+"""ctypes front-end of tests/hostsim (host-compiled copy of the per-ray device functions; test aid only)."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB = os.path.join(HERE, "_build", "libhostsim.so")
+CSRC = os.path.join(HERE, "..", "..", "python-raytracer_b200", "csrc")
+_lib = None
+
+
+def build(force=False):
+    deps = [os.path.join(HERE, "hostsim.cpp")] + [os.path.join(CSRC, f) for f in
+            ("rt_core.cuh", "rt_bvh.cuh", "rt_types.cuh", "rt_math.cuh", "rt_scene_build.hpp")]
+    if not force and os.path.exists(LIB) and os.path.getmtime(LIB) >= max(os.path.getmtime(d) for d in deps):
+        return LIB
+    os.makedirs(os.path.dirname(LIB), exist_ok=True)
+    subprocess.run(["g++", "-O2", "-std=c++17", "-fopenmp", "-fPIC", "-shared", "-ffp-contract=off",
+                    "-I/usr/local/cuda/include", "-o", LIB, os.path.join(HERE, "hostsim.cpp")], check=True)
+    return LIB
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        _lib = C.CDLL(LIB)
+        vp = C.c_void_p
+        _lib.hostsim_render_pixels.argtypes = [vp, vp, vp, C.c_int64, vp, C.c_int, vp]
+        _lib.hostsim_bvh.argtypes = [vp, C.c_int, vp, vp]
+    return _lib
+
+
+def render_pixels(flat, abi, cols, rows, mesh_mode=0):
+    cols = np.ascontiguousarray(cols, dtype=np.int32)
+    rows = np.ascontiguousarray(rows, dtype=np.int32)
+    out = np.empty((len(cols), 3), dtype=np.float32)
+    ctr = abi.RtCounters()
+    rc = lib().hostsim_render_pixels(C.addressof(flat.desc), cols.ctypes.data, rows.ctypes.data, len(cols),
+                                     out.ctypes.data, mesh_mode, C.addressof(ctr))
+    assert rc == 0, rc
+    return out, ctr.as_dict()
+
+
+def render(flat, abi, mesh_mode=0):
+    W, H = flat.desc.width, flat.desc.height
+    cc, rr = np.meshgrid(np.arange(W), np.arange(H), indexing="ij")
+    out, ctr = render_pixels(flat, abi, cc.reshape(-1), rr.reshape(-1), mesh_mode)
+    return out.reshape(W, H, 3), ctr
+
+
+def bvh(flat, mesh=0):
+    n = C.cast(flat.desc.meshes, C.POINTER(type("M", (C.Structure,), {"_fields_": [("n_verts", C.c_int32), ("n_faces", C.c_int32)]})))[0].n_faces
+    nodes = np.zeros((max(n - 1, 0), 16), dtype=np.float32)
+    order = np.zeros(n, dtype=np.int32)
+    rc = lib().hostsim_bvh(C.addressof(flat.desc), mesh, nodes.ctypes.data, order.ctypes.data)
+    assert rc == 0
+    return nodes, order
+
+
+def job_pixels(job):
+    L = lib()
+    L.hostsim_job_pixels.restype = C.c_longlong
+    L.hostsim_job_pixels.argtypes = [C.c_void_p] * 4
+    n = L.hostsim_job_pixels(C.addressof(job), None, None, None)
+    assert n >= 0
+    cols, rows, valid = (np.zeros(n, dtype=np.int32) for _ in range(3))
+    L.hostsim_job_pixels(C.addressof(job), cols.ctypes.data, rows.ctypes.data, valid.ctypes.data)
+    return cols, rows, valid.astype(bool)

@@ -1,0 +1,189 @@
+"""CPU tests of the host side: parser semantics, flattening, the C ABI library's exports, and the
+per-ray device functions compiled for the host (tests/hostsim) against the oracle."""
+import ctypes as C
+import json
+import os
+import re
+
+import numpy as np
+import pytest
+
+import hostsim
+import oracle
+import python_raytracer_b200 as rt
+from conftest import ALL_CASES, GOLDEN, PARITY_FRACTION, ROOT, load_case, parity_stats, to_png_array
+
+abi = rt._abi
+
+
+def _scene_dict(**over):
+    base = {"camera": {"position": [0, 1, 5], "lookAt": [0, 1, 0], "up": [0, 1, 0], "fov": 45.0},
+            "materials": [{"name": "a", "ID": 0, "diffuse": [1, 0, 0]}], "objects": [], "lights": []}
+    base.update(over)
+    return base
+
+
+def test_parser_defaults_match_reference():
+    rt.scene_parser.VERBOSE = False
+    sc = rt.scene_parser.load_scene_dict(_scene_dict())
+    assert (sc.vc.width, sc.vc.height) == (1080, 720)            # scene_parser.py:62
+    assert sc.samples == 1 and sc.jitter is False                 # :68-74
+    assert sc.vc.dof_samples == 1 and sc.vc.aperture == 0 and sc.vc.focal_length == 1   # :76-85
+    assert sc.vc.motion_times == [0.0]                            # :87-96, helperclasses.py:103-108
+    m = sc.materials[0]
+    assert m.hardness == 32 and m.tint == 0.0 and m.refr_index == 1.0 and m.mat_type == "diffuse"  # :133-138
+    assert np.array_equal(m.specular, [0, 0, 0])
+
+
+def test_parser_grouped_defaults_and_light_quirks():
+    rt.scene_parser.VERBOSE = False
+    # a missing key inside AA resets BOTH values (scene_parser.py:68-74)
+    sc = rt.scene_parser.load_scene_dict(_scene_dict(AA={"samples": 4}))
+    assert sc.samples == 1 and sc.jitter is False
+    # directional power is forced to 1.0 (:118); an unknown type is skipped (:120)
+    lights = [{"type": "directional", "name": "d", "colour": [1, 1, 1], "direction": [0, -1, 0], "power": 7.0},
+              {"type": "spot", "name": "s", "colour": [1, 1, 1]},
+              {"type": "point", "name": "p", "colour": [1, 1, 1], "position": [0, 5, 0], "power": 0.5}]
+    sc = rt.scene_parser.load_scene_dict(_scene_dict(lights=lights))
+    assert [l.type for l in sc.lights] == ["directional", "point"] and sc.lights[0].power == 1.0
+    # a KeyError in one light drops ALL lights (:123-125)
+    lights[2].pop("power")
+    sc = rt.scene_parser.load_scene_dict(_scene_dict(lights=lights))
+    assert sc.lights == []
+
+
+def test_motion_times():
+    vc = rt.helperclasses.ViewportCamera().set_motion(2.0, 16, 1)
+    assert len(vc.motion_times) == 17 and vc.motion_times[-1] == 2.0 and vc.motion_times[1] == 0.125
+
+
+def test_node_speed_pushdown_fallback_materials_and_ref_copy():
+    sc = load_case("NovelScene1_small")
+    bike = sc.objects[5]
+    assert isinstance(bike, rt.geometry.Hierarchy) and bike.name == "bike"
+    # the ROOT speed reaches every primitive leaf, nested nodes pass it on unchanged (scene_parser.py:268-283)
+    inner = bike.children[0].children[0].children[0].children[0]
+    assert isinstance(inner, rt.geometry.Sphere) and np.array_equal(inner.speed, [0, 0, 0.5])
+    # set_fallback_material APPENDS the root's materials (hierarchy.py:21-28)
+    outer = bike.children[0].children[0].children[0].children[1]
+    assert [m.name for m in outer.materials] == ["blue"]
+    assert [m.name for m in inner.materials] == ["gloss_black", "blue"]
+    bike2 = sc.objects[6]
+    assert bike2.name == "bike2" and bike2 is not bike and bike2.children[0] is not bike.children[0]
+    assert [m.name for m in bike2.children[0].children[0].children[0].children[1].materials] == ["gold"]
+    assert np.array_equal(bike2.t, [-2.0, -2.5, 2.0])
+
+
+def test_plane_axes_and_box_corners():
+    P = rt.geometry.Plane
+    assert np.array_equal(P("p", "plane", [], (0, 0, 0), (0, 1, 0), None).width_axis, [1, 0, 0])
+    assert np.array_equal(P("p", "plane", [], (0, 0, 0), (1, 0, 0), None).width_axis, [0, 0, -1])
+    assert np.array_equal(P("p", "plane", [], (0, 0, 0), (1, 0, 0), None).height_axis, [0, -1, 0])
+    b = rt.geometry.AABB("b", "box", [], (1.5, 4.0, -15.0), (6, 6, 6), None)
+    assert np.array_equal(b.minpos, [-1.5, 1.0, -18.0]) and np.array_equal(b.maxpos, [4.5, 7.0, -12.0])
+
+
+def test_trs_matrix_inverse():
+    M, Minv = rt._vecmath.trs((1, 2, 3), (15, 30, 45), (0.7, 1.0, 2.0))
+    assert M.dtype == np.float32
+    # column-major storage m[col,row]: as a maths matrix it is M.T
+    assert np.allclose(M.T @ Minv.T, np.eye(4), atol=1e-6)
+    assert np.allclose(M[3, :3], [1, 2, 3])
+
+
+def test_mesh_host_setup_matches_reference_semantics():
+    sc = load_case("TorusMesh_smooth")
+    mesh = sc.objects[1]
+    assert mesh.verts.shape == (64, 3) and mesh.faces.shape == (128, 3) and mesh.norms.shape == (64, 3)
+    assert np.allclose(np.linalg.norm(mesh.norms, axis=1), 1.0, atol=1e-6)
+    # mesh.py:45-51: torus is flat -> AABB volume < sphere volume
+    assert isinstance(mesh.bounding_volume, rt.geometry.BoundingAABB)
+
+
+def test_flatten_layout():
+    sc = load_case("NovelScene1_small")
+    fs = sc.flatten()
+    d = fs.desc
+    assert d.n_top == 9 and d.n_objects == 91 and d.n_xforms == 38 and d.n_textures == 5
+    objs = C.cast(d.objects, C.POINTER(abi.RtObject))
+    assert C.sizeof(abi.RtObject) == 128 and C.sizeof(abi.RtMaterial) == 56 and C.sizeof(abi.RtLight) == 32
+    for i in range(d.n_objects):
+        o = objs[i]
+        if o.kind == abi.KIND_NODE:
+            assert d.n_top <= o.first_child and o.first_child + o.n_children <= d.n_objects
+    assert objs[0].kind == abi.KIND_PLANE and objs[0].tex == 0 and objs[0].tex_scale == 4.0
+    # inverted box (scenes/NovelScene1.json:402-403) is kept as given
+    assert objs[7].kind == abi.KIND_BOX and objs[7].a[2] > objs[7].b[2]
+
+
+def test_header_and_ctypes_agree_on_entry_points():
+    with open(os.path.join(ROOT, "include", "b200rt.h")) as fh:
+        hdr = fh.read()
+    declared = set(re.findall(r"^(?:int|const char\*)\s+(rt_\w+)\s*\(", hdr, flags=re.M))
+    assert declared == set(abi.ENTRY_POINTS)
+
+
+def test_library_loads_and_exports_every_declared_symbol():
+    # no compute calls here (no GPU in this container): dlopen + symbol presence + ABI version
+    assert os.path.exists(abi.LIB_PATH), "build with `python __graft_entry__.py`"
+    lib = abi.load_library()
+    for name in abi.ENTRY_POINTS:
+        assert hasattr(lib, name), name
+    assert lib.rt_abi_version() == abi.RT_ABI_VERSION
+
+
+def test_missing_library_fails_loudly(tmp_path):
+    with pytest.raises(abi.B200RTError):
+        abi.load_library(str(tmp_path / "nope.so"))
+
+
+@pytest.mark.parametrize("case", ALL_CASES)
+def test_device_functions_on_host_match_oracle(case):
+    """The RT_HD per-ray functions the kernels call (fp32, LBVH traversal, folded per-level clamp,
+    iterative CSG walk), compiled for the host, against the oracle: the parity statistic of the gpu tests."""
+    sc = load_case(case)
+    fs = sc.flatten()
+    ref, c_ref = oracle.render(fs, abi)
+    img, c_sim = hostsim.render(fs, abi)
+    frac, dmax, _ = parity_stats(to_png_array(ref), to_png_array(img))
+    assert frac >= 0.9995, (frac, dmax)
+    for k in ("rays_primary",):
+        assert c_ref[k] == c_sim[k]
+    for k in ("rays_shadow", "rays_reflect", "rays_refract", "shaded_hits"):
+        assert abs(c_ref[k] - c_sim[k]) <= max(4, 2e-4 * c_ref[k]), (k, c_ref[k], c_sim[k])
+    assert c_sim["error_flags"] == 0
+
+
+def test_bvh_traversal_equals_brute_force_on_host():
+    sc = load_case("TorusMesh_smooth")
+    fs = sc.flatten()
+    a, ca = hostsim.render(fs, abi, mesh_mode=0)
+    b, cb = hostsim.render(fs, abi, mesh_mode=1)
+    assert np.array_equal(a, b)
+    assert ca["tri_tests"] < cb["tri_tests"] / 10
+
+
+def test_lbvh_structure_is_a_valid_tree():
+    sc = load_case("TorusMesh_flat")
+    nodes, order = hostsim.bvh(sc.flatten())
+    n = len(order)
+    assert sorted(order.tolist()) == list(range(n))
+    ch = nodes[:, 12:14].copy().view(np.int32)
+    seen_leaf, seen_node = np.zeros(n, int), np.zeros(n - 1, int)
+    for c in ch.reshape(-1):
+        if c < 0:
+            seen_leaf[~c] += 1
+        else:
+            seen_node[c] += 1
+    assert (seen_leaf == 1).all() and seen_node[0] == 0 and (seen_node[1:] == 1).all()
+
+
+def test_tile_interleave_partitions_the_region():
+    for (ncols, nrows, tw, th, world) in [(640, 480, 8, 8, 1), (37, 23, 8, 8, 3), (5, 3, 8, 8, 2), (64, 64, 16, 4, 8)]:
+        seen = np.zeros((ncols, nrows), int)
+        for rank in range(world):
+            job = abi.RtRenderJob(col0=3, ncols=ncols, row0=2, nrows=nrows, tile_w=tw, tile_h=th, rank=rank, world=world)
+            cols, rows, valid = hostsim.job_pixels(job)
+            assert len(cols) % (tw * th) == 0
+            np.add.at(seen, (cols[valid] - 3, rows[valid] - 2), 1)
+        assert (seen == 1).all()

@@ -1,0 +1,46 @@
+"""Pins the tier-1 oracle (oracle/rt_oracle.c) to the reference: it must reproduce the committed
+renders of the UNMODIFIED reference (tests/golden, made by oracle/make_golden.py; five of them are
+bit-identical to the author's own stored PNGs, see MANIFEST.json) EXACTLY - uint8 image and the
+float32 sub-sample - on every bundled scene."""
+import numpy as np
+import pytest
+
+import oracle
+import python_raytracer_b200 as rt
+from conftest import ALL_CASES, golden_f32, golden_png, load_case, manifest, to_png_array
+
+
+def test_manifest_records_author_render_equality():
+    m = manifest()
+    for case in ("TwoSpheresPlane", "MirrorRefraction", "MotionBlur", "TorusMesh_flat", "TorusMesh_smooth"):
+        assert m[case]["author_render_max_abs_diff_u8"] == 0
+
+
+@pytest.mark.parametrize("case", ALL_CASES)
+def test_oracle_reproduces_reference_exactly(case):
+    sc = load_case(case)
+    img, ctr = oracle.render(sc.flatten(), rt._abi)
+    assert ctr["error_flags"] == 0
+    assert np.array_equal(to_png_array(img), golden_png(case))
+    cols, rows, rgb = golden_f32(case)
+    assert np.array_equal(img[np.ix_(cols, rows)].astype(np.float32), rgb)
+    assert np.array_equal(img[np.ix_(cols, rows)], rgb.astype(np.float64))   # values are float32-exact (scene.py:73)
+
+
+def test_oracle_strip_equals_full_frame_columns():
+    # Scene.render(subimage, tasks) (scene.py:36-37): a strip is the same pixels as the full frame
+    sc = load_case("TwoSpheresPlane")
+    fs = sc.flatten()
+    full, _ = oracle.render(fs, rt._abi, 0, 64, 0, 480)
+    strip, _ = oracle.render(fs, rt._abi, 32, 32, 0, 480)
+    # x is re-accumulated from the strip's first column (scene.py:42): equal after the float32 cast
+    assert np.array_equal(full[32:64], strip)
+
+
+def test_oracle_pixel_list_matches_rectangle():
+    sc = load_case("DepthOfField")
+    fs = sc.flatten()
+    rect, _ = oracle.render(fs, rt._abi, 100, 8, 50, 8)
+    cc, rr = np.meshgrid(np.arange(100, 108), np.arange(50, 58), indexing="ij")
+    px, _ = oracle.render_pixels(fs, rt._abi, cc.reshape(-1), rr.reshape(-1))
+    assert np.allclose(px.reshape(8, 8, 3), rect, atol=0, rtol=0) or np.abs(px.reshape(8, 8, 3) - rect).max() < 1e-6
