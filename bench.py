@@ -267,7 +267,7 @@ def run_ours(a):
         n_launch = max(1, int(prof.n_primary))
         launches_per_frame = max(1, n_launch // max(1, a.steps))
         primary_rays_rank = W * H * a.spp / world
-        alg_bytes_frame = 64 * pc.bvh_nodes + 48 * pc.tri_tests + 48 * pc.mesh_hits_smooth + 80 * pc.queued_rays + 16 * primary_rays_rank
+        alg_bytes_frame = 64 * pc.bvh_nodes + 48 * pc.tri_tests + 64 * pc.mesh_hits_smooth + 80 * pc.queued_rays + 16 * primary_rays_rank
         ms_primary = prof.ms_primary / n_launch
         achieved = alg_bytes_frame / launches_per_frame / (ms_primary * 1e-3) / 1e9 if ms_primary > 0 else None
         kernel_share = prof.ms_primary / max(1e-9, prof.ms_primary + prof.ms_secondary + prof.ms_resolve)

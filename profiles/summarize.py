@@ -1,0 +1,63 @@
+"""Turn gpurun_out/ ncu artefacts into the small text summaries committed under profiles/.
+usage: python profiles/summarize.py <tag> [launches.csv] [report.ncu-rep]"""
+import csv
+import subprocess
+import sys
+from collections import defaultdict
+
+KEYS = ["gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "launch__registers_per_thread",
+        "launch__occupancy_limit_registers", "launch__occupancy_limit_shared_mem", "sm__warps_active.avg.pct_of_peak_sustained_active",
+        "dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+        "lts__t_sector_hit_rate.pct", "l1tex__t_sector_hit_rate.pct", "lts__t_bytes.sum", "l1tex__t_bytes.sum",
+        "sm__throughput.avg.pct_of_peak_sustained_elapsed", "smsp__issue_active.avg.pct_of_peak_sustained_active",
+        "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
+        "smsp__thread_inst_executed_per_inst_executed.ratio", "smsp__sass_inst_executed_op_local_ld.sum",
+        "smsp__sass_inst_executed_op_local_st.sum",
+        "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_branch_resolving_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_no_instruction_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio"]
+
+
+def launches(path, out):
+    rows = [r for r in csv.reader(open(path)) if len(r) > 10]
+    h = rows[0]
+    ki, vi, mi = h.index("Kernel Name"), h.index("Metric Value"), h.index("Metric Name")
+    data = [(r[ki].split("(")[0], float(r[vi].replace(",", ""))) for r in rows[1:] if r[mi] == "gpu__time_duration.sum"]
+    agg, cnt = defaultdict(float), defaultdict(int)
+    for k, v in data:
+        agg[k] += v; cnt[k] += 1
+    tot = sum(agg.values())
+    out.write(f"# ncu --metrics gpu__time_duration.sum --clock-control none: {len(data)} launches, cold-cache serialised (compare SHARES)\n")
+    out.write(f"{'kernel':48s} {'launches':>8s} {'total_ms':>10s} {'share':>7s} {'mean_us':>10s}\n")
+    for k, v in sorted(agg.items(), key=lambda x: -x[1]):
+        out.write(f"{k[:48]:48s} {cnt[k]:8d} {v/1e6:10.3f} {100*v/tot:6.1f}% {v/cnt[k]/1e3:10.1f}\n")
+    out.write("\n# last launches in order (us)\n")
+    for k, v in data[-26:]:
+        out.write(f"{k[:48]:48s} {v/1e3:10.1f}\n")
+
+
+def report(path, out):
+    raw = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(raw.splitlines()))
+    h, u = rows[0], rows[1]
+    for r in rows[2:]:
+        out.write(f"\n# ncu --set full: {r[h.index('Kernel Name')][:80]}  (ID {r[0]})\n")
+        for k in KEYS:
+            if k in h:
+                i = h.index(k)
+                out.write(f"{k:90s} {r[i]:>16s} {u[i]}\n")
+
+
+if __name__ == "__main__":
+    tag = sys.argv[1]
+    with open(f"profiles/{tag}.txt", "w") as out:
+        for p in sys.argv[2:]:
+            if p.endswith(".csv"):
+                launches(p, out)
+            else:
+                report(p, out)
+    print(open(f"profiles/{tag}.txt").read())
