@@ -16,7 +16,9 @@ from . import _abi
 class TileSharder:
     def __init__(self, scene, rank, world, device=None, group=None):
         self.scene, self.rank, self.world, self.group = scene, rank, world, group
-        self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+        if device is None:
+            device = torch.device("cuda", torch.cuda.current_device())
+        self.device = torch.device(device)
         self.lib = _abi.load_library()
         W, H = scene.vc.width, scene.vc.height
         self.W, self.H = W, H
@@ -32,12 +34,32 @@ class TileSharder:
         self.local = torch.zeros(n_local, dtype=torch.float32, device=self.device)
         self.image = None
         self.gathered = None
+        self.offsets = (C.c_int64 * world)(*[r * self.pad for r in range(world)])
         if rank == 0 and world > 1:
             self.gathered = torch.empty(world * self.pad, dtype=torch.float32, device=self.device)
-            self.image = torch.empty(W * H * 3, dtype=torch.float32, device=self.device)
-            self.offsets = (C.c_int64 * world)(*[r * self.pad for r in range(world)])
+            if self.device.type == "cuda":
+                self.image = torch.empty(W * H * 3, dtype=torch.float32, device=self.device)
         elif world == 1:
             self.image = self.local
+
+    def gather(self):
+        """Fan-in of the compact tile buffers to rank 0 (glue.py:19: the N.npy files).  Device-agnostic
+        (NCCL for CUDA tensors, gloo for CPU tensors in the tests)."""
+        if self.world == 1:
+            return self.local
+        if self.rank == 0:
+            chunks = list(self.gathered.view(self.world, self.pad).unbind(0))
+            dist.gather(self.local, chunks, dst=0, group=self.group)
+            return self.gathered
+        dist.gather(self.local, None, dst=0, group=self.group)
+        return None
+
+    def assemble(self, stream=None):
+        """rank 0: scatter the gathered tiles into the reference layout (glue.py:22)."""
+        asm = self.scene.make_job(0, self.W, 0, self.H, rank=0, world=self.world, direct=False)
+        _abi.check(self.lib, self.lib.rt_assemble_tiles(C.byref(asm), self.gathered.data_ptr(), self.offsets,
+                                                         self.image.data_ptr(), stream), "rt_assemble_tiles")
+        return self.image
 
     def render(self, counters=None):
         """One frame.  Returns the (W*H*3,) device image on rank 0 (reference layout), None elsewhere."""
@@ -45,12 +67,5 @@ class TileSharder:
         self.scene.render_device(self.local.data_ptr(), self.job, counters=counters, stream=stream)
         if self.world == 1:
             return self.image
-        if self.rank == 0:
-            chunks = list(self.gathered.view(self.world, self.pad).unbind(0))
-            dist.gather(self.local, chunks, dst=0, group=self.group)
-            asm = self.scene.make_job(0, self.W, 0, self.H, rank=0, world=self.world, direct=False)
-            _abi.check(self.lib, self.lib.rt_assemble_tiles(C.byref(asm), self.gathered.data_ptr(), self.offsets,
-                                                             self.image.data_ptr(), stream), "rt_assemble_tiles")
-            return self.image
-        dist.gather(self.local, None, dst=0, group=self.group)
-        return None
+        self.gather()
+        return self.assemble(stream) if self.rank == 0 else None

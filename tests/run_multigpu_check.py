@@ -1,0 +1,36 @@
+"""torchrun --nproc-per-node N tests/run_multigpu_check.py : N-rank tile-sharded render gathered over NCCL
+must equal the single-rank render bit for bit.  Prints one JSON line on rank 0."""
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+from conftest import load_case  # noqa: E402
+from python_raytracer_b200.distributed import TileSharder  # noqa: E402
+from python_raytracer_b200 import synthetic  # noqa: E402
+
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+res = {}
+scenes = {"MirrorRefraction": load_case("MirrorRefraction"),
+          "synthetic_640x360x4": synthetic.make_scene(width=640, height=360, aa_samples=4, grid=(256, 128))}
+for name, sc in scenes.items():
+    sh = TileSharder(sc, rank, world)
+    img = sh.render()
+    torch.cuda.synchronize()
+    if rank == 0:
+        got = img.cpu().numpy().reshape(sc.vc.width, sc.vc.height, 3)
+        ref = sc.render_region(0, sc.vc.width, 0, sc.vc.height)
+        res[name] = {"bit_identical": bool(np.array_equal(got, ref)), "max_abs_diff": float(np.abs(got - ref).max())}
+    dist.barrier()
+if rank == 0:
+    print(json.dumps({"world": world, "results": res}))
+    assert all(v["bit_identical"] for v in res.values())
+dist.destroy_process_group()
