@@ -168,7 +168,8 @@ typedef struct RtRenderJob {
     int32_t tile_w, tile_h;
     int32_t rank, world;
     int32_t direct;
-    int32_t mesh_mode;       /* 0 = LBVH traversal, 1 = brute force over all faces (test aid, mesh.py:77) */
+    int32_t mesh_mode;       /* test aids, bit field: 0 = accelerated; bit 0 = brute force over all faces (mesh.py:77);
+                              * bit 1 = plain in-order loop over the top-level objects (scene.py:87,160) instead of the object BVH */
     int64_t max_batch_rays;  /* 0 = default */
 } RtRenderJob;
 

@@ -45,7 +45,7 @@ struct RtScene {
     std::vector<MeshBuild> meshes;
     std::vector<DevMesh> h_meshes;
     DevMesh* d_meshes = nullptr;
-    bool has_nodes = false, has_specular = false, has_mesh = false;
+    bool has_nodes = false, has_specular = false, has_mesh = false, has_tlas = false;
     int samples_per_pixel = 1;
     // work buffers of rt_render, grown on demand
     float4* d_samples = nullptr; long long samples_cap = 0;
@@ -106,6 +106,13 @@ static int scene_create_impl(const RtSceneDesc* d, RtScene* sc) {
     static_assert(sizeof(DevXform) == sizeof(RtXform), "xform layout");
     DevXform* d_xf; UP(upload(sc, (const DevXform*)d->xforms, (size_t)d->n_xforms, &d_xf));
     V.objects = d_objs; V.materials = d_mats; V.lights = d_lights; V.xforms = d_xf;
+    // ---- object BVH over the bounded top-level objects (host-built in convert_scene)
+    sc->has_tlas = !hs.tlas_nodes.empty();
+    if (sc->has_tlas) {
+        BvhNode* d_tn; UP(upload(sc, hs.tlas_nodes.data(), hs.tlas_nodes.size(), &d_tn));
+        int* d_lin; UP(upload(sc, hs.lin_objs.data(), hs.lin_objs.size(), &d_lin));
+        V.tlas_nodes = d_tn; V.lin_objs = d_lin; V.n_lin = (int)hs.lin_objs.size();
+    }
     // ---- textures
     std::vector<DevTexture> texs(d->n_textures);
     for (int i = 0; i < d->n_textures; i++) {
@@ -290,9 +297,15 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
     SceneView V = sc->view;
     V.mesh_mode = job->mesh_mode;
     const int N = sc->samples_per_pixel;
-    long long max_rays = job->max_batch_rays > 0 ? job->max_batch_rays : (16ll << 20);
+    // batch = as many whole pixels as fit in max_batch_rays (default 128 Mi rays: 2 GiB of samples + 2 x 10 GiB of
+    // queue planes out of 180 GB), evened out over the batches so the last one is not a sliver
+    long long max_rays = job->max_batch_rays > 0 ? job->max_batch_rays : (128ll << 20);
     max_rays = std::min(max_rays, 1ll << 30);
-    const long long px_per_batch = std::max(1ll, max_rays / N);
+    long long px_per_batch = std::max(1ll, max_rays / N);
+    if (pm.n_local_pixels > px_per_batch) {
+        const long long n_batches = (pm.n_local_pixels + px_per_batch - 1) / px_per_batch;
+        px_per_batch = std::min(px_per_batch, (pm.n_local_pixels + n_batches - 1) / n_batches);
+    }
     const long long batch_cap = std::min(px_per_batch, std::max(1ll, pm.n_local_pixels)) * N;
     UP(grow(&sc->d_samples, &sc->samples_cap, batch_cap));
     const bool secondary = sc->has_specular && V.max_depth > 1;
@@ -304,7 +317,7 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
         }
         sc->queue_cap = batch_cap;
     }
-    const size_t smem = sc->has_mesh ? sizeof(int) * RT_STACK_DEPTH * RT_BLOCK : 0;
+    const size_t smem = (sc->has_mesh || sc->has_tlas) ? sizeof(int) * RT_STACK_DEPTH * RT_BLOCK : 0;
     if (smem) {
         CU(cudaFuncSetAttribute(k_primary<HAS_NODES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         CU(cudaFuncSetAttribute(k_secondary<HAS_NODES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -429,7 +442,7 @@ extern "C" int rt_trace_rays(RtScene* sc, int64_t n, const float* h_org, const f
     UP(tmp.get(&rgb, 3 * n)); UP(tmp.get(&t, n)); UP(tmp.get(&nn, 3 * n)); UP(tmp.get(&pp, 3 * n));
     UP(tmp.get(&geom, n)); UP(tmp.get(&mat, n));
     SceneView V = sc->view; V.mesh_mode = mesh_mode;
-    const size_t smem = sc->has_mesh ? sizeof(int) * RT_STACK_DEPTH * RT_BLOCK : 0;
+    const size_t smem = (sc->has_mesh || sc->has_tlas) ? sizeof(int) * RT_STACK_DEPTH * RT_BLOCK : 0;
     const int grid = (int)((n + RT_BLOCK - 1) / RT_BLOCK);
     CU(cudaMemsetAsync(sc->d_counters, 0, sizeof(RtCounters), st));
     if (sc->has_nodes) {
@@ -462,7 +475,7 @@ extern "C" int rt_occluded(RtScene* sc, int64_t n, const float* h_org, const flo
     UP(tmp.get(&org, 3 * n, h_org)); UP(tmp.get(&dir, 3 * n, h_dir)); UP(tmp.get(&times, n, h_times)); UP(tmp.get(&tmax, n, h_tmax));
     UP(tmp.get(&occ, n));
     SceneView V = sc->view; V.mesh_mode = mesh_mode;
-    const size_t smem = sc->has_mesh ? sizeof(int) * RT_STACK_DEPTH * RT_BLOCK : 0;
+    const size_t smem = (sc->has_mesh || sc->has_tlas) ? sizeof(int) * RT_STACK_DEPTH * RT_BLOCK : 0;
     const int grid = (int)((n + RT_BLOCK - 1) / RT_BLOCK);
     if (sc->has_nodes) {
         if (smem) CU(cudaFuncSetAttribute(k_occluded<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

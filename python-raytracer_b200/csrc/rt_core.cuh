@@ -24,6 +24,7 @@ struct TraceCtx {
     Tally& tally;
     int* stack;          // BVH traversal stack of this thread: entry k at stack[k * stack_stride]
     int stack_stride;
+    int sbase = 0;       // entries below sbase belong to the object-BVH walk in progress (top_next)
 };
 
 // `center + speed * current_time` (simple_geometry.py:21-24,106-109,189-194)
@@ -160,14 +161,15 @@ template <class OnTri>
 RT_HD void mesh_visit(TraceCtx& cx, const DevMesh* m, const Ray& r, float tmin, float& tmax, OnTri&& onTri) {
     const int n = m->n_tris;
     if (n <= 0) return;
-    if (cx.S.mesh_mode == 1 || n == 1) {
+    if ((cx.S.mesh_mode & RT_MODE_BRUTE_MESH) || n == 1) {
         for (int s = 0; s < n; s++) { cx.tally.tris++; if (onTri(s, tmax)) return; }
         return;
     }
     const BvhNode* nodes = m->nodes;
     float3 inv = f3(1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z);
     int* stk = cx.stack; const int stride = cx.stack_stride;
-    int sp = 0, node = 0;
+    const int sbase = cx.sbase;
+    int sp = sbase, node = 0;
     for (;;) {
         BvhNode nd;
         nd.q0 = ld4(&nodes[node].q0); nd.q1 = ld4(&nodes[node].q1);
@@ -189,9 +191,67 @@ RT_HD void mesh_visit(TraceCtx& cx, const DevMesh* m, const Ray& r, float tmin, 
         } else if (h0) node = c0;
         else if (h1) node = c1;
         else {
-            if (sp == 0) return;
+            if (sp == sbase) return;
             node = stk[(--sp) * stride];
         }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Which top-level objects a ray has to be tested against, one at a time: replaces the plain
+// `for obj in self.objects` of scene.py:87 and :160-164.  Objects without finite bounds come first (scene
+// order), then the leaves of the object BVH whose (padded, motion-swept) boxes the ray segment [0, tmax]
+// touches, nearer child first.  The order differs from the reference's list order, so the closest-hit
+// consumer breaks equal-t ties by object index itself; the any-hit consumer is order-free.
+#define RT_TOP_NONE 0x7fffffff
+struct TopIter { int lin_i; int cur; int sp; };
+RT_HD TopIter top_begin() { TopIter it; it.lin_i = 0; it.cur = 0; it.sp = 0; return it; }
+
+// IGNORE_TMAX_FLAGGED: shadow rays -- subtrees holding a mesh / CSG node are walked without the t_max bound
+// because their shadow tests ignore it
+template <bool SHADOW>
+RT_HD int top_next(TraceCtx& cx, TopIter& it, const Ray& r, float3 inv, float tmax) {
+    const SceneView& S = cx.S;
+    if (S.tlas_nodes == nullptr || (S.mesh_mode & RT_MODE_LINEAR_TOP)) return it.lin_i < S.n_top ? it.lin_i++ : -1;
+    if (it.lin_i < S.n_lin) return RT_LDG(S.lin_objs + it.lin_i++);
+    int* stk = cx.stack; const int stride = cx.stack_stride;
+    int cur = it.cur;
+    for (;;) {
+        if (cur == RT_TOP_NONE) {
+            if (it.sp == 0) { it.cur = RT_TOP_NONE; return -1; }
+            cur = stk[(--it.sp) * stride];
+        }
+        if (cur < 0) { it.cur = RT_TOP_NONE; return ~cur; }
+        const BvhNode* np = S.tlas_nodes + cur;
+        BvhNode nd;
+        nd.q0 = ld4(&np->q0); nd.q1 = ld4(&np->q1); nd.q2 = ld4(&np->q2); nd.q3 = ld4(&np->q3);
+        cx.tally.nodes++;
+        float t0 = tmax, t1 = tmax;
+        if (SHADOW) {
+            if (as_int(nd.q3.z) & RT_TLAS_NO_TMAX) t0 = RT_INF;
+            if (as_int(nd.q3.w) & RT_TLAS_NO_TMAX) t1 = RT_INF;
+        }
+        float ax = (nd.q0.x - r.o.x) * inv.x, bx = (nd.q0.w - r.o.x) * inv.x;
+        float ay = (nd.q0.y - r.o.y) * inv.y, by = (nd.q1.x - r.o.y) * inv.y;
+        float az = (nd.q0.z - r.o.z) * inv.z, bz = (nd.q1.y - r.o.z) * inv.z;
+        const float n0 = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
+        const float f0 = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t0));
+        ax = (nd.q1.z - r.o.x) * inv.x; bx = (nd.q2.y - r.o.x) * inv.x;
+        ay = (nd.q1.w - r.o.y) * inv.y; by = (nd.q2.z - r.o.y) * inv.y;
+        az = (nd.q2.x - r.o.z) * inv.z; bz = (nd.q2.w - r.o.z) * inv.z;
+        const float n1 = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
+        const float f1 = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t1));
+        const bool h0 = n0 <= f0, h1 = n1 <= f1;
+        const int c0 = as_int(nd.q3.x), c1 = as_int(nd.q3.y);
+        if (h0 && h1) {
+            int nearc = c0, farc = c1;
+            if (n1 < n0) { nearc = c1; farc = c0; }
+            if (it.sp < RT_STACK_DEPTH) stk[(it.sp++) * stride] = farc;
+            else cx.tally.err |= 1u << RT_ERR_LIMIT;
+            cur = nearc;
+        } else if (h0) cur = c0;
+        else if (h1) cur = c1;
+        else cur = RT_TOP_NONE;
     }
 }
 
@@ -545,41 +605,48 @@ template <bool HAS_NODES>
 RT_HD bool closest_hit(TraceCtx& cx, const Ray& r, Hit& out) {
     const SceneView& S = cx.S;
     float best = RT_INF;
-    int best_obj = -1, best_aux = 0;
+    int best_obj = 0x7fffffff, best_aux = 0;
     Hit node_hit; node_hit.t = RT_INF; node_hit.mat = -1; node_hit.geom = -1; node_hit.n = f3(0, 0, 0); node_hit.p = f3(0, 0, 0);
     const float A = dot(r.d, r.d);
-    for (int oi = 0; oi < S.n_top; oi++) {
+    const float3 inv = f3(1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z);
+    TopIter it = top_begin();
+    for (;;) {
+        const int oi = top_next<false>(cx, it, r, inv, best);
+        if (oi < 0) break;
+        cx.sbase = it.sp;
         const DevObject* o = S.objects + oi;
         const int kind = o->kind;
+        // a candidate at time t replaces the current best iff it is earlier, or equally early and earlier in scene.objects
+        #define RT_BETTER(t) ((t) < best || ((t) == best && oi < best_obj))
         if (kind == RT_KIND_SPHERE) {
             cx.tally.prims++;
             float4 a = ld4(&o->a);
             float t1, t2;
             if (sphere_roots(moved(o, f3(a), cx.time), a.w, r, A, t1, t2)) {
                 float t = t1 > 0.0f ? t1 : t2;                       // t1 <= t2: first positive root is the list minimum
-                if (t > 0.0f && t < best) { best = t; best_obj = oi; }
+                if (t > 0.0f && RT_BETTER(t)) { best = t; best_obj = oi; }
             }
         } else if (kind == RT_KIND_PLANE) {
             cx.tally.prims++;
             float t;
-            if (plane_t(moved(o, f3(ld4(&o->a)), cx.time), f3(ld4(&o->b)), r, t) && t >= 0.0f && t < best) { best = t; best_obj = oi; }
+            if (plane_t(moved(o, f3(ld4(&o->a)), cx.time), f3(ld4(&o->b)), r, t) && t >= 0.0f && RT_BETTER(t)) { best = t; best_obj = oi; }
         } else if (kind == RT_KIND_BOX) {
             cx.tally.prims++;
             float en, ex; int label;
             if (box_slabs(moved(o, f3(ld4(&o->a)), cx.time), moved(o, f3(ld4(&o->b)), cx.time), r, en, ex, label) &&
-                !(en > ex || en < 0.0f) && en < best) { best = en; best_obj = oi; best_aux = label; }
+                !(en > ex || en < 0.0f) && RT_BETTER(en)) { best = en; best_obj = oi; best_aux = label; }
         } else if (kind == RT_KIND_MESH) {
             cx.tally.prims++;
             const DevMesh* m = S.meshes + o->mesh;
             if (mesh_gate(m, r)) {
-                // strict '<' against earlier objects; among this mesh's own faces an equal t goes to the lower face index (list order)
+                // against other objects: RT_BETTER; among this mesh's own faces an equal t goes to the lower face index (list order)
                 float tmax = best;
                 int best_face = 0x7fffffff, best_slot = -1;
                 mesh_visit(cx, m, r, 0.0f, tmax, [&](int slot, float& tm) {
                     float3 v0, v1, v2; int face; float t;
                     tri_load(m, slot, v0, v1, v2, face);
                     if (tri_hit(v0, v1, v2, r, t)) {
-                        if ((best_slot < 0 && t < best) || (best_slot >= 0 && (t < tm || (t == tm && face < best_face)))) {
+                        if ((best_slot < 0 && RT_BETTER(t)) || (best_slot >= 0 && (t < tm || (t == tm && face < best_face)))) {
                             tm = t; best_face = face; best_slot = slot;
                         }
                     }
@@ -588,11 +655,14 @@ RT_HD bool closest_hit(TraceCtx& cx, const Ray& r, Hit& out) {
                 if (best_slot >= 0) { best = tmax; best_obj = oi; best_aux = best_slot; }
             }
         } else if (HAS_NODES && kind == RT_KIND_NODE) {
-            object_hits(cx, oi, r, [&](float t) { return t < best; },
-                        [&](const Hit& h) { if (h.t < best) { best = h.t; best_obj = oi; node_hit = h; } });
+            // inside one node the first hit in DFS (= list) order wins equal t: strict '<' once this node holds the best
+            object_hits(cx, oi, r, [&](float t) { return RT_BETTER(t); },
+                        [&](const Hit& h) { if (RT_BETTER(h.t)) { best = h.t; best_obj = oi; node_hit = h; } });
         }
+        #undef RT_BETTER
     }
-    if (best_obj < 0) return false;
+    cx.sbase = 0;
+    if (best_obj == 0x7fffffff) return false;
     const DevObject* o = S.objects + best_obj;
     if (HAS_NODES && o->kind == RT_KIND_NODE) { out = node_hit; return true; }
     out.t = best; out.geom = best_obj;
@@ -612,7 +682,13 @@ template <bool HAS_NODES>
 RT_HD bool occluded(TraceCtx& cx, const Ray& r, float tmax) {
     const SceneView& S = cx.S;
     const float A = dot(r.d, r.d);
-    for (int oi = 0; oi < S.n_top; oi++) {
+    const float3 inv = f3(1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z);
+    TopIter it = top_begin();
+    bool occ = false;
+    for (;;) {
+        const int oi = top_next<true>(cx, it, r, inv, tmax);
+        if (oi < 0) break;
+        cx.sbase = it.sp;
         const DevObject* o = S.objects + oi;
         const int kind = o->kind;
         if (kind == RT_KIND_SPHERE) {
@@ -620,14 +696,15 @@ RT_HD bool occluded(TraceCtx& cx, const Ray& r, float tmax) {
             float4 a = ld4(&o->a);
             float t1, t2;
             if (sphere_roots(moved(o, f3(a), cx.time), a.w, r, A, t1, t2) &&
-                ((RT_SHADOW_EPS_SPHERE < t1 && t1 < tmax) || (RT_SHADOW_EPS_SPHERE < t2 && t2 < tmax))) return true;
+                ((RT_SHADOW_EPS_SPHERE < t1 && t1 < tmax) || (RT_SHADOW_EPS_SPHERE < t2 && t2 < tmax))) { occ = true; break; }
         } else if (kind != RT_KIND_NODE) {
-            if (leaf_shadow(cx, oi, r, tmax)) return true;
+            if (leaf_shadow(cx, oi, r, tmax)) { occ = true; break; }
         } else if (HAS_NODES) {
-            if (Nest<RT_MAX_NEST>::shadow(cx, oi, r, tmax)) return true;
+            if (Nest<RT_MAX_NEST>::shadow(cx, oi, r, tmax)) { occ = true; break; }
         }
     }
-    return false;
+    cx.sbase = 0;
+    return occ;
 }
 
 // ------------------------------------------------------------------------------------------------

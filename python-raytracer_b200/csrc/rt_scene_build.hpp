@@ -16,6 +16,8 @@ struct HostScene {
     std::vector<DevLight> lights;
     std::vector<float> col_x, row_y, times;
     std::vector<float4> dof_origin, ray_origin;
+    std::vector<BvhNode> tlas_nodes;   // object BVH over the bounded top-level objects (empty: none)
+    std::vector<int> lin_objs;         // top-level objects tested one by one (no finite bounds)
     bool has_nodes = false, has_specular = false, has_mesh = false;
     SceneView view{};          // scalars filled; pointers are the caller's business
 };
@@ -41,6 +43,129 @@ inline int nest_depth(const RtSceneDesc* d, int oi, int depth) {
     int m = depth + 1;
     for (int k = 0; k < o.n_children; k++) m = std::max(m, nest_depth(d, o.first_child + k, depth + 1));
     return m;
+}
+
+inline void mesh_bounds(const RtMesh& m, float3& lo, float3& hi, float& pad);
+
+// ---- object BVH (host-built: a scene has tens..thousands of objects; the per-mesh LBVH is the GPU-built one) ----
+// Conservative world-space bounds of everything an object can return from intersect()/shadow_intersect()
+// over the frame's motion-time range: every accepted hit point lies ON a primitive's surface.
+struct ObjBound { float3 lo, hi; bool finite; };
+inline float3 min3(float3 a, float3 b) { return f3(fminf(a.x, b.x), fminf(a.y, b.y), fminf(a.z, b.z)); }
+inline float3 max3(float3 a, float3 b) { return f3(fmaxf(a.x, b.x), fmaxf(a.y, b.y), fmaxf(a.z, b.z)); }
+inline bool finite3(float3 a) { return std::isfinite(a.x) && std::isfinite(a.y) && std::isfinite(a.z); }
+
+inline ObjBound object_bound(const RtSceneDesc* d, int oi, float tlo, float thi) {
+    const RtObject& o = d->objects[oi];
+    ObjBound b; b.finite = false; b.lo = f3(INFINITY, INFINITY, INFINITY); b.hi = f3(-INFINITY, -INFINITY, -INFINITY);
+    const float3 sp = h3(o.speed);
+    const float ts[2] = {tlo, thi};
+    switch (o.kind) {
+        case RT_KIND_SPHERE:                                   // centre moves linearly (simple_geometry.py:21-24)
+            for (int k = 0; k < 2; k++) {
+                float3 c = h3(o.a) + sp * ts[k]; float r = fabsf(o.radius);
+                b.lo = min3(b.lo, c - f3(r, r, r)); b.hi = max3(b.hi, c + f3(r, r, r));
+            }
+            b.finite = true; break;
+        case RT_KIND_BOX:                                      // corners sorted like AAInterval (helperclasses.py:64-65)
+            for (int k = 0; k < 2; k++) {
+                float3 p = h3(o.a) + sp * ts[k], q = h3(o.b) + sp * ts[k];
+                b.lo = min3(b.lo, min3(p, q)); b.hi = max3(b.hi, max3(p, q));
+            }
+            b.finite = true; break;
+        case RT_KIND_MESH: {                                   // meshes do not move
+            const RtMesh& m = d->meshes[o.mesh];
+            if (m.n_faces <= 0 || m.n_verts <= 0) break;
+            float pad; mesh_bounds(m, b.lo, b.hi, pad);
+            b.finite = true; break;
+        }
+        case RT_KIND_NODE: {                                   // hierarchy.py:42-78: hits of the children, mapped by M
+            const int c0 = o.first_child, nc = o.n_children;
+            int use = 0;
+            if (o.csg == RT_CSG_UNION || o.csg == RT_CSG_INTERSECTION) use = nc;
+            else if (o.csg == RT_CSG_DIFFERENCE && nc >= 2) use = 1;   // A-hits, and B-hits inside A (is_inside(A) => within A's bound)
+            if (use == 0) break;
+            float3 lo = b.lo, hi = b.hi;
+            for (int k = 0; k < use; k++) {
+                ObjBound cb = object_bound(d, c0 + k, tlo, thi);
+                if (!cb.finite) return b;
+                lo = min3(lo, cb.lo); hi = max3(hi, cb.hi);
+            }
+            const float* M = d->xforms[o.xform].M;
+            for (int c = 0; c < 8; c++) {
+                float3 p = f3((c & 1) ? hi.x : lo.x, (c & 2) ? hi.y : lo.y, (c & 4) ? hi.z : lo.z);
+                float3 q = xform_point(M, p);
+                b.lo = min3(b.lo, q); b.hi = max3(b.hi, q);
+            }
+            b.finite = true; break;
+        }
+        default: break;                                        // plane: unbounded
+    }
+    if (b.finite && !(finite3(b.lo) && finite3(b.hi))) b.finite = false;
+    return b;
+}
+
+struct TlasItem { float3 lo, hi; int obj; int flags; };
+inline float half_area(float3 lo, float3 hi) { float3 e = hi - lo; return e.x * e.y + e.y * e.z + e.z * e.x; }
+
+// top-down sweep SAH; returns the child link of the subtree over items [b, e) (>= 0 node index, < 0 ~object)
+inline int tlas_build(std::vector<TlasItem>& it, int b, int e, std::vector<BvhNode>& nodes, float3& lo, float3& hi, int& flags) {
+    if (e - b == 1) { lo = it[b].lo; hi = it[b].hi; flags = it[b].flags; return ~it[b].obj; }
+    const int idx = (int)nodes.size();
+    nodes.emplace_back();
+    const int n = e - b;
+    int best_axis = 0, best_split = n / 2; float best_cost = INFINITY;
+    std::vector<float> right(n);
+    for (int ax = 0; ax < 3; ax++) {
+        std::stable_sort(it.begin() + b, it.begin() + e, [ax](const TlasItem& p, const TlasItem& q) {
+            return comp(p.lo, ax) + comp(p.hi, ax) < comp(q.lo, ax) + comp(q.hi, ax); });
+        float3 l = f3(INFINITY, INFINITY, INFINITY), h = f3(-INFINITY, -INFINITY, -INFINITY);
+        for (int k = n - 1; k >= 1; k--) { l = min3(l, it[b + k].lo); h = max3(h, it[b + k].hi); right[k] = half_area(l, h) * (n - k); }
+        l = f3(INFINITY, INFINITY, INFINITY); h = f3(-INFINITY, -INFINITY, -INFINITY);
+        for (int k = 1; k < n; k++) {
+            l = min3(l, it[b + k - 1].lo); h = max3(h, it[b + k - 1].hi);
+            float cost = half_area(l, h) * k + right[k];
+            if (cost < best_cost) { best_cost = cost; best_axis = ax; best_split = k; }
+        }
+    }
+    const int ax = best_axis;
+    std::stable_sort(it.begin() + b, it.begin() + e, [ax](const TlasItem& p, const TlasItem& q) {
+        return comp(p.lo, ax) + comp(p.hi, ax) < comp(q.lo, ax) + comp(q.hi, ax); });
+    float3 l0, h0, l1, h1; int f0, f1;
+    const int c0 = tlas_build(it, b, b + best_split, nodes, l0, h0, f0);
+    const int c1 = tlas_build(it, b + best_split, e, nodes, l1, h1, f1);
+    BvhNode nd;
+    nd.q0 = f4(l0.x, l0.y, l0.z, h0.x);
+    nd.q1 = f4(h0.y, h0.z, l1.x, l1.y);
+    nd.q2 = f4(l1.z, h1.x, h1.y, h1.z);
+    nd.q3 = f4(as_float(c0), as_float(c1), as_float(f0), as_float(f1));
+    nodes[idx] = nd;
+    lo = min3(l0, l1); hi = max3(h0, h1); flags = f0 | f1;
+    return idx;
+}
+
+// splits the top-level objects into the object BVH (finite bounds) and the linear list (the rest, scene order)
+inline void build_tlas(const RtSceneDesc* d, HostScene& hs) {
+    hs.tlas_nodes.clear(); hs.lin_objs.clear();
+    float tlo = INFINITY, thi = -INFINITY;
+    for (int t = 0; t < d->n_times; t++) { float v = (float)d->motion_times[t]; tlo = fminf(tlo, v); thi = fmaxf(thi, v); }
+    std::vector<TlasItem> items;
+    for (int i = 0; i < d->n_top; i++) {
+        ObjBound b = (std::isfinite(tlo) && std::isfinite(thi)) ? object_bound(d, i, tlo, thi) : ObjBound{f3(0, 0, 0), f3(0, 0, 0), false};
+        if (!b.finite) { hs.lin_objs.push_back(i); continue; }
+        const float m = fmaxf(fmaxf(fabsf(b.lo.x), fabsf(b.hi.x)), fmaxf(fmaxf(fabsf(b.lo.y), fabsf(b.hi.y)), fmaxf(fabsf(b.lo.z), fabsf(b.hi.z))));
+        const float pad = 1e-4f * m + 1e-5f;                 // fp32 slack of the exact tests (hit points a few ulp off the surface)
+        TlasItem ti; ti.lo = b.lo - f3(pad, pad, pad); ti.hi = b.hi + f3(pad, pad, pad); ti.obj = i;
+        const int kind = d->objects[i].kind;                  // mesh.py:121-153 and hierarchy.py:94-107 ignore t_max
+        ti.flags = (kind == RT_KIND_MESH || kind == RT_KIND_NODE) ? RT_TLAS_NO_TMAX : 0;
+        items.push_back(ti);
+    }
+    if (items.size() < 2) {                                   // nothing to gain: plain loop in scene order
+        hs.lin_objs.clear();
+        return;
+    }
+    float3 lo, hi; int flags;
+    tlas_build(items, 0, (int)items.size(), hs.tlas_nodes, lo, hi, flags);
 }
 
 // returns RT_OK or an RtStatus with `err` set
@@ -113,6 +238,8 @@ inline int convert_scene(const RtSceneDesc* d, HostScene& hs, std::string& err) 
     V.ambient = h3(d->ambient);
     V.max_depth = d->max_depth;
     V.mesh_mode = 0;
+    build_tlas(d, hs);
+    V.tlas_nodes = nullptr; V.lin_objs = nullptr; V.n_lin = (int)hs.lin_objs.size();
     return RT_OK;
 }
 

@@ -4,7 +4,10 @@
 #include "../../include/b200rt.h"
 
 #define RT_MAX_NEST 8        // CSG / transform nesting depth supported (NovelScene uses 5)
-#define RT_STACK_DEPTH 64    // BVH traversal stack entries per ray
+#define RT_STACK_DEPTH 64    // BVH traversal stack entries per ray (object BVH + mesh LBVH share it)
+#define RT_TLAS_NO_TMAX 1    // object-BVH child flag
+#define RT_MODE_BRUTE_MESH 1
+#define RT_MODE_LINEAR_TOP 2
 
 // One geometry object, 16-byte aligned so fields load as 128-bit vectors (warp-uniform index
 // -> one broadcast transaction).  Meaning of a/b per kind as in RtObject (include/b200rt.h).
@@ -66,7 +69,13 @@ struct SceneView {
     const DevTexture* textures;
     float3 ambient;
     int max_depth;
-    int mesh_mode;    // 0 = LBVH, 1 = brute force (test aid)
+    int mesh_mode;    // test aids: bit 0 = brute force over all faces (mesh.py:77), bit 1 = linear loop over the top-level objects
+    // object BVH over the bounded top-level objects (replaces the `for obj in self.objects` loops of scene.py:87,160
+    // for everything that has a finite extent); same 64-B node layout as the mesh LBVH, child < 0: ~object index,
+    // q3.z / q3.w = per-child flags (RT_TLAS_NO_TMAX: the subtree holds an object whose shadow test ignores t_max).
+    const BvhNode* tlas_nodes;   // NULL: no object BVH (fewer than 2 bounded objects) -> plain loop over n_top
+    const int* lin_objs;         // top-level objects without finite bounds (planes, nodes holding planes), scene order
+    int n_lin;
     // sampling tables (scene.py:41-43,118-138 precomputed once per scene)
     const float* col_x;          // [W]  (float)x of pixel-centre column
     const float* row_y;          // [H]

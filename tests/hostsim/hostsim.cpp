@@ -111,6 +111,8 @@ static int make_sim(const RtSceneDesc* d, Sim& sim) {
     V.xforms = (const DevXform*)d->xforms; V.meshes = sim.mesh_hdr.data(); V.textures = sim.texs.data();
     V.col_x = sim.hs.col_x.data(); V.row_y = sim.hs.row_y.data(); V.dof_origin = sim.hs.dof_origin.data();
     V.ray_origin = sim.hs.ray_origin.data(); V.times = sim.hs.times.data();
+    V.tlas_nodes = sim.hs.tlas_nodes.empty() ? nullptr : sim.hs.tlas_nodes.data();
+    V.lin_objs = sim.hs.lin_objs.data(); V.n_lin = (int)sim.hs.lin_objs.size();
     return 0;
 }
 

@@ -114,6 +114,20 @@ def test_bvh_traversal_equals_brute_force_on_device():
         assert nodes > 0 and sc.last_counters["bvh_nodes"] == 0
 
 
+@pytest.mark.parametrize("case", ["TwoSpheresPlane", "MotionBlur", "MirrorRefraction", "TorusMesh_smooth", "NovelScene1_small"])
+def test_object_bvh_equals_linear_object_loop_on_device(case):
+    """mesh_mode bit 1 = plain in-order loop over scene.objects (scene.py:87,160); the object BVH must not change a bit."""
+    sc = load_case(case)
+    W, H = sc.vc.width, sc.vc.height
+    a = sc.render_region(0, W, 0, H, mesh_mode=0).copy()
+    ca = dict(sc.last_counters)
+    b = sc.render_region(0, W, 0, H, mesh_mode=2)
+    cb = dict(sc.last_counters)
+    assert np.array_equal(a, b)
+    for k in ("rays_primary", "rays_shadow", "rays_reflect", "rays_refract", "shaded_hits"):
+        assert ca[k] == cb[k], k
+
+
 def test_gpu_lbvh_equals_host_restatement(lib):
     """Radix sort + Karras hierarchy + refit on the GPU vs the same RT_HD functions run sequentially on the host."""
     import hostsim
@@ -191,6 +205,8 @@ def test_synthetic_mesh_scene_sampled_parity_and_bvh_equivalence():
     a = sc.render_region(0, 160, 0, 90, mesh_mode=0).copy()
     b = sc.render_region(0, 160, 0, 90, mesh_mode=1)
     assert np.array_equal(a, b)
+    c = sc.render_region(0, 160, 0, 90, mesh_mode=3)       # brute-force faces AND plain object loop: the reference's own loops
+    assert np.array_equal(a, c)
     ref, _ = oracle.render(sc.flatten(), abi)
     frac, dmax, _ = parity_stats(to_png_array(ref), to_png_array(a))
     assert frac >= PARITY_FRACTION, (frac, dmax)

@@ -163,6 +163,30 @@ def test_bvh_traversal_equals_brute_force_on_host():
     assert ca["tri_tests"] < cb["tri_tests"] / 10
 
 
+@pytest.mark.parametrize("case", ALL_CASES)
+def test_object_bvh_equals_linear_object_loop_on_host(case):
+    """The object BVH over the bounded top-level objects (replaces the `for obj in self.objects` loops of
+    scene.py:87,160) must give the image of the plain in-order loop bit for bit (equal-t ties included)."""
+    sc = load_case(case)
+    fs = sc.flatten()
+    a, ca = hostsim.render(fs, abi, mesh_mode=0)
+    b, cb = hostsim.render(fs, abi, mesh_mode=2)
+    assert np.array_equal(a, b)
+    for k in ("rays_primary", "rays_shadow", "rays_reflect", "rays_refract", "shaded_hits"):
+        assert ca[k] == cb[k], k
+    assert ca["error_flags"] == 0 and cb["error_flags"] == 0
+
+
+def test_object_bvh_synthetic_scene_fewer_tests_same_image():
+    from python_raytracer_b200 import synthetic
+    sc = synthetic.make_scene(width=96, height=54, aa_samples=2, grid=(32, 16), n_spheres=64)
+    fs = sc.flatten()
+    a, ca = hostsim.render(fs, abi, mesh_mode=0)
+    b, cb = hostsim.render(fs, abi, mesh_mode=2)
+    assert np.array_equal(a, b)
+    assert ca["prim_tests"] < cb["prim_tests"] / 4
+
+
 def test_lbvh_structure_is_a_valid_tree():
     sc = load_case("TorusMesh_flat")
     nodes, order = hostsim.bvh(sc.flatten())
