@@ -262,15 +262,29 @@ def run_ours(a):
             with open(pk) as fh:
                 peaks = _json.load(fh)
         hbm_peak, peak_src = (peaks.get("hbm_gbs"), "measured (MEASURED_PEAKS.json)") if peaks.get("hbm_gbs") else (6650.0, "fallback")
-        # roofline of the dominant kernel (k_primary): algorithmic bytes per launch / mean launch time (DESIGN.md "Measurement")
-        pc = prof.primary
-        n_launch = max(1, int(prof.n_primary))
-        launches_per_frame = max(1, n_launch // max(1, a.steps))
+        # roofline of the dominant kernel: algorithmic bytes per launch / mean launch time (DESIGN.md "Measurement").
+        # Bytes per unit: 128 B per 4-wide BVH node fetched, 48 B per triangle tested, 64 B of vertex ids + normals per
+        # smooth-shaded mesh hit, 48 B hit record per ray (k_hit writes, k_shade reads), 16 B hit position per shadow
+        # ray + 1 B flag, 16 B per finished sample, 80 B per queued secondary ray.
         primary_rays_rank = W * H * a.spp / world
-        alg_bytes_frame = 64 * pc.bvh_nodes + 48 * pc.tri_tests + 64 * pc.mesh_hits_smooth + 80 * pc.queued_rays + 16 * primary_rays_rank
-        ms_primary = prof.ms_primary / n_launch
-        achieved = alg_bytes_frame / launches_per_frame / (ms_primary * 1e-3) / 1e9 if ms_primary > 0 else None
-        kernel_share = prof.ms_primary / max(1e-9, prof.ms_primary + prof.ms_secondary + prof.ms_resolve)
+        n_lights = len(sc.lights)
+        kinds = {
+            "k_hit": (prof.ms_hit, prof.n_hit, prof.hit,
+                      lambda c: 128 * c.bvh_nodes + 48 * c.tri_tests + 64 * c.mesh_hits_smooth + 48 * primary_rays_rank),
+            "k_shadow": (prof.ms_shadow, prof.n_shadow, prof.shadow,
+                         lambda c: 128 * c.bvh_nodes + 48 * c.tri_tests + 16 * primary_rays_rank * n_lights + c.rays_shadow),
+            "k_shade": (prof.ms_shade, prof.n_shade, prof.shade,
+                        lambda c: (48 + n_lights) * c.shaded_hits + 16 * primary_rays_rank + 80 * c.queued_rays),
+        }
+        dom = max(kinds, key=lambda k: kinds[k][0])
+        ms_dom_total, n_launch, pc, bytes_of = kinds[dom]
+        n_launch = max(1, int(n_launch))
+        launches_per_frame = max(1, n_launch // max(1, a.steps))
+        alg_bytes_frame = bytes_of(pc)
+        ms_dom = ms_dom_total / n_launch
+        achieved = alg_bytes_frame / launches_per_frame / (ms_dom * 1e-3) / 1e9 if ms_dom > 0 else None
+        ms_all = prof.ms_hit + prof.ms_shadow + prof.ms_shade + prof.ms_secondary + prof.ms_resolve
+        kernel_share = ms_dom_total / max(1e-9, ms_all)
         value = rays_frame * a.steps / (ms_total * 1e-3) / 1e6
         e2e_value = rays_frame * e2e_steps / (ms2_total * 1e-3) / 1e6
         out = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
@@ -284,14 +298,15 @@ def run_ours(a):
                        "what": "frame rendered through the C ABI and copied to pinned HOST memory every step (scene resident: "
                                "uploaded once like the reference's load_scene)"},
                "gpu_launches": launches_frame * a.steps,
-               "roofline": {"bound": "hbm", "kernel": "k_primary", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+               "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                             "frac": (achieved / hbm_peak) if achieved else None, "traffic": None, "peak_source": peak_src,
                             "algorithmic_bytes_per_launch": alg_bytes_frame / launches_per_frame,
-                            "launch_ms": ms_primary, "launches_per_frame": launches_per_frame,
+                            "launch_ms": ms_dom, "launches_per_frame": launches_per_frame,
                             "kernel_share_of_step": kernel_share,
                             "counts_rank0_per_frame": {"bvh_nodes": int(pc.bvh_nodes), "tri_tests": int(pc.tri_tests),
                                                        "queued_rays": int(pc.queued_rays)}},
-               "kernel_ms_per_frame": {"k_primary": prof.ms_primary / a.steps, "k_secondary": prof.ms_secondary / a.steps,
+               "kernel_ms_per_frame": {"k_hit": prof.ms_hit / a.steps, "k_shadow": prof.ms_shadow / a.steps,
+                                       "k_shade": prof.ms_shade / a.steps, "levels>=1 (hit+shadow+shade)": prof.ms_secondary / a.steps,
                                        "k_resolve": prof.ms_resolve / a.steps},
                "setup_ms": {"scene_python": 1e3 * t_scene, "upload": 1e3 * t_upload, "lbvh_build": 1e3 * t_bvh},
                "clocks": clocks}

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define RT_ABI_VERSION 1
+#define RT_ABI_VERSION 2
 
 /* ---- enums ------------------------------------------------------------------------- */
 enum RtKind { RT_KIND_SPHERE = 0, RT_KIND_PLANE = 1, RT_KIND_BOX = 2, RT_KIND_MESH = 3, RT_KIND_NODE = 4 };
@@ -189,13 +189,15 @@ typedef struct RtCounters {
     uint64_t error_flags;    /* bit (RtStatus) set by kernels */
 } RtCounters;
 
-/* Per-kernel-class device timing (CUDA events on the launch stream) + the tallies of each class for the
- * last rt_render call; used by bench.py for the roofline of the dominant kernel. */
+/* Per-kernel-class device timing (CUDA events on the launch stream) + the tallies of each class for the last
+ * rt_render call; used by bench.py for the roofline of the dominant kernel.  One cast_ray level is three launches
+ * (closest hit, shadow rays, shading); level 0 (the generated rays) is timed per kernel, deeper levels as a whole. */
 typedef struct RtProfile {
-    double ms_primary, ms_secondary, ms_resolve;   /* summed event time since profiling was enabled */
-    uint64_t n_primary, n_secondary, n_resolve;    /* launches timed */
-    RtCounters primary;                            /* tallies of k_primary launches of the last rt_render */
-    RtCounters secondary;                          /* tallies of k_secondary launches of the last rt_render */
+    double ms_hit, ms_shadow, ms_shade;            /* level 0: k_hit / k_shadow / k_shade, summed since profiling was enabled */
+    double ms_secondary, ms_resolve;               /* all kernels of levels >= 1 ; k_resolve */
+    uint64_t n_hit, n_shadow, n_shade, n_secondary, n_resolve;   /* timed launches (n_secondary: levels) */
+    RtCounters hit, shadow, shade;                 /* tallies of the level-0 kernels of the last rt_render */
+    RtCounters secondary;                          /* tallies of all deeper-level kernels of the last rt_render */
 } RtProfile;
 
 typedef struct RtScene RtScene;  /* opaque, device-resident */
@@ -235,7 +237,8 @@ int rt_scene_destroy(RtScene* scene);
 
 /* Introspection used by tests and the bench */
 int rt_scene_bvh_stats(const RtScene* scene, int32_t mesh, int64_t* n_nodes, int64_t* n_leaf_tris, int64_t* bytes);
-/* Copies the LBVH of `mesh` back to host buffers for validation: nodes (n_nodes*16 floats), leaf order (n_faces int32) */
+/* Copies the LBVH of `mesh` back to host buffers for validation: 4-wide nodes (n_nodes*32 floats: 6 float4 child boxes in
+ * SoA, int4 links, int4 flags), leaf order (n_faces int32) */
 int rt_scene_bvh_download(const RtScene* scene, int32_t mesh, float* h_nodes, int32_t* h_order);
 /* Unit-test aids: cast_ray (scene.py:81-116) and the any-hit loop (scene.py:160-164) for explicit rays.
  * All pointers are HOST buffers: origins/dirs (n,3) f32, times (n) f32; outputs rgb (n,3), first-hit t (n, inf = miss),

@@ -11,7 +11,7 @@ import numpy as np
 
 from . import geometry as geom
 
-RT_ABI_VERSION = 1
+RT_ABI_VERSION = 2
 KIND_SPHERE, KIND_PLANE, KIND_BOX, KIND_MESH, KIND_NODE = range(5)
 MAT_TYPES = {"mirror": 1, "refractive": 2}            # anything else shades as diffuse, scene.py:97-111
 LIGHT_TYPES = {"point": 0, "directional": 1}
@@ -89,9 +89,11 @@ class RtCounters(C.Structure):
 
 
 class RtProfile(C.Structure):
-    _fields_ = [("ms_primary", C.c_double), ("ms_secondary", C.c_double), ("ms_resolve", C.c_double),
-                ("n_primary", C.c_uint64), ("n_secondary", C.c_uint64), ("n_resolve", C.c_uint64),
-                ("primary", RtCounters), ("secondary", RtCounters)]
+    _fields_ = [("ms_hit", C.c_double), ("ms_shadow", C.c_double), ("ms_shade", C.c_double),
+                ("ms_secondary", C.c_double), ("ms_resolve", C.c_double),
+                ("n_hit", C.c_uint64), ("n_shadow", C.c_uint64), ("n_shade", C.c_uint64),
+                ("n_secondary", C.c_uint64), ("n_resolve", C.c_uint64),
+                ("hit", RtCounters), ("shadow", RtCounters), ("shade", RtCounters), ("secondary", RtCounters)]
 
 
 DEFAULT_JITTER_SEED = 0x5EED
@@ -266,7 +268,7 @@ def flatten(scene, jitter_seed=DEFAULT_JITTER_SEED, max_depth=DEFAULT_MAX_DEPTH)
 # ---------------------------------------------------------------------------- library
 
 _LIB = None
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "libb200rt.so")
+LIB_PATH = os.environ.get("B200RT_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "libb200rt.so")
 
 ENTRY_POINTS = ["rt_scene_create", "rt_scene_build_bvh", "rt_render", "rt_render_host", "rt_job_extent",
                 "rt_assemble_tiles", "rt_finalize_u8", "rt_scene_destroy", "rt_scene_bvh_stats",

@@ -13,6 +13,8 @@
 #include "rt_kernels.cuh"
 #include "rt_scene_build.hpp"
 
+#define RT_PROF_CLASSES 5
+#define RT_COUNTER_CLASSES 4     // tallies kept apart for level-0 k_hit / k_shadow / k_shade and for the deeper levels
 static thread_local std::string g_last_error;
 
 static int fail(int code, const std::string& msg) { g_last_error = msg; return code; }
@@ -32,7 +34,8 @@ struct MeshBuild {
     float4* d_vnormals = nullptr;   // n_verts
     float4* d_tri = nullptr;        // 3*n_faces
     int4* d_face_vidx = nullptr;    // n_faces
-    BvhNode* d_nodes = nullptr;     // n_faces-1
+    BvhNode4* d_nodes = nullptr;    // n_nodes4 traversal nodes
+    int n_nodes4 = 0;
     int* d_order = nullptr;         // n_faces: slot -> original face
     float3 lo, hi;
     float pad = 0.0f;
@@ -50,6 +53,8 @@ struct RtScene {
     // work buffers of rt_render, grown on demand
     float4* d_samples = nullptr; long long samples_cap = 0;
     float4* d_queue[2] = {nullptr, nullptr}; long long queue_cap = 0;
+    float4* d_hit = nullptr; long long hit_cap = 0;          // hit record planes of the level in flight
+    uint8_t* d_occ = nullptr; long long occ_cap = 0;         // n_lights planes of occlusion flags
     unsigned long long* d_qcount = nullptr;   // [max_depth + 1]
     RtCounters* d_counters = nullptr;
     float* d_stage = nullptr; long long stage_cap = 0;   // rt_render_host staging
@@ -57,9 +62,10 @@ struct RtScene {
     int sm_count = 148;
     unsigned long long last_launches = 0;
     bool profiling = false;
-    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev[3];   // primary / secondary / resolve
-    double prof_ms[3] = {0, 0, 0};
-    unsigned long long prof_n[3] = {0, 0, 0};
+    // profiling classes: level-0 k_hit / k_shadow / k_shade, all kernels of the deeper levels, k_resolve
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev[RT_PROF_CLASSES];
+    double prof_ms[RT_PROF_CLASSES] = {0, 0, 0, 0, 0};
+    unsigned long long prof_n[RT_PROF_CLASSES] = {0, 0, 0, 0, 0};
 };
 
 struct ProfScope {   // event pair around one launch when profiling is on
@@ -78,7 +84,7 @@ static int upload(RtScene* sc, const T* host, size_t n, T** out) {
     CU(cudaMalloc(&p, alloc_n * sizeof(T)));
     sc->allocs.push_back(p);
     if (host && n) CU(cudaMemcpy(p, host, n * sizeof(T), cudaMemcpyHostToDevice));
-    else CU(cudaMemset(p, 0, alloc_n * sizeof(T)));
+    else { CU(cudaMemset(p, 0, alloc_n * sizeof(T))); CU(cudaDeviceSynchronize()); }   // set-up time only: later kernels run on caller streams
     *out = (T*)p;
     return RT_OK;
 }
@@ -108,11 +114,11 @@ static int scene_create_impl(const RtSceneDesc* d, RtScene* sc) {
     V.objects = d_objs; V.materials = d_mats; V.lights = d_lights; V.xforms = d_xf;
     // ---- object BVH over the bounded top-level objects (host-built in convert_scene)
     sc->has_tlas = !hs.tlas_nodes.empty();
-    if (sc->has_tlas) {
-        BvhNode* d_tn; UP(upload(sc, hs.tlas_nodes.data(), hs.tlas_nodes.size(), &d_tn));
-        int* d_lin; UP(upload(sc, hs.lin_objs.data(), hs.lin_objs.size(), &d_lin));
-        V.tlas_nodes = d_tn; V.lin_objs = d_lin; V.n_lin = (int)hs.lin_objs.size();
-    }
+    if (sc->has_tlas) { BvhNode4* d_tn; UP(upload(sc, hs.tlas_nodes.data(), hs.tlas_nodes.size(), &d_tn)); V.tlas_nodes = d_tn; }
+    int* d_lin; UP(upload(sc, hs.lin_objs.data(), hs.lin_objs.size(), &d_lin));
+    V.lin_objs = d_lin; V.n_lin = (int)hs.lin_objs.size();
+    int* d_sep; UP(upload(sc, hs.sep_mesh.data(), hs.sep_mesh.size(), &d_sep));
+    V.sep_mesh = d_sep; V.n_sep_mesh = (int)hs.sep_mesh.size();
     // ---- textures
     std::vector<DevTexture> texs(d->n_textures);
     for (int i = 0; i < d->n_textures; i++) {
@@ -151,7 +157,7 @@ static int scene_create_impl(const RtSceneDesc* d, RtScene* sc) {
     V.col_x = d_colx; V.row_y = d_rowy; V.dof_origin = d_dof; V.ray_origin = d_org; V.times = d_times;
     sc->samples_per_pixel = d->dof_samples * d->aa_samples * d->n_times;
     UP(upload(sc, (const unsigned long long*)nullptr, (size_t)d->max_depth + 2, &sc->d_qcount));
-    UP(upload(sc, (const RtCounters*)nullptr, 2, &sc->d_counters));
+    UP(upload(sc, (const RtCounters*)nullptr, RT_COUNTER_CLASSES, &sc->d_counters));
     return RT_OK;
 }
 
@@ -162,6 +168,8 @@ extern "C" int rt_scene_destroy(RtScene* sc) {
     for (void* p : sc->allocs) cudaFree(p);
     if (sc->d_samples) cudaFree(sc->d_samples);
     for (int k = 0; k < 2; k++) if (sc->d_queue[k]) cudaFree(sc->d_queue[k]);
+    if (sc->d_hit) cudaFree(sc->d_hit);
+    if (sc->d_occ) cudaFree(sc->d_occ);
     if (sc->d_stage) cudaFree(sc->d_stage);
     drain_events(sc);
     delete sc;
@@ -189,9 +197,8 @@ static int build_mesh_bvh(RtScene* sc, int mi, cudaStream_t st) {
     UP(upload(sc, (const float4*)nullptr, (size_t)n * 3, &b.d_tri));
     UP(upload(sc, (const int4*)nullptr, (size_t)n, &b.d_face_vidx));
     UP(upload(sc, (const int*)nullptr, (size_t)n, &b.d_order));
-    UP(upload(sc, (const BvhNode*)nullptr, (size_t)std::max(1, n - 1), &b.d_nodes));
     // temporaries
-    uint64_t *keys[2]; int* vals[2]; unsigned* hist; int2* children; int *parent_node, *parent_leaf; unsigned* arrive;
+    uint64_t *keys[2]; int* vals[2]; unsigned* hist; int2* children; int *parent_node, *parent_leaf; unsigned *arrive, *even, *remap;
     float4 *leaf_lo, *leaf_hi, *node_lo, *node_hi;
     const int n_tiles = (n + RS_TILE - 1) / RS_TILE;
     std::vector<void*> tmp;
@@ -202,7 +209,7 @@ static int build_mesh_bvh(RtScene* sc, int mi, cudaStream_t st) {
     TA(vals[0], sizeof(int) * n); TA(vals[1], sizeof(int) * n);
     TA(hist, sizeof(unsigned) * 256 * n_tiles);
     TA(children, sizeof(int2) * n); TA(parent_node, sizeof(int) * n); TA(parent_leaf, sizeof(int) * n);
-    TA(arrive, sizeof(unsigned) * n);
+    TA(arrive, sizeof(unsigned) * n); TA(even, sizeof(unsigned) * n); TA(remap, sizeof(unsigned) * n);
     TA(leaf_lo, sizeof(float4) * n); TA(leaf_hi, sizeof(float4) * n); TA(node_lo, sizeof(float4) * n); TA(node_hi, sizeof(float4) * n);
 #undef TA
     float3 ext = b.hi - b.lo;
@@ -222,8 +229,24 @@ static int build_mesh_bvh(RtScene* sc, int mi, cudaStream_t st) {
     if (n >= 2) k_lbvh_hierarchy<<<G, T, 0, st>>>(keys[cur], n, children, parent_node, parent_leaf);
     k_lbvh_leaves_refit<<<G, T, 0, st>>>(b.d_verts, b.d_faces, vals[cur], n, children, parent_node, parent_leaf, b.d_tri, b.d_face_vidx,
                                         leaf_lo, leaf_hi, node_lo, node_hi, arrive);
-    if (n >= 2) k_lbvh_emit<<<G, T, 0, st>>>(n, children, leaf_lo, leaf_hi, node_lo, node_hi, b.pad, b.d_nodes);
-    cudaError_t e = cudaStreamSynchronize(st);
+    // 4-wide collapse: even-depth nodes survive; exclusive scan of the flags = compact, deterministic node indices
+    cudaError_t e = cudaSuccess;
+    b.n_nodes4 = 0;
+    if (n >= 2) {
+        k_lbvh_even<<<G, T, 0, st>>>(n, parent_node, even, remap);
+        k_rs_scan<<<1, 1024, 0, st>>>(remap, n - 1);
+        unsigned last_idx = 0, last_even = 0;
+        e = cudaMemcpyAsync(&last_idx, remap + (n - 2), sizeof(unsigned), cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(&last_even, even + (n - 2), sizeof(unsigned), cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        if (e == cudaSuccess) {
+            b.n_nodes4 = (int)(last_idx + last_even);
+            int rc = upload(sc, (const BvhNode4*)nullptr, (size_t)std::max(1, b.n_nodes4), &b.d_nodes);
+            if (rc != RT_OK) { tfree(); return rc; }
+            k_lbvh_emit4<<<G, T, 0, st>>>(n, children, even, remap, leaf_lo, leaf_hi, node_lo, node_hi, b.pad, b.d_nodes);
+        }
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
     if (e == cudaSuccess) e = cudaGetLastError();
     tfree();
     if (e != cudaSuccess) return fail(RT_ERR_CUDA, std::string("LBVH build: ") + cudaGetErrorString(e));
@@ -245,9 +268,9 @@ extern "C" int rt_scene_build_bvh(RtScene* sc, void* stream) {
 extern "C" int rt_scene_bvh_stats(const RtScene* sc, int32_t mesh, int64_t* n_nodes, int64_t* n_leaf_tris, int64_t* bytes) {
     if (!sc || mesh < 0 || mesh >= (int)sc->meshes.size()) return fail(RT_ERR_INVALID, "mesh index");
     const MeshBuild& b = sc->meshes[mesh];
-    if (n_nodes) *n_nodes = std::max(0, b.n_faces - 1);
+    if (n_nodes) *n_nodes = b.n_nodes4;
     if (n_leaf_tris) *n_leaf_tris = b.n_faces;
-    if (bytes) *bytes = (int64_t)std::max(0, b.n_faces - 1) * 64 + (int64_t)b.n_faces * (48 + 16) + (b.d_vnormals ? (int64_t)b.n_verts * 16 : 0);
+    if (bytes) *bytes = (int64_t)b.n_nodes4 * (int64_t)sizeof(BvhNode4) + (int64_t)b.n_faces * (48 + 16) + (b.d_vnormals ? (int64_t)b.n_verts * 16 : 0);
     return RT_OK;
 }
 
@@ -255,7 +278,7 @@ extern "C" int rt_scene_bvh_download(const RtScene* sc, int32_t mesh, float* h_n
     if (!sc || mesh < 0 || mesh >= (int)sc->meshes.size()) return fail(RT_ERR_INVALID, "mesh index");
     const MeshBuild& b = sc->meshes[mesh];
     if (!b.built) return fail(RT_ERR_INVALID, "BVH not built");
-    if (h_nodes && b.n_faces >= 2) CU(cudaMemcpy(h_nodes, b.d_nodes, sizeof(BvhNode) * (size_t)(b.n_faces - 1), cudaMemcpyDeviceToHost));
+    if (h_nodes && b.n_nodes4 > 0) CU(cudaMemcpy(h_nodes, b.d_nodes, sizeof(BvhNode4) * (size_t)b.n_nodes4, cudaMemcpyDeviceToHost));
     if (h_order && b.n_faces >= 1) CU(cudaMemcpy(h_order, b.d_order, sizeof(int) * (size_t)b.n_faces, cudaMemcpyDeviceToHost));
     return RT_OK;
 }
@@ -285,11 +308,15 @@ static int grow(T** buf, long long* cap, long long need, size_t elems_per_unit =
     return RT_OK;
 }
 
-static void sum_counters(const RtCounters* two, RtCounters* out) {
-    const uint64_t* a = (const uint64_t*)&two[0]; const uint64_t* b = (const uint64_t*)&two[1];
+static void sum_counters(const RtCounters* cls, RtCounters* out) {
+    memset(out, 0, sizeof *out);
     uint64_t* o = (uint64_t*)out;
-    for (size_t k = 0; k < sizeof(RtCounters) / sizeof(uint64_t); k++) o[k] = a[k] + b[k];
-    out->error_flags = two[0].error_flags | two[1].error_flags;
+    for (int c = 0; c < RT_COUNTER_CLASSES; c++) {
+        const uint64_t* a = (const uint64_t*)&cls[c];
+        for (size_t k = 0; k < sizeof(RtCounters) / sizeof(uint64_t); k++) o[k] += a[k];
+    }
+    out->error_flags = 0;
+    for (int c = 0; c < RT_COUNTER_CLASSES; c++) out->error_flags |= cls[c].error_flags;
 }
 
 template <bool HAS_NODES>
@@ -308,6 +335,13 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
     }
     const long long batch_cap = std::min(px_per_batch, std::max(1ll, pm.n_local_pixels)) * N;
     UP(grow(&sc->d_samples, &sc->samples_cap, batch_cap));
+    UP(grow(&sc->d_hit, &sc->hit_cap, batch_cap, RT_HIT_PLANES));
+    const int L = std::max(1, V.n_lights);
+    if (sc->hit_cap * L > sc->occ_cap) {                      // occlusion planes share the hit planes' stride
+        if (sc->d_occ) { cudaFree(sc->d_occ); sc->d_occ = nullptr; sc->occ_cap = 0; }
+        CU(cudaMalloc((void**)&sc->d_occ, (size_t)sc->hit_cap * L));
+        sc->occ_cap = sc->hit_cap * L;
+    }
     const bool secondary = sc->has_specular && V.max_depth > 1;
     if (secondary && batch_cap > sc->queue_cap) {
         for (int k = 0; k < 2; k++) {
@@ -319,34 +353,44 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
     }
     const size_t smem = (sc->has_mesh || sc->has_tlas) ? sizeof(int) * RT_STACK_DEPTH * RT_BLOCK : 0;
     if (smem) {
-        CU(cudaFuncSetAttribute(k_primary<HAS_NODES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        CU(cudaFuncSetAttribute(k_secondary<HAS_NODES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CU(cudaFuncSetAttribute(k_hit<HAS_NODES, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CU(cudaFuncSetAttribute(k_hit<HAS_NODES, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CU(cudaFuncSetAttribute(k_shadow<HAS_NODES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     }
     const int direct = (job->direct && job->world == 1) ? 1 : 0;
     const int max_grid = sc->sm_count * 16;
+    HitPlanes H{sc->d_hit, sc->hit_cap};
+    // the hit/occlusion planes are indexed with the stride of their allocation; occ planes use H.cap as stride
     for (long long p0 = 0; p0 < pm.n_local_pixels; p0 += px_per_batch) {
         const long long npx = std::min(px_per_batch, pm.n_local_pixels - p0);
         const long long n_rays = npx * N;
         CU(cudaMemsetAsync(sc->d_qcount, 0, sizeof(unsigned long long) * (size_t)(V.max_depth + 2), st));
         RayQueue q0{sc->d_queue[0], sc->queue_cap}, q1{sc->d_queue[1], sc->queue_cap};
         const int grid = (int)std::min<long long>((n_rays + RT_BLOCK - 1) / RT_BLOCK, max_grid);
-        {
-            ProfScope ps_(sc, 0, st);
-            k_primary<HAS_NODES><<<grid, RT_BLOCK, smem, st>>>(V, pm, p0, n_rays, sc->d_samples, q0, sc->d_qcount, sc->d_counters);
+        const int grid_sh = (int)std::min<long long>((n_rays * V.n_lights + RT_BLOCK - 1) / RT_BLOCK, max_grid);
+        {   // level 0: generated rays
+            { ProfScope ps_(sc, 0, st);
+              k_hit<HAS_NODES, true><<<grid, RT_BLOCK, smem, st>>>(V, pm, p0, n_rays, q0, nullptr, H, sc->d_counters + 0); }
+            if (V.n_lights > 0) { ProfScope ps_(sc, 1, st);
+              k_shadow<HAS_NODES><<<std::max(1, grid_sh), RT_BLOCK, smem, st>>>(V, n_rays, nullptr, H, sc->d_occ, sc->d_counters + 1); (*launches)++; }
+            { ProfScope ps_(sc, 2, st);
+              k_shade<true><<<grid, RT_BLOCK, 0, st>>>(V, n_rays, q0, nullptr, H, sc->d_occ, sc->d_samples, q0, sc->d_qcount, sc->d_counters + 2); }
+            (*launches) += 2;
         }
-        (*launches)++;
         if (secondary) {
             for (int level = 1; level < V.max_depth; level++) {       // level L consumes the rays spawned by level L-1
                 RayQueue& qin = (level & 1) ? q0 : q1;
                 RayQueue& qout = (level & 1) ? q1 : q0;
-                ProfScope ps_(sc, 1, st);
-                k_secondary<HAS_NODES><<<max_grid, RT_BLOCK, smem, st>>>(V, qin, sc->d_qcount + (level - 1), sc->d_samples, qout,
-                                                                         sc->d_qcount + level, sc->d_counters + 1);
-                (*launches)++;
+                const unsigned long long* n_in = sc->d_qcount + (level - 1);
+                ProfScope ps_(sc, 3, st);
+                k_hit<HAS_NODES, false><<<max_grid, RT_BLOCK, smem, st>>>(V, pm, 0, 0, qin, n_in, H, sc->d_counters + 3);
+                if (V.n_lights > 0) { k_shadow<HAS_NODES><<<max_grid, RT_BLOCK, smem, st>>>(V, 0, n_in, H, sc->d_occ, sc->d_counters + 3); (*launches)++; }
+                k_shade<false><<<max_grid, RT_BLOCK, 0, st>>>(V, 0, qin, n_in, H, sc->d_occ, sc->d_samples, qout, sc->d_qcount + level, sc->d_counters + 3);
+                (*launches) += 2;
             }
         }
         {
-            ProfScope ps_(sc, 2, st);
+            ProfScope ps_(sc, 4, st);
             k_resolve<<<(int)((npx + 127) / 128), 128, 0, st>>>(pm, p0, (int)npx, N, sc->d_samples, d_out, direct);
         }
         (*launches)++;
@@ -362,16 +406,16 @@ extern "C" int rt_render(RtScene* sc, const RtRenderJob* job, float* d_out, RtCo
     UP(make_pixel_map(job, pm, nt));
     cudaStream_t st = (cudaStream_t)stream;
     CU(cudaSetDevice(sc->device));
-    CU(cudaMemsetAsync(sc->d_counters, 0, 2 * sizeof(RtCounters), st));
+    CU(cudaMemsetAsync(sc->d_counters, 0, RT_COUNTER_CLASSES * sizeof(RtCounters), st));
     unsigned long long launches = 0;
     int rc = sc->has_nodes ? render_impl<true>(sc, job, pm, d_out, st, &launches) : render_impl<false>(sc, job, pm, d_out, st, &launches);
     if (rc != RT_OK) return rc;
     sc->last_launches = launches;
     if (counters) {
-        RtCounters two[2];
-        CU(cudaMemcpyAsync(two, sc->d_counters, 2 * sizeof(RtCounters), cudaMemcpyDeviceToHost, st));
+        RtCounters cls[RT_COUNTER_CLASSES];
+        CU(cudaMemcpyAsync(cls, sc->d_counters, sizeof cls, cudaMemcpyDeviceToHost, st));
         CU(cudaStreamSynchronize(st));
-        sum_counters(two, counters);
+        sum_counters(cls, counters);
         counters->kernel_launches = launches;
     }
     return RT_OK;
@@ -385,10 +429,10 @@ extern "C" int rt_render_host(RtScene* sc, const RtRenderJob* job, float* h_out,
     cudaStream_t st = (cudaStream_t)stream;
     UP(rt_render(sc, job, sc->d_stage, nullptr, stream));
     CU(cudaMemcpyAsync(h_out, sc->d_stage, sizeof(float) * (size_t)n_floats, cudaMemcpyDeviceToHost, st));
-    RtCounters two[2];
-    if (counters) CU(cudaMemcpyAsync(two, sc->d_counters, 2 * sizeof(RtCounters), cudaMemcpyDeviceToHost, st));
+    RtCounters cls[RT_COUNTER_CLASSES];
+    if (counters) CU(cudaMemcpyAsync(cls, sc->d_counters, sizeof cls, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
-    if (counters) { sum_counters(two, counters); counters->kernel_launches = sc->last_launches; }
+    if (counters) { sum_counters(cls, counters); counters->kernel_launches = sc->last_launches; }
     return RT_OK;
 }
 
@@ -493,7 +537,7 @@ extern "C" int rt_occluded(RtScene* sc, int64_t n, const float* h_org, const flo
 // ---------------------------------------------------------------------------------------------------
 // profiling
 static void drain_events(RtScene* sc) {
-    for (int c = 0; c < 3; c++) {
+    for (int c = 0; c < RT_PROF_CLASSES; c++) {
         for (auto& pr : sc->ev[c]) {
             cudaEventSynchronize(pr.second);
             float ms = 0.0f;
@@ -508,17 +552,19 @@ extern "C" int rt_scene_profile(RtScene* sc, int32_t enable) {
     if (!sc) return fail(RT_ERR_INVALID, "null scene");
     drain_events(sc);
     sc->profiling = enable != 0;
-    if (enable) for (int c = 0; c < 3; c++) { sc->prof_ms[c] = 0; sc->prof_n[c] = 0; }
+    if (enable) for (int c = 0; c < RT_PROF_CLASSES; c++) { sc->prof_ms[c] = 0; sc->prof_n[c] = 0; }
     return RT_OK;
 }
 
 extern "C" int rt_scene_profile_read(RtScene* sc, RtProfile* out) {
     if (!sc || !out) return fail(RT_ERR_INVALID, "null argument");
     drain_events(sc);
-    out->ms_primary = sc->prof_ms[0]; out->ms_secondary = sc->prof_ms[1]; out->ms_resolve = sc->prof_ms[2];
-    out->n_primary = sc->prof_n[0]; out->n_secondary = sc->prof_n[1]; out->n_resolve = sc->prof_n[2];
-    RtCounters two[2];
-    CU(cudaMemcpy(two, sc->d_counters, 2 * sizeof(RtCounters), cudaMemcpyDeviceToHost));
-    out->primary = two[0]; out->secondary = two[1];
+    out->ms_hit = sc->prof_ms[0]; out->ms_shadow = sc->prof_ms[1]; out->ms_shade = sc->prof_ms[2];
+    out->ms_secondary = sc->prof_ms[3]; out->ms_resolve = sc->prof_ms[4];
+    out->n_hit = sc->prof_n[0]; out->n_shadow = sc->prof_n[1]; out->n_shade = sc->prof_n[2];
+    out->n_secondary = sc->prof_n[3]; out->n_resolve = sc->prof_n[4];
+    RtCounters cls[RT_COUNTER_CLASSES];
+    CU(cudaMemcpy(cls, sc->d_counters, sizeof cls, cudaMemcpyDeviceToHost));
+    out->hit = cls[0]; out->shadow = cls[1]; out->shade = cls[2]; out->secondary = cls[3];
     return RT_OK;
 }

@@ -12,11 +12,15 @@ FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std
 
 
 def build(force=False, verbose=False):
+    global OUT
+    extra = os.environ.get("B200RT_EXTRA_NVCC", "").split()       # developer knob for tuning experiments (-DRT_MIN_BLOCKS=...)
+    if os.environ.get("B200RT_OUT"):
+        OUT = os.path.join(HERE, os.environ["B200RT_OUT"]); force = True
     newest = max(os.path.getmtime(os.path.join(HERE, d)) for d in DEPS)
     if not force and os.path.exists(OUT) and os.path.getmtime(OUT) >= newest:
         return OUT
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + FLAGS + ["-o", OUT] + [os.path.join(HERE, s) for s in SRCS]
+    cmd = [nvcc] + FLAGS + extra + ["-o", OUT] + [os.path.join(HERE, s) for s in SRCS]
     r = subprocess.run(cmd, capture_output=True, text=True)
     with open(os.path.join(HERE, "build.log"), "w") as fh:
         fh.write(" ".join(cmd) + "\n" + r.stdout + r.stderr)

@@ -2,7 +2,9 @@
 // mesh.py:72-77): 63-bit Morton codes of triangle centroids -> LSD radix sort (8 x 8 bits, hand
 // written: per-tile histograms, one scan, stable scatter by warp match + per-round block offsets)
 // -> Karras 2012 radix-tree hierarchy -> bottom-up AABB refit with atomic arrival counters ->
-// 64-byte traversal nodes holding both children's boxes + triangles re-laid in Morton order.
+// collapse of every other level into 4-wide 128-byte traversal nodes (even-depth binary nodes survive; their
+// children are the grandchildren, or a leaf child as is; compact indices by a prefix sum, so the layout is
+// deterministic) + triangles re-laid in Morton order.
 #pragma once
 #include "rt_types.cuh"
 
@@ -70,6 +72,38 @@ RT_HD void lbvh_node(const uint64_t* keys, int n, int i, int& left, int& right) 
     int lo = i < j ? i : j, hi = i < j ? j : i;
     left = (lo == gamma) ? ~gamma : gamma;
     right = (hi == gamma + 1) ? ~(gamma + 1) : gamma + 1;
+}
+
+// ---- 4-wide collapse (shared by the GPU emit kernel, the host object-BVH builder and tests/hostsim) ----------
+// links of the up-to-4 children of even-depth binary node i: an internal (odd-depth) child is replaced by its two children
+RT_HD int wide_children(const int2* children, int i, int out[4]) {
+    const int2 ch = children[i];
+    int n = 0;
+    if (ch.x < 0) out[n++] = ch.x; else { const int2 g = children[ch.x]; out[n++] = g.x; out[n++] = g.y; }
+    if (ch.y < 0) out[n++] = ch.y; else { const int2 g = children[ch.y]; out[n++] = g.x; out[n++] = g.y; }
+    return n;
+}
+RT_HD void set4(float4& v, int k, float x) { if (k == 0) v.x = x; else if (k == 1) v.y = x; else if (k == 2) v.z = x; else v.w = x; }
+RT_HD void set4i(int4& v, int k, int x) { if (k == 0) v.x = x; else if (k == 1) v.y = x; else if (k == 2) v.z = x; else v.w = x; }
+// one traversal node from the binary tree: boxes padded by `pad`; remap: binary index -> compact wide index;
+// leaf_flags may be NULL (mesh LBVH)
+RT_HD BvhNode4 make_wide_node(const int2* children, int i, const unsigned* remap, const float4* leaf_lo, const float4* leaf_hi,
+                              const float4* node_lo, const float4* node_hi, const int* leaf_flags, const int* node_flags, float pad) {
+    BvhNode4 nd;
+    nd.lox = nd.loy = nd.loz = nd.hix = nd.hiy = nd.hiz = f4(0.0f, 0.0f, 0.0f, 0.0f);   // empty slots: skipped by their link
+    nd.link.x = nd.link.y = nd.link.z = nd.link.w = RT_LINK_NONE;
+    nd.flags.x = nd.flags.y = nd.flags.z = nd.flags.w = 0;
+    int c[4];
+    const int n = wide_children(children, i, c);
+    for (int k = 0; k < n; k++) {
+        const bool leaf = c[k] < 0;
+        const float4 lo = leaf ? leaf_lo[~c[k]] : node_lo[c[k]], hi = leaf ? leaf_hi[~c[k]] : node_hi[c[k]];
+        set4(nd.lox, k, lo.x - pad); set4(nd.loy, k, lo.y - pad); set4(nd.loz, k, lo.z - pad);
+        set4(nd.hix, k, hi.x + pad); set4(nd.hiy, k, hi.y + pad); set4(nd.hiz, k, hi.z + pad);
+        set4i(nd.link, k, leaf ? c[k] : (int)remap[c[k]]);
+        if (leaf_flags) set4i(nd.flags, k, leaf ? leaf_flags[~c[k]] : node_flags[c[k]]);
+    }
+    return nd;
 }
 
 #if defined(__CUDACC__)
@@ -205,19 +239,22 @@ __global__ void k_lbvh_leaves_refit(const float* __restrict__ verts, const int* 
     }
 }
 
-// final 64-byte traversal nodes: both children's (padded) boxes in the parent
-__global__ void k_lbvh_emit(int n, const int2* __restrict__ children, const float4* __restrict__ leaf_lo, const float4* __restrict__ leaf_hi,
-                            const float4* __restrict__ node_lo, const float4* __restrict__ node_hi, float pad, BvhNode* __restrict__ out) {
+// depth parity of every internal node (walk the parent links to the root): even-depth nodes become traversal nodes
+__global__ void k_lbvh_even(int n, const int* __restrict__ parent_node, unsigned* __restrict__ even, unsigned* __restrict__ remap) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n - 1) return;
-    int2 ch = children[i];
-    float4 l0 = ch.x < 0 ? leaf_lo[~ch.x] : node_lo[ch.x], h0 = ch.x < 0 ? leaf_hi[~ch.x] : node_hi[ch.x];
-    float4 l1 = ch.y < 0 ? leaf_lo[~ch.y] : node_lo[ch.y], h1 = ch.y < 0 ? leaf_hi[~ch.y] : node_hi[ch.y];
-    BvhNode nd;
-    nd.q0 = f4(l0.x - pad, l0.y - pad, l0.z - pad, h0.x + pad);
-    nd.q1 = f4(h0.y + pad, h0.z + pad, l1.x - pad, l1.y - pad);
-    nd.q2 = f4(l1.z - pad, h1.x + pad, h1.y + pad, h1.z + pad);
-    nd.q3 = f4(as_float(ch.x), as_float(ch.y), 0.0f, 0.0f);
-    out[i] = nd;
+    unsigned depth = 0;
+    for (int p = parent_node[i]; p >= 0; p = parent_node[p]) depth++;
+    const unsigned e = (depth & 1u) ? 0u : 1u;
+    even[i] = e; remap[i] = e;          // remap is turned into compact indices by an exclusive scan
+}
+
+// final 128-byte 4-wide traversal nodes (padded boxes of the up-to-4 children in SoA)
+__global__ void k_lbvh_emit4(int n, const int2* __restrict__ children, const unsigned* __restrict__ even, const unsigned* __restrict__ remap,
+                             const float4* __restrict__ leaf_lo, const float4* __restrict__ leaf_hi,
+                             const float4* __restrict__ node_lo, const float4* __restrict__ node_hi, float pad, BvhNode4* __restrict__ out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1 || !even[i]) return;
+    out[remap[i]] = make_wide_node(children, i, remap, leaf_lo, leaf_hi, node_lo, node_hi, nullptr, nullptr, pad);
 }
 #endif  // __CUDACC__

@@ -139,60 +139,159 @@ RT_HD bool tri_shadow(float3 v0, float3 v1, float3 v2, const Ray& r) {
            dot(cross(v0 - v2, p - v2), n) >= 0.0f;
 }
 
-// Ray / two-child-box node test.  Conservative: NaNs from 0*inf drop out of fminf/fmaxf.
-RT_HD void node_slabs(const BvhNode& nd, float3 o, float3 inv, float tmin, float tmax, bool& h0, bool& h1, float& n0, float& n1) {
-    float ax = (nd.q0.x - o.x) * inv.x, bx = (nd.q0.w - o.x) * inv.x;
-    float ay = (nd.q0.y - o.y) * inv.y, by = (nd.q1.x - o.y) * inv.y;
-    float az = (nd.q0.z - o.z) * inv.z, bz = (nd.q1.y - o.z) * inv.z;
-    n0 = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), tmin));
-    float f0 = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), tmax));
-    h0 = n0 <= f0;
-    ax = (nd.q1.z - o.x) * inv.x; bx = (nd.q2.y - o.x) * inv.x;
-    ay = (nd.q1.w - o.y) * inv.y; by = (nd.q2.z - o.y) * inv.y;
-    az = (nd.q2.x - o.z) * inv.z; bz = (nd.q2.w - o.z) * inv.z;
-    n1 = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), tmin));
-    float f1 = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), tmax));
-    h1 = n1 <= f1;
+// ------------------------------------------------------------------------------------------------
+// 4-wide BVH walk shared by the per-mesh LBVH and the object BVH.
+// Slab tests in FMA form t = plane * (1/d) + (-o/d).  A direction component smaller than 2^-60 gets a reciprocal
+// of +-2^60 instead of inf, so the two products stay finite (inf - inf would poison the interval).
+struct RayInv { float3 inv, oinv; };
+RT_HD float safe_rcp(float d) { return fabsf(d) >= 8.673617e-19f ? 1.0f / d : copysignf(1.1529215e18f, d); }
+RT_HD RayInv ray_inv(const Ray& r) {
+    RayInv ri;
+    ri.inv = f3(safe_rcp(r.d.x), safe_rcp(r.d.y), safe_rcp(r.d.z));
+    ri.oinv = f3(-r.o.x * ri.inv.x, -r.o.y * ri.inv.y, -r.o.z * ri.inv.z);
+    return ri;
+}
+RT_HD unsigned as_uint(float f) { return (unsigned)as_int(f); }
+RT_HD int link_of(const int4& l, unsigned slot) { return (slot & 2u) ? ((slot & 1u) ? l.w : l.z) : ((slot & 1u) ? l.y : l.x); }
+RT_HD void key_swap(unsigned& a, unsigned& b) { unsigned lo = a < b ? a : b, hi = a < b ? b : a; a = lo; b = hi; }
+
+#define RT_SLAB4(LINK, LOX, LOY, LOZ, HIX, HIY, HIZ, TMAXK, NEAR, HIT)                                             \
+    {                                                                                                            \
+        const float ax_ = fmaf(LOX, ri.inv.x, ri.oinv.x), bx_ = fmaf(HIX, ri.inv.x, ri.oinv.x);                  \
+        const float ay_ = fmaf(LOY, ri.inv.y, ri.oinv.y), by_ = fmaf(HIY, ri.inv.y, ri.oinv.y);                  \
+        const float az_ = fmaf(LOZ, ri.inv.z, ri.oinv.z), bz_ = fmaf(HIZ, ri.inv.z, ri.oinv.z);                  \
+        NEAR = fmaxf(fmaxf(fminf(ax_, bx_), fminf(ay_, by_)), fmaxf(fminf(az_, bz_), tmin));                    \
+        const float far_ = fminf(fminf(fmaxf(ax_, bx_), fmaxf(ay_, by_)), fminf(fmaxf(az_, bz_), TMAXK));       \
+        HIT = (NEAR <= far_) && (LINK != RT_LINK_NONE);      /* min/max sort the interval ends: an empty slot needs the link test */ \
+    }
+
+// Advances the walk to the next leaf whose box the ray segment [tmin, tmax] touches; returns the leaf id
+// (triangle slot / object index) or -1 when the walk is over.  `cur` = link being processed (RT_LINK_NONE: pop),
+// stack entries [sbase, sp) are this walk's.  ORDERED: children entered nearest first (closest hit);
+// FLAGS: children flagged RT_TLAS_NO_TMAX are tested without the tmax bound (shadow rays).
+template <bool ORDERED, bool FLAGS>
+RT_HD int bvh4_next(TraceCtx& cx, const BvhNode4* __restrict__ nodes, int& cur, int& sp, const int sbase, const RayInv& ri,
+                    const float tmin, const float tmax, unsigned& visits) {
+    int* stk = cx.stack; const int stride = cx.stack_stride;
+    for (;;) {
+        if (cur == RT_LINK_NONE) {
+            if (sp == sbase) return -1;
+            cur = stk[(--sp) * stride];
+        }
+        if (cur < 0) { const int leaf = ~cur; cur = RT_LINK_NONE; return leaf; }
+        const BvhNode4* np = nodes + cur;
+        const float4 lox = ld4(&np->lox), loy = ld4(&np->loy), loz = ld4(&np->loz);
+        const float4 hix = ld4(&np->hix), hiy = ld4(&np->hiy), hiz = ld4(&np->hiz);
+        const int4 link = RT_LDG(&np->link);
+        visits++;
+        float t0 = tmax, t1 = tmax, t2 = tmax, t3 = tmax;
+        if (FLAGS) {
+            const int4 fl = RT_LDG(&np->flags);
+            if (fl.x & RT_TLAS_NO_TMAX) t0 = RT_INF;
+            if (fl.y & RT_TLAS_NO_TMAX) t1 = RT_INF;
+            if (fl.z & RT_TLAS_NO_TMAX) t2 = RT_INF;
+            if (fl.w & RT_TLAS_NO_TMAX) t3 = RT_INF;
+        }
+        float n0, n1, n2, n3; bool h0, h1, h2, h3;
+        RT_SLAB4(link.x, lox.x, loy.x, loz.x, hix.x, hiy.x, hiz.x, t0, n0, h0)
+        RT_SLAB4(link.y, lox.y, loy.y, loz.y, hix.y, hiy.y, hiz.y, t1, n1, h1)
+        RT_SLAB4(link.z, lox.z, loy.z, loz.z, hix.z, hiy.z, hiz.z, t2, n2, h2)
+        RT_SLAB4(link.w, lox.w, loy.w, loz.w, hix.w, hiy.w, hiz.w, t3, n3, h3)
+        if (ORDERED) {
+            // sort (entry distance, slot) keys: entry distances are >= tmin >= 0, so their bit patterns order as integers
+            unsigned k0 = h0 ? ((as_uint(n0) & 0x7ffffffcu) | 0u) : 0xffffffffu;
+            unsigned k1 = h1 ? ((as_uint(n1) & 0x7ffffffcu) | 1u) : 0xffffffffu;
+            unsigned k2 = h2 ? ((as_uint(n2) & 0x7ffffffcu) | 2u) : 0xffffffffu;
+            unsigned k3 = h3 ? ((as_uint(n3) & 0x7ffffffcu) | 3u) : 0xffffffffu;
+            key_swap(k0, k1); key_swap(k2, k3); key_swap(k0, k2); key_swap(k1, k3); key_swap(k1, k2);
+            const int nhit = (int)h0 + (int)h1 + (int)h2 + (int)h3;
+            if (sp + 3 > RT_STACK_DEPTH && nhit > 1) { cx.tally.err |= 1u << RT_ERR_LIMIT; cur = nhit ? link_of(link, k0 & 3u) : RT_LINK_NONE; continue; }
+            if (nhit > 3) stk[(sp++) * stride] = link_of(link, k3 & 3u);
+            if (nhit > 2) stk[(sp++) * stride] = link_of(link, k2 & 3u);
+            if (nhit > 1) stk[(sp++) * stride] = link_of(link, k1 & 3u);
+            cur = nhit ? link_of(link, k0 & 3u) : RT_LINK_NONE;
+        } else {
+            if (sp + 3 > RT_STACK_DEPTH) { cx.tally.err |= 1u << RT_ERR_LIMIT; h1 = h1 && !h0; h2 = h2 && !h0 && !h1; h3 = h3 && !h0 && !h1 && !h2; }
+            cur = RT_LINK_NONE;
+            if (h0) cur = link.x;
+            if (h1) { if (cur == RT_LINK_NONE) cur = link.y; else stk[(sp++) * stride] = link.y; }
+            if (h2) { if (cur == RT_LINK_NONE) cur = link.z; else stk[(sp++) * stride] = link.z; }
+            if (h3) { if (cur == RT_LINK_NONE) cur = link.w; else stk[(sp++) * stride] = link.w; }
+        }
+    }
 }
 
-// LBVH traversal.  `onTri(slot, tmax)` tests triangle `slot`, may shrink tmax, returns true to stop.
-// Replaces the face loops of mesh.py:77 and :125 (brute force kept as mesh_mode 1 for the equivalence test).
-template <class OnTri>
-RT_HD void mesh_visit(TraceCtx& cx, const DevMesh* m, const Ray& r, float tmin, float& tmax, OnTri&& onTri) {
+RT_HD int first_bit(unsigned m) {
+#if defined(__CUDA_ARCH__)
+    return __ffs((int)m) - 1;
+#else
+    return __builtin_ffs((int)m) - 1;
+#endif
+}
+RT_HD float sel4(float a, float b, float c, float d, int k) { return (k & 2) ? ((k & 1) ? d : c) : ((k & 1) ? b : a); }
+
+// LBVH traversal of one mesh.  `onTri(slot, tmax)` tests triangle `slot`, may shrink tmax, returns true to stop.
+// Replaces the face loops of mesh.py:77 and :125 (brute force kept as a mesh_mode bit for the equivalence test).
+// ONE loop level: every iteration is a node step (four slab tests) followed by the triangle tests of that node's leaf
+// children, so the lanes of a warp advance node by node in lock-step; an iterator that returns to the caller at every
+// leaf makes each lane wait for the slowest lane's walk to ITS next leaf (measured: 12 of 32 lanes active).
+template <bool ORDERED, class OnTri>
+RT_HD void mesh_visit(TraceCtx& cx, const DevMesh* m, const RayInv& ri, float tmin, float& tmax, OnTri&& onTri) {
     const int n = m->n_tris;
     if (n <= 0) return;
     if ((cx.S.mesh_mode & RT_MODE_BRUTE_MESH) || n == 1) {
         for (int s = 0; s < n; s++) { cx.tally.tris++; if (onTri(s, tmax)) return; }
         return;
     }
-    const BvhNode* nodes = m->nodes;
-    float3 inv = f3(1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z);
+    const BvhNode4* __restrict__ nodes = m->nodes;
     int* stk = cx.stack; const int stride = cx.stack_stride;
     const int sbase = cx.sbase;
-    int sp = sbase, node = 0;
+    int cur = 0, sp = sbase;
     for (;;) {
-        BvhNode nd;
-        nd.q0 = ld4(&nodes[node].q0); nd.q1 = ld4(&nodes[node].q1);
-        nd.q2 = ld4(&nodes[node].q2); nd.q3 = ld4(&nodes[node].q3);
-        cx.tally.nodes++;
-        bool h0, h1; float n0, n1;
-        node_slabs(nd, r.o, inv, tmin, tmax, h0, h1, n0, n1);
-        int c0 = as_int(nd.q3.x), c1 = as_int(nd.q3.y);
-        if (h0 && c0 < 0) { cx.tally.tris++; if (onTri(~c0, tmax)) return; h0 = false; }
-        if (h1 && c1 < 0) { if (n1 <= tmax) { cx.tally.tris++; if (onTri(~c1, tmax)) return; } h1 = false; }
-        if (h0 && n0 > tmax) h0 = false;
-        if (h1 && n1 > tmax) h1 = false;
-        if (h0 && h1) {
-            int nearc = c0, farc = c1;
-            if (n1 < n0) { nearc = c1; farc = c0; }
-            if (sp < RT_STACK_DEPTH) stk[(sp++) * stride] = farc;
-            else cx.tally.err |= 1u << RT_ERR_LIMIT;
-            node = nearc;
-        } else if (h0) node = c0;
-        else if (h1) node = c1;
-        else {
+        if (cur == RT_LINK_NONE) {
             if (sp == sbase) return;
-            node = stk[(--sp) * stride];
+            cur = stk[(--sp) * stride];
+        }
+        const BvhNode4* np = nodes + cur;
+        const float4 lox = ld4(&np->lox), loy = ld4(&np->loy), loz = ld4(&np->loz);
+        const float4 hix = ld4(&np->hix), hiy = ld4(&np->hiy), hiz = ld4(&np->hiz);
+        const int4 link = RT_LDG(&np->link);
+        cx.tally.nodes++;
+        float n0, n1, n2, n3; bool h0, h1, h2, h3;
+        RT_SLAB4(link.x, lox.x, loy.x, loz.x, hix.x, hiy.x, hiz.x, tmax, n0, h0)
+        RT_SLAB4(link.y, lox.y, loy.y, loz.y, hix.y, hiy.y, hiz.y, tmax, n1, h1)
+        RT_SLAB4(link.z, lox.z, loy.z, loz.z, hix.z, hiy.z, hiz.z, tmax, n2, h2)
+        RT_SLAB4(link.w, lox.w, loy.w, loz.w, hix.w, hiy.w, hiz.w, tmax, n3, h3)
+        // leaf children: their triangles are tested here and now
+        unsigned lm = (h0 && link.x < 0 ? 1u : 0u) | (h1 && link.y < 0 ? 2u : 0u) | (h2 && link.z < 0 ? 4u : 0u) | (h3 && link.w < 0 ? 8u : 0u);
+        h0 = h0 && link.x >= 0; h1 = h1 && link.y >= 0; h2 = h2 && link.z >= 0; h3 = h3 && link.w >= 0;
+        while (lm) {
+            const int k = first_bit(lm);
+            lm &= lm - 1u;
+            if (ORDERED && sel4(n0, n1, n2, n3, k) > tmax) continue;        // an earlier leaf of this node already came closer
+            cx.tally.tris++;
+            if (onTri(~link_of(link, (unsigned)k), tmax)) return;
+        }
+        if (ORDERED) {
+            h0 = h0 && n0 <= tmax; h1 = h1 && n1 <= tmax; h2 = h2 && n2 <= tmax; h3 = h3 && n3 <= tmax;
+            unsigned k0 = h0 ? ((as_uint(n0) & 0x7ffffffcu) | 0u) : 0xffffffffu;
+            unsigned k1 = h1 ? ((as_uint(n1) & 0x7ffffffcu) | 1u) : 0xffffffffu;
+            unsigned k2 = h2 ? ((as_uint(n2) & 0x7ffffffcu) | 2u) : 0xffffffffu;
+            unsigned k3 = h3 ? ((as_uint(n3) & 0x7ffffffcu) | 3u) : 0xffffffffu;
+            key_swap(k0, k1); key_swap(k2, k3); key_swap(k0, k2); key_swap(k1, k3); key_swap(k1, k2);
+            const int nhit = (int)h0 + (int)h1 + (int)h2 + (int)h3;
+            if (sp + 3 > RT_STACK_DEPTH && nhit > 1) { cx.tally.err |= 1u << RT_ERR_LIMIT; cur = link_of(link, k0 & 3u); continue; }
+            if (nhit > 3) stk[(sp++) * stride] = link_of(link, k3 & 3u);
+            if (nhit > 2) stk[(sp++) * stride] = link_of(link, k2 & 3u);
+            if (nhit > 1) stk[(sp++) * stride] = link_of(link, k1 & 3u);
+            cur = nhit ? link_of(link, k0 & 3u) : RT_LINK_NONE;
+        } else {
+            if (sp + 3 > RT_STACK_DEPTH) { cx.tally.err |= 1u << RT_ERR_LIMIT; h1 = h1 && !h0; h2 = h2 && !h0 && !h1; h3 = h3 && !h0 && !h1 && !h2; }
+            cur = RT_LINK_NONE;
+            if (h0) cur = link.x;
+            if (h1) { if (cur == RT_LINK_NONE) cur = link.y; else stk[(sp++) * stride] = link.y; }
+            if (h2) { if (cur == RT_LINK_NONE) cur = link.z; else stk[(sp++) * stride] = link.z; }
+            if (h3) { if (cur == RT_LINK_NONE) cur = link.w; else stk[(sp++) * stride] = link.w; }
         }
     }
 }
@@ -203,56 +302,18 @@ RT_HD void mesh_visit(TraceCtx& cx, const DevMesh* m, const Ray& r, float tmin, 
 // order), then the leaves of the object BVH whose (padded, motion-swept) boxes the ray segment [0, tmax]
 // touches, nearer child first.  The order differs from the reference's list order, so the closest-hit
 // consumer breaks equal-t ties by object index itself; the any-hit consumer is order-free.
-#define RT_TOP_NONE 0x7fffffff
 struct TopIter { int lin_i; int cur; int sp; };
 RT_HD TopIter top_begin() { TopIter it; it.lin_i = 0; it.cur = 0; it.sp = 0; return it; }
 
-// IGNORE_TMAX_FLAGGED: shadow rays -- subtrees holding a mesh / CSG node are walked without the t_max bound
-// because their shadow tests ignore it
+// SHADOW: subtrees holding a mesh / CSG node are walked without the t_max bound because their shadow tests
+// ignore it
 template <bool SHADOW>
-RT_HD int top_next(TraceCtx& cx, TopIter& it, const Ray& r, float3 inv, float tmax) {
+RT_HD int top_next(TraceCtx& cx, TopIter& it, const RayInv& ri, float tmax) {
     const SceneView& S = cx.S;
-    if (S.tlas_nodes == nullptr || (S.mesh_mode & RT_MODE_LINEAR_TOP)) return it.lin_i < S.n_top ? it.lin_i++ : -1;
+    if (S.mesh_mode & RT_MODE_LINEAR_TOP) return it.lin_i < S.n_top ? it.lin_i++ : -1;     // test aid: the reference's own loop (meshes skipped by the callers)
     if (it.lin_i < S.n_lin) return RT_LDG(S.lin_objs + it.lin_i++);
-    int* stk = cx.stack; const int stride = cx.stack_stride;
-    int cur = it.cur;
-    for (;;) {
-        if (cur == RT_TOP_NONE) {
-            if (it.sp == 0) { it.cur = RT_TOP_NONE; return -1; }
-            cur = stk[(--it.sp) * stride];
-        }
-        if (cur < 0) { it.cur = RT_TOP_NONE; return ~cur; }
-        const BvhNode* np = S.tlas_nodes + cur;
-        BvhNode nd;
-        nd.q0 = ld4(&np->q0); nd.q1 = ld4(&np->q1); nd.q2 = ld4(&np->q2); nd.q3 = ld4(&np->q3);
-        cx.tally.nodes++;
-        float t0 = tmax, t1 = tmax;
-        if (SHADOW) {
-            if (as_int(nd.q3.z) & RT_TLAS_NO_TMAX) t0 = RT_INF;
-            if (as_int(nd.q3.w) & RT_TLAS_NO_TMAX) t1 = RT_INF;
-        }
-        float ax = (nd.q0.x - r.o.x) * inv.x, bx = (nd.q0.w - r.o.x) * inv.x;
-        float ay = (nd.q0.y - r.o.y) * inv.y, by = (nd.q1.x - r.o.y) * inv.y;
-        float az = (nd.q0.z - r.o.z) * inv.z, bz = (nd.q1.y - r.o.z) * inv.z;
-        const float n0 = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
-        const float f0 = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t0));
-        ax = (nd.q1.z - r.o.x) * inv.x; bx = (nd.q2.y - r.o.x) * inv.x;
-        ay = (nd.q1.w - r.o.y) * inv.y; by = (nd.q2.z - r.o.y) * inv.y;
-        az = (nd.q2.x - r.o.z) * inv.z; bz = (nd.q2.w - r.o.z) * inv.z;
-        const float n1 = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
-        const float f1 = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t1));
-        const bool h0 = n0 <= f0, h1 = n1 <= f1;
-        const int c0 = as_int(nd.q3.x), c1 = as_int(nd.q3.y);
-        if (h0 && h1) {
-            int nearc = c0, farc = c1;
-            if (n1 < n0) { nearc = c1; farc = c0; }
-            if (it.sp < RT_STACK_DEPTH) stk[(it.sp++) * stride] = farc;
-            else cx.tally.err |= 1u << RT_ERR_LIMIT;
-            cur = nearc;
-        } else if (h0) cur = c0;
-        else if (h1) cur = c1;
-        else cur = RT_TOP_NONE;
-    }
+    if (S.tlas_nodes == nullptr) return -1;
+    return bvh4_next<!SHADOW, SHADOW>(cx, S.tlas_nodes, it.cur, it.sp, 0, ri, 0.0f, tmax, cx.tally.prims);
 }
 
 RT_HD void tri_load(const DevMesh* m, int slot, float3& v0, float3& v1, float3& v2, int& face) {
@@ -278,11 +339,11 @@ RT_HD float3 tri_normal(TraceCtx& cx, const DevMesh* m, int slot, float3 p) {
 }
 
 // Mesh.shadow_intersect (mesh.py:121-153): gate, then any accepted face; t_max is ignored by the reference
-RT_HD bool mesh_shadow(TraceCtx& cx, const DevMesh* m, const Ray& r) {
+RT_HD bool mesh_shadow(TraceCtx& cx, const DevMesh* m, const Ray& r, const RayInv& ri) {
     if (!mesh_gate(m, r)) return false;
     bool occ = false;
     float tmax = RT_INF;
-    mesh_visit(cx, m, r, RT_SHADOW_EPS * 0.5f, tmax, [&](int slot, float&) {
+    mesh_visit<false>(cx, m, ri, RT_SHADOW_EPS * 0.5f, tmax, [&](int slot, float&) {
         float3 v0, v1, v2; int face;
         tri_load(m, slot, v0, v1, v2, face);
         if (tri_shadow(v0, v1, v2, r)) { occ = true; return true; }
@@ -290,7 +351,30 @@ RT_HD bool mesh_shadow(TraceCtx& cx, const DevMesh* m, const Ray& r) {
     });
     return occ;
 }
+// out-of-line copy for meshes under CSG nodes: keeps that traversal code out of the hot instruction stream
+RT_HD_NOINLINE bool mesh_shadow_cold(TraceCtx& cx, const DevMesh* m, const Ray& r) { return mesh_shadow(cx, m, r, ray_inv(r)); }
 
+// Closest accepted face of one top-level mesh against the running best (mesh.py:72-119 + scene.py:94).
+// better(t): would a hit at t replace the current best of OTHER objects; among this mesh's own faces an equal t
+// goes to the lower face index (list order).
+template <class Better>
+RT_HD void mesh_closest(TraceCtx& cx, const DevMesh* m, const Ray& r, const RayInv& ri, float best, Better&& better, float& t_out, int& slot_out) {
+    slot_out = -1; t_out = best;
+    if (!mesh_gate(m, r)) return;
+    float tmax = best;
+    int best_face = 0x7fffffff, best_slot = -1;
+    mesh_visit<true>(cx, m, ri, 0.0f, tmax, [&](int slot, float& tm) {
+        float3 v0, v1, v2; int face; float t;
+        tri_load(m, slot, v0, v1, v2, face);
+        if (tri_hit(v0, v1, v2, r, t)) {
+            if ((best_slot < 0 && better(t)) || (best_slot >= 0 && (t < tm || (t == tm && face < best_face)))) {
+                tm = t; best_face = face; best_slot = slot;
+            }
+        }
+        return false;
+    });
+    slot_out = best_slot; t_out = tmax;
+}
 // ------------------------------------------------------------------------------------------------
 // Texture / diffuse lookups (scene.py:143-146)
 RT_HD float3 texel(const DevTexture* t, long long i, long long j) {
@@ -347,6 +431,7 @@ RT_HD float3 box_diffuse(const SceneView& S, const DevObject* o, float3 p, float
 // RT_MAX_NEST levels (template depth), no device call stack.
 
 // shadow_intersect of a leaf primitive (simple_geometry.py:48-72,122-131,251-294; mesh.py:121-153)
+template <bool WITH_MESH>
 RT_HD bool leaf_shadow(TraceCtx& cx, int oi, const Ray& r, float tmax) {
     const DevObject* o = cx.S.objects + oi;
     cx.tally.prims++;
@@ -368,7 +453,7 @@ RT_HD bool leaf_shadow(TraceCtx& cx, int oi, const Ray& r, float tmax) {
         if (en > ex) return false;
         return RT_SHADOW_EPS < en && en < tmax;
     }
-    case RT_KIND_MESH: return mesh_shadow(cx, cx.S.meshes + o->mesh, r);
+    case RT_KIND_MESH: return WITH_MESH ? mesh_shadow_cold(cx, cx.S.meshes + o->mesh, r) : false;   // top-level meshes: see occluded()
             default: return false;
     }
 }
@@ -422,7 +507,7 @@ template <int D> struct Nest {
     // shadow_intersect (hierarchy.py:80-109 and the leaf versions)
     static RT_HD_NOINLINE bool shadow(TraceCtx& cx, int oi, const Ray& r, float tmax) {
         const DevObject* o = cx.S.objects + oi;
-        if (o->kind != RT_KIND_NODE) return leaf_shadow(cx, oi, r, tmax);
+        if (o->kind != RT_KIND_NODE) return leaf_shadow<true>(cx, oi, r, tmax);
         cx.tally.prims++;
         switch (o->kind) {
             case RT_KIND_NODE: {
@@ -503,7 +588,8 @@ RT_HD void leaf_hits(TraceCtx& cx, int oi, const Ray& r, Want&& want, Cand&& can
             if (!mesh_gate(m, r)) return;
             float tmax = RT_INF;
             const int mat = o->n_mats > 0 ? o->mat0 : -2;
-            mesh_visit(cx, m, r, 0.0f, tmax, [&](int slot, float&) {
+            const RayInv ri = ray_inv(r);
+            mesh_visit<true>(cx, m, ri, 0.0f, tmax, [&](int slot, float&) {
                 float3 v0, v1, v2; int face; float t;
                 tri_load(m, slot, v0, v1, v2, face);
                 if (tri_hit(v0, v1, v2, r, t) && want(t)) {
@@ -608,10 +694,10 @@ RT_HD bool closest_hit(TraceCtx& cx, const Ray& r, Hit& out) {
     int best_obj = 0x7fffffff, best_aux = 0;
     Hit node_hit; node_hit.t = RT_INF; node_hit.mat = -1; node_hit.geom = -1; node_hit.n = f3(0, 0, 0); node_hit.p = f3(0, 0, 0);
     const float A = dot(r.d, r.d);
-    const float3 inv = f3(1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z);
+    const RayInv ri = ray_inv(r);
     TopIter it = top_begin();
     for (;;) {
-        const int oi = top_next<false>(cx, it, r, inv, best);
+        const int oi = top_next<false>(cx, it, ri, best);
         if (oi < 0) break;
         cx.sbase = it.sp;
         const DevObject* o = S.objects + oi;
@@ -635,33 +721,23 @@ RT_HD bool closest_hit(TraceCtx& cx, const Ray& r, Hit& out) {
             float en, ex; int label;
             if (box_slabs(moved(o, f3(ld4(&o->a)), cx.time), moved(o, f3(ld4(&o->b)), cx.time), r, en, ex, label) &&
                 !(en > ex || en < 0.0f) && RT_BETTER(en)) { best = en; best_obj = oi; best_aux = label; }
-        } else if (kind == RT_KIND_MESH) {
-            cx.tally.prims++;
-            const DevMesh* m = S.meshes + o->mesh;
-            if (mesh_gate(m, r)) {
-                // against other objects: RT_BETTER; among this mesh's own faces an equal t goes to the lower face index (list order)
-                float tmax = best;
-                int best_face = 0x7fffffff, best_slot = -1;
-                mesh_visit(cx, m, r, 0.0f, tmax, [&](int slot, float& tm) {
-                    float3 v0, v1, v2; int face; float t;
-                    tri_load(m, slot, v0, v1, v2, face);
-                    if (tri_hit(v0, v1, v2, r, t)) {
-                        if ((best_slot < 0 && RT_BETTER(t)) || (best_slot >= 0 && (t < tm || (t == tm && face < best_face)))) {
-                            tm = t; best_face = face; best_slot = slot;
-                        }
-                    }
-                    return false;
-                });
-                if (best_slot >= 0) { best = tmax; best_obj = oi; best_aux = best_slot; }
-            }
         } else if (HAS_NODES && kind == RT_KIND_NODE) {
             // inside one node the first hit in DFS (= list) order wins equal t: strict '<' once this node holds the best
             object_hits(cx, oi, r, [&](float t) { return RT_BETTER(t); },
                         [&](const Hit& h) { if (RT_BETTER(h.t)) { best = h.t; best_obj = oi; node_hit = h; } });
         }
-        #undef RT_BETTER
     }
     cx.sbase = 0;
+    for (int k = 0; k < S.n_sep_mesh; k++) {                          // top-level meshes: all lanes of the warp enter the LBVH together
+        {
+            const int oi = RT_LDG(S.sep_mesh + k);
+            cx.tally.prims++;
+            float t; int slot;
+            mesh_closest(cx, S.meshes + S.objects[oi].mesh, r, ri, best, [&](float tt) { return RT_BETTER(tt); }, t, slot);
+            if (slot >= 0) { best = t; best_obj = oi; best_aux = slot; }
+        }
+    }
+    #undef RT_BETTER
     if (best_obj == 0x7fffffff) return false;
     const DevObject* o = S.objects + best_obj;
     if (HAS_NODES && o->kind == RT_KIND_NODE) { out = node_hit; return true; }
@@ -682,11 +758,11 @@ template <bool HAS_NODES>
 RT_HD bool occluded(TraceCtx& cx, const Ray& r, float tmax) {
     const SceneView& S = cx.S;
     const float A = dot(r.d, r.d);
-    const float3 inv = f3(1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z);
+    const RayInv ri = ray_inv(r);
     TopIter it = top_begin();
     bool occ = false;
     for (;;) {
-        const int oi = top_next<true>(cx, it, r, inv, tmax);
+        const int oi = top_next<true>(cx, it, ri, tmax);
         if (oi < 0) break;
         cx.sbase = it.sp;
         const DevObject* o = S.objects + oi;
@@ -697,20 +773,37 @@ RT_HD bool occluded(TraceCtx& cx, const Ray& r, float tmax) {
             float t1, t2;
             if (sphere_roots(moved(o, f3(a), cx.time), a.w, r, A, t1, t2) &&
                 ((RT_SHADOW_EPS_SPHERE < t1 && t1 < tmax) || (RT_SHADOW_EPS_SPHERE < t2 && t2 < tmax))) { occ = true; break; }
+        } else if (kind == RT_KIND_MESH) {                            // (linear test mode only) traversed after the walk, below
         } else if (kind != RT_KIND_NODE) {
-            if (leaf_shadow(cx, oi, r, tmax)) { occ = true; break; }
+            if (leaf_shadow<false>(cx, oi, r, tmax)) { occ = true; break; }
         } else if (HAS_NODES) {
             if (Nest<RT_MAX_NEST>::shadow(cx, oi, r, tmax)) { occ = true; break; }
         }
     }
     cx.sbase = 0;
+    for (int k = 0; k < S.n_sep_mesh && !occ; k++) {
+        cx.tally.prims++;
+        occ = mesh_shadow(cx, S.meshes + S.objects[RT_LDG(S.sep_mesh + k)].mesh, r, ri);
+    }
     return occ;
 }
 
 // ------------------------------------------------------------------------------------------------
-// _compute_regular_lighting (scene.py:140-187): Blinn-Phong + shadow rays + ambient
+// Shadow ray of light `li` from hit point p (scene.py:148-167): un-offset origin, un-normalised direction (Q12)
 template <bool HAS_NODES>
-RT_HD float3 shade_local(TraceCtx& cx, const Ray& ray, const Hit& hit) {
+RT_HD bool light_occluded(TraceCtx& cx, float3 p, int li) {
+    const float4 lv = ld4(&cx.S.lights[li].vector);
+    const bool point = as_int(lv.w) == RT_LIGHT_POINT;
+    Ray sr; sr.o = p;
+    sr.d = point ? f3(lv) - p : -f3(lv);
+    cx.tally.shadow++;
+    return occluded<HAS_NODES>(cx, sr, point ? 1.0f : RT_INF);
+}
+
+// _compute_regular_lighting (scene.py:140-187): Blinn-Phong + ambient; lit(li) says whether light li reaches the
+// hit point (the shadow-ray results: traced in place by trace_level, read back from k_shadow's flags by k_shade)
+template <class Lit>
+RT_HD float3 shade_local(TraceCtx& cx, const Ray& ray, const Hit& hit, Lit&& lit) {
     const SceneView& S = cx.S;
     const DevMaterial* mat = S.materials + hit.mat;
     float4 md = ld4(&mat->diffuse), ms = ld4(&mat->specular);
@@ -722,14 +815,11 @@ RT_HD float3 shade_local(TraceCtx& cx, const Ray& ray, const Hit& hit) {
     cx.tally.shaded++;
     float3 colour = f3(0, 0, 0);
     for (int li = 0; li < S.n_lights; li++) {
+        if (!lit(li)) continue;
         const DevLight* L = S.lights + li;
         float4 lv = ld4(&L->vector);
         const bool point = as_int(lv.w) == RT_LIGHT_POINT;
-        Ray sr; sr.o = hit.p;                                          // un-offset origin, un-normalised direction (Q12)
-        sr.d = point ? f3(lv) - hit.p : -f3(lv);
-        cx.tally.shadow++;
-        if (occluded<HAS_NODES>(cx, sr, point ? 1.0f : RT_INF)) continue;
-        float3 light_dir = point ? normalize(sr.d) : f3(ld4(&L->dir_norm));
+        float3 light_dir = point ? normalize(f3(lv) - hit.p) : f3(ld4(&L->dir_norm));
         float3 lambert = diffuse * fmaxf(0.0f, dot(hit.n, light_dir));
         float3 half_vect = normalize(light_dir - ray.d);
         float3 specular = f3(ms) * powf(fmaxf(0.0f, dot(hit.n, half_vect)), md.w);   // 0**0 == 1 both sides
@@ -758,40 +848,48 @@ RT_HD PathFold fold_compose(const PathFold& f, float3 A, float W) {
 // `next` (reflection / refraction ray); otherwise `sample` holds the finished sample value.
 struct PathState { Ray ray; PathFold fold; int depth_left; int in_shape; };
 
+// Everything of cast_ray after the closest hit is known (scene.py:96-116): material branch, local lighting, fold,
+// next ray.  `hit` may get its normal flipped (Q19).
+template <class Lit>
+RT_HD bool shade_level(TraceCtx& cx, PathState& ps, Hit& hit, Lit&& lit, float3& sample) {
+    if (hit.mat < 0) { cx.tally.err |= 1u << RT_ERR_NO_MATERIAL; sample = fold_eval(ps.fold, f3(0, 0, 0)); return false; }
+    const DevMaterial* mat = cx.S.materials + hit.mat;
+    const int type = mat->type;
+    // secondary ray first (scene.py:99-101,191-206), then ONE local-lighting evaluation shared by the three material branches
+    float3 rd = f3(0, 0, 0), ro = f3(0, 0, 0);
+    bool dead = false;                                                 // total internal reflection
+    if (type == RT_MAT_MIRROR) {                                       // scene.py:97-104
+        rd = reflect3(ps.ray.d, hit.n);
+        ro = hit.p + rd * 0.01f;
+    } else if (type == RT_MAT_REFRACTIVE) {                            // scene.py:105-108,189-209
+        float eta;
+        if (ps.in_shape) { eta = mat->refr_index; hit.n = -hit.n; }    // normal flipped BEFORE local lighting (Q19)
+        else eta = mat->inv_refr;
+        rd = refract3(ps.ray.d, hit.n, eta, dead);
+        if (!dead && rd.x == 0.0f && rd.y == 0.0f && rd.z == 0.0f) dead = true;   // `refract_dir == vec3(0)`
+        ro = hit.p + rd * 0.0001f;
+    }
+    const float3 local = shade_local(cx, ps.ray, hit, lit);
+    if (type != RT_MAT_MIRROR && type != RT_MAT_REFRACTIVE) {          // scene.py:109-116
+        sample = fold_eval(ps.fold, clamp01(local));
+        return false;
+    }
+    ps.fold = fold_compose(ps.fold, local * ld4(&mat->specular).w, mat->one_minus_tint);
+    if (dead || ps.depth_left - 1 <= 0) { sample = fold_eval(ps.fold, f3(0, 0, 0)); return false; }
+    if (type == RT_MAT_MIRROR) { cx.tally.reflect++; ps.in_shape = 0; }
+    else { cx.tally.refract++; ps.in_shape = !ps.in_shape; }
+    ps.ray.o = ro; ps.ray.d = rd; ps.depth_left -= 1;
+    return true;
+}
+
+// One whole level in one thread (unit-test kernels and tests/hostsim; the render kernels run the three stages as
+// separate launches: k_hit, k_shadow, k_shade)
 template <bool HAS_NODES>
 RT_HD bool trace_level(TraceCtx& cx, PathState& ps, float3& sample) {
     Hit hit;
     if (ps.depth_left <= 0 || !closest_hit<HAS_NODES>(cx, ps.ray, hit)) { sample = fold_eval(ps.fold, f3(0, 0, 0)); return false; }
-    if (hit.mat < 0) { cx.tally.err |= 1u << RT_ERR_NO_MATERIAL; sample = fold_eval(ps.fold, f3(0, 0, 0)); return false; }
-    const DevMaterial* mat = cx.S.materials + hit.mat;
-    const int type = mat->type;
-    if (type == RT_MAT_MIRROR) {                                       // scene.py:97-104
-        float3 rd = reflect3(ps.ray.d, hit.n);
-        float3 ro = hit.p + rd * 0.01f;
-        float3 local = shade_local<HAS_NODES>(cx, ps.ray, hit);
-        ps.fold = fold_compose(ps.fold, local * ld4(&mat->specular).w, mat->one_minus_tint);
-        if (ps.depth_left - 1 <= 0) { sample = fold_eval(ps.fold, f3(0, 0, 0)); return false; }
-        cx.tally.reflect++;
-        ps.ray.o = ro; ps.ray.d = rd; ps.depth_left -= 1; ps.in_shape = 0;
-        return true;
-    }
-    if (type == RT_MAT_REFRACTIVE) {                                   // scene.py:105-108,189-209
-        float eta;
-        if (ps.in_shape) { eta = mat->refr_index; hit.n = -hit.n; }    // normal flipped BEFORE local lighting (Q19)
-        else eta = mat->inv_refr;
-        bool tir;
-        float3 rd = refract3(ps.ray.d, hit.n, eta, tir);
-        if (!tir && rd.x == 0.0f && rd.y == 0.0f && rd.z == 0.0f) tir = true;   // `refract_dir == vec3(0)`
-        float3 ro = hit.p + rd * 0.0001f;
-        float3 local = shade_local<HAS_NODES>(cx, ps.ray, hit);
-        ps.fold = fold_compose(ps.fold, local * ld4(&mat->specular).w, mat->one_minus_tint);
-        if (tir || ps.depth_left - 1 <= 0) { sample = fold_eval(ps.fold, f3(0, 0, 0)); return false; }
-        cx.tally.refract++;
-        ps.ray.o = ro; ps.ray.d = rd; ps.depth_left -= 1; ps.in_shape = !ps.in_shape;
-        return true;
-    }
-    sample = fold_eval(ps.fold, clamp01(shade_local<HAS_NODES>(cx, ps.ray, hit)));   // scene.py:109-116
-    return false;
+    const float3 p = hit.p;
+    return shade_level(cx, ps, hit, [&](int li) { return !light_occluded<HAS_NODES>(cx, p, li); }, sample);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -1,16 +1,30 @@
 // rt_kernels.cuh - the wavefront kernels of the render path (one thread per (pixel, sample) ray).
 //
-//   k_primary   : raygen + closest hit + shading (inline shadow rays) for every primary ray of a batch;
-//                 finished samples go to the sample buffer, reflection/refraction rays are compacted
-//                 (warp ballot + prefix popcount + one atomic per warp) into the next ray queue
-//   k_secondary : one recursion level of cast_ray for a compacted queue (replaces scene.py:102,203,208)
-//   k_resolve   : per-pixel sum in the reference's loop order and division (scene.py:69,73)
-//   k_assemble  : scatter gathered tile buffers into the reference layout (glue.py:19-22)
-//   k_finalize  : rot90 + *255 truncation (main.py:31-33)
+// One cast_ray level (scene.py:81-116) = three launches over the same rays, each a SMALL kernel whose code stays
+// in the SM's instruction caches (a single fused kernel measured 94 % of the GPC instruction-fetch bandwidth and
+// a third of its issue slots stalled on "no instruction"):
+//   k_hit     : raygen (level 0) or queue load, closest hit over the scene -> hit record planes
+//   k_shadow  : one thread per (light, ray): any-hit shadow ray -> one occlusion byte
+//   k_shade   : Blinn-Phong with those flags, per-level clamp fold; finished samples go to the sample buffer,
+//               reflection/refraction rays are compacted (warp ballot + prefix popcount + one atomic per warp)
+//               into the next level's ray queue (replaces the recursion of scene.py:102,203,208)
+//   k_resolve : per-pixel sum in the reference's loop order and division (scene.py:69,73)
+//   k_assemble: scatter gathered tile buffers into the reference layout (glue.py:19-22)
+//   k_finalize: rot90 + *255 truncation (main.py:31-33)
 #pragma once
 #include "rt_core.cuh"
 
 #define RT_BLOCK 128
+// resident blocks per SM each kernel's register allocation is held to (tuned on B200)
+#ifndef RT_MIN_BLOCKS_HIT
+#define RT_MIN_BLOCKS_HIT 1
+#endif
+#ifndef RT_MIN_BLOCKS_SHADOW
+#define RT_MIN_BLOCKS_SHADOW 1
+#endif
+#ifndef RT_MIN_BLOCKS_SHADE
+#define RT_MIN_BLOCKS_SHADE 1
+#endif
 
 // Compacted ray queue, SoA of float4 planes (coalesced 128-bit accesses):
 //   plane 0: origin.xyz, time           plane 1: dir.xyz, bits(sample slot)
@@ -83,63 +97,105 @@ __device__ __forceinline__ void tally_flush(const Tally& t, unsigned long long p
 
 __device__ __forceinline__ Tally tally_zero() { Tally t; t.shadow = t.reflect = t.refract = t.nodes = t.tris = t.prims = t.shaded = t.smooth = t.err = 0; return t; }
 
-extern __shared__ int rt_smem_stack[];   // RT_STACK_DEPTH * blockDim.x ints when the scene has a mesh
+extern __shared__ int rt_smem_stack[];   // RT_STACK_DEPTH * blockDim.x ints when the scene has a mesh or an object BVH
 
-// ---- primary rays ---------------------------------------------------------------------------------
-// ray i of the batch: pixel = pixel_begin + i / N, slot = i % N = (d*S + s)*T + t  (loop order of scene.py:57-67)
-template <bool HAS_NODES>
-__global__ void __launch_bounds__(RT_BLOCK) k_primary(SceneView S, PixelMap pm, long long pixel_begin, long long n_rays,
-                                                       float4* __restrict__ samples, RayQueue qout, unsigned long long* qcount,
-                                                       RtCounters* counters) {
+// Hit records of one level, SoA float4 planes of `cap` entries, indexed like the level's rays:
+//   plane 0: hit position xyz, w = ray time (NaN: the ray hit nothing / ended)
+//   plane 1: shading normal xyz, w = bits(material index)
+//   plane 2: ray direction xyz, w = bits(leaf object index)
+struct HitPlanes { float4* planes; long long cap; };
+#define RT_HIT_PLANES 3
+
+// ---- stage 1: closest hit ------------------------------------------------------------------------------
+// PRIMARY: ray i of the batch is generated here: pixel = pixel_begin + i / N, slot = i % N = (d*S + s)*T + t (loop
+// order of scene.py:57-67).  Otherwise ray i is entry i of the compacted queue `qin` (count on the device).
+template <bool HAS_NODES, bool PRIMARY>
+__global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS_HIT) k_hit(SceneView S, PixelMap pm, long long pixel_begin, long long n_rays,
+                                                                     RayQueue qin, const unsigned long long* qin_count,
+                                                                     HitPlanes H, RtCounters* counters) {
     Tally tally = tally_zero();
-    unsigned long long n_primary = 0, n_queued = 0;
+    unsigned long long n_primary = 0;
     const int N = S.D * S.S * S.T;
+    const long long n = PRIMARY ? n_rays : (long long)*qin_count;
     const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long base = (long long)blockIdx.x * blockDim.x; base < n_rays; base += stride) {
-        const long long i = base + threadIdx.x;
-        bool cont = false;
-        PathState ps; float time = 0.0f;
-        if (i < n_rays) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        Ray ray; float time; bool live = true;
+        if (PRIMARY) {
             const long long lp = pixel_begin + i / N;
             const int slot = (int)(i % N);
             int col, row;
-            float3 sample = f3(0, 0, 0);
-            if (pixel_of(pm, lp, col, row)) {
-                const int t = slot % S.T, ds = slot / S.T;
-                const int s = ds % S.S, d = ds / S.S;
-                ps.ray = generate_ray(S, col, row, d, s);
-                ps.fold = fold_identity(); ps.depth_left = S.max_depth; ps.in_shape = 0;
-                time = RT_LDG(S.times + t);
-                TraceCtx cx{S, time, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x};
-                n_primary++;
-                cont = trace_level<HAS_NODES>(cx, ps, sample);
-            }
-            if (!cont) samples[i] = f4(sample.x, sample.y, sample.z, 0.0f);
+            live = pixel_of(pm, lp, col, row) && S.max_depth > 0;
+            const int t = slot % S.T, ds = slot / S.T;
+            const int s = ds % S.S, d = ds / S.S;
+            if (live) { ray = generate_ray(S, col, row, d, s); n_primary++; }
+            time = RT_LDG(S.times + t);
+        } else {
+            const float4 p0 = qin.planes[0 * qin.cap + i], p1 = qin.planes[1 * qin.cap + i];
+            ray.o = f3(p0); ray.d = f3(p1); time = p0.w;
         }
-        long long qi = queue_reserve(qcount, cont);
-        if (cont) { queue_store(qout, qi, ps, time, (unsigned)i); n_queued++; }
+        Hit hit;
+        if (live) {
+            TraceCtx cx{S, time, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x};
+            live = closest_hit<HAS_NODES>(cx, ray, hit);
+        }
+        if (live) {
+            H.planes[0 * H.cap + i] = f4(hit.p.x, hit.p.y, hit.p.z, time);
+            H.planes[1 * H.cap + i] = f4(hit.n.x, hit.n.y, hit.n.z, as_float(hit.mat));
+            H.planes[2 * H.cap + i] = f4(ray.d.x, ray.d.y, ray.d.z, as_float(hit.geom));
+        } else {
+            H.planes[0 * H.cap + i] = f4(0.0f, 0.0f, 0.0f, as_float(0x7fc00000));
+        }
     }
-    tally_flush(tally, n_primary, n_queued, counters);
+    tally_flush(tally, n_primary, 0, counters);
 }
 
-// ---- one recursion level over a compacted queue -----------------------------------------------------
+// ---- stage 2: shadow rays (scene.py:148-167) -------------------------------------------------------------
+// thread = (light li, ray i), li slowest so a warp works on ONE light and 32 neighbouring hit points
 template <bool HAS_NODES>
-__global__ void __launch_bounds__(RT_BLOCK) k_secondary(SceneView S, RayQueue qin, const unsigned long long* qin_count,
-                                                         float4* __restrict__ samples, RayQueue qout, unsigned long long* qout_count,
-                                                         RtCounters* counters) {
+__global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS_SHADOW) k_shadow(SceneView S, long long n_rays, const unsigned long long* n_dev,
+                                                                           HitPlanes H, uint8_t* __restrict__ occ, RtCounters* counters) {
+    Tally tally = tally_zero();
+    const long long n = n_dev ? (long long)*n_dev : n_rays;
+    const long long total = n * S.n_lights;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x; j < total; j += stride) {
+        const int li = (int)(j / n);
+        const long long i = j - (long long)li * n;
+        const float4 h0 = H.planes[0 * H.cap + i];
+        if (h0.w != h0.w) continue;                                   // no hit: no shadow rays
+        TraceCtx cx{S, h0.w, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x};
+        occ[(long long)li * H.cap + i] = light_occluded<HAS_NODES>(cx, f3(h0), li) ? 1 : 0;
+    }
+    tally_flush(tally, 0, 0, counters);
+}
+
+// ---- stage 3: shading, fold, next ray ----------------------------------------------------------------------
+template <bool PRIMARY>
+__global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS_SHADE) k_shade(SceneView S, long long n_rays, RayQueue qin, const unsigned long long* qin_count,
+                                                                         HitPlanes H, const uint8_t* __restrict__ occ, float4* __restrict__ samples,
+                                                                         RayQueue qout, unsigned long long* qout_count, RtCounters* counters) {
     Tally tally = tally_zero();
     unsigned long long n_queued = 0;
-    const long long n = (long long)*qin_count;
+    const long long n = PRIMARY ? n_rays : (long long)*qin_count;
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long base = (long long)blockIdx.x * blockDim.x; base < n; base += stride) {
         const long long i = base + threadIdx.x;
         bool cont = false;
-        PathState ps; float time = 0.0f; unsigned slot = 0;
+        PathState ps; float time = 0.0f; unsigned slot = (unsigned)i;
         if (i < n) {
-            queue_load(qin, i, ps, time, slot);
-            TraceCtx cx{S, time, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x};
+            if (PRIMARY) { ps.fold = fold_identity(); ps.depth_left = S.max_depth; ps.in_shape = 0; ps.ray.o = f3(0, 0, 0); }
+            else queue_load(qin, i, ps, time, slot);
+            const float4 h0 = H.planes[0 * H.cap + i];
             float3 sample;
-            cont = trace_level<HAS_NODES>(cx, ps, sample);
+            if (h0.w != h0.w) sample = fold_eval(ps.fold, f3(0, 0, 0));          // miss: cast_ray returns black (scene.py:91-92)
+            else {
+                const float4 h1 = H.planes[1 * H.cap + i], h2 = H.planes[2 * H.cap + i];
+                Hit hit; hit.p = f3(h0); hit.n = f3(h1); hit.mat = as_int(h1.w); hit.geom = as_int(h2.w); hit.t = 0.0f;
+                time = h0.w;
+                ps.ray.d = f3(h2);
+                TraceCtx cx{S, time, tally, nullptr, 0};
+                cont = shade_level(cx, ps, hit, [&](int li) { return occ[(long long)li * H.cap + i] == 0; }, sample);
+            }
             if (!cont) samples[slot] = f4(sample.x, sample.y, sample.z, 0.0f);
         }
         long long qi = queue_reserve(qout_count, cont);

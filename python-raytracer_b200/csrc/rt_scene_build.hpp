@@ -8,6 +8,7 @@
 #include <string>
 #include <vector>
 
+#include "rt_bvh.cuh"
 #include "rt_core.cuh"
 
 struct HostScene {
@@ -16,8 +17,9 @@ struct HostScene {
     std::vector<DevLight> lights;
     std::vector<float> col_x, row_y, times;
     std::vector<float4> dof_origin, ray_origin;
-    std::vector<BvhNode> tlas_nodes;   // object BVH over the bounded top-level objects (empty: none)
+    std::vector<BvhNode4> tlas_nodes;  // object BVH over the bounded top-level objects (empty: none)
     std::vector<int> lin_objs;         // top-level objects tested one by one (no finite bounds)
+    std::vector<int> sep_mesh;         // top-level meshes, traversed after the walk over the other objects
     bool has_nodes = false, has_specular = false, has_mesh = false;
     SceneView view{};          // scalars filled; pointers are the caller's business
 };
@@ -108,11 +110,17 @@ inline ObjBound object_bound(const RtSceneDesc* d, int oi, float tlo, float thi)
 struct TlasItem { float3 lo, hi; int obj; int flags; };
 inline float half_area(float3 lo, float3 hi) { float3 e = hi - lo; return e.x * e.y + e.y * e.z + e.z * e.x; }
 
+// binary tree under construction (same shape as the GPU LBVH builder's arrays, so the 4-wide collapse is shared)
+struct BinTree {
+    std::vector<int2> children; std::vector<float4> node_lo, node_hi; std::vector<int> node_flags, depth;
+    std::vector<float4> leaf_lo, leaf_hi; std::vector<int> leaf_flags;     // indexed by object index
+};
+
 // top-down sweep SAH; returns the child link of the subtree over items [b, e) (>= 0 node index, < 0 ~object)
-inline int tlas_build(std::vector<TlasItem>& it, int b, int e, std::vector<BvhNode>& nodes, float3& lo, float3& hi, int& flags) {
+inline int tlas_build(std::vector<TlasItem>& it, int b, int e, BinTree& bt, int depth, float3& lo, float3& hi, int& flags) {
     if (e - b == 1) { lo = it[b].lo; hi = it[b].hi; flags = it[b].flags; return ~it[b].obj; }
-    const int idx = (int)nodes.size();
-    nodes.emplace_back();
+    const int idx = (int)bt.children.size();
+    bt.children.emplace_back(); bt.node_lo.emplace_back(); bt.node_hi.emplace_back(); bt.node_flags.push_back(0); bt.depth.push_back(depth);
     const int n = e - b;
     int best_axis = 0, best_split = n / 2; float best_cost = INFINITY;
     std::vector<float> right(n);
@@ -132,15 +140,11 @@ inline int tlas_build(std::vector<TlasItem>& it, int b, int e, std::vector<BvhNo
     std::stable_sort(it.begin() + b, it.begin() + e, [ax](const TlasItem& p, const TlasItem& q) {
         return comp(p.lo, ax) + comp(p.hi, ax) < comp(q.lo, ax) + comp(q.hi, ax); });
     float3 l0, h0, l1, h1; int f0, f1;
-    const int c0 = tlas_build(it, b, b + best_split, nodes, l0, h0, f0);
-    const int c1 = tlas_build(it, b + best_split, e, nodes, l1, h1, f1);
-    BvhNode nd;
-    nd.q0 = f4(l0.x, l0.y, l0.z, h0.x);
-    nd.q1 = f4(h0.y, h0.z, l1.x, l1.y);
-    nd.q2 = f4(l1.z, h1.x, h1.y, h1.z);
-    nd.q3 = f4(as_float(c0), as_float(c1), as_float(f0), as_float(f1));
-    nodes[idx] = nd;
+    const int c0 = tlas_build(it, b, b + best_split, bt, depth + 1, l0, h0, f0);
+    const int c1 = tlas_build(it, b + best_split, e, bt, depth + 1, l1, h1, f1);
     lo = min3(l0, l1); hi = max3(h0, h1); flags = f0 | f1;
+    bt.children[idx].x = c0; bt.children[idx].y = c1;
+    bt.node_lo[idx] = f4(lo.x, lo.y, lo.z, 0.0f); bt.node_hi[idx] = f4(hi.x, hi.y, hi.z, 0.0f); bt.node_flags[idx] = flags;
     return idx;
 }
 
@@ -149,8 +153,10 @@ inline void build_tlas(const RtSceneDesc* d, HostScene& hs) {
     hs.tlas_nodes.clear(); hs.lin_objs.clear();
     float tlo = INFINITY, thi = -INFINITY;
     for (int t = 0; t < d->n_times; t++) { float v = (float)d->motion_times[t]; tlo = fminf(tlo, v); thi = fmaxf(thi, v); }
+    hs.sep_mesh.clear();
     std::vector<TlasItem> items;
     for (int i = 0; i < d->n_top; i++) {
+        if (d->objects[i].kind == RT_KIND_MESH) { hs.sep_mesh.push_back(i); continue; }
         ObjBound b = (std::isfinite(tlo) && std::isfinite(thi)) ? object_bound(d, i, tlo, thi) : ObjBound{f3(0, 0, 0), f3(0, 0, 0), false};
         if (!b.finite) { hs.lin_objs.push_back(i); continue; }
         const float m = fmaxf(fmaxf(fabsf(b.lo.x), fabsf(b.hi.x)), fmaxf(fmaxf(fabsf(b.lo.y), fabsf(b.hi.y)), fmaxf(fabsf(b.lo.z), fabsf(b.hi.z))));
@@ -160,12 +166,30 @@ inline void build_tlas(const RtSceneDesc* d, HostScene& hs) {
         ti.flags = (kind == RT_KIND_MESH || kind == RT_KIND_NODE) ? RT_TLAS_NO_TMAX : 0;
         items.push_back(ti);
     }
-    if (items.size() < 2) {                                   // nothing to gain: plain loop in scene order
+    if (items.size() < 2) {                                   // nothing to gain: plain loop in scene order over everything but the separate meshes
         hs.lin_objs.clear();
+        for (int i = 0; i < d->n_top; i++)
+            if (d->objects[i].kind != RT_KIND_MESH) hs.lin_objs.push_back(i);
         return;
     }
+    BinTree bt;
+    bt.leaf_lo.assign(d->n_top, f4(0, 0, 0, 0)); bt.leaf_hi.assign(d->n_top, f4(0, 0, 0, 0)); bt.leaf_flags.assign(d->n_top, 0);
+    for (const TlasItem& ti : items) {
+        bt.leaf_lo[ti.obj] = f4(ti.lo.x, ti.lo.y, ti.lo.z, 0.0f); bt.leaf_hi[ti.obj] = f4(ti.hi.x, ti.hi.y, ti.hi.z, 0.0f);
+        bt.leaf_flags[ti.obj] = ti.flags;
+    }
     float3 lo, hi; int flags;
-    tlas_build(items, 0, (int)items.size(), hs.tlas_nodes, lo, hi, flags);
+    tlas_build(items, 0, (int)items.size(), bt, 0, lo, hi, flags);
+    // 4-wide collapse: even-depth nodes survive, numbered in index order (rt_bvh.cuh)
+    const int nb = (int)bt.children.size();
+    std::vector<unsigned> remap(nb, 0);
+    unsigned n4 = 0;
+    for (int i = 0; i < nb; i++) if ((bt.depth[i] & 1) == 0) remap[i] = n4++;
+    hs.tlas_nodes.resize(n4);
+    for (int i = 0; i < nb; i++)
+        if ((bt.depth[i] & 1) == 0)
+            hs.tlas_nodes[remap[i]] = make_wide_node(bt.children.data(), i, remap.data(), bt.leaf_lo.data(), bt.leaf_hi.data(),
+                                                     bt.node_lo.data(), bt.node_hi.data(), bt.leaf_flags.data(), bt.node_flags.data(), 0.0f);
 }
 
 // returns RT_OK or an RtStatus with `err` set
@@ -240,6 +264,7 @@ inline int convert_scene(const RtSceneDesc* d, HostScene& hs, std::string& err) 
     V.mesh_mode = 0;
     build_tlas(d, hs);
     V.tlas_nodes = nullptr; V.lin_objs = nullptr; V.n_lin = (int)hs.lin_objs.size();
+    V.sep_mesh = nullptr; V.n_sep_mesh = (int)hs.sep_mesh.size();
     return RT_OK;
 }
 

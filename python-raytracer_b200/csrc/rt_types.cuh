@@ -41,14 +41,19 @@ struct __attribute__((aligned(16))) DevLight {
 
 struct DevXform { float M[16]; float Minv[16]; };
 
-// LBVH node, 64 B = 4 x float4, both children's boxes in the parent so one fetch decides both:
-//   q0 = (c0.min.xyz, c0.max.x)  q1 = (c0.max.yz, c1.min.xy)  q2 = (c1.min.z, c1.max.xyz)
-//   q3 = (bits child0, bits child1, -, -)   child >= 0: node index ; child < 0: ~child = triangle slot
+// Binary LBVH node as the builder emits it before the 4-wide collapse (build-time only), 64 B:
+//   q0 = (c0.min.xyz, c0.max.x)  q1 = (c0.max.yz, c1.min.xy)  q2 = (c1.min.z, c1.max.xyz)  q3 = (bits child0, bits child1, -, -)
 struct __attribute__((aligned(16))) BvhNode { float4 q0, q1, q2, q3; };
+
+// Traversal node: 4-wide, 128 B = one cache line, boxes of the (up to) four children in SoA so the four slab
+// tests vectorise over registers; link >= 0: node index, < 0: ~leaf (triangle slot / object index),
+// RT_LINK_NONE: empty slot (skipped by the walk).  flags: per-child bits (object BVH only).
+#define RT_LINK_NONE 0x7fffffff
+struct __attribute__((aligned(16))) BvhNode4 { float4 lox, loy, loz, hix, hiy, hiz; int4 link; int4 flags; };
 
 struct DevMesh {
     const float4* tri;       // 3 float4 per triangle slot (Morton order): v0|v1|v2, w of v0 = bits(original face index)
-    const BvhNode* nodes;    // n_tris - 1 nodes (root = 0); NULL when n_tris < 2
+    const BvhNode4* nodes;   // 4-wide nodes (root = 0); NULL when n_tris < 2
     const int4* face_vidx;   // per triangle slot: vertex indices (for smooth normals) + original face
     const float4* vnormals;  // per vertex, NULL when flat shaded
     int n_tris;
@@ -71,11 +76,15 @@ struct SceneView {
     int max_depth;
     int mesh_mode;    // test aids: bit 0 = brute force over all faces (mesh.py:77), bit 1 = linear loop over the top-level objects
     // object BVH over the bounded top-level objects (replaces the `for obj in self.objects` loops of scene.py:87,160
-    // for everything that has a finite extent); same 64-B node layout as the mesh LBVH, child < 0: ~object index,
-    // q3.z / q3.w = per-child flags (RT_TLAS_NO_TMAX: the subtree holds an object whose shadow test ignores t_max).
-    const BvhNode* tlas_nodes;   // NULL: no object BVH (fewer than 2 bounded objects) -> plain loop over n_top
-    const int* lin_objs;         // top-level objects without finite bounds (planes, nodes holding planes), scene order
-    int n_lin;
+    // for everything that has a finite extent); same 4-wide node layout as the mesh LBVH, link < 0: ~object index,
+    // flags = per-child bits (RT_TLAS_NO_TMAX: the subtree holds an object whose shadow test ignores t_max).
+    const BvhNode4* tlas_nodes;  // NULL: no object BVH (fewer than 2 bounded objects) -> plain loop over n_top
+    const int* lin_objs;         // top-level objects tested one by one, scene order: no finite bounds (planes, nodes holding
+    int n_lin;                   // planes), or everything but the separate meshes when there is no object BVH
+    // top-level meshes are kept OUT of that walk and traversed after it (gate test each, scene order), so that the lanes
+    // of a warp enter the (long) LBVH traversal together instead of at whatever step their walk happens to reach the mesh
+    const int* sep_mesh;
+    int n_sep_mesh;
     // sampling tables (scene.py:41-43,118-138 precomputed once per scene)
     const float* col_x;          // [W]  (float)x of pixel-centre column
     const float* row_y;          // [H]

@@ -15,7 +15,7 @@
 struct HostMesh {
     std::vector<float4> tri, vn;
     std::vector<int4> vidx;
-    std::vector<BvhNode> nodes;
+    std::vector<BvhNode4> nodes;
     std::vector<int> order;
 };
 
@@ -27,20 +27,16 @@ struct Sim {
     SceneView V;
 };
 
-static void box_of(const HostMesh& hm, const std::vector<int2>& ch, int c, std::vector<float3>& nlo, std::vector<float3>& nhi, float3& lo, float3& hi) {
-    if (c < 0) {
-        int s = ~c;
-        float3 a = f3(hm.tri[3 * s]), b = f3(hm.tri[3 * s + 1]), d = f3(hm.tri[3 * s + 2]);
-        lo = f3(fminf(a.x, fminf(b.x, d.x)), fminf(a.y, fminf(b.y, d.y)), fminf(a.z, fminf(b.z, d.z)));
-        hi = f3(fmaxf(a.x, fmaxf(b.x, d.x)), fmaxf(a.y, fmaxf(b.y, d.y)), fmaxf(a.z, fmaxf(b.z, d.z)));
-        return;
-    }
-    float3 l0, h0, l1, h1;
-    box_of(hm, ch, ch[c].x, nlo, nhi, l0, h0);
-    box_of(hm, ch, ch[c].y, nlo, nhi, l1, h1);
-    lo = f3(fminf(l0.x, l1.x), fminf(l0.y, l1.y), fminf(l0.z, l1.z));
-    hi = f3(fmaxf(h0.x, h1.x), fmaxf(h0.y, h1.y), fmaxf(h0.z, h1.z));
-    nlo[c] = lo; nhi[c] = hi;
+// bottom-up boxes + depths of the binary radix tree (sequential restatement of k_lbvh_leaves_refit / k_lbvh_even)
+static void refit(const std::vector<int2>& ch, int c, int depth, const std::vector<float4>& leaf_lo, const std::vector<float4>& leaf_hi,
+                  std::vector<float4>& nlo, std::vector<float4>& nhi, std::vector<int>& dep, float4& lo, float4& hi) {
+    if (c < 0) { lo = leaf_lo[~c]; hi = leaf_hi[~c]; return; }
+    float4 l0, h0, l1, h1;
+    refit(ch, ch[c].x, depth + 1, leaf_lo, leaf_hi, nlo, nhi, dep, l0, h0);
+    refit(ch, ch[c].y, depth + 1, leaf_lo, leaf_hi, nlo, nhi, dep, l1, h1);
+    lo = f4(fminf(l0.x, l1.x), fminf(l0.y, l1.y), fminf(l0.z, l1.z), 0.0f);
+    hi = f4(fmaxf(h0.x, h1.x), fmaxf(h0.y, h1.y), fmaxf(h0.z, h1.z), 0.0f);
+    nlo[c] = lo; nhi[c] = hi; dep[c] = depth;
 }
 
 static void build_mesh(const RtMesh& m, HostMesh& hm, DevMesh& g) {
@@ -77,21 +73,23 @@ static void build_mesh(const RtMesh& m, HostMesh& hm, DevMesh& g) {
     if (n >= 2) {
         std::vector<int2> ch(n - 1);
         for (int i = 0; i < n - 1; i++) lbvh_node(sk.data(), n, i, ch[i].x, ch[i].y);
-        std::vector<float3> nlo(n - 1), nhi(n - 1);
-        float3 rl, rh;
-        box_of(hm, ch, 0, nlo, nhi, rl, rh);
-        hm.nodes.resize(n - 1);
-        for (int i = 0; i < n - 1; i++) {
-            float3 l0, h0, l1, h1;
-            box_of(hm, ch, ch[i].x, nlo, nhi, l0, h0);   // (recomputes subtrees; fine at test sizes) 
-            box_of(hm, ch, ch[i].y, nlo, nhi, l1, h1);
-            BvhNode nd;
-            nd.q0 = f4(l0.x - pad, l0.y - pad, l0.z - pad, h0.x + pad);
-            nd.q1 = f4(h0.y + pad, h0.z + pad, l1.x - pad, l1.y - pad);
-            nd.q2 = f4(l1.z - pad, h1.x + pad, h1.y + pad, h1.z + pad);
-            nd.q3 = f4(as_float(ch[i].x), as_float(ch[i].y), 0, 0);
-            hm.nodes[i] = nd;
+        std::vector<float4> leaf_lo(n), leaf_hi(n), nlo(n - 1), nhi(n - 1);
+        std::vector<int> dep(n - 1, 0);
+        for (int s = 0; s < n; s++) {
+            float3 a = f3(hm.tri[3 * s]), b = f3(hm.tri[3 * s + 1]), d = f3(hm.tri[3 * s + 2]);
+            leaf_lo[s] = f4(fminf(a.x, fminf(b.x, d.x)), fminf(a.y, fminf(b.y, d.y)), fminf(a.z, fminf(b.z, d.z)), 0.0f);
+            leaf_hi[s] = f4(fmaxf(a.x, fmaxf(b.x, d.x)), fmaxf(a.y, fmaxf(b.y, d.y)), fmaxf(a.z, fmaxf(b.z, d.z)), 0.0f);
         }
+        float4 rl, rh;
+        refit(ch, 0, 0, leaf_lo, leaf_hi, nlo, nhi, dep, rl, rh);
+        std::vector<unsigned> remap(n - 1, 0);
+        unsigned n4 = 0;
+        for (int i = 0; i < n - 1; i++) if ((dep[i] & 1) == 0) remap[i] = n4++;
+        hm.nodes.resize(n4);
+        for (int i = 0; i < n - 1; i++)
+            if ((dep[i] & 1) == 0)
+                hm.nodes[remap[i]] = make_wide_node(ch.data(), i, remap.data(), leaf_lo.data(), leaf_hi.data(), nlo.data(), nhi.data(),
+                                                    nullptr, nullptr, pad);
     }
     g.tri = hm.tri.data(); g.nodes = n >= 2 ? hm.nodes.data() : nullptr; g.face_vidx = hm.vidx.data();
     g.vnormals = hm.vn.empty() ? nullptr : hm.vn.data();
@@ -113,6 +111,7 @@ static int make_sim(const RtSceneDesc* d, Sim& sim) {
     V.ray_origin = sim.hs.ray_origin.data(); V.times = sim.hs.times.data();
     V.tlas_nodes = sim.hs.tlas_nodes.empty() ? nullptr : sim.hs.tlas_nodes.data();
     V.lin_objs = sim.hs.lin_objs.data(); V.n_lin = (int)sim.hs.lin_objs.size();
+    V.sep_mesh = sim.hs.sep_mesh.data(); V.n_sep_mesh = (int)sim.hs.sep_mesh.size();
     return 0;
 }
 
@@ -163,14 +162,39 @@ extern "C" int hostsim_render_pixels(const RtSceneDesc* d, const int32_t* cols, 
     return 0;
 }
 
-extern "C" int hostsim_bvh(const RtSceneDesc* d, int mesh, float* nodes_out, int32_t* order_out) {
+// diagnostics: LBVH nodes visited by the first cast_ray level (closest hit + its shadow rays) of every (pixel, sample)
+// ray, to estimate how evenly the lanes of a warp are loaded (scripts/warp_balance.py)
+extern "C" int hostsim_node_counts(const RtSceneDesc* d, const int32_t* cols, const int32_t* rows, int64_t n, uint32_t* out) {
     Sim sim;
     int rc = make_sim(d, sim);
     if (rc) return rc;
-    const HostMesh& hm = sim.meshes[mesh];
-    if (nodes_out && !hm.nodes.empty()) memcpy(nodes_out, hm.nodes.data(), sizeof(BvhNode) * hm.nodes.size());
-    if (order_out) memcpy(order_out, hm.order.data(), sizeof(int) * hm.order.size());
+    const SceneView& V = sim.V;
+    const int N = V.D * V.S * V.T;
+#pragma omp parallel for schedule(dynamic, 16)
+    for (int64_t i = 0; i < n; i++) {
+        int stack[RT_STACK_DEPTH];
+        for (int slot = 0; slot < N; slot++) {
+            const int t = slot % V.T, ds = slot / V.T, s = ds % V.S, dd = ds / V.S;
+            Tally tally{};
+            PathState ps; ps.ray = generate_ray(V, cols[i], rows[i], dd, s); ps.fold = fold_identity(); ps.depth_left = V.max_depth; ps.in_shape = 0;
+            TraceCtx cx{V, V.times[t], tally, stack, 1};
+            float3 sample;
+            if (sim.hs.has_nodes) trace_level<true>(cx, ps, sample); else trace_level<false>(cx, ps, sample);
+            out[i * N + slot] = tally.nodes;
+        }
+    }
     return 0;
+}
+
+// returns the number of 4-wide nodes (>= 0) or -(status); nodes_out holds up to n_faces-1 nodes of 32 floats
+extern "C" int hostsim_bvh(const RtSceneDesc* d, int mesh, float* nodes_out, int32_t* order_out) {
+    Sim sim;
+    int rc = make_sim(d, sim);
+    if (rc) return -rc;
+    const HostMesh& hm = sim.meshes[mesh];
+    if (nodes_out && !hm.nodes.empty()) memcpy(nodes_out, hm.nodes.data(), sizeof(BvhNode4) * hm.nodes.size());
+    if (order_out) memcpy(order_out, hm.order.data(), sizeof(int) * hm.order.size());
+    return (int)hm.nodes.size();
 }
 
 // pixel mapping of a render job: (col,row,valid) of every local pixel slot, in compact-buffer order

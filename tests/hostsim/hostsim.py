@@ -53,11 +53,11 @@ def render(flat, abi, mesh_mode=0):
 
 def bvh(flat, mesh=0):
     n = C.cast(flat.desc.meshes, C.POINTER(type("M", (C.Structure,), {"_fields_": [("n_verts", C.c_int32), ("n_faces", C.c_int32)]})))[0].n_faces
-    nodes = np.zeros((max(n - 1, 0), 16), dtype=np.float32)
+    nodes = np.zeros((max(n - 1, 0), 32), dtype=np.float32)      # 4-wide nodes, 128 B each (BvhNode4)
     order = np.zeros(n, dtype=np.int32)
-    rc = lib().hostsim_bvh(C.addressof(flat.desc), mesh, nodes.ctypes.data, order.ctypes.data)
-    assert rc == 0
-    return nodes, order
+    n4 = lib().hostsim_bvh(C.addressof(flat.desc), mesh, nodes.ctypes.data, order.ctypes.data)
+    assert n4 >= 0
+    return nodes[:n4].copy(), order
 
 
 def job_pixels(job):

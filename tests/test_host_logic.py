@@ -188,18 +188,32 @@ def test_object_bvh_synthetic_scene_fewer_tests_same_image():
 
 
 def test_lbvh_structure_is_a_valid_tree():
+    """4-wide nodes (BvhNode4: 6 float4 of child boxes, int4 links, int4 flags): every triangle slot is the leaf of
+    exactly one node, every node but the root has exactly one parent, child boxes contain their subtrees."""
     sc = load_case("TorusMesh_flat")
     nodes, order = hostsim.bvh(sc.flatten())
-    n = len(order)
-    assert sorted(order.tolist()) == list(range(n))
-    ch = nodes[:, 12:14].copy().view(np.int32)
-    seen_leaf, seen_node = np.zeros(n, int), np.zeros(n - 1, int)
-    for c in ch.reshape(-1):
+    n, n4 = len(order), len(nodes)
+    assert sorted(order.tolist()) == list(range(n)) and 0 < n4 < n - 1
+    links = nodes[:, 24:28].copy().view(np.int32)
+    NONE = 0x7fffffff
+    seen_leaf, seen_node = np.zeros(n, int), np.zeros(n4, int)
+    for c in links.reshape(-1):
+        if c == NONE:
+            continue
         if c < 0:
             seen_leaf[~c] += 1
         else:
             seen_node[c] += 1
     assert (seen_leaf == 1).all() and seen_node[0] == 0 and (seen_node[1:] == 1).all()
+    assert ((links != NONE).sum(axis=1) >= 2).all()
+    # a child's box contains the boxes of that child's own children
+    lo, hi = nodes[:, 0:12].reshape(n4, 3, 4), nodes[:, 12:24].reshape(n4, 3, 4)
+    for i in range(n4):
+        for k in range(4):
+            c = links[i, k]
+            if c != NONE and c >= 0:
+                used = links[c] != NONE
+                assert (lo[c][:, used].min(axis=1) >= lo[i][:, k] - 1e-6).all() and (hi[c][:, used].max(axis=1) <= hi[i][:, k] + 1e-6).all()
 
 
 def test_tile_interleave_partitions_the_region():
