@@ -206,6 +206,7 @@ def run_ours(a):
     # ---- warm-up (also yields the per-frame ray tallies: deterministic for a fixed scene)
     ctr = _abi.RtCounters()
     sharder.render(counters=ctr)
+    assert ctr.error_flags == 0, f"kernels flagged errors 0x{ctr.error_flags:x} (traversal stack / material limits)"
     for _ in range(max(0, a.warmup - 1)):
         sharder.render()
     tallies = torch.tensor([getattr(ctr, k) for k in RAY_KEYS] + [ctr.kernel_launches, ctr.bvh_nodes, ctr.tri_tests, ctr.queued_rays,

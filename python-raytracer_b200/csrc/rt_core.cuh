@@ -24,8 +24,21 @@ struct TraceCtx {
     Tally& tally;
     int* stack;          // BVH traversal stack of this thread: entry k at stack[k * stack_stride]
     int stack_stride;
-    int sbase = 0;       // entries below sbase belong to the object-BVH walk in progress (top_next)
+    int sbase;           // entries below sbase belong to the object-BVH walk in progress (top_next)
+    int spill[RT_STACK_SPILL];   // entries RT_STACK_DEPTH.. of the stack (thread-local memory, touched only by unusually deep walks)
+    RT_HD TraceCtx(const SceneView& S_, float time_, Tally& tally_, int* stack_, int stride_)
+        : S(S_), time(time_), tally(tally_), stack(stack_), stack_stride(stride_), sbase(0) {}   // spill[] deliberately left uninitialised
 };
+RT_HD void stk_push(TraceCtx& cx, int& sp, int v) {
+    if (sp < RT_STACK_DEPTH) cx.stack[sp * cx.stack_stride] = v;
+    else if (sp < RT_STACK_DEPTH + RT_STACK_SPILL) cx.spill[sp - RT_STACK_DEPTH] = v;
+    else { cx.tally.err |= 1u << RT_ERR_LIMIT; return; }                 // deeper than both: entry dropped, render reports RT_ERR_LIMIT
+    sp++;
+}
+RT_HD int stk_pop(TraceCtx& cx, int& sp) {
+    --sp;
+    return sp < RT_STACK_DEPTH ? cx.stack[sp * cx.stack_stride] : cx.spill[sp - RT_STACK_DEPTH];
+}
 
 // `center + speed * current_time` (simple_geometry.py:21-24,106-109,189-194)
 RT_HD float3 moved(const DevObject* o, float3 base, float time) { return base + f3(ld4(&o->speed)) * time; }
@@ -151,6 +164,25 @@ RT_HD RayInv ray_inv(const Ray& r) {
     ri.oinv = f3(-r.o.x * ri.inv.x, -r.o.y * ri.inv.y, -r.o.z * ri.inv.z);
     return ri;
 }
+// Mesh gate for rays whose reciprocal direction is at hand (top-level meshes): same decisions as mesh_gate up to the
+// last ulp of the slab distances ((lo - o) * (1/d) instead of (lo - o) / d; six IEEE divisions saved per ray)
+RT_HD bool mesh_gate_rcp(const DevMesh* m, const Ray& r, const RayInv& ri) {
+    if (m->gate == RT_GATE_SPHERE) return mesh_gate(m, r);
+    const float3 mn = f3(ld4(&m->gate_min)), mx = f3(ld4(&m->gate_max));
+    float entry = -RT_INF, exit_ = RT_INF;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int k = 0; k < 3; k++) {
+        const float o = comp(r.o, k), d = comp(r.d, k), lo = comp(mn, k), hi = comp(mx, k), iv = comp(ri.inv, k);
+        if (d == 0.0f) { if (!(lo < o && o < hi)) return false; }
+        else {
+            const float t1 = (lo - o) * iv, t2 = (hi - o) * iv;
+            entry = fmaxf(entry, fminf(t1, t2)); exit_ = fminf(exit_, fmaxf(t1, t2));
+        }
+    }
+    return !(entry > exit_ || entry < 0.0f);
+}
 RT_HD unsigned as_uint(float f) { return (unsigned)as_int(f); }
 RT_HD int link_of(const int4& l, unsigned slot) { return (slot & 2u) ? ((slot & 1u) ? l.w : l.z) : ((slot & 1u) ? l.y : l.x); }
 RT_HD void key_swap(unsigned& a, unsigned& b) { unsigned lo = a < b ? a : b, hi = a < b ? b : a; a = lo; b = hi; }
@@ -172,11 +204,10 @@ RT_HD void key_swap(unsigned& a, unsigned& b) { unsigned lo = a < b ? a : b, hi 
 template <bool ORDERED, bool FLAGS>
 RT_HD int bvh4_next(TraceCtx& cx, const BvhNode4* __restrict__ nodes, int& cur, int& sp, const int sbase, const RayInv& ri,
                     const float tmin, const float tmax, unsigned& visits) {
-    int* stk = cx.stack; const int stride = cx.stack_stride;
     for (;;) {
         if (cur == RT_LINK_NONE) {
             if (sp == sbase) return -1;
-            cur = stk[(--sp) * stride];
+            cur = stk_pop(cx, sp);
         }
         if (cur < 0) { const int leaf = ~cur; cur = RT_LINK_NONE; return leaf; }
         const BvhNode4* np = nodes + cur;
@@ -205,18 +236,16 @@ RT_HD int bvh4_next(TraceCtx& cx, const BvhNode4* __restrict__ nodes, int& cur, 
             unsigned k3 = h3 ? ((as_uint(n3) & 0x7ffffffcu) | 3u) : 0xffffffffu;
             key_swap(k0, k1); key_swap(k2, k3); key_swap(k0, k2); key_swap(k1, k3); key_swap(k1, k2);
             const int nhit = (int)h0 + (int)h1 + (int)h2 + (int)h3;
-            if (sp + 3 > RT_STACK_DEPTH && nhit > 1) { cx.tally.err |= 1u << RT_ERR_LIMIT; cur = nhit ? link_of(link, k0 & 3u) : RT_LINK_NONE; continue; }
-            if (nhit > 3) stk[(sp++) * stride] = link_of(link, k3 & 3u);
-            if (nhit > 2) stk[(sp++) * stride] = link_of(link, k2 & 3u);
-            if (nhit > 1) stk[(sp++) * stride] = link_of(link, k1 & 3u);
+            if (nhit > 3) stk_push(cx, sp, link_of(link, k3 & 3u));
+            if (nhit > 2) stk_push(cx, sp, link_of(link, k2 & 3u));
+            if (nhit > 1) stk_push(cx, sp, link_of(link, k1 & 3u));
             cur = nhit ? link_of(link, k0 & 3u) : RT_LINK_NONE;
         } else {
-            if (sp + 3 > RT_STACK_DEPTH) { cx.tally.err |= 1u << RT_ERR_LIMIT; h1 = h1 && !h0; h2 = h2 && !h0 && !h1; h3 = h3 && !h0 && !h1 && !h2; }
             cur = RT_LINK_NONE;
             if (h0) cur = link.x;
-            if (h1) { if (cur == RT_LINK_NONE) cur = link.y; else stk[(sp++) * stride] = link.y; }
-            if (h2) { if (cur == RT_LINK_NONE) cur = link.z; else stk[(sp++) * stride] = link.z; }
-            if (h3) { if (cur == RT_LINK_NONE) cur = link.w; else stk[(sp++) * stride] = link.w; }
+            if (h1) { if (cur == RT_LINK_NONE) cur = link.y; else stk_push(cx, sp, link.y); }
+            if (h2) { if (cur == RT_LINK_NONE) cur = link.z; else stk_push(cx, sp, link.z); }
+            if (h3) { if (cur == RT_LINK_NONE) cur = link.w; else stk_push(cx, sp, link.w); }
         }
     }
 }
@@ -244,13 +273,12 @@ RT_HD void mesh_visit(TraceCtx& cx, const DevMesh* m, const RayInv& ri, float tm
         return;
     }
     const BvhNode4* __restrict__ nodes = m->nodes;
-    int* stk = cx.stack; const int stride = cx.stack_stride;
     const int sbase = cx.sbase;
     int cur = 0, sp = sbase;
     for (;;) {
         if (cur == RT_LINK_NONE) {
             if (sp == sbase) return;
-            cur = stk[(--sp) * stride];
+            cur = stk_pop(cx, sp);
         }
         const BvhNode4* np = nodes + cur;
         const float4 lox = ld4(&np->lox), loy = ld4(&np->loy), loz = ld4(&np->loz);
@@ -280,18 +308,16 @@ RT_HD void mesh_visit(TraceCtx& cx, const DevMesh* m, const RayInv& ri, float tm
             unsigned k3 = h3 ? ((as_uint(n3) & 0x7ffffffcu) | 3u) : 0xffffffffu;
             key_swap(k0, k1); key_swap(k2, k3); key_swap(k0, k2); key_swap(k1, k3); key_swap(k1, k2);
             const int nhit = (int)h0 + (int)h1 + (int)h2 + (int)h3;
-            if (sp + 3 > RT_STACK_DEPTH && nhit > 1) { cx.tally.err |= 1u << RT_ERR_LIMIT; cur = link_of(link, k0 & 3u); continue; }
-            if (nhit > 3) stk[(sp++) * stride] = link_of(link, k3 & 3u);
-            if (nhit > 2) stk[(sp++) * stride] = link_of(link, k2 & 3u);
-            if (nhit > 1) stk[(sp++) * stride] = link_of(link, k1 & 3u);
+            if (nhit > 3) stk_push(cx, sp, link_of(link, k3 & 3u));
+            if (nhit > 2) stk_push(cx, sp, link_of(link, k2 & 3u));
+            if (nhit > 1) stk_push(cx, sp, link_of(link, k1 & 3u));
             cur = nhit ? link_of(link, k0 & 3u) : RT_LINK_NONE;
         } else {
-            if (sp + 3 > RT_STACK_DEPTH) { cx.tally.err |= 1u << RT_ERR_LIMIT; h1 = h1 && !h0; h2 = h2 && !h0 && !h1; h3 = h3 && !h0 && !h1 && !h2; }
             cur = RT_LINK_NONE;
             if (h0) cur = link.x;
-            if (h1) { if (cur == RT_LINK_NONE) cur = link.y; else stk[(sp++) * stride] = link.y; }
-            if (h2) { if (cur == RT_LINK_NONE) cur = link.z; else stk[(sp++) * stride] = link.z; }
-            if (h3) { if (cur == RT_LINK_NONE) cur = link.w; else stk[(sp++) * stride] = link.w; }
+            if (h1) { if (cur == RT_LINK_NONE) cur = link.y; else stk_push(cx, sp, link.y); }
+            if (h2) { if (cur == RT_LINK_NONE) cur = link.z; else stk_push(cx, sp, link.z); }
+            if (h3) { if (cur == RT_LINK_NONE) cur = link.w; else stk_push(cx, sp, link.w); }
         }
     }
 }
@@ -340,7 +366,7 @@ RT_HD float3 tri_normal(TraceCtx& cx, const DevMesh* m, int slot, float3 p) {
 
 // Mesh.shadow_intersect (mesh.py:121-153): gate, then any accepted face; t_max is ignored by the reference
 RT_HD bool mesh_shadow(TraceCtx& cx, const DevMesh* m, const Ray& r, const RayInv& ri) {
-    if (!mesh_gate(m, r)) return false;
+    if (!mesh_gate_rcp(m, r, ri)) return false;
     bool occ = false;
     float tmax = RT_INF;
     mesh_visit<false>(cx, m, ri, RT_SHADOW_EPS * 0.5f, tmax, [&](int slot, float&) {
@@ -360,7 +386,7 @@ RT_HD_NOINLINE bool mesh_shadow_cold(TraceCtx& cx, const DevMesh* m, const Ray& 
 template <class Better>
 RT_HD void mesh_closest(TraceCtx& cx, const DevMesh* m, const Ray& r, const RayInv& ri, float best, Better&& better, float& t_out, int& slot_out) {
     slot_out = -1; t_out = best;
-    if (!mesh_gate(m, r)) return;
+    if (!mesh_gate_rcp(m, r, ri)) return;
     float tmax = best;
     int best_face = 0x7fffffff, best_slot = -1;
     mesh_visit<true>(cx, m, ri, 0.0f, tmax, [&](int slot, float& tm) {

@@ -17,13 +17,13 @@
 #define RT_BLOCK 128
 // resident blocks per SM each kernel's register allocation is held to (tuned on B200)
 #ifndef RT_MIN_BLOCKS_HIT
-#define RT_MIN_BLOCKS_HIT 1
+#define RT_MIN_BLOCKS_HIT 6
 #endif
 #ifndef RT_MIN_BLOCKS_SHADOW
-#define RT_MIN_BLOCKS_SHADOW 1
+#define RT_MIN_BLOCKS_SHADOW 8
 #endif
 #ifndef RT_MIN_BLOCKS_SHADE
-#define RT_MIN_BLOCKS_SHADE 1
+#define RT_MIN_BLOCKS_SHADE 8
 #endif
 
 // Compacted ray queue, SoA of float4 planes (coalesced 128-bit accesses):
@@ -185,16 +185,19 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS_SHADE) k_shade(SceneVi
         if (i < n) {
             if (PRIMARY) { ps.fold = fold_identity(); ps.depth_left = S.max_depth; ps.in_shape = 0; ps.ray.o = f3(0, 0, 0); }
             else queue_load(qin, i, ps, time, slot);
-            const float4 h0 = H.planes[0 * H.cap + i];
+            // every load of this ray issued up front (the kernel is latency-bound: hit planes + one flag byte per light)
+            const float4 h0 = H.planes[0 * H.cap + i], h1 = H.planes[1 * H.cap + i], h2 = H.planes[2 * H.cap + i];
+            unsigned lit_mask = 0;
+            const int n_pre = S.n_lights < 32 ? S.n_lights : 32;
+            for (int li = 0; li < n_pre; li++) lit_mask |= (occ[(long long)li * H.cap + i] == 0 ? 1u : 0u) << li;
             float3 sample;
             if (h0.w != h0.w) sample = fold_eval(ps.fold, f3(0, 0, 0));          // miss: cast_ray returns black (scene.py:91-92)
             else {
-                const float4 h1 = H.planes[1 * H.cap + i], h2 = H.planes[2 * H.cap + i];
                 Hit hit; hit.p = f3(h0); hit.n = f3(h1); hit.mat = as_int(h1.w); hit.geom = as_int(h2.w); hit.t = 0.0f;
                 time = h0.w;
                 ps.ray.d = f3(h2);
                 TraceCtx cx{S, time, tally, nullptr, 0};
-                cont = shade_level(cx, ps, hit, [&](int li) { return occ[(long long)li * H.cap + i] == 0; }, sample);
+                cont = shade_level(cx, ps, hit, [&](int li) { return li < 32 ? ((lit_mask >> li) & 1u) != 0 : occ[(long long)li * H.cap + i] == 0; }, sample);
             }
             if (!cont) samples[slot] = f4(sample.x, sample.y, sample.z, 0.0f);
         }

@@ -4,7 +4,13 @@
 #include "../../include/b200rt.h"
 
 #define RT_MAX_NEST 8        // CSG / transform nesting depth supported (NovelScene uses 5)
-#define RT_STACK_DEPTH 64    // BVH traversal stack entries per ray (object BVH + mesh LBVH share it)
+#ifndef RT_STACK_DEPTH
+#define RT_STACK_DEPTH 40    // BVH traversal stack entries per ray held in shared memory (object BVH + mesh LBVH share it)
+#endif
+#ifndef RT_STACK_SPILL
+#define RT_STACK_SPILL 88
+#endif
+// RT_STACK_SPILL: further entries in thread-local memory; beyond both the render reports RT_ERR_LIMIT
 #define RT_TLAS_NO_TMAX 1    // object-BVH child flag
 #define RT_MODE_BRUTE_MESH 1
 #define RT_MODE_LINEAR_TOP 2

@@ -103,6 +103,8 @@ class Scene:
         self.last_counters = ctr.as_dict()
         if ctr.error_flags & (1 << 4):
             raise IndexError("list index out of range (a shaded hit had no material; geometry/__init__.py:57)")
+        if ctr.error_flags & (1 << 5):
+            raise _abi.B200RTError("RT_ERR_LIMIT: the scene exceeds a compiled limit (traversal stack or CSG nesting depth)")
         return out
 
     def render_device(self, d_out_ptr, job, counters=None, stream=None):

@@ -11,6 +11,15 @@ CSRC = os.path.join(HERE, "..", "..", "python-raytracer_b200", "csrc")
 _lib = None
 
 
+def build_variant(tag, defines):
+    """A second copy of the library with other compile-time limits (e.g. a 3-entry traversal stack to exercise the spill)."""
+    out = os.path.join(HERE, "_build", f"libhostsim_{tag}.so")
+    os.makedirs(os.path.dirname(out), exist_ok=True)
+    subprocess.run(["g++", "-O2", "-std=c++17", "-fopenmp", "-fPIC", "-shared", "-ffp-contract=off", *defines,
+                    "-I/usr/local/cuda/include", "-o", out, os.path.join(HERE, "hostsim.cpp")], check=True)
+    return C.CDLL(out)
+
+
 def build(force=False):
     deps = [os.path.join(HERE, "hostsim.cpp")] + [os.path.join(CSRC, f) for f in
             ("rt_core.cuh", "rt_bvh.cuh", "rt_types.cuh", "rt_math.cuh", "rt_scene_build.hpp")]
@@ -33,21 +42,23 @@ def lib():
     return _lib
 
 
-def render_pixels(flat, abi, cols, rows, mesh_mode=0):
+def render_pixels(flat, abi, cols, rows, mesh_mode=0, library=None):
     cols = np.ascontiguousarray(cols, dtype=np.int32)
     rows = np.ascontiguousarray(rows, dtype=np.int32)
     out = np.empty((len(cols), 3), dtype=np.float32)
     ctr = abi.RtCounters()
-    rc = lib().hostsim_render_pixels(C.addressof(flat.desc), cols.ctypes.data, rows.ctypes.data, len(cols),
+    L = library or lib()
+    L.hostsim_render_pixels.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_void_p]
+    rc = L.hostsim_render_pixels(C.addressof(flat.desc), cols.ctypes.data, rows.ctypes.data, len(cols),
                                      out.ctypes.data, mesh_mode, C.addressof(ctr))
     assert rc == 0, rc
     return out, ctr.as_dict()
 
 
-def render(flat, abi, mesh_mode=0):
+def render(flat, abi, mesh_mode=0, library=None):
     W, H = flat.desc.width, flat.desc.height
     cc, rr = np.meshgrid(np.arange(W), np.arange(H), indexing="ij")
-    out, ctr = render_pixels(flat, abi, cc.reshape(-1), rr.reshape(-1), mesh_mode)
+    out, ctr = render_pixels(flat, abi, cc.reshape(-1), rr.reshape(-1), mesh_mode, library)
     return out.reshape(W, H, 3), ctr
 
 

@@ -187,6 +187,20 @@ def test_object_bvh_synthetic_scene_fewer_tests_same_image():
     assert ca["prim_tests"] < cb["prim_tests"] / 4
 
 
+def test_traversal_stack_spill_gives_the_same_image():
+    """Walks deeper than the shared-memory stack continue in thread-local memory (stk_push/stk_pop): with a 3-entry
+    stack nearly every walk spills, and the image must not change; with no spill room at all RT_ERR_LIMIT is flagged."""
+    sc = load_case("TorusMesh_smooth")
+    fs = sc.flatten()
+    a, ca = hostsim.render(fs, abi)
+    tiny = hostsim.build_variant("stack3", ["-DRT_STACK_DEPTH=3"])
+    b, cb = hostsim.render(fs, abi, library=tiny)
+    assert np.array_equal(a, b) and cb["error_flags"] == 0 and ca["bvh_nodes"] == cb["bvh_nodes"]
+    none = hostsim.build_variant("stack1", ["-DRT_STACK_DEPTH=1", "-DRT_STACK_SPILL=1"])
+    _, cc = hostsim.render(fs, abi, library=none)
+    assert cc["error_flags"] & (1 << 5)
+
+
 def test_lbvh_structure_is_a_valid_tree():
     """4-wide nodes (BvhNode4: 6 float4 of child boxes, int4 links, int4 flags): every triangle slot is the leaf of
     exactly one node, every node but the root has exactly one parent, child boxes contain their subtrees."""
