@@ -90,7 +90,9 @@ RT_HD void set4i(int4& v, int k, int x) { if (k == 0) v.x = x; else if (k == 1) 
 RT_HD BvhNode4 make_wide_node(const int2* children, int i, const unsigned* remap, const float4* leaf_lo, const float4* leaf_hi,
                               const float4* node_lo, const float4* node_hi, const int* leaf_flags, const int* node_flags, float pad) {
     BvhNode4 nd;
-    nd.lox = nd.loy = nd.loz = nd.hix = nd.hiy = nd.hiz = f4(0.0f, 0.0f, 0.0f, 0.0f);   // empty slots: skipped by their link
+    const float inf = RT_INF;                  // empty slots: [+inf, -inf] boxes, missed by every ray (see RT_SLAB4)
+    nd.lox = nd.loy = nd.loz = f4(inf, inf, inf, inf);
+    nd.hix = nd.hiy = nd.hiz = f4(-inf, -inf, -inf, -inf);
     nd.link.x = nd.link.y = nd.link.z = nd.link.w = RT_LINK_NONE;
     nd.flags.x = nd.flags.y = nd.flags.z = nd.flags.w = 0;
     int c[4];

@@ -25,9 +25,10 @@ struct TraceCtx {
     int* stack;          // BVH traversal stack of this thread: entry k at stack[k * stack_stride]
     int stack_stride;
     int sbase;           // entries below sbase belong to the object-BVH walk in progress (top_next)
-    int spill[RT_STACK_SPILL];   // entries RT_STACK_DEPTH.. of the stack (thread-local memory, touched only by unusually deep walks)
-    RT_HD TraceCtx(const SceneView& S_, float time_, Tally& tally_, int* stack_, int stride_)
-        : S(S_), time(time_), tally(tally_), stack(stack_), stack_stride(stride_), sbase(0) {}   // spill[] deliberately left uninitialised
+    int* spill;          // entries RT_STACK_DEPTH.. of the stack: RT_STACK_SPILL ints of thread-local memory owned by the kernel,
+                         // touched only by unusually deep walks (kept OUT of this struct so its scalars stay in registers)
+    RT_HD TraceCtx(const SceneView& S_, float time_, Tally& tally_, int* stack_, int stride_, int* spill_)
+        : S(S_), time(time_), tally(tally_), stack(stack_), stack_stride(stride_), sbase(0), spill(spill_) {}
 };
 RT_HD void stk_push(TraceCtx& cx, int& sp, int v) {
     if (sp < RT_STACK_DEPTH) cx.stack[sp * cx.stack_stride] = v;
@@ -156,12 +157,16 @@ RT_HD bool tri_shadow(float3 v0, float3 v1, float3 v2, const Ray& r) {
 // 4-wide BVH walk shared by the per-mesh LBVH and the object BVH.
 // Slab tests in FMA form t = plane * (1/d) + (-o/d).  A direction component smaller than 2^-60 gets a reciprocal
 // of +-2^60 instead of inf, so the two products stay finite (inf - inf would poison the interval).
-struct RayInv { float3 inv, oinv; };
+// nx/ny/nz: byte offset inside a BvhNode4 of the plane set the ray ENTERS through on each axis (lo planes for a
+// non-negative direction component, hi planes otherwise); the exit planes are at (nx ^ 48), (80 - ny), (112 - nz).
+// Picking near/far by address removes the per-box min/max of the classic slab test.
+struct RayInv { float3 inv, oinv; int nx, ny, nz; };
 RT_HD float safe_rcp(float d) { return fabsf(d) >= 8.673617e-19f ? 1.0f / d : copysignf(1.1529215e18f, d); }
 RT_HD RayInv ray_inv(const Ray& r) {
     RayInv ri;
     ri.inv = f3(safe_rcp(r.d.x), safe_rcp(r.d.y), safe_rcp(r.d.z));
     ri.oinv = f3(-r.o.x * ri.inv.x, -r.o.y * ri.inv.y, -r.o.z * ri.inv.z);
+    ri.nx = ri.inv.x < 0.0f ? 48 : 0; ri.ny = ri.inv.y < 0.0f ? 64 : 16; ri.nz = ri.inv.z < 0.0f ? 80 : 32;
     return ri;
 }
 // Mesh gate for rays whose reciprocal direction is at hand (top-level meshes): same decisions as mesh_gate up to the
@@ -187,15 +192,20 @@ RT_HD unsigned as_uint(float f) { return (unsigned)as_int(f); }
 RT_HD int link_of(const int4& l, unsigned slot) { return (slot & 2u) ? ((slot & 1u) ? l.w : l.z) : ((slot & 1u) ? l.y : l.x); }
 RT_HD void key_swap(unsigned& a, unsigned& b) { unsigned lo = a < b ? a : b, hi = a < b ? b : a; a = lo; b = hi; }
 
-#define RT_SLAB4(LINK, LOX, LOY, LOZ, HIX, HIY, HIZ, TMAXK, NEAR, HIT)                                             \
-    {                                                                                                            \
-        const float ax_ = fmaf(LOX, ri.inv.x, ri.oinv.x), bx_ = fmaf(HIX, ri.inv.x, ri.oinv.x);                  \
-        const float ay_ = fmaf(LOY, ri.inv.y, ri.oinv.y), by_ = fmaf(HIY, ri.inv.y, ri.oinv.y);                  \
-        const float az_ = fmaf(LOZ, ri.inv.z, ri.oinv.z), bz_ = fmaf(HIZ, ri.inv.z, ri.oinv.z);                  \
-        NEAR = fmaxf(fmaxf(fminf(ax_, bx_), fminf(ay_, by_)), fmaxf(fminf(az_, bz_), tmin));                    \
-        const float far_ = fminf(fminf(fmaxf(ax_, bx_), fmaxf(ay_, by_)), fminf(fmaxf(az_, bz_), TMAXK));       \
-        HIT = (NEAR <= far_) && (LINK != RT_LINK_NONE);      /* min/max sort the interval ends: an empty slot needs the link test */ \
+// entry/exit distances of one child box from its entry planes (NX,NY,NZ) and exit planes (FX,FY,FZ); an empty slot
+// holds [+inf, -inf] boxes: its entry distance is +inf and its exit distance -inf for every direction sign
+#define RT_SLAB4(NX, NY, NZ, FX, FY, FZ, TMAXK, NEAR, HIT)                                                                      \
+    {                                                                                                                          \
+        NEAR = fmaxf(fmaxf(fmaf(NX, ri.inv.x, ri.oinv.x), fmaf(NY, ri.inv.y, ri.oinv.y)), fmaxf(fmaf(NZ, ri.inv.z, ri.oinv.z), tmin));          \
+        const float far_ = fminf(fminf(fmaf(FX, ri.inv.x, ri.oinv.x), fmaf(FY, ri.inv.y, ri.oinv.y)), fminf(fmaf(FZ, ri.inv.z, ri.oinv.z), TMAXK)); \
+        HIT = NEAR <= far_;                                                                                                    \
     }
+#define RT_LOAD_NODE4(NP)                                                                                                       \
+    const char* nb_ = (const char*)(NP);                                                                                       \
+    const float4 pnx = ld4((const float4*)(nb_ + ri.nx)), pny = ld4((const float4*)(nb_ + ri.ny)), pnz = ld4((const float4*)(nb_ + ri.nz)); \
+    const float4 pfx = ld4((const float4*)(nb_ + (ri.nx ^ 48))), pfy = ld4((const float4*)(nb_ + (80 - ri.ny))),               \
+                 pfz = ld4((const float4*)(nb_ + (112 - ri.nz)));                                                              \
+    const int4 link = RT_LDG(&(NP)->link);
 
 // Advances the walk to the next leaf whose box the ray segment [tmin, tmax] touches; returns the leaf id
 // (triangle slot / object index) or -1 when the walk is over.  `cur` = link being processed (RT_LINK_NONE: pop),
@@ -211,9 +221,7 @@ RT_HD int bvh4_next(TraceCtx& cx, const BvhNode4* __restrict__ nodes, int& cur, 
         }
         if (cur < 0) { const int leaf = ~cur; cur = RT_LINK_NONE; return leaf; }
         const BvhNode4* np = nodes + cur;
-        const float4 lox = ld4(&np->lox), loy = ld4(&np->loy), loz = ld4(&np->loz);
-        const float4 hix = ld4(&np->hix), hiy = ld4(&np->hiy), hiz = ld4(&np->hiz);
-        const int4 link = RT_LDG(&np->link);
+        RT_LOAD_NODE4(np)
         visits++;
         float t0 = tmax, t1 = tmax, t2 = tmax, t3 = tmax;
         if (FLAGS) {
@@ -224,10 +232,10 @@ RT_HD int bvh4_next(TraceCtx& cx, const BvhNode4* __restrict__ nodes, int& cur, 
             if (fl.w & RT_TLAS_NO_TMAX) t3 = RT_INF;
         }
         float n0, n1, n2, n3; bool h0, h1, h2, h3;
-        RT_SLAB4(link.x, lox.x, loy.x, loz.x, hix.x, hiy.x, hiz.x, t0, n0, h0)
-        RT_SLAB4(link.y, lox.y, loy.y, loz.y, hix.y, hiy.y, hiz.y, t1, n1, h1)
-        RT_SLAB4(link.z, lox.z, loy.z, loz.z, hix.z, hiy.z, hiz.z, t2, n2, h2)
-        RT_SLAB4(link.w, lox.w, loy.w, loz.w, hix.w, hiy.w, hiz.w, t3, n3, h3)
+        RT_SLAB4(pnx.x, pny.x, pnz.x, pfx.x, pfy.x, pfz.x, t0, n0, h0)
+        RT_SLAB4(pnx.y, pny.y, pnz.y, pfx.y, pfy.y, pfz.y, t1, n1, h1)
+        RT_SLAB4(pnx.z, pny.z, pnz.z, pfx.z, pfy.z, pfz.z, t2, n2, h2)
+        RT_SLAB4(pnx.w, pny.w, pnz.w, pfx.w, pfy.w, pfz.w, t3, n3, h3)
         if (ORDERED) {
             // sort (entry distance, slot) keys: entry distances are >= tmin >= 0, so their bit patterns order as integers
             unsigned k0 = h0 ? ((as_uint(n0) & 0x7ffffffcu) | 0u) : 0xffffffffu;
@@ -281,15 +289,13 @@ RT_HD void mesh_visit(TraceCtx& cx, const DevMesh* m, const RayInv& ri, float tm
             cur = stk_pop(cx, sp);
         }
         const BvhNode4* np = nodes + cur;
-        const float4 lox = ld4(&np->lox), loy = ld4(&np->loy), loz = ld4(&np->loz);
-        const float4 hix = ld4(&np->hix), hiy = ld4(&np->hiy), hiz = ld4(&np->hiz);
-        const int4 link = RT_LDG(&np->link);
+        RT_LOAD_NODE4(np)
         cx.tally.nodes++;
         float n0, n1, n2, n3; bool h0, h1, h2, h3;
-        RT_SLAB4(link.x, lox.x, loy.x, loz.x, hix.x, hiy.x, hiz.x, tmax, n0, h0)
-        RT_SLAB4(link.y, lox.y, loy.y, loz.y, hix.y, hiy.y, hiz.y, tmax, n1, h1)
-        RT_SLAB4(link.z, lox.z, loy.z, loz.z, hix.z, hiy.z, hiz.z, tmax, n2, h2)
-        RT_SLAB4(link.w, lox.w, loy.w, loz.w, hix.w, hiy.w, hiz.w, tmax, n3, h3)
+        RT_SLAB4(pnx.x, pny.x, pnz.x, pfx.x, pfy.x, pfz.x, tmax, n0, h0)
+        RT_SLAB4(pnx.y, pny.y, pnz.y, pfx.y, pfy.y, pfz.y, tmax, n1, h1)
+        RT_SLAB4(pnx.z, pny.z, pnz.z, pfx.z, pfy.z, pfz.z, tmax, n2, h2)
+        RT_SLAB4(pnx.w, pny.w, pnz.w, pfx.w, pfy.w, pfz.w, tmax, n3, h3)
         // leaf children: their triangles are tested here and now
         unsigned lm = (h0 && link.x < 0 ? 1u : 0u) | (h1 && link.y < 0 ? 2u : 0u) | (h2 && link.z < 0 ? 4u : 0u) | (h3 && link.w < 0 ? 8u : 0u);
         h0 = h0 && link.x >= 0; h1 = h1 && link.y >= 0; h2 = h2 && link.z >= 0; h3 = h3 && link.w >= 0;

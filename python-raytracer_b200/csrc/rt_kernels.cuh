@@ -114,6 +114,7 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS_HIT) k_hit(SceneView S
                                                                      RayQueue qin, const unsigned long long* qin_count,
                                                                      HitPlanes H, RtCounters* counters) {
     Tally tally = tally_zero();
+    int spill[RT_STACK_SPILL];       // overflow of the shared-memory traversal stack (thread-local memory)
     unsigned long long n_primary = 0;
     const int N = S.D * S.S * S.T;
     const long long n = PRIMARY ? n_rays : (long long)*qin_count;
@@ -135,7 +136,7 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS_HIT) k_hit(SceneView S
         }
         Hit hit;
         if (live) {
-            TraceCtx cx{S, time, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x};
+            TraceCtx cx{S, time, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill};
             live = closest_hit<HAS_NODES>(cx, ray, hit);
         }
         if (live) {
@@ -155,6 +156,7 @@ template <bool HAS_NODES>
 __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS_SHADOW) k_shadow(SceneView S, long long n_rays, const unsigned long long* n_dev,
                                                                            HitPlanes H, uint8_t* __restrict__ occ, RtCounters* counters) {
     Tally tally = tally_zero();
+    int spill[RT_STACK_SPILL];       // overflow of the shared-memory traversal stack (thread-local memory)
     const long long n = n_dev ? (long long)*n_dev : n_rays;
     const long long total = n * S.n_lights;
     const long long stride = (long long)gridDim.x * blockDim.x;
@@ -163,7 +165,7 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS_SHADOW) k_shadow(Scene
         const long long i = j - (long long)li * n;
         const float4 h0 = H.planes[0 * H.cap + i];
         if (h0.w != h0.w) continue;                                   // no hit: no shadow rays
-        TraceCtx cx{S, h0.w, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x};
+        TraceCtx cx{S, h0.w, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill};
         occ[(long long)li * H.cap + i] = light_occluded<HAS_NODES>(cx, f3(h0), li) ? 1 : 0;
     }
     tally_flush(tally, 0, 0, counters);
@@ -196,7 +198,7 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS_SHADE) k_shade(SceneVi
                 Hit hit; hit.p = f3(h0); hit.n = f3(h1); hit.mat = as_int(h1.w); hit.geom = as_int(h2.w); hit.t = 0.0f;
                 time = h0.w;
                 ps.ray.d = f3(h2);
-                TraceCtx cx{S, time, tally, nullptr, 0};
+                TraceCtx cx{S, time, tally, nullptr, 0, nullptr};
                 cont = shade_level(cx, ps, hit, [&](int li) { return li < 32 ? ((lit_mask >> li) & 1u) != 0 : occ[(long long)li * H.cap + i] == 0; }, sample);
             }
             if (!cont) samples[slot] = f4(sample.x, sample.y, sample.z, 0.0f);
@@ -260,12 +262,13 @@ __global__ void __launch_bounds__(RT_BLOCK) k_trace(SceneView S, long long n, co
                                                      const float* __restrict__ times, float* rgb, float* hit_t, float* hit_n, float* hit_p,
                                                      int* hit_geom, int* hit_mat, RtCounters* counters) {
     Tally tally = tally_zero();
+    int spill[RT_STACK_SPILL];       // overflow of the shared-memory traversal stack (thread-local memory)
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) {
         PathState ps;
         ps.ray.o = f3(org[3 * i], org[3 * i + 1], org[3 * i + 2]);
         ps.ray.d = f3(dir[3 * i], dir[3 * i + 1], dir[3 * i + 2]);
-        TraceCtx cx{S, times[i], tally, rt_smem_stack + threadIdx.x, (int)blockDim.x};
+        TraceCtx cx{S, times[i], tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill};
         Hit h;
         if (closest_hit<HAS_NODES>(cx, ps.ray, h)) {
             hit_t[i] = h.t; hit_geom[i] = h.geom; hit_mat[i] = h.mat;
@@ -288,10 +291,11 @@ __global__ void __launch_bounds__(RT_BLOCK) k_occluded(SceneView S, long long n,
                                                         const float* __restrict__ times, const float* __restrict__ tmax, int* occ,
                                                         RtCounters* counters) {
     Tally tally = tally_zero();
+    int spill[RT_STACK_SPILL];       // overflow of the shared-memory traversal stack (thread-local memory)
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) {
         Ray r; r.o = f3(org[3 * i], org[3 * i + 1], org[3 * i + 2]); r.d = f3(dir[3 * i], dir[3 * i + 1], dir[3 * i + 2]);
-        TraceCtx cx{S, times[i], tally, rt_smem_stack + threadIdx.x, (int)blockDim.x};
+        TraceCtx cx{S, times[i], tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill};
         occ[i] = occluded<HAS_NODES>(cx, r, tmax[i]) ? 1 : 0;
     }
     tally_flush(tally, 0, 0, counters);

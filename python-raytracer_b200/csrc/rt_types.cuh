@@ -53,7 +53,7 @@ struct __attribute__((aligned(16))) BvhNode { float4 q0, q1, q2, q3; };
 
 // Traversal node: 4-wide, 128 B = one cache line, boxes of the (up to) four children in SoA so the four slab
 // tests vectorise over registers; link >= 0: node index, < 0: ~leaf (triangle slot / object index),
-// RT_LINK_NONE: empty slot (skipped by the walk).  flags: per-child bits (object BVH only).
+// RT_LINK_NONE: empty slot, box [+inf, -inf] (never hit).  The walk addresses the planes by byte offset (RayInv).  flags: per-child bits (object BVH only).
 #define RT_LINK_NONE 0x7fffffff
 struct __attribute__((aligned(16))) BvhNode4 { float4 lox, loy, loz, hix, hiy, hiz; int4 link; int4 flags; };
 

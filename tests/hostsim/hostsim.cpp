@@ -127,7 +127,7 @@ static void render_px(const Sim& sim, const SceneView& V, const int32_t* cols, c
 #pragma omp parallel
     {
         Tally tally{}; uint64_t primary = 0;
-        int stack[RT_STACK_DEPTH];
+        int stack[RT_STACK_DEPTH], spill[RT_STACK_SPILL];
 #pragma omp for schedule(dynamic, 16)
         for (int64_t i = 0; i < n; i++) {
             float3 colour = f3(0, 0, 0);
@@ -136,7 +136,7 @@ static void render_px(const Sim& sim, const SceneView& V, const int32_t* cols, c
                     Ray ray = generate_ray(V, cols[i], rows[i], d, s);
                     for (int t = 0; t < V.T; t++) {
                         PathState ps; ps.ray = ray; ps.fold = fold_identity(); ps.depth_left = V.max_depth; ps.in_shape = 0;
-                        TraceCtx cx{V, V.times[t], tally, stack, 1};
+                        TraceCtx cx{V, V.times[t], tally, stack, 1, spill};
                         float3 sample;
                         primary++;
                         while (trace_level<HN>(cx, ps, sample)) {}
@@ -172,12 +172,12 @@ extern "C" int hostsim_node_counts(const RtSceneDesc* d, const int32_t* cols, co
     const int N = V.D * V.S * V.T;
 #pragma omp parallel for schedule(dynamic, 16)
     for (int64_t i = 0; i < n; i++) {
-        int stack[RT_STACK_DEPTH];
+        int stack[RT_STACK_DEPTH], spill[RT_STACK_SPILL];
         for (int slot = 0; slot < N; slot++) {
             const int t = slot % V.T, ds = slot / V.T, s = ds % V.S, dd = ds / V.S;
             Tally tally{};
             PathState ps; ps.ray = generate_ray(V, cols[i], rows[i], dd, s); ps.fold = fold_identity(); ps.depth_left = V.max_depth; ps.in_shape = 0;
-            TraceCtx cx{V, V.times[t], tally, stack, 1};
+            TraceCtx cx{V, V.times[t], tally, stack, 1, spill};
             float3 sample;
             if (sim.hs.has_nodes) trace_level<true>(cx, ps, sample); else trace_level<false>(cx, ps, sample);
             out[i * N + slot] = tally.nodes;
