@@ -79,7 +79,7 @@ class Scene:
         job.rank, job.world = int(rank), int(world)
         job.direct = 1 if direct else 0
         job.mesh_mode = int(mesh_mode)
-        job.max_batch_rays = int(max_batch_rays)
+        job.max_batch_rays = int(max_batch_rays or getattr(self, "max_batch_rays", 0))
         return job
 
     def render(self, subimage: int = 0, tasks: int = 1) -> np.ndarray:

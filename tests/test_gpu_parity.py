@@ -212,3 +212,24 @@ def test_synthetic_mesh_scene_sampled_parity_and_bvh_equivalence():
     ref, _ = oracle.render(sc.flatten(), abi)
     frac, dmax, _ = parity_stats(to_png_array(ref), to_png_array(a))
     assert frac >= PARITY_FRACTION, (frac, dmax)
+
+
+@pytest.mark.parametrize("case,over", [
+    ("DepthOfField", {"resolution": [1920, 1080], "DOF": {"samples": 64}, "AA": {"jitter": True, "samples": 1}}),
+    ("MotionBlur", {"resolution": [1920, 1080], "motion": {"time": 2.0, "samples": 63, "final": 1}}),
+])
+def test_config4_1080p_64spp_sampled_parity(case, over):
+    """BASELINE.json configs[3]: thin-lens DOF / motion blur at 1920x1080 x 64 samples (132.7 M primary rays, several
+    wavefront batches).  Full frame on the GPU; parity on 3000 random pixels (all 64 samples each) against the oracle."""
+    sc = load_case(case, over)
+    assert sc.vc.dof_samples * sc.samples * len(sc.vc.motion_times) == 64
+    img = sc.render_region(0, 1920, 0, 1080)
+    c = dict(sc.last_counters)
+    assert c["rays_primary"] == 1920 * 1080 * 64 and c["error_flags"] == 0
+    rng = np.random.default_rng(5)
+    cols, rows = rng.integers(0, 1920, 3000), rng.integers(0, 1080, 3000)
+    ref, _ = oracle.render_pixels(sc.flatten(), abi, cols, rows)
+    a = (np.asarray(img[cols, rows], dtype=np.float64) * 255).astype(np.uint8).astype(int)
+    b = (ref * 255).astype(np.uint8).astype(int)
+    frac = float((np.abs(a - b).max(axis=1) <= 1).mean())
+    assert frac >= PARITY_FRACTION, (case, frac)
