@@ -233,6 +233,11 @@ int rt_assemble_tiles(const RtRenderJob* job, const float* d_gathered, const int
 /* Replaces main.py:31-33 / glue.py:23-25: rot90 + (image*255) truncation, (ncols,nrows,3) f32 -> (nrows,ncols,3) u8 */
 int rt_finalize_u8(const float* d_image, int32_t ncols, int32_t nrows, uint8_t* d_out_u8, void* stream);
 
+/* Scene.render() + main.py:31-33 in one call, HOST output already in PNG layout: renders the whole region of `job`
+ * (world must be 1), converts on the device (rot90 + *255 truncation) and copies (nrows, ncols, 3) uint8 to h_out_u8:
+ * a quarter of the float image's bytes cross PCIe.  Synchronous. */
+int rt_render_u8_host(RtScene* scene, const RtRenderJob* job, uint8_t* h_out_u8, RtCounters* counters, void* stream);
+
 int rt_scene_destroy(RtScene* scene);
 
 /* Introspection used by tests and the bench */

@@ -58,6 +58,7 @@ struct RtScene {
     unsigned long long* d_qcount = nullptr;   // [max_depth + 1]
     RtCounters* d_counters = nullptr;
     float* d_stage = nullptr; long long stage_cap = 0;   // rt_render_host staging
+    uint8_t* d_stage_u8 = nullptr; long long stage_u8_cap = 0;
     int device = 0;
     int sm_count = 148;
     unsigned long long last_launches = 0;
@@ -171,6 +172,7 @@ extern "C" int rt_scene_destroy(RtScene* sc) {
     if (sc->d_hit) cudaFree(sc->d_hit);
     if (sc->d_occ) cudaFree(sc->d_occ);
     if (sc->d_stage) cudaFree(sc->d_stage);
+    if (sc->d_stage_u8) cudaFree(sc->d_stage_u8);
     drain_events(sc);
     delete sc;
     return RT_OK;
@@ -433,6 +435,24 @@ extern "C" int rt_render_host(RtScene* sc, const RtRenderJob* job, float* h_out,
     if (counters) CU(cudaMemcpyAsync(cls, sc->d_counters, sizeof cls, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     if (counters) { sum_counters(cls, counters); counters->kernel_launches = sc->last_launches; }
+    return RT_OK;
+}
+
+extern "C" int rt_render_u8_host(RtScene* sc, const RtRenderJob* job, uint8_t* h_out, RtCounters* counters, void* stream) {
+    if (!sc || !h_out || !job) return fail(RT_ERR_INVALID, "null argument");
+    if (job->world != 1) return fail(RT_ERR_INVALID, "rt_render_u8_host renders a whole region (world must be 1)");
+    RtRenderJob j = *job; j.direct = 1;
+    const long long n = (long long)j.ncols * j.nrows * 3;
+    UP(grow(&sc->d_stage, &sc->stage_cap, std::max<long long>(n, 1)));
+    UP(grow(&sc->d_stage_u8, &sc->stage_u8_cap, std::max<long long>(n, 1)));
+    cudaStream_t st = (cudaStream_t)stream;
+    UP(rt_render(sc, &j, sc->d_stage, nullptr, stream));
+    UP(rt_finalize_u8(sc->d_stage, j.ncols, j.nrows, sc->d_stage_u8, stream));
+    CU(cudaMemcpyAsync(h_out, sc->d_stage_u8, (size_t)n, cudaMemcpyDeviceToHost, st));
+    RtCounters cls[RT_COUNTER_CLASSES];
+    if (counters) CU(cudaMemcpyAsync(cls, sc->d_counters, sizeof cls, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (counters) { sum_counters(cls, counters); counters->kernel_launches = sc->last_launches + 1; }
     return RT_OK;
 }
 

@@ -101,10 +101,29 @@ class Scene:
         rc = self._lib.rt_render_host(h, C.byref(job), out.ctypes.data, C.byref(ctr), stream)
         _abi.check(self._lib, rc, "rt_render_host")
         self.last_counters = ctr.as_dict()
+        self._raise_flags(ctr)
+        return out
+
+    def _raise_flags(self, ctr):
         if ctr.error_flags & (1 << 4):
             raise IndexError("list index out of range (a shaded hit had no material; geometry/__init__.py:57)")
         if ctr.error_flags & (1 << 5):
             raise _abi.B200RTError("RT_ERR_LIMIT: the scene exceeds a compiled limit (traversal stack or CSG nesting depth)")
+
+    def render_u8(self, subimage: int = 0, tasks: int = 1, stream=None) -> np.ndarray:
+        """`render()` followed by main.py:31-33 (rot90, *255 truncated to uint8), converted ON THE DEVICE
+        (`rt_render_u8_host`): returns the (H, W_sub, 3) uint8 array `PIL.Image.fromarray` takes."""
+        width = self.strip_columns(subimage, tasks)
+        out = np.empty((self.vc.height, len(width), 3), dtype=np.uint8)
+        if len(width) == 0:
+            return out
+        h = self.upload(stream)
+        job = self.make_job(int(width[0]), len(width), 0, self.vc.height)
+        ctr = _abi.RtCounters()
+        rc = self._lib.rt_render_u8_host(h, C.byref(job), out.ctypes.data, C.byref(ctr), stream)
+        _abi.check(self._lib, rc, "rt_render_u8_host")
+        self.last_counters = ctr.as_dict()
+        self._raise_flags(ctr)
         return out
 
     def render_device(self, d_out_ptr, job, counters=None, stream=None):

@@ -104,6 +104,28 @@ def test_finalize_u8_equals_main_py_conversion(lib):
     assert np.array_equal(d_u8.cpu().numpy(), to_png_array(img))
 
 
+def test_render_u8_and_cli_equal_main_py_output(tmp_path):
+    """Device-side rot90 + *255 truncation (rt_render_u8_host) == main.py:31-33 applied to render(); the CLI writes that PNG,
+    and strips saved by `main --subimage` glue back to the same image (render.nu:10-15)."""
+    from PIL import Image
+    from python_raytracer_b200 import cli
+    import os
+    sc = load_case("MotionBlur")
+    want = to_png_array(sc.render())
+    assert np.array_equal(sc.render_u8(), want)
+    assert np.array_equal(np.concatenate([sc.render_u8(n, 3) for n in range(3)], axis=1), want)
+    scene_json = os.path.join(os.path.dirname(__file__), "golden", "scenes", "TwoSpheresPlane.json")
+    png = tmp_path / "a.png"
+    assert cli.main(["main", "--infile", scene_json, "--outfile", str(png)]) == 0
+    assert np.array_equal(np.array(Image.open(png)), golden_png("TwoSpheresPlane")) or \
+        parity_stats(np.array(Image.open(png)), golden_png("TwoSpheresPlane"))[0] >= PARITY_FRACTION
+    os.makedirs(tmp_path / "temp")
+    for n in range(4):
+        assert cli.main(["main", "--infile", scene_json, "--outfile", str(tmp_path / "temp" / str(n)), "--subimage", str(n), "--tasks", "4"]) == 0
+    assert cli.main(["glue", "--dir", str(tmp_path / "temp"), "--outfile", str(tmp_path / "g.png")]) == 0
+    assert np.array_equal(np.array(Image.open(tmp_path / "g.png")), np.array(Image.open(png)))
+
+
 def test_bvh_traversal_equals_brute_force_on_device():
     for case in ("TorusMesh_flat", "TorusMesh_smooth"):
         sc = load_case(case)

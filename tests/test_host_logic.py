@@ -230,6 +230,19 @@ def test_lbvh_structure_is_a_valid_tree():
                 assert (lo[c][:, used].min(axis=1) >= lo[i][:, k] - 1e-6).all() and (hi[c][:, used].max(axis=1) <= hi[i][:, k] + 1e-6).all()
 
 
+def test_cli_glue_matches_glue_py(tmp_path):
+    """glue.py:17-26: strips sorted by int(stem) (10.npy after 9.npy), concatenated on axis 0, rot90, *255 truncated."""
+    from python_raytracer_b200 import cli
+    from PIL import Image
+    rng = np.random.default_rng(3)
+    full = rng.random((23, 7, 3))
+    for n, part in enumerate(np.array_split(full, 11, axis=0)):
+        np.save(tmp_path / f"{n}.npy", part)
+    out = tmp_path / "o.png"
+    assert cli.main(["glue", "--dir", str(tmp_path), "--outfile", str(out)]) == 0
+    assert np.array_equal(np.array(Image.open(out)), to_png_array(full))
+
+
 def test_tile_interleave_partitions_the_region():
     for (ncols, nrows, tw, th, world) in [(640, 480, 8, 8, 1), (37, 23, 8, 8, 3), (5, 3, 8, 8, 2), (64, 64, 16, 4, 8)]:
         seen = np.zeros((ncols, nrows), int)
