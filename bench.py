@@ -43,6 +43,7 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--batch-rays", type=int, default=0, help="rays per wavefront batch (0 = library default)")
+    ap.add_argument("--mode-bits", type=int, default=0, help="RtRenderJob.mesh_mode test-aid bits OR-ed into every job (tuning experiments)")
     return ap.parse_args()
 
 
@@ -207,6 +208,7 @@ def run_ours(a):
     t_bvh = time.perf_counter() - t0
     sc._lib, sc._handle = lib, h
     sc.max_batch_rays = a.batch_rays
+    sc.debug_mode_bits = a.mode_bits
 
     sharder = TileSharder(sc, rank, world)
     W, H = a.width, a.height

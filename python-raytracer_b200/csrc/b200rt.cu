@@ -357,11 +357,15 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
     if (smem) {
         CU(cudaFuncSetAttribute(k_hit<HAS_NODES, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         CU(cudaFuncSetAttribute(k_hit<HAS_NODES, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        CU(cudaFuncSetAttribute(k_shadow<HAS_NODES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CU(cudaFuncSetAttribute(k_shadow<HAS_NODES, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CU(cudaFuncSetAttribute(k_shadow<HAS_NODES, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     }
     const int direct = (job->direct && job->world == 1) ? 1 : 0;
     const int max_grid = sc->sm_count * 16;
     HitPlanes H{sc->d_hit, sc->hit_cap};
+    PixelMap pmk = pm;                                   // + the sample-slot divisors of this scene
+    pmk.fd_N = make_fastdiv((unsigned)N); pmk.fd_T = make_fastdiv((unsigned)V.T); pmk.fd_S = make_fastdiv((unsigned)V.S);
+
     // the hit/occlusion planes are indexed with the stride of their allocation; occ planes use H.cap as stride
     for (long long p0 = 0; p0 < pm.n_local_pixels; p0 += px_per_batch) {
         const long long npx = std::min(px_per_batch, pm.n_local_pixels - p0);
@@ -369,12 +373,12 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
         CU(cudaMemsetAsync(sc->d_qcount, 0, sizeof(unsigned long long) * (size_t)(V.max_depth + 2), st));
         RayQueue q0{sc->d_queue[0], sc->queue_cap}, q1{sc->d_queue[1], sc->queue_cap};
         const int grid = (int)std::min<long long>((n_rays + RT_BLOCK - 1) / RT_BLOCK, max_grid);
-        const int grid_sh = (int)std::min<long long>((n_rays * V.n_lights + RT_BLOCK - 1) / RT_BLOCK, max_grid);
+        const int grid_sh = grid;
         {   // level 0: generated rays
             { ProfScope ps_(sc, 0, st);
-              k_hit<HAS_NODES, true><<<grid, RT_BLOCK, smem, st>>>(V, pm, p0, n_rays, q0, nullptr, H, sc->d_counters + 0); }
+              k_hit<HAS_NODES, true><<<grid, RT_BLOCK, smem, st>>>(V, pmk, p0, n_rays, q0, nullptr, H, sc->d_counters + 0); }
             if (V.n_lights > 0) { ProfScope ps_(sc, 1, st);
-              k_shadow<HAS_NODES><<<std::max(1, grid_sh), RT_BLOCK, smem, st>>>(V, n_rays, nullptr, H, sc->d_occ, sc->d_counters + 1); (*launches)++; }
+              k_shadow<HAS_NODES, false><<<grid_sh, RT_BLOCK, smem, st>>>(V, n_rays, nullptr, H, sc->d_occ, sc->d_counters + 1); (*launches)++; }
             { ProfScope ps_(sc, 2, st);
               k_shade<true><<<grid, RT_BLOCK, 0, st>>>(V, n_rays, q0, nullptr, H, sc->d_occ, sc->d_samples, q0, sc->d_qcount, sc->d_counters + 2); }
             (*launches) += 2;
@@ -385,8 +389,8 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
                 RayQueue& qout = (level & 1) ? q1 : q0;
                 const unsigned long long* n_in = sc->d_qcount + (level - 1);
                 ProfScope ps_(sc, 3, st);
-                k_hit<HAS_NODES, false><<<max_grid, RT_BLOCK, smem, st>>>(V, pm, 0, 0, qin, n_in, H, sc->d_counters + 3);
-                if (V.n_lights > 0) { k_shadow<HAS_NODES><<<max_grid, RT_BLOCK, smem, st>>>(V, 0, n_in, H, sc->d_occ, sc->d_counters + 3); (*launches)++; }
+                k_hit<HAS_NODES, false><<<max_grid, RT_BLOCK, smem, st>>>(V, pmk, 0, 0, qin, n_in, H, sc->d_counters + 3);
+                if (V.n_lights > 0) { k_shadow<HAS_NODES, true><<<dim3((unsigned)std::max(1, max_grid / V.n_lights), (unsigned)V.n_lights), RT_BLOCK, smem, st>>>(V, 0, n_in, H, sc->d_occ, sc->d_counters + 3); (*launches)++; }
                 k_shade<false><<<max_grid, RT_BLOCK, 0, st>>>(V, 0, qin, n_in, H, sc->d_occ, sc->d_samples, qout, sc->d_qcount + level, sc->d_counters + 3);
                 (*launches) += 2;
             }

@@ -161,7 +161,13 @@ RT_HD bool tri_shadow(float3 v0, float3 v1, float3 v2, const Ray& r) {
 // non-negative direction component, hi planes otherwise); the exit planes are at (nx ^ 48), (80 - ny), (112 - nz).
 // Picking near/far by address removes the per-box min/max of the classic slab test.
 struct RayInv { float3 inv, oinv; int nx, ny, nz; };
-RT_HD float safe_rcp(float d) { return fabsf(d) >= 8.673617e-19f ? 1.0f / d : copysignf(1.1529215e18f, d); }
+// the reciprocal only scales conservative (padded) box tests: the 1-ulp MUFU.RCP is enough on the device
+#if defined(__CUDA_ARCH__)
+#define RT_RCP(x) __fdividef(1.0f, (x))
+#else
+#define RT_RCP(x) (1.0f / (x))
+#endif
+RT_HD float safe_rcp(float d) { return fabsf(d) >= 8.673617e-19f ? RT_RCP(d) : copysignf(1.1529215e18f, d); }
 RT_HD RayInv ray_inv(const Ray& r) {
     RayInv ri;
     ri.inv = f3(safe_rcp(r.d.x), safe_rcp(r.d.y), safe_rcp(r.d.z));
@@ -945,21 +951,45 @@ RT_HD Ray generate_ray(const SceneView& S, int col, int row, int d, int s) {
 
 // ------------------------------------------------------------------------------------------------
 // Which pixels a launch covers (see RtRenderJob in include/b200rt.h)
+// Division of a 32-bit unsigned by a launch-invariant divisor without the divide sequence (Granlund-Montgomery):
+// q = (t + ((n - t) >> s1)) >> s2 with t = mulhi(n, mul).  The index arithmetic of one ray (pixel, tile, sample slots) is six
+// divisions; as plain 64-bit '/' and '%' they were a fifth of k_hit's instructions on a scene with nothing to intersect.
+struct FastDiv { unsigned mul, s1, s2, d; };
+RT_HD unsigned umulhi32(unsigned a, unsigned b) {
+#if defined(__CUDA_ARCH__)
+    return __umulhi(a, b);
+#else
+    return (unsigned)(((unsigned long long)a * b) >> 32);
+#endif
+}
+RT_HD unsigned fdiv(unsigned n, const FastDiv& f) { const unsigned t = umulhi32(n, f.mul); return (t + ((n - t) >> f.s1)) >> f.s2; }
+inline FastDiv make_fastdiv(unsigned d) {
+    FastDiv f; f.d = d < 1 ? 1 : d;
+    unsigned l = 0; while ((1ull << l) < f.d) l++;                          // ceil(log2 d)
+    f.mul = (unsigned)(((1ull << 32) * ((1ull << l) - f.d)) / f.d + 1);
+    f.s1 = l < 1 ? l : 1; f.s2 = l < 1 ? 0 : l - 1;
+    return f;
+}
+
 struct PixelMap {
     int col0, ncols, row0, nrows;
     int tile_w, tile_h, rank, world;
     int n_tile_rows;            // tiles per tile-column
     int tile_px;                // tile_w * tile_h
-    long long n_local_pixels;   // n_local_tiles * tile_px (partial tiles padded)
+    long long n_local_pixels;   // n_local_tiles * tile_px (partial tiles padded); < 2^31
+    FastDiv fd_tile_px, fd_tile_rows, fd_tile_w;      // filled by make_pixel_map
+    FastDiv fd_N, fd_T, fd_S;                         // samples per pixel, motion times, AA samples: filled by the renderer
 };
 
-RT_HD bool pixel_of(const PixelMap& pm, long long lp, int& col, int& row) {
-    long long lt = lp / pm.tile_px;
-    int q = (int)(lp - lt * pm.tile_px);
-    long long gt = lt * pm.world + pm.rank;
-    int tcol = (int)(gt / pm.n_tile_rows), trow = (int)(gt - (long long)tcol * pm.n_tile_rows);
-    col = pm.col0 + tcol * pm.tile_w + q % pm.tile_w;
-    row = pm.row0 + trow * pm.tile_h + q / pm.tile_w;
+// local pixel slot lp (compact tile order of this rank) -> (col, row); false for the padding of partial tiles
+RT_HD bool pixel_of(const PixelMap& pm, unsigned lp, int& col, int& row) {
+    const unsigned lt = fdiv(lp, pm.fd_tile_px);
+    const unsigned q = lp - lt * (unsigned)pm.tile_px;
+    const unsigned gt = lt * (unsigned)pm.world + (unsigned)pm.rank;
+    const unsigned tcol = fdiv(gt, pm.fd_tile_rows), trow = gt - tcol * (unsigned)pm.n_tile_rows;
+    const unsigned qr = fdiv(q, pm.fd_tile_w), qc = q - qr * (unsigned)pm.tile_w;
+    col = pm.col0 + (int)(tcol * (unsigned)pm.tile_w + qc);
+    row = pm.row0 + (int)(trow * (unsigned)pm.tile_h + qr);
     return col < pm.col0 + pm.ncols && row < pm.row0 + pm.nrows;
 }
 

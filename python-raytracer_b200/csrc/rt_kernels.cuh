@@ -117,18 +117,19 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS_HIT) k_hit(SceneView S
     int spill[RT_STACK_SPILL];       // overflow of the shared-memory traversal stack (thread-local memory)
     unsigned long long n_primary = 0;
     const int N = S.D * S.S * S.T;
+    (void)N;
     const long long n = PRIMARY ? n_rays : (long long)*qin_count;
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         Ray ray; float time; bool live = true;
         if (PRIMARY) {
-            const long long lp = pixel_begin + i / N;
-            const int slot = (int)(i % N);
+            const unsigned iu = (unsigned)i;                                   // a batch holds < 2^30 rays
+            const unsigned px = fdiv(iu, pm.fd_N), slot = iu - px * (unsigned)N;
             int col, row;
-            live = pixel_of(pm, lp, col, row) && S.max_depth > 0;
-            const int t = slot % S.T, ds = slot / S.T;
-            const int s = ds % S.S, d = ds / S.S;
-            if (live) { ray = generate_ray(S, col, row, d, s); n_primary++; }
+            live = pixel_of(pm, (unsigned)pixel_begin + px, col, row) && S.max_depth > 0;
+            const unsigned ds = fdiv(slot, pm.fd_T), t = slot - ds * (unsigned)S.T;
+            const unsigned d = fdiv(ds, pm.fd_S), s = ds - d * (unsigned)S.S;
+            if (live) { ray = generate_ray(S, col, row, (int)d, (int)s); n_primary++; }
             time = RT_LDG(S.times + t);
         } else {
             const float4 p0 = qin.planes[0 * qin.cap + i], p1 = qin.planes[1 * qin.cap + i];
@@ -151,23 +152,24 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS_HIT) k_hit(SceneView S
 }
 
 // ---- stage 2: shadow rays (scene.py:148-167) -------------------------------------------------------------
-// thread = (light li, ray i), li slowest so a warp works on ONE light and 32 neighbouring hit points
-template <bool HAS_NODES>
+// light-major: a warp works on ONE light and 32 neighbouring hit points
+// LIGHT_ROWS: gridDim.y = lights (small queues of the deeper levels: every (light, ray) pair gets its own thread);
+// otherwise the whole grid sweeps the rays once per light (big level-0 batches: all resident warps on one light).
+template <bool HAS_NODES, bool LIGHT_ROWS>
 __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS_SHADOW) k_shadow(SceneView S, long long n_rays, const unsigned long long* n_dev,
                                                                            HitPlanes H, uint8_t* __restrict__ occ, RtCounters* counters) {
     Tally tally = tally_zero();
     int spill[RT_STACK_SPILL];       // overflow of the shared-memory traversal stack (thread-local memory)
     const long long n = n_dev ? (long long)*n_dev : n_rays;
-    const long long total = n * S.n_lights;
     const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x; j < total; j += stride) {
-        const int li = (int)(j / n);
-        const long long i = j - (long long)li * n;
-        const float4 h0 = H.planes[0 * H.cap + i];
-        if (h0.w != h0.w) continue;                                   // no hit: no shadow rays
-        TraceCtx cx{S, h0.w, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill};
-        occ[(long long)li * H.cap + i] = light_occluded<HAS_NODES>(cx, f3(h0), li) ? 1 : 0;
-    }
+    const int li0 = LIGHT_ROWS ? (int)blockIdx.y : 0, li1 = LIGHT_ROWS ? li0 + 1 : S.n_lights;
+    for (int li = li0; li < li1; li++)                                     // light-major without an index division: the whole grid
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {   // sweeps the rays once per light
+            const float4 h0 = H.planes[0 * H.cap + i];
+            if (h0.w != h0.w) continue;                                   // no hit: no shadow rays
+            TraceCtx cx{S, h0.w, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill};
+            occ[(long long)li * H.cap + i] = light_occluded<HAS_NODES>(cx, f3(h0), li) ? 1 : 0;
+        }
     tally_flush(tally, 0, 0, counters);
 }
 
@@ -215,7 +217,7 @@ __global__ void k_resolve(PixelMap pm, long long pixel_begin, int n_pixels, int 
                           float* __restrict__ out, int direct) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n_pixels) return;
-    const long long lp = pixel_begin + p;
+    const unsigned lp = (unsigned)(pixel_begin + p);
     int col, row;
     const bool valid = pixel_of(pm, lp, col, row);
     float3 c = f3(0, 0, 0);

@@ -300,6 +300,10 @@ inline bool make_pixel_map(const RtRenderJob* job, PixelMap& pm, long long& n_lo
     const long long n_tiles = (job->ncols == 0 || job->nrows == 0) ? 0 : n_tile_cols * pm.n_tile_rows;
     n_local_tiles = n_tiles > job->rank ? (n_tiles - job->rank + job->world - 1) / job->world : 0;
     pm.n_local_pixels = n_local_tiles * pm.tile_px;
+    if (pm.n_local_pixels >= (1ll << 31) || n_tiles * (long long)std::max(1, job->world) >= (1ll << 31)) return false;   // 32-bit pixel slots
+    pm.fd_tile_px = make_fastdiv((unsigned)pm.tile_px); pm.fd_tile_rows = make_fastdiv((unsigned)pm.n_tile_rows);
+    pm.fd_tile_w = make_fastdiv((unsigned)pm.tile_w);
+    pm.fd_N = pm.fd_T = pm.fd_S = make_fastdiv(1);
     return true;
 }
 }  // namespace rtb

@@ -78,7 +78,7 @@ class Scene:
         job.tile_w, job.tile_h = self.tile
         job.rank, job.world = int(rank), int(world)
         job.direct = 1 if direct else 0
-        job.mesh_mode = int(mesh_mode)
+        job.mesh_mode = int(mesh_mode) | int(getattr(self, "debug_mode_bits", 0))
         job.max_batch_rays = int(max_batch_rays or getattr(self, "max_batch_rays", 0))
         return job
 

@@ -204,7 +204,7 @@ extern "C" long long hostsim_job_pixels(const RtRenderJob* job, int32_t* cols, i
     if (cols)
         for (long long lp = 0; lp < pm.n_local_pixels; lp++) {
             int c, r;
-            valid[lp] = pixel_of(pm, lp, c, r) ? 1 : 0;
+            valid[lp] = pixel_of(pm, (unsigned)lp, c, r) ? 1 : 0;
             cols[lp] = c; rows[lp] = r;
         }
     return pm.n_local_pixels;
