@@ -57,7 +57,32 @@ def report(path, out):
                 out.write(f"{k:90s} {r[i]:>16s} {u[i]}\n")
 
 
+def traffic(workload, paths):
+    """profiles/traffic.json: "<kernel>@<WxHxspp>" -> dram__bytes_read.sum + dram__bytes_write.sum of ONE launch
+    (bench.py reports it as roofline.traffic for the same workload)."""
+    import json
+    import os
+    unit_scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    dst = "profiles/traffic.json"
+    table = json.load(open(dst)) if os.path.exists(dst) else {}
+    for path in paths:
+        raw = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+        rows = list(csv.reader(raw.splitlines()))
+        h, u, r = rows[0], rows[1], rows[2]
+        tot = 0.0
+        for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+            i = h.index(k)
+            tot += float(r[i].replace(",", "")) * unit_scale[u[i]]
+        kern = r[h.index("Kernel Name")].split("(")[0].split("<")[0].replace("void ", "").strip()
+        table[f"{kern}@{workload}"] = tot
+    json.dump(table, open(dst, "w"), indent=1, sort_keys=True)
+    print(json.dumps(table, indent=1))
+
+
 if __name__ == "__main__":
+    if sys.argv[1] == "--traffic":   # python profiles/summarize.py --traffic 3840x2160x64 a.ncu-rep b.ncu-rep ...
+        traffic(sys.argv[2], sys.argv[3:])
+        sys.exit(0)
     tag = sys.argv[1]
     with open(f"profiles/{tag}.txt", "w") as out:
         for p in sys.argv[2:]:
