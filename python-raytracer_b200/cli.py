@@ -2,6 +2,7 @@
 
     python -m python_raytracer_b200.cli main --infile S.json --outfile out.png [--subimage n --tasks N]
     python -m python_raytracer_b200.cli glue --dir temp --outfile out.png
+    python -m python_raytracer_b200.cli render INFILE NUM_TASKS OUTFILE        (render.nu:1-23)
 
 `main` without --subimage renders the frame and writes the PNG (rot90 + *255 truncation done on the device);
 with --subimage it saves the float64 column strip as `<outfile>.npy` exactly like main.py:26-28, so strips made
@@ -48,12 +49,49 @@ def run_glue(argv):
     return 0
 
 
+def run_render(argv):
+    """`render.nu infile num_tasks outfile` (render.nu:1-23): NUM_TASKS column strips into ./temp/<n>.npy, glue, remove
+    temp.  The reference queues one `main.py --subimage n` process per strip on pueue; here the strips are rendered by
+    this process (scene uploaded once), or, when launched under torchrun, strip n by rank n % WORLD_SIZE on that
+    rank's GPU, with rank 0 gluing after a barrier."""
+    ap = argparse.ArgumentParser(prog="render")
+    ap.add_argument("infile", type=str)
+    ap.add_argument("num_tasks", type=int)
+    ap.add_argument("outfile", type=str)
+    ap.add_argument("--temp", type=str, default="temp")
+    a = ap.parse_args(argv)
+    import shutil
+    from . import load_scene
+    from PIL import Image
+    world, rank = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0"))
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        if torch.cuda.is_available():
+            torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+        dist.init_process_group("gloo")          # control plane only: the strips travel through ./temp like the reference's
+    os.makedirs(a.temp, exist_ok=True)                                                    # render.nu:5
+    sc = load_scene(a.infile)
+    for n in range(rank, a.num_tasks, world):                                             # render.nu:9-12
+        np.save(os.path.join(a.temp, str(n)), sc.render(n, a.num_tasks))
+    if world > 1:
+        dist.barrier()
+    if rank == 0:
+        Image.fromarray((glue_strips(a.temp) * 255).astype(np.uint8)).save(a.outfile)     # render.nu:14, glue.py:25-26
+        shutil.rmtree(a.temp)                                                             # render.nu:18
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
 def main(argv=None):
     argv = list(sys.argv[1:] if argv is None else argv)
-    if not argv or argv[0] not in ("main", "glue"):
+    table = {"main": run_main, "glue": run_glue, "render": run_render}
+    if not argv or argv[0] not in table:
         print(__doc__)
         return 2
-    return run_main(argv[1:]) if argv[0] == "main" else run_glue(argv[1:])
+    return table[argv[0]](argv[1:])
 
 
 if __name__ == "__main__":

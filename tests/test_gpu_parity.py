@@ -124,6 +124,10 @@ def test_render_u8_and_cli_equal_main_py_output(tmp_path):
         assert cli.main(["main", "--infile", scene_json, "--outfile", str(tmp_path / "temp" / str(n)), "--subimage", str(n), "--tasks", "4"]) == 0
     assert cli.main(["glue", "--dir", str(tmp_path / "temp"), "--outfile", str(tmp_path / "g.png")]) == 0
     assert np.array_equal(np.array(Image.open(tmp_path / "g.png")), np.array(Image.open(png)))
+    # the whole render.nu pipeline in one call: strips -> temp -> glue -> temp removed
+    assert cli.main(["render", scene_json, "5", str(tmp_path / "r.png"), "--temp", str(tmp_path / "temp5")]) == 0
+    assert np.array_equal(np.array(Image.open(tmp_path / "r.png")), np.array(Image.open(png)))
+    assert not os.path.exists(tmp_path / "temp5")
 
 
 def test_bvh_traversal_equals_brute_force_on_device():
