@@ -240,6 +240,24 @@ int rt_render_u8_host(RtScene* scene, const RtRenderJob* job, uint8_t* h_out_u8,
 
 int rt_scene_destroy(RtScene* scene);
 
+/* ---- mesh ingestion at scale: the per-mesh load-time work of Mesh.__init__ (mesh.py:17-51) ---- */
+typedef struct RtObj RtObj;
+/* Replaces igl.read_obj (mesh.py:20) for large files: parses the `v`, `vn` and `f` rows on the host (doubles, first index of
+ * every corner token, 1-based or negative, polygons fan-triangulated); returns the counts, rt_obj_copy fills caller arrays
+ * (verts n_verts*3 f64, norms n_norms*3 f64, faces n_faces*3 i32; any may be NULL), rt_obj_free releases the handle. */
+int rt_obj_load(const char* path, RtObj** out, int64_t* n_verts, int64_t* n_norms, int64_t* n_faces);
+int rt_obj_copy(const RtObj* obj, double* verts, double* norms, int32_t* faces);
+int rt_obj_free(RtObj* obj);
+/* Replaces the vertex loop of mesh.py:23-24 ((v + translate) * scale in fp32), Mesh._compute_normals (mesh.py:53-70:
+ * area-weighted face normals accumulated per vertex IN FACE ORDER, then normalised) and the extent / centre / farthest
+ * vertex of mesh.py:29-43, all on the device.  Pointers are HOST buffers: raw vertices as read from the OBJ (n_verts*3
+ * f64), faces (n_faces*3 i32); outputs verts and vnormals (n_verts*3 f32; vnormals only when want_normals), extent min /
+ * max / centre (3 f32 each) and the bounding-sphere radius.  Synchronous.  Results are bit-identical to the host-side
+ * numpy loader of the Python package (tests/test_gpu_parity.py). */
+int rt_mesh_ingest(int32_t n_verts, const double* h_raw_verts, int32_t n_faces, const int32_t* h_faces,
+                   const float* translate, float scale, int32_t want_normals, float* h_verts, float* h_vnormals,
+                   float* h_extent_min, float* h_extent_max, float* h_center, float* h_max_dist, void* stream);
+
 /* Introspection used by tests and the bench */
 int rt_scene_bvh_stats(const RtScene* scene, int32_t mesh, int64_t* n_nodes, int64_t* n_leaf_tris, int64_t* bytes);
 /* Copies the LBVH of `mesh` back to host buffers for validation: 4-wide nodes (n_nodes*32 floats: 6 float4 child boxes in

@@ -273,7 +273,7 @@ LIB_PATH = os.environ.get("B200RT_LIB") or os.path.join(os.path.dirname(os.path.
 ENTRY_POINTS = ["rt_scene_create", "rt_scene_build_bvh", "rt_render", "rt_render_host", "rt_render_u8_host", "rt_job_extent",
                 "rt_assemble_tiles", "rt_finalize_u8", "rt_scene_destroy", "rt_scene_bvh_stats",
                 "rt_scene_bvh_download", "rt_last_error", "rt_abi_version", "rt_trace_rays", "rt_occluded",
-                "rt_scene_profile", "rt_scene_profile_read"]
+                "rt_scene_profile", "rt_scene_profile_read", "rt_obj_load", "rt_obj_copy", "rt_obj_free", "rt_mesh_ingest"]
 
 
 class B200RTError(RuntimeError):
@@ -310,6 +310,10 @@ def load_library(path=None):
     lib.rt_last_error.restype = C.c_char_p
     lib.rt_last_error.argtypes = []
     lib.rt_abi_version.argtypes = []
+    lib.rt_obj_load.argtypes = [C.c_char_p, C.POINTER(vp), i64p, i64p, i64p]
+    lib.rt_obj_copy.argtypes = [vp, vp, vp, vp]
+    lib.rt_obj_free.argtypes = [vp]
+    lib.rt_mesh_ingest.argtypes = [i32, vp, i32, vp, vp, C.c_float, i32, vp, vp, vp, vp, vp, C.POINTER(C.c_float), vp]
     for n in ENTRY_POINTS:
         if n not in ("rt_last_error",):
             getattr(lib, n).restype = C.c_int
@@ -324,3 +328,37 @@ def check(lib, rc, what):
     if rc != 0:
         msg = lib.rt_last_error()
         raise B200RTError(f"{what} failed: {STATUS_NAMES.get(rc, rc)}: {msg.decode() if msg else ''}")
+
+
+def obj_load(path):
+    """Native OBJ reader (`rt_obj_load`): (verts f64 (n,3), norms f64 (m,3), faces i32 (k,3)), same conventions as
+    geometry.read_obj."""
+    lib = load_library()
+    h, nv, nn, nf = C.c_void_p(), C.c_int64(), C.c_int64(), C.c_int64()
+    check(lib, lib.rt_obj_load(os.fsencode(path), C.byref(h), C.byref(nv), C.byref(nn), C.byref(nf)), "rt_obj_load")
+    try:
+        verts = np.empty((nv.value, 3), np.float64)
+        norms = np.empty((nn.value, 3), np.float64)
+        faces = np.empty((nf.value, 3), np.int32)
+        check(lib, lib.rt_obj_copy(h, verts.ctypes.data, norms.ctypes.data, faces.ctypes.data), "rt_obj_copy")
+    finally:
+        lib.rt_obj_free(h)
+    return verts, norms, faces
+
+
+def mesh_ingest(raw_verts, faces, translate, scale, want_normals, stream=None):
+    """Device-side Mesh.__init__ arithmetic (`rt_mesh_ingest`): returns (verts f32, vnormals f32 or None, extent min,
+    extent max, centre, max_dist)."""
+    lib = load_library()
+    raw = np.ascontiguousarray(raw_verts, dtype=np.float64).reshape(-1, 3)
+    f = np.ascontiguousarray(faces, dtype=np.int32).reshape(-1, 3)
+    t = np.ascontiguousarray(translate, dtype=np.float32).reshape(3)
+    verts = np.empty((raw.shape[0], 3), np.float32)
+    vn = np.empty((raw.shape[0], 3), np.float32) if want_normals else None
+    mn, mx, cen = np.empty(3, np.float32), np.empty(3, np.float32), np.empty(3, np.float32)
+    md = C.c_float()
+    rc = lib.rt_mesh_ingest(raw.shape[0], raw.ctypes.data, f.shape[0], f.ctypes.data, t.ctypes.data, float(np.float32(scale)),
+                            1 if want_normals else 0, verts.ctypes.data, None if vn is None else vn.ctypes.data,
+                            mn.ctypes.data, mx.ctypes.data, cen.ctypes.data, C.byref(md), stream)
+    check(lib, rc, "rt_mesh_ingest")
+    return verts, vn, mn, mx, cen, float(md.value)

@@ -10,7 +10,9 @@
 #include <vector>
 
 #include "rt_bvh.cuh"
+#include "rt_ingest.cuh"
 #include "rt_kernels.cuh"
+#include "rt_obj.hpp"
 #include "rt_scene_build.hpp"
 
 #define RT_PROF_CLASSES 5
@@ -590,5 +592,107 @@ extern "C" int rt_scene_profile_read(RtScene* sc, RtProfile* out) {
     RtCounters cls[RT_COUNTER_CLASSES];
     CU(cudaMemcpy(cls, sc->d_counters, sizeof cls, cudaMemcpyDeviceToHost));
     out->hit = cls[0]; out->shadow = cls[1]; out->shade = cls[2]; out->secondary = cls[3];
+    return RT_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Mesh ingestion: OBJ rows -> arrays on the host cores, everything per-vertex / per-face on the device
+struct RtObj { ObjData d; };
+
+extern "C" int rt_obj_load(const char* path, RtObj** out, int64_t* n_verts, int64_t* n_norms, int64_t* n_faces) {
+    if (!path || !out) return fail(RT_ERR_INVALID, "rt_obj_load: null argument");
+    RtObj* o = new RtObj();
+    const std::string err = objio::load(path, o->d);
+    if (!err.empty()) { delete o; return fail(RT_ERR_INVALID, err); }
+    const int64_t nv = (int64_t)(o->d.verts.size() / 3);
+    for (int32_t i : o->d.faces)
+        if (i < 0 || i >= nv) { delete o; return fail(RT_ERR_INVALID, std::string(path) + ": face index out of range"); }
+    if (n_verts) *n_verts = nv;
+    if (n_norms) *n_norms = (int64_t)(o->d.norms.size() / 3);
+    if (n_faces) *n_faces = (int64_t)(o->d.faces.size() / 3);
+    *out = o;
+    return RT_OK;
+}
+
+extern "C" int rt_obj_copy(const RtObj* o, double* verts, double* norms, int32_t* faces) {
+    if (!o) return fail(RT_ERR_INVALID, "rt_obj_copy: null handle");
+    if (verts && !o->d.verts.empty()) memcpy(verts, o->d.verts.data(), sizeof(double) * o->d.verts.size());
+    if (norms && !o->d.norms.empty()) memcpy(norms, o->d.norms.data(), sizeof(double) * o->d.norms.size());
+    if (faces && !o->d.faces.empty()) memcpy(faces, o->d.faces.data(), sizeof(int32_t) * o->d.faces.size());
+    return RT_OK;
+}
+
+extern "C" int rt_obj_free(RtObj* o) { delete o; return RT_OK; }
+
+extern "C" int rt_mesh_ingest(int32_t n_verts, const double* h_raw_verts, int32_t n_faces, const int32_t* h_faces,
+                              const float* translate, float scale, int32_t want_normals, float* h_verts, float* h_vnormals,
+                              float* h_extent_min, float* h_extent_max, float* h_center, float* h_max_dist, void* stream) {
+    if (n_verts < 0 || n_faces < 0 || (n_verts && (!h_raw_verts || !h_verts)) || (n_faces && !h_faces) || !translate)
+        return fail(RT_ERR_INVALID, "rt_mesh_ingest: bad argument");
+    if (want_normals && n_verts && !h_vnormals) return fail(RT_ERR_INVALID, "rt_mesh_ingest: normals wanted but no output buffer");
+    if ((long long)n_faces * 3 > 0x7fffffffLL) return fail(RT_ERR_LIMIT, "rt_mesh_ingest: more than 2^31 face corners");
+    for (long long i = 0; i < (long long)n_faces * 3; i++)
+        if (h_faces[i] < 0 || h_faces[i] >= n_verts) return fail(RT_ERR_INVALID, "rt_mesh_ingest: face index out of range");
+    if (n_verts == 0) return fail(RT_ERR_INVALID, "rt_mesh_ingest: a mesh needs at least one vertex (mesh.py:29 takes max() of them)");
+    cudaStream_t st = (cudaStream_t)stream;
+    std::vector<void*> tmp;
+    auto tfree = [&]() { for (void* p : tmp) cudaFree(p); };
+    auto talloc = [&](void** p, size_t bytes) { cudaError_t e = cudaMalloc(p, std::max<size_t>(bytes, 16)); if (e == cudaSuccess) tmp.push_back(*p); return e; };
+#define TA(ptr, bytes) do { cudaError_t e_ = talloc((void**)&(ptr), (bytes)); if (e_ != cudaSuccess) { tfree(); return fail(RT_ERR_NOMEM, cudaGetErrorString(e_)); } } while (0)
+#define TC(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { tfree(); return fail(RT_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); } } while (0)
+    double* d_raw; float* d_verts; unsigned* d_ext;
+    TA(d_raw, sizeof(double) * 3 * (size_t)n_verts); TA(d_verts, sizeof(float) * 3 * (size_t)n_verts); TA(d_ext, sizeof(unsigned) * 8);
+    const unsigned ext_init[8] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u, 0u, 0u};
+    TC(cudaMemcpyAsync(d_raw, h_raw_verts, sizeof(double) * 3 * (size_t)n_verts, cudaMemcpyHostToDevice, st));
+    TC(cudaMemcpyAsync(d_ext, ext_init, sizeof(ext_init), cudaMemcpyHostToDevice, st));
+    const int T = 256, GV = (n_verts + T - 1) / T;
+    ing::k_transform<<<GV, T, 0, st>>>(d_raw, n_verts, f3(translate[0], translate[1], translate[2]), scale, d_verts, d_ext);
+    unsigned ext[8];
+    TC(cudaMemcpyAsync(ext, d_ext, sizeof(ext), cudaMemcpyDeviceToHost, st));
+    TC(cudaMemcpyAsync(h_verts, d_verts, sizeof(float) * 3 * (size_t)n_verts, cudaMemcpyDeviceToHost, st));
+    TC(cudaStreamSynchronize(st));
+    float mn[3], mx[3], cen[3];
+    for (int k = 0; k < 3; k++) {
+        mn[k] = ing::ord2f(ext[k]); mx[k] = ing::ord2f(ext[3 + k]);
+        cen[k] = (float)(((double)mx[k] + (double)mn[k]) / 2.0);                 // mesh.py:36-41 (Python floats), stored as a vec3
+    }
+    ing::k_max_dist<<<GV, T, 0, st>>>(d_verts, n_verts, f3(cen[0], cen[1], cen[2]), d_ext + 6);
+    TC(cudaMemcpyAsync(ext + 6, d_ext + 6, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+    if (want_normals) {
+        const int n_pairs = 3 * n_faces;
+        int* d_faces; float4* d_weighted; float* d_vn; uint64_t* keys[2]; int* vals[2]; unsigned* hist;
+        const int n_tiles = std::max(1, (n_pairs + RS_TILE - 1) / RS_TILE);
+        TA(d_faces, sizeof(int) * (size_t)std::max(1, n_pairs)); TA(d_weighted, sizeof(float4) * (size_t)std::max(1, n_faces));
+        TA(d_vn, sizeof(float) * 3 * (size_t)n_verts);
+        TA(keys[0], sizeof(uint64_t) * (size_t)std::max(1, n_pairs)); TA(keys[1], sizeof(uint64_t) * (size_t)std::max(1, n_pairs));
+        TA(vals[0], sizeof(int) * (size_t)std::max(1, n_pairs)); TA(vals[1], sizeof(int) * (size_t)std::max(1, n_pairs));
+        TA(hist, sizeof(unsigned) * 256 * (size_t)n_tiles);
+        int cur = 0;
+        if (n_faces > 0) {
+            TC(cudaMemcpyAsync(d_faces, h_faces, sizeof(int) * (size_t)n_pairs, cudaMemcpyHostToDevice, st));
+            ing::k_face_normals<<<(n_faces + T - 1) / T, T, 0, st>>>(d_verts, d_faces, n_faces, d_weighted, keys[0], vals[0]);
+            int bits = 1;
+            while (bits < 32 && (1u << bits) < (unsigned)n_verts) bits++;
+            for (int shift = 0; shift < bits; shift += 8) {          // stable LSD passes over the digits a vertex index can occupy
+                k_rs_hist<<<n_tiles, RS_THREADS, 0, st>>>(keys[cur], n_pairs, shift, n_tiles, hist);
+                k_rs_scan<<<1, 1024, 0, st>>>(hist, 256 * n_tiles);
+                k_rs_scatter<<<n_tiles, RS_THREADS, 0, st>>>(keys[cur], vals[cur], n_pairs, shift, n_tiles, hist, keys[cur ^ 1], vals[cur ^ 1]);
+                cur ^= 1;
+            }
+        }
+        ing::k_vertex_normals<<<GV, T, 0, st>>>(keys[cur], vals[cur], n_pairs, d_weighted, n_verts, d_vn);
+        TC(cudaMemcpyAsync(h_vnormals, d_vn, sizeof(float) * 3 * (size_t)n_verts, cudaMemcpyDeviceToHost, st));
+    }
+    TC(cudaStreamSynchronize(st));
+    TC(cudaGetLastError());
+#undef TA
+#undef TC
+    tfree();
+    for (int k = 0; k < 3; k++) {
+        if (h_extent_min) h_extent_min[k] = mn[k];
+        if (h_extent_max) h_extent_max[k] = mx[k];
+        if (h_center) h_center[k] = cen[k];
+    }
+    if (h_max_dist) *h_max_dist = ing::ord2f(ext[6]);
     return RT_OK;
 }

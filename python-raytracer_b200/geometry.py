@@ -132,30 +132,46 @@ def read_obj(filepath):
 
 class Mesh(Geometry):
     """mesh.py:16-51.  `filepath` may also be a (verts, faces) tuple of arrays for
-    procedurally generated meshes (the 1M-triangle benchmark scene)."""
+    procedurally generated meshes (the 1M-triangle benchmark scene).
+
+    `ingest` picks where the load-time arithmetic runs (an explicit choice, never a fallback): "host" = the numpy
+    restatement below, mirroring the reference's loops; "device" = the native OBJ reader plus `rt_mesh_ingest`
+    (CUDA, bit-identical results, for meshes of 10^5..10^7 faces where the Python-side loops dominate the set-up)."""
+
+    DEFAULT_INGEST = "host"
 
     def __init__(self, name, gtype, materials, translate, scale: float, filepath,
-                 flat_shaded: bool = False, speed=None):
+                 flat_shaded: bool = False, speed=None, ingest=None):
         super().__init__(name, gtype, materials, speed)
+        ingest = ingest or Mesh.DEFAULT_INGEST
+        if ingest not in ("host", "device"):
+            raise ValueError(f"ingest must be 'host' or 'device', not {ingest!r}")
         if isinstance(filepath, (tuple, list)):
             verts, faces = filepath
             verts = np.asarray(verts, dtype=np.float64).reshape(-1, 3)
             self.faces = np.ascontiguousarray(faces, dtype=np.int32).reshape(-1, 3)
+        elif ingest == "device":
+            from . import _abi
+            verts, _norms, self.faces = _abi.obj_load(filepath)
         else:
             verts, _norms, self.faces = read_obj(filepath)
-        # (vec3(v) + translate) * scale, float32 (mesh.py:24)
-        t = vm.vec3(translate)
-        self.verts = np.ascontiguousarray((verts.astype(np.float32) + t) * np.float32(scale), dtype=np.float32)
         self.flat_shaded = flat_shaded
         self.norms = None
-        if not flat_shaded:
-            self._compute_normals()
-
-        v = self.verts
-        mx = v.max(axis=0).astype(np.float64)
-        mn = v.min(axis=0).astype(np.float64)
-        center = ((mx + mn) / 2).astype(np.float32)                      # mesh.py:38-41
-        max_dist = float(np.sqrt(vm.dot_rows(v - center, v - center)).max())  # mesh.py:43
+        t = vm.vec3(translate)
+        if ingest == "device":
+            from . import _abi
+            self.verts, self.norms, mn32, mx32, center, max_dist = _abi.mesh_ingest(verts, self.faces, t, scale, not flat_shaded)
+            mn, mx = mn32.astype(np.float64), mx32.astype(np.float64)
+        else:
+            # (vec3(v) + translate) * scale, float32 (mesh.py:24)
+            self.verts = np.ascontiguousarray((verts.astype(np.float32) + t) * np.float32(scale), dtype=np.float32)
+            if not flat_shaded:
+                self._compute_normals()
+            v = self.verts
+            mx = v.max(axis=0).astype(np.float64)
+            mn = v.min(axis=0).astype(np.float64)
+            center = ((mx + mn) / 2).astype(np.float32)                      # mesh.py:38-41
+            max_dist = float(np.sqrt(vm.dot_rows(v - center, v - center)).max())  # mesh.py:43
         ext = mx - mn
         aabb_volume = ext[0] * ext[1] * ext[2]
         sphere_volume = 4 / 3 * math.pi * max_dist ** 3

@@ -65,15 +65,21 @@ def _resolve(path):
     return path
 
 
-def load_scene(infile):
+def load_scene(infile, ingest=None):
+    """scene_parser.py:19-163.  `ingest` ("host" | "device", default geometry.Mesh.DEFAULT_INGEST) says where meshes are
+    read and prepared: see geometry.Mesh."""
     _say("Parsing file:", infile)
     with open(infile) as f:
         data = json.load(f)
-    return load_scene_dict(data, os.path.dirname(os.path.abspath(infile)))
+    return load_scene_dict(data, os.path.dirname(os.path.abspath(infile)), ingest=ingest)
 
 
-def load_scene_dict(data, base_dir=None):
-    global _search_roots
+_mesh_ingest = None
+
+
+def load_scene_dict(data, base_dir=None, ingest=None):
+    global _search_roots, _mesh_ingest
+    _mesh_ingest = ingest
     _search_roots = [] if base_dir is None else [base_dir, os.path.dirname(base_dir)]
 
     cam_pos = populateVec(data["camera"]["position"])
@@ -221,7 +227,7 @@ def add_basic_shape(g_name, g_type, g_pos, g_speed, g_mats, g, objects):
         objects.append(box)
     elif g_type == "mesh":
         objects.append(geom.Mesh(g_name, g_type, g_mats, g_pos, g["scale"], _resolve(g["filepath"]),
-                                 get_or(g, "flat_shaded", False), g_speed))
+                                 get_or(g, "flat_shaded", False), g_speed, ingest=_mesh_ingest))
     else:
         return False
     return True

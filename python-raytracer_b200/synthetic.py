@@ -41,7 +41,7 @@ def displaced_torus(nu, nv, seed=1234):
 
 
 def make_scene(width=3840, height=2160, aa_samples=64, grid=(1024, 512), n_spheres=64, jitter=True, seed=1234,
-               dof_samples=1, flat_shaded=False):
+               dof_samples=1, flat_shaded=False, ingest=None):
     rng = np.random.default_rng(seed)
     vc = hc.ViewportCamera().set_viewport(width, height) \
         .set_camera((0.0, 4.0, 8.0), (0.0, 1.0, 0.0), (0.0, 1.0, 0.0), 45.0) \
@@ -56,7 +56,7 @@ def make_scene(width=3840, height=2160, aa_samples=64, grid=(1024, 512), n_spher
     mats[5].refr_index = 1.458
     objects = [geom.Plane("ground", "plane", [mats[1], mats[2]], (0.0, -1.0, 0.0), (0.0, 1.0, 0.0), None)]
     verts, faces = displaced_torus(grid[0], grid[1], seed)
-    objects.append(geom.Mesh("torus", "mesh", [mats[0]], (0.0, 0.0, 0.0), 1.0, (verts, faces), flat_shaded, None))
+    objects.append(geom.Mesh("torus", "mesh", [mats[0]], (0.0, 0.0, 0.0), 1.0, (verts, faces), flat_shaded, None, ingest=ingest))
     for k in range(n_spheres):
         ang = 2 * math.pi * k / max(1, n_spheres)
         rad = float(rng.uniform(0.1, 0.3))

@@ -45,7 +45,7 @@ def manifest():
         return json.load(fh)
 
 
-def load_case(case, extra_overrides=None):
+def load_case(case, extra_overrides=None, ingest=None):
     """Scene of a golden case (tests/golden/MANIFEST.json), through the package's own parser."""
     import python_raytracer_b200 as rt
     rt.scene_parser.VERBOSE = False
@@ -53,7 +53,7 @@ def load_case(case, extra_overrides=None):
     with open(os.path.join(GOLDEN, "scenes", e["scene"])) as fh:
         data = _merge(json.load(fh), e["overrides"])
     data = _merge(data, extra_overrides)
-    sc = rt.scene_parser.load_scene_dict(data, os.path.join(GOLDEN, "scenes"))
+    sc = rt.scene_parser.load_scene_dict(data, os.path.join(GOLDEN, "scenes"), ingest=ingest)
     sc.jitter_seed = e["seed"]
     return sc
 

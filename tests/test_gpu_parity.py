@@ -130,6 +130,40 @@ def test_render_u8_and_cli_equal_main_py_output(tmp_path):
     assert not os.path.exists(tmp_path / "temp5")
 
 
+def test_device_mesh_ingestion_is_bit_identical_to_the_host_loader(tmp_path):
+    """rt_mesh_ingest (transform, face-ordered area-weighted vertex normals, extent, gate radius on the GPU) + rt_obj_load
+    against the numpy loader that the golden fixtures pin to the reference (mesh.py:17-70)."""
+    import os
+    from python_raytracer_b200 import geometry, synthetic
+    torus = os.path.join(os.path.dirname(__file__), "golden", "meshes", "torus.obj")
+    verts, faces = synthetic.displaced_torus(256, 128, 7)
+    big = tmp_path / "big.obj"
+    with open(big, "w") as fh:
+        fh.write("".join(f"v {x!r} {y!r} {z!r}\n" for x, y, z in verts.tolist()))
+        fh.write("".join(f"f {a + 1} {b + 1} {c + 1}\n" for a, b, c in faces.tolist()))
+    lonely = (np.concatenate([verts[:100], [[9.0, 9.0, 9.0]]]), faces[(faces < 100).all(axis=1)])   # a vertex no face uses
+    for src, t, s in ((torus, (0.0, 0.0, 0.0), 1.0), (torus, (0.3, -1.25, 2.0), 0.37), (str(big), (0.1, 0.2, -0.3), 1.7),
+                      ((verts, faces), (0.0, 1.5, 0.0), 1.0), (lonely, (0.0, 0.0, 0.0), 2.0)):
+        for flat in (False, True):
+            h = geometry.Mesh("m", "mesh", [], t, s, src, flat, None, ingest="host")
+            d = geometry.Mesh("m", "mesh", [], t, s, src, flat, None, ingest="device")
+            assert np.array_equal(h.faces, d.faces)
+            assert h.verts.dtype == d.verts.dtype and np.array_equal(h.verts, d.verts)
+            if flat:
+                assert h.norms is None and d.norms is None
+            else:
+                assert np.array_equal(h.norms, d.norms, equal_nan=True)
+                assert np.isnan(d.norms).any() == (src is lonely)
+            assert type(h.bounding_volume) is type(d.bounding_volume)
+            for k, v in vars(h.bounding_volume).items():
+                if v is None:
+                    continue
+                assert np.array_equal(np.asarray(v, dtype=np.float64), np.asarray(getattr(d.bounding_volume, k), dtype=np.float64)), k
+    # the whole scene through the parser
+    a, b = load_case("TorusMesh_smooth"), load_case("TorusMesh_smooth", ingest="device")
+    assert np.array_equal(a.render(), b.render())
+
+
 def test_bvh_traversal_equals_brute_force_on_device():
     for case in ("TorusMesh_flat", "TorusMesh_smooth"):
         sc = load_case(case)

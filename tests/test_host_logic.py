@@ -132,6 +132,41 @@ def test_library_loads_and_exports_every_declared_symbol():
     assert lib.rt_abi_version() == abi.RT_ABI_VERSION
 
 
+def test_native_obj_reader_equals_python_reader(tmp_path):
+    """rt_obj_load (host code of the C ABI library) against geometry.read_obj: bundled torus, and a file with the row
+    kinds OBJ exporters produce (comments, CRLF, v/vt/vn corners, negative indices, quads and a pentagon, exponents)."""
+    from python_raytracer_b200 import geometry
+    torus = os.path.join(GOLDEN, "meshes", "torus.obj")
+    for a, b in zip(geometry.read_obj(torus), abi.obj_load(torus)):
+        assert a.dtype == b.dtype and np.array_equal(a, b)
+    rng = np.random.default_rng(5)
+    rows = ["# made by a test", "o thing", ""]
+    for k in range(40):
+        x, y, z = rng.normal(size=3).tolist()
+        rows.append(f"v {x!r} {y:.7e} {z:.3f} 1.0" if k % 3 else f"v  {x:.17g}\t{y:.9f}   {z!r}")
+        rows.append(f"vn {x:.4f} {y:.4f} {z:.4f}")
+        rows.append(f"vt {x:.4f} {y:.4f}")
+        if k >= 5:
+            rows.append([f"f {k} {k - 1} {k - 2}", f"f {k}/1/1 {k - 1}/2/2 {k - 2}//3 {k - 3}/4", "f -1 -2 -3 -4 -5",
+                         f"f {k}//{k} -2//1 {k - 4}//2"][k % 4])
+    rows += ["s off", "usemtl m", "f 1 2 3"]
+    path = tmp_path / "t.obj"
+    path.write_bytes("\r\n".join(rows).encode())
+    want, got = geometry.read_obj(str(path)), abi.obj_load(str(path))
+    assert want[0].shape == (40, 3) and want[2].shape[0] > 40
+    for a, b in zip(want, got):
+        assert a.dtype == b.dtype and np.array_equal(a, b)
+    bad = tmp_path / "bad.obj"
+    bad.write_text("v 0 0 0\nv 1 0 0\nv 0 1 x\nf 1 2 3\n")
+    with pytest.raises(abi.B200RTError, match="bad.obj:3"):
+        abi.obj_load(str(bad))
+    bad.write_text("v 0 0 0\nv 1 0 0\nv 0 1 0\nf 1 2 4\n")
+    with pytest.raises(abi.B200RTError, match="out of range"):
+        abi.obj_load(str(bad))
+    with pytest.raises(abi.B200RTError, match="cannot open"):
+        abi.obj_load(str(tmp_path / "missing.obj"))
+
+
 def test_missing_library_fails_loudly(tmp_path):
     with pytest.raises(abi.B200RTError):
         abi.load_library(str(tmp_path / "nope.so"))
