@@ -465,8 +465,7 @@ RT_HD float3 box_diffuse(const SceneView& S, const DevObject* o, float3 p, float
 }
 
 // ------------------------------------------------------------------------------------------------
-// CSG / transform nodes (hierarchy.py:42-138).  Recursion is unrolled at compile time to
-// RT_MAX_NEST levels (template depth), no device call stack.
+// CSG / transform nodes (hierarchy.py:42-138).
 
 // shadow_intersect of a leaf primitive (simple_geometry.py:48-72,122-131,251-294; mesh.py:121-153)
 template <bool WITH_MESH>
@@ -498,147 +497,182 @@ RT_HD bool leaf_shadow(TraceCtx& cx, int oi, const Ray& r, float tmax) {
 
 RT_HD_NOINLINE bool difference_shadow(TraceCtx& cx, int c0, const Ray& mr);
 
-template <int D> struct Nest {
-    // is_inside (hierarchy.py:111-129; Sphere :74-80, AABB :296-307; Plane/Mesh: base class False)
-    static RT_HD_NOINLINE bool inside(TraceCtx& cx, int oi, float3 p) {
-        const DevObject* o = cx.S.objects + oi;
-        switch (o->kind) {
-            case RT_KIND_SPHERE: {
-                float4 a = ld4(&o->a);
-                float3 q = p - moved(o, f3(a), cx.time);
-                return sqrtf(dot(q, q)) < a.w;
-            }
-            case RT_KIND_BOX: {
-                float3 mn = moved(o, f3(ld4(&o->a)), cx.time), mx = moved(o, f3(ld4(&o->b)), cx.time);
-                return mn.x < p.x && p.x < mx.x && mn.y < p.y && p.y < mx.y && mn.z < p.z && p.z < mx.z;
-            }
-            case RT_KIND_NODE: {
-                float3 q = xform_point(cx.S.xforms[o->xform].Minv, p);
-                const int c0 = o->first_child, nc = o->n_children;
-                if (o->csg == RT_CSG_UNION) {
-                    for (int k = 0; k < nc; k++) if (Nest<D - 1>::inside(cx, c0 + k, q)) return true;
-                    return false;
-                } else if (o->csg == RT_CSG_INTERSECTION) {
-                    for (int k = 0; k < nc; k++) if (!Nest<D - 1>::inside(cx, c0 + k, q)) return false;
-                    return true;
-                } else if (o->csg == RT_CSG_DIFFERENCE && nc >= 2) {
-                    return Nest<D - 1>::inside(cx, c0, q) && !Nest<D - 1>::inside(cx, c0 + 1, q);
-                }
-                return false;
-            }
-            default: return false;
-        }
-    }
-    // get_material (hierarchy.py:131-138; Plane :133; others materials[0])
-    static RT_HD_NOINLINE int material(TraceCtx& cx, int oi, float3 p) {
-        const DevObject* o = cx.S.objects + oi;
-        if (o->kind == RT_KIND_PLANE) return plane_material(o, p, cx.time);
-        if (o->kind == RT_KIND_NODE) {
-            float3 q = xform_point(cx.S.xforms[o->xform].Minv, p);
-            for (int k = 0; k < o->n_children; k++)
-                if (Nest<D - 1>::inside(cx, o->first_child + k, q)) return Nest<D - 1>::material(cx, o->first_child + k, q);
-            return -1;   // None
-        }
-        return o->n_mats > 0 ? o->mat0 : -2;
-    }
+// The recursions of hierarchy.py (is_inside :111-129, get_material :131-138, shadow_intersect :80-109) run as loops over
+// an explicit frame stack of RT_MAX_NEST entries: ONE copy of each function in the instruction stream (the first version
+// unrolled the recursion through templates, eight copies of everything, and the node kernels were instruction-fetch bound).
+// Nesting deeper than RT_MAX_NEST is flagged (RT_ERR_LIMIT) and treated as empty.
 
-    // shadow_intersect (hierarchy.py:80-109 and the leaf versions)
-    static RT_HD_NOINLINE bool shadow(TraceCtx& cx, int oi, const Ray& r, float tmax) {
-        const DevObject* o = cx.S.objects + oi;
-        if (o->kind != RT_KIND_NODE) return leaf_shadow<true>(cx, oi, r, tmax);
-        cx.tally.prims++;
-        switch (o->kind) {
-            case RT_KIND_NODE: {
-                const DevXform* xf = cx.S.xforms + o->xform;
-                Ray mr; mr.o = xform_point(xf->Minv, r.o); mr.d = xform_dir(xf->Minv, r.d);
-                const int c0 = o->first_child, nc = o->n_children;
-                if (o->csg == RT_CSG_UNION) {
-                    for (int k = 0; k < nc; k++) if (Nest<D - 1>::shadow(cx, c0 + k, mr, tmax)) return true;
-                    return false;
-                } else if (o->csg == RT_CSG_INTERSECTION) {            // ALL children must report shadow
-                    for (int k = 0; k < nc; k++) if (!Nest<D - 1>::shadow(cx, c0 + k, mr, tmax)) return false;
-                    return true;
-                } else if (o->csg == RT_CSG_DIFFERENCE && nc >= 2) {   // via intersect(); t_max ignored
-                    return difference_shadow(cx, c0, mr);
-                }
-                return false;
+// is_inside of a leaf (Sphere simple_geometry.py:74-80, AABB :296-307; Plane/Mesh: base class False)
+RT_HD bool leaf_inside(const TraceCtx& cx, const DevObject* o, float3 p) {
+    if (o->kind == RT_KIND_SPHERE) {
+        float4 a = ld4(&o->a);
+        float3 q = p - moved(o, f3(a), cx.time);
+        return sqrtf(dot(q, q)) < a.w;
+    }
+    if (o->kind == RT_KIND_BOX) {
+        float3 mn = moved(o, f3(ld4(&o->a)), cx.time), mx = moved(o, f3(ld4(&o->b)), cx.time);
+        return mn.x < p.x && p.x < mx.x && mn.y < p.y && p.y < mx.y && mn.z < p.z && p.z < mx.z;
+    }
+    return false;
+}
+
+// How many children a node's boolean looks at, and what it is worth with none: union/intersection all of them
+// (any([]) = False, all([]) = True), difference exactly two (fewer: nothing).
+RT_HD int csg_arity(const DevObject* nd) {
+    return (nd->csg == RT_CSG_UNION || nd->csg == RT_CSG_INTERSECTION) ? nd->n_children : ((nd->csg == RT_CSG_DIFFERENCE && nd->n_children >= 2) ? 2 : 0);
+}
+// After child number `k` of `nd` evaluated to `val`: true = the node's value is decided (in `val`), false = evaluate child k+1
+RT_HD bool csg_step(const DevObject* nd, int k, int arity, bool& val) {
+    if (nd->csg == RT_CSG_UNION) { if (val) return true; if (k + 1 < arity) return false; val = false; return true; }
+    if (nd->csg == RT_CSG_INTERSECTION) { if (!val) return true; if (k + 1 < arity) return false; val = true; return true; }
+    if (k == 0) { if (!val) return true; return false; }      // difference: c0 and not c1
+    val = !val; return true;
+}
+
+struct InsideFrame { int obj, cursor; float3 q; };
+RT_HD_NOINLINE bool csg_inside(TraceCtx& cx, int root, float3 p) {
+    const DevObject* objs = cx.S.objects;
+    InsideFrame st[RT_MAX_NEST];
+    int d = -1, cur = root;
+    float3 cp = p;
+    for (;;) {
+        const DevObject* o = objs + cur;
+        bool val;
+        if (o->kind == RT_KIND_NODE) {
+            const int ar = csg_arity(o);
+            if (d + 1 >= RT_MAX_NEST) { cx.tally.err |= 1u << RT_ERR_LIMIT; val = false; }
+            else if (ar == 0) val = o->csg == RT_CSG_INTERSECTION;
+            else {
+                d++;
+                st[d].obj = cur; st[d].cursor = 0; st[d].q = xform_point(cx.S.xforms[o->xform].Minv, cp);
+                cp = st[d].q; cur = o->first_child;
+                continue;
             }
+        } else val = leaf_inside(cx, o, cp);
+        for (;;) {                                               // hand the value up until a node wants its next child
+            if (d < 0) return val;
+            const DevObject* nd = objs + st[d].obj;
+            if (csg_step(nd, st[d].cursor, csg_arity(nd), val)) { d--; continue; }
+            st[d].cursor++;
+            cur = nd->first_child + st[d].cursor; cp = st[d].q;
+            break;
+        }
+    }
+}
+
+// get_material (hierarchy.py:131-138: the first child that contains the point answers; Plane :133; others materials[0])
+RT_HD_NOINLINE int csg_material(TraceCtx& cx, int oi, float3 p) {
+    const DevObject* objs = cx.S.objects;
+    for (int depth = 0;; depth++) {
+        const DevObject* o = objs + oi;
+        if (o->kind == RT_KIND_PLANE) return plane_material(o, p, cx.time);
+        if (o->kind != RT_KIND_NODE) return o->n_mats > 0 ? o->mat0 : -2;
+        if (depth >= RT_MAX_NEST) { cx.tally.err |= 1u << RT_ERR_LIMIT; return -1; }
+        const float3 q = xform_point(cx.S.xforms[o->xform].Minv, p);
+        int next = -1;
+        for (int k = 0; k < o->n_children && next < 0; k++)
+            if (csg_inside(cx, o->first_child + k, q)) next = o->first_child + k;
+        if (next < 0) return -1;   // None
+        oi = next; p = q;
+    }
+}
+
+// shadow_intersect (hierarchy.py:80-109 and the leaf versions): union = any child, intersection = ALL children report
+// shadow, difference goes through intersect() and ignores t_max
+struct ShadowFrame { int obj, cursor; Ray ray; };
+RT_HD_NOINLINE bool csg_shadow(TraceCtx& cx, int root, const Ray& r, float tmax) {
+    const DevObject* objs = cx.S.objects;
+    ShadowFrame st[RT_MAX_NEST];
+    int d = -1, cur = root;
+    Ray cr = r;
+    for (;;) {
+        const DevObject* o = objs + cur;
+        bool val;
+        if (o->kind == RT_KIND_NODE) {
+            cx.tally.prims++;
+            if (d + 1 >= RT_MAX_NEST) { cx.tally.err |= 1u << RT_ERR_LIMIT; val = false; }
+            else {
+                const DevXform* xf = cx.S.xforms + o->xform;
+                Ray mr; mr.o = xform_point(xf->Minv, cr.o); mr.d = xform_dir(xf->Minv, cr.d);
+                const int ar = csg_arity(o);
+                if (ar == 0) val = o->csg == RT_CSG_INTERSECTION;
+                else if (o->csg == RT_CSG_DIFFERENCE) val = difference_shadow(cx, o->first_child, mr);
+                else {
+                    d++;
+                    st[d].obj = cur; st[d].cursor = 0; st[d].ray = mr;
+                    cr = mr; cur = o->first_child;
+                    continue;
+                }
+            }
+        } else val = leaf_shadow<true>(cx, cur, cr, tmax);
+        for (;;) {
+            if (d < 0) return val;
+            const DevObject* nd = objs + st[d].obj;
+            if (csg_step(nd, st[d].cursor, csg_arity(nd), val)) { d--; continue; }
+            st[d].cursor++;
+            cur = nd->first_child + st[d].cursor; cr = st[d].ray;
+            break;
+        }
+    }
+}
+
+// A mesh as a node's child (mesh.py:72-119: every accepted face).  Kept out of line so that the LBVH walk is not part of
+// every node kernel's hot instruction stream.
+template <class Want, class Cand>
+RT_HD_NOINLINE void mesh_leaf_hits(TraceCtx& cx, int oi, const Ray& r, Want& want, Cand& cand) {
+    const DevObject* o = cx.S.objects + oi;
+    const DevMesh* m = cx.S.meshes + o->mesh;
+    if (!mesh_gate(m, r)) return;
+    float tmax = RT_INF;
+    const int mat = o->n_mats > 0 ? o->mat0 : -2;
+    const RayInv ri = ray_inv(r);
+    mesh_visit<true>(cx, m, ri, 0.0f, tmax, [&](int slot, float&) {
+        float3 v0, v1, v2; int face; float t;
+        tri_load(m, slot, v0, v1, v2, face);
+        if (tri_hit(v0, v1, v2, r, t) && want(t)) {
+            Hit h; h.t = t; h.p = r.o + r.d * t; h.n = tri_normal(cx, m, slot, h.p); h.mat = mat; h.geom = oi;
+            cand(h);
         }
         return false;
-    }
-};
+    });
+}
 
-// nesting deeper than RT_MAX_NEST: flagged, treated as empty
-template <> struct Nest<0> {
-    static RT_HD bool inside(TraceCtx& cx, int, float3) { cx.tally.err |= 1u << RT_ERR_LIMIT; return false; }
-    static RT_HD int material(TraceCtx& cx, int, float3) { cx.tally.err |= 1u << RT_ERR_LIMIT; return -1; }
-    static RT_HD bool shadow(TraceCtx& cx, int, const Ray&, float) { cx.tally.err |= 1u << RT_ERR_LIMIT; return false; }
-};
-
-// Candidate hits of ONE leaf primitive for `r`, in the reference's list order; `want(t)` prunes early.
+// Candidate hits of ONE leaf primitive for `r`, in the reference's list order; `want(t)` prunes early.  The (at most two)
+// hit times of an analytic leaf are collected first and handed to `cand` from ONE call site: `cand` is the whole climb
+// through the ancestors' CSG filters, and a copy of it per primitive kind tripled the size of the node kernels.
 template <class Want, class Cand>
 RT_HD void leaf_hits(TraceCtx& cx, int oi, const Ray& r, Want&& want, Cand&& cand) {
     const DevObject* o = cx.S.objects + oi;
     cx.tally.prims++;
-    switch (o->kind) {
-        case RT_KIND_SPHERE: {                                     // simple_geometry.py:20-46: both roots with t > 0
-            float4 a = ld4(&o->a);
-            float3 center = moved(o, f3(a), cx.time);
-            float t1, t2;
-            if (!sphere_roots(center, a.w, r, dot(r.d, r.d), t1, t2)) return;
-            float ts[2] = {t1, t2};
-            for (int k = 0; k < 2; k++) {
-                float t = ts[k];
-                if (t > 0.0f && want(t)) {
-                    Hit h; h.t = t; h.p = r.o + r.d * t; h.n = normalize(h.p - center);
-                    h.mat = o->n_mats > 0 ? o->mat0 : -2; h.geom = oi;
-                    cand(h);
-                }
-            }
-            return;
-        }
-        case RT_KIND_PLANE: {                                      // simple_geometry.py:105-120
-            float3 n = f3(ld4(&o->b)); float t;
-            if (!plane_t(moved(o, f3(ld4(&o->a)), cx.time), n, r, t)) return;
-            if (t >= 0.0f && want(t)) {
-                Hit h; h.t = t; h.p = r.o + r.d * t; h.n = n;
-                h.mat = plane_material(o, h.p, cx.time); h.geom = oi;
-                cand(h);
-            }
-            return;
-        }
-        case RT_KIND_BOX: {                                        // simple_geometry.py:188-249: entry AND exit, both with the entry normal
-            float en, ex; int label;
-            if (!box_slabs(moved(o, f3(ld4(&o->a)), cx.time), moved(o, f3(ld4(&o->b)), cx.time), r, en, ex, label)) return;
-            if (en > ex || en < 0.0f) return;
-            float3 n = box_normal(r, label);
-            float ts[2] = {en, ex};
-            for (int k = 0; k < 2; k++)
-                if (want(ts[k])) {
-                    Hit h; h.t = ts[k]; h.p = r.o + r.d * ts[k]; h.n = n;
-                    h.mat = o->n_mats > 0 ? o->mat0 : -2; h.geom = oi;
-                    cand(h);
-                }
-            return;
-        }
-        case RT_KIND_MESH: {                                       // mesh.py:72-119 (every accepted face)
-            const DevMesh* m = cx.S.meshes + o->mesh;
-            if (!mesh_gate(m, r)) return;
-            float tmax = RT_INF;
-            const int mat = o->n_mats > 0 ? o->mat0 : -2;
-            const RayInv ri = ray_inv(r);
-            mesh_visit<true>(cx, m, ri, 0.0f, tmax, [&](int slot, float&) {
-                float3 v0, v1, v2; int face; float t;
-                tri_load(m, slot, v0, v1, v2, face);
-                if (tri_hit(v0, v1, v2, r, t) && want(t)) {
-                    Hit h; h.t = t; h.p = r.o + r.d * t; h.n = tri_normal(cx, m, slot, h.p); h.mat = mat; h.geom = oi;
-                    cand(h);
-                }
-                return false;
-            });
-            return;
-        }
-        default: return;
+    const int kind = o->kind;
+    if (kind == RT_KIND_MESH) { mesh_leaf_hits(cx, oi, r, want, cand); return; }   // out of line: rare under nodes, and large
+    float ts[2]; int nt = 0;
+    float3 nrm = f3(0, 0, 0), center = f3(0, 0, 0);
+    if (kind == RT_KIND_SPHERE) {                                  // simple_geometry.py:20-46: both roots with t > 0
+        float4 a = ld4(&o->a);
+        center = moved(o, f3(a), cx.time);
+        float t1, t2;
+        if (!sphere_roots(center, a.w, r, dot(r.d, r.d), t1, t2)) return;
+        if (t1 > 0.0f) ts[nt++] = t1;
+        if (t2 > 0.0f) ts[nt++] = t2;
+    } else if (kind == RT_KIND_PLANE) {                            // simple_geometry.py:105-120
+        nrm = f3(ld4(&o->b)); float t;
+        if (!plane_t(moved(o, f3(ld4(&o->a)), cx.time), nrm, r, t)) return;
+        if (t >= 0.0f) ts[nt++] = t;
+    } else if (kind == RT_KIND_BOX) {                              // simple_geometry.py:188-249: entry AND exit, both with the entry normal
+        float en, ex; int label;
+        if (!box_slabs(moved(o, f3(ld4(&o->a)), cx.time), moved(o, f3(ld4(&o->b)), cx.time), r, en, ex, label)) return;
+        if (en > ex || en < 0.0f) return;
+        nrm = box_normal(r, label);
+        ts[0] = en; ts[1] = ex; nt = 2;
+    }
+    for (int k = 0; k < nt; k++) {
+        const float t = k == 0 ? ts[0] : ts[1];
+        if (!want(t)) continue;
+        Hit h; h.t = t; h.p = r.o + r.d * t; h.geom = oi;
+        h.n = kind == RT_KIND_SPHERE ? normalize(h.p - center) : nrm;
+        h.mat = kind == RT_KIND_PLANE ? plane_material(o, h.p, cx.time) : (o->n_mats > 0 ? o->mat0 : -2);
+        cand(h);
     }
 }
 
@@ -663,12 +697,12 @@ RT_HD void object_hits(TraceCtx& cx, int root, const Ray& r, Want&& want, Emit&&
             const int c0 = nd->first_child, nc = nd->n_children;
             if (nd->csg == RT_CSG_INTERSECTION) {                  // hierarchy.py:52-57: every OTHER child contains it
                 for (int j = 0; j < nc; j++)
-                    if (c0 + j != child && !Nest<RT_MAX_NEST>::inside(cx, c0 + j, h.p)) return;
+                    if (c0 + j != child && !csg_inside(cx, c0 + j, h.p)) return;
             } else if (nd->csg == RT_CSG_DIFFERENCE) {             // hierarchy.py:58-70
-                if (child == c0) { if (Nest<RT_MAX_NEST>::inside(cx, c0 + 1, h.p)) return; }
+                if (child == c0) { if (csg_inside(cx, c0 + 1, h.p)) return; }
                 else {
-                    if (!Nest<RT_MAX_NEST>::inside(cx, c0, h.p)) return;
-                    h.mat = Nest<RT_MAX_NEST>::material(cx, c0, h.p);
+                    if (!csg_inside(cx, c0, h.p)) return;
+                    h.mat = csg_material(cx, c0, h.p);
                     h.n = -h.n;
                 }
             }
@@ -711,14 +745,10 @@ RT_HD void object_hits(TraceCtx& cx, int root, const Ray& r, Want&& want, Emit&&
 // children, `time > shadow_epsilon`, and ignores t_max.
 RT_HD_NOINLINE bool difference_shadow(TraceCtx& cx, int c0, const Ray& mr) {
     bool occ = false;
-    auto want = [&](float t) { return !occ && t > RT_SHADOW_EPS; };
-    object_hits(cx, c0, mr, want, [&](const Hit& h) {
-        if (!occ && !Nest<RT_MAX_NEST>::inside(cx, c0 + 1, h.p)) occ = true;
-    });
-    if (occ) return true;
-    object_hits(cx, c0 + 1, mr, want, [&](const Hit& h) {
-        if (!occ && Nest<RT_MAX_NEST>::inside(cx, c0, h.p)) occ = true;
-    });
+    for (int side = 0; side < 2 && !occ; side++)       // hits of c0 outside c1, then hits of c1 inside c0 (one instantiation of the walk)
+        object_hits(cx, c0 + side, mr, [&](float t) { return !occ && t > RT_SHADOW_EPS; }, [&](const Hit& h) {
+            if (!occ && csg_inside(cx, c0 + 1 - side, h.p) == (side == 1)) occ = true;
+        });
     return occ;
 }
 
@@ -815,7 +845,7 @@ RT_HD bool occluded(TraceCtx& cx, const Ray& r, float tmax) {
         } else if (kind != RT_KIND_NODE) {
             if (leaf_shadow<false>(cx, oi, r, tmax)) { occ = true; break; }
         } else if (HAS_NODES) {
-            if (Nest<RT_MAX_NEST>::shadow(cx, oi, r, tmax)) { occ = true; break; }
+            if (csg_shadow(cx, oi, r, tmax)) { occ = true; break; }
         }
     }
     cx.sbase = 0;

@@ -22,6 +22,13 @@
 #ifndef RT_MIN_BLOCKS_SHADOW
 #define RT_MIN_BLOCKS_SHADOW 8
 #endif
+// scenes with CSG / transform nodes (HAS_NODES): the node code needs far more registers than the plain walkers
+#ifndef RT_MIN_BLOCKS_HIT_CSG
+#define RT_MIN_BLOCKS_HIT_CSG 3
+#endif
+#ifndef RT_MIN_BLOCKS_SHADOW_CSG
+#define RT_MIN_BLOCKS_SHADOW_CSG 3
+#endif
 #ifndef RT_MIN_BLOCKS_SHADE
 #define RT_MIN_BLOCKS_SHADE 8
 #endif
@@ -110,7 +117,7 @@ struct HitPlanes { float4* planes; long long cap; };
 // PRIMARY: ray i of the batch is generated here: pixel = pixel_begin + i / N, slot = i % N = (d*S + s)*T + t (loop
 // order of scene.py:57-67).  Otherwise ray i is entry i of the compacted queue `qin` (count on the device).
 template <bool HAS_NODES, bool PRIMARY>
-__global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS_HIT) k_hit(SceneView S, PixelMap pm, long long pixel_begin, long long n_rays,
+__global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_HIT_CSG : RT_MIN_BLOCKS_HIT) k_hit(SceneView S, PixelMap pm, long long pixel_begin, long long n_rays,
                                                                      RayQueue qin, const unsigned long long* qin_count,
                                                                      HitPlanes H, RtCounters* counters) {
     Tally tally = tally_zero();
@@ -156,7 +163,7 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS_HIT) k_hit(SceneView S
 // LIGHT_ROWS: gridDim.y = lights (small queues of the deeper levels: every (light, ray) pair gets its own thread);
 // otherwise the whole grid sweeps the rays once per light (big level-0 batches: all resident warps on one light).
 template <bool HAS_NODES, bool LIGHT_ROWS>
-__global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS_SHADOW) k_shadow(SceneView S, long long n_rays, const unsigned long long* n_dev,
+__global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_SHADOW_CSG : RT_MIN_BLOCKS_SHADOW) k_shadow(SceneView S, long long n_rays, const unsigned long long* n_dev,
                                                                            HitPlanes H, uint8_t* __restrict__ occ, RtCounters* counters) {
     Tally tally = tally_zero();
     int spill[RT_STACK_SPILL];       // overflow of the shared-memory traversal stack (thread-local memory)

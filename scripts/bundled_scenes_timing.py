@@ -9,7 +9,13 @@ from conftest import ALL_CASES, load_case, manifest
 RAYS = ("rays_primary", "rays_shadow", "rays_reflect", "rays_refract")
 cases = [(c, None) for c in ALL_CASES] + [
     ("DepthOfField", {"resolution": [1920, 1080], "DOF": {"samples": 64}, "AA": {"jitter": True, "samples": 1}}),
-    ("MotionBlur", {"resolution": [1920, 1080], "motion": {"time": 2.0, "samples": 63, "final": 1}})]
+    ("MotionBlur", {"resolution": [1920, 1080], "motion": {"time": 2.0, "samples": 63, "final": 1}}),
+    # the two CSG showcase scenes at the values their files ship with (scenes/NovelScene1.json:2-4, NovelScene2.json:2-6)
+    ("NovelScene1_small", {"resolution": [2048, 1024], "AA": {"jitter": True, "samples": 32}}),
+    ("NovelScene2_small", {"resolution": [1024, 512], "AA": {"jitter": True, "samples": 2}, "DOF": {"samples": 15},
+                           "motion": {"time": 1.0, "final": 1, "samples": 15}})]
+if len(sys.argv) > 1:
+    cases = [c for c in cases if any(a in c[0] for a in sys.argv[1:]) and c[1]]
 man = manifest()
 for case, over in cases:
     sc = load_case(case, over)
@@ -20,7 +26,7 @@ for case, over in cases:
     ms = 1e3 * sorted(t)[len(t) // 2]
     c = sc.last_counters
     rays = sum(c[k] for k in RAYS)
-    out = {"case": case + ("@1920x1080x64" if over else ""), "W": sc.vc.width, "H": sc.vc.height, "rays": rays,
+    out = {"case": case + (f"@{sc.vc.width}x{sc.vc.height}x{sc.samples * sc.vc.dof_samples * len(sc.vc.motion_times)}" if over else ""), "W": sc.vc.width, "H": sc.vc.height, "rays": rays,
            "gpu_ms_e2e_u8": round(ms, 3), "gpu_mrays_s": round(rays / ms / 1e3, 1), "launches": c["kernel_launches"]}
     if not over:
         out["reference_python_cpu_seconds_dev_container"] = man[case].get("reference_cpu_seconds")
