@@ -118,6 +118,11 @@ static int scene_create_impl(const RtSceneDesc* d, RtScene* sc) {
     // ---- object BVH over the bounded top-level objects (host-built in convert_scene)
     sc->has_tlas = !hs.tlas_nodes.empty();
     if (sc->has_tlas) { BvhNode4* d_tn; UP(upload(sc, hs.tlas_nodes.data(), hs.tlas_nodes.size(), &d_tn)); V.tlas_nodes = d_tn; }
+    if (hs.has_nodes) {
+        float4 *d_clo, *d_chi;
+        UP(upload(sc, hs.child_lo.data(), hs.child_lo.size(), &d_clo)); UP(upload(sc, hs.child_hi.data(), hs.child_hi.size(), &d_chi));
+        V.child_lo = d_clo; V.child_hi = d_chi;
+    }
     int* d_lin; UP(upload(sc, hs.lin_objs.data(), hs.lin_objs.size(), &d_lin));
     V.lin_objs = d_lin; V.n_lin = (int)hs.lin_objs.size();
     int* d_sep; UP(upload(sc, hs.sep_mesh.data(), hs.sep_mesh.size(), &d_sep));

@@ -502,6 +502,24 @@ RT_HD_NOINLINE bool difference_shadow(TraceCtx& cx, int c0, const Ray& mr);
 // unrolled the recursion through templates, eight copies of everything, and the node kernels were instruction-fetch bound).
 // Nesting deeper than RT_MAX_NEST is flagged (RT_ERR_LIMIT) and treated as empty.
 
+// Pruning by the children's bounds (SceneView::child_lo/hi, parent space).  Both tests only ever say "cannot": the
+// boxes are padded, an unbounded or top-level object carries [-inf, +inf] and always passes.
+RT_HD float3 csg_ray_inv(const Ray& r) { return f3(safe_rcp(r.d.x), safe_rcp(r.d.y), safe_rcp(r.d.z)); }
+RT_HD bool child_may_hit(const SceneView& S, int oi, const Ray& r, float3 inv) {
+    const float4 lo = ld4(S.child_lo + oi), hi = ld4(S.child_hi + oi);
+    if (lo.x == -RT_INF) return true;
+    const float ax = (lo.x - r.o.x) * inv.x, bx = (hi.x - r.o.x) * inv.x;
+    const float ay = (lo.y - r.o.y) * inv.y, by = (hi.y - r.o.y) * inv.y;
+    const float az = (lo.z - r.o.z) * inv.z, bz = (hi.z - r.o.z) * inv.z;
+    const float entry = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
+    const float exit_ = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
+    return entry <= exit_;
+}
+RT_HD bool child_may_contain(const SceneView& S, int oi, float3 p) {
+    const float4 lo = ld4(S.child_lo + oi), hi = ld4(S.child_hi + oi);
+    return !(p.x < lo.x || p.x > hi.x || p.y < lo.y || p.y > hi.y || p.z < lo.z || p.z > hi.z);
+}
+
 // is_inside of a leaf (Sphere simple_geometry.py:74-80, AABB :296-307; Plane/Mesh: base class False)
 RT_HD bool leaf_inside(const TraceCtx& cx, const DevObject* o, float3 p) {
     if (o->kind == RT_KIND_SPHERE) {
@@ -538,7 +556,8 @@ RT_HD_NOINLINE bool csg_inside(TraceCtx& cx, int root, float3 p) {
     for (;;) {
         const DevObject* o = objs + cur;
         bool val;
-        if (o->kind == RT_KIND_NODE) {
+        if (!child_may_contain(cx.S, cur, cp)) val = false;      // outside the child's bound: not inside it
+        else if (o->kind == RT_KIND_NODE) {
             const int ar = csg_arity(o);
             if (d + 1 >= RT_MAX_NEST) { cx.tally.err |= 1u << RT_ERR_LIMIT; val = false; }
             else if (ar == 0) val = o->csg == RT_CSG_INTERSECTION;
@@ -579,16 +598,18 @@ RT_HD_NOINLINE int csg_material(TraceCtx& cx, int oi, float3 p) {
 
 // shadow_intersect (hierarchy.py:80-109 and the leaf versions): union = any child, intersection = ALL children report
 // shadow, difference goes through intersect() and ignores t_max
-struct ShadowFrame { int obj, cursor; Ray ray; };
+struct ShadowFrame { int obj, cursor; Ray ray; float3 inv; };
 RT_HD_NOINLINE bool csg_shadow(TraceCtx& cx, int root, const Ray& r, float tmax) {
     const DevObject* objs = cx.S.objects;
     ShadowFrame st[RT_MAX_NEST];
     int d = -1, cur = root;
     Ray cr = r;
+    float3 cinv = csg_ray_inv(r);
     for (;;) {
         const DevObject* o = objs + cur;
         bool val;
-        if (o->kind == RT_KIND_NODE) {
+        if (!child_may_hit(cx.S, cur, cr, cinv)) val = false;    // the ray misses the child's bound: it casts no shadow on it
+        else if (o->kind == RT_KIND_NODE) {
             cx.tally.prims++;
             if (d + 1 >= RT_MAX_NEST) { cx.tally.err |= 1u << RT_ERR_LIMIT; val = false; }
             else {
@@ -599,7 +620,8 @@ RT_HD_NOINLINE bool csg_shadow(TraceCtx& cx, int root, const Ray& r, float tmax)
                 else if (o->csg == RT_CSG_DIFFERENCE) val = difference_shadow(cx, o->first_child, mr);
                 else {
                     d++;
-                    st[d].obj = cur; st[d].cursor = 0; st[d].ray = mr;
+                    cinv = csg_ray_inv(mr);
+                    st[d].obj = cur; st[d].cursor = 0; st[d].ray = mr; st[d].inv = cinv;
                     cr = mr; cur = o->first_child;
                     continue;
                 }
@@ -610,7 +632,7 @@ RT_HD_NOINLINE bool csg_shadow(TraceCtx& cx, int root, const Ray& r, float tmax)
             const DevObject* nd = objs + st[d].obj;
             if (csg_step(nd, st[d].cursor, csg_arity(nd), val)) { d--; continue; }
             st[d].cursor++;
-            cur = nd->first_child + st[d].cursor; cr = st[d].ray;
+            cur = nd->first_child + st[d].cursor; cr = st[d].ray; cinv = st[d].inv;
             break;
         }
     }
@@ -682,7 +704,7 @@ RT_HD void leaf_hits(TraceCtx& cx, int oi, const Ray& r, Want&& want, Cand&& can
 // (times never change on the way up, so `want(t)` prunes before any of that work).  The reference
 // enumerates hits in list order; consumers here are order-free (strict-< running minimum in DFS
 // order == list order; boolean any).
-struct NodeFrame { int obj; int cursor; Ray ray; };
+struct NodeFrame { int obj; int cursor; Ray ray; float3 inv; };
 
 template <class Want, class Emit>
 RT_HD void object_hits(TraceCtx& cx, int root, const Ray& r, Want&& want, Emit&& emit) {
@@ -714,6 +736,7 @@ RT_HD void object_hits(TraceCtx& cx, int root, const Ray& r, Want&& want, Emit&&
         }
         emit(h);
     };
+    if (!child_may_hit(cx.S, root, r, csg_ray_inv(r))) return;      // (roots that are top-level objects always pass)
     if (objs[root].kind != RT_KIND_NODE) { leaf_hits(cx, root, r, want, cand); return; }
     auto push = [&](int oi, const Ray& pr) {
         const DevXform* xf = cx.S.xforms + objs[oi].xform;
@@ -721,6 +744,7 @@ RT_HD void object_hits(TraceCtx& cx, int root, const Ray& r, Want&& want, Emit&&
         fr[depth].obj = oi; fr[depth].cursor = 0;
         fr[depth].ray.o = xform_point(xf->Minv, pr.o);              // hierarchy.py:43-45 (direction NOT renormalised)
         fr[depth].ray.d = xform_dir(xf->Minv, pr.d);
+        fr[depth].inv = csg_ray_inv(fr[depth].ray);
         cx.tally.prims++;
     };
     push(root, r);
@@ -730,6 +754,7 @@ RT_HD void object_hits(TraceCtx& cx, int root, const Ray& r, Want&& want, Emit&&
         const int limit = (csg == RT_CSG_UNION || csg == RT_CSG_INTERSECTION) ? nc : ((csg == RT_CSG_DIFFERENCE && nc >= 2) ? 2 : 0);
         if (fr[depth].cursor >= limit) { depth--; continue; }
         const int child = nd->first_child + fr[depth].cursor++;
+        if (!child_may_hit(cx.S, child, fr[depth].ray, fr[depth].inv)) continue;   // no hit of this child (or anything below it) is possible
         if (objs[child].kind == RT_KIND_NODE) {
             if (depth + 1 >= RT_MAX_NEST) { cx.tally.err |= 1u << RT_ERR_LIMIT; continue; }
             Ray pr = fr[depth].ray;

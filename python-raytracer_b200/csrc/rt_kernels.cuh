@@ -24,10 +24,10 @@
 #endif
 // scenes with CSG / transform nodes (HAS_NODES): the node code needs far more registers than the plain walkers
 #ifndef RT_MIN_BLOCKS_HIT_CSG
-#define RT_MIN_BLOCKS_HIT_CSG 3
+#define RT_MIN_BLOCKS_HIT_CSG 4
 #endif
 #ifndef RT_MIN_BLOCKS_SHADOW_CSG
-#define RT_MIN_BLOCKS_SHADOW_CSG 3
+#define RT_MIN_BLOCKS_SHADOW_CSG 4
 #endif
 #ifndef RT_MIN_BLOCKS_SHADE
 #define RT_MIN_BLOCKS_SHADE 8

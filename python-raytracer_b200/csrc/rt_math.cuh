@@ -58,24 +58,34 @@ RT_HD float3 refract3(float3 i, float3 n, float eta, bool& tir) {
     return i * eta - n * (eta * d + sqrtf(k));
 }
 
-// column-major 4x4 (m[col*4+row]) times (p,1) / (d,0), GLM order (m0*x + m1*y) + (m2*z + m3*w)
+// column-major 4x4 (m[col*4+row]) times (p,1) / (d,0), GLM order (m0*x + m1*y) + (m2*z + m3*w).  The matrix is read as
+// its four columns (128-bit loads; DevXform is 16-byte aligned), not as 12-16 scalar loads.
+#if defined(__CUDA_ARCH__)
+#define RT_COL(m, k) __ldg(reinterpret_cast<const float4*>(m) + (k))
+#else
+inline float4 rt_col_host(const float* m, int k) { float4 r; __builtin_memcpy(&r, m + 4 * k, sizeof(r)); return r; }   // caller buffers: any alignment
+#define RT_COL(m, k) rt_col_host(m, k)
+#endif
 RT_HD float3 xform_point(const float* __restrict__ m, float3 p) {
-    return f3((RT_LDG(m + 0) * p.x + RT_LDG(m + 4) * p.y) + (RT_LDG(m + 8) * p.z + RT_LDG(m + 12)),
-              (RT_LDG(m + 1) * p.x + RT_LDG(m + 5) * p.y) + (RT_LDG(m + 9) * p.z + RT_LDG(m + 13)),
-              (RT_LDG(m + 2) * p.x + RT_LDG(m + 6) * p.y) + (RT_LDG(m + 10) * p.z + RT_LDG(m + 14)));
+    const float4 c0 = RT_COL(m, 0), c1 = RT_COL(m, 1), c2 = RT_COL(m, 2), c3 = RT_COL(m, 3);
+    return f3((c0.x * p.x + c1.x * p.y) + (c2.x * p.z + c3.x),
+              (c0.y * p.x + c1.y * p.y) + (c2.y * p.z + c3.y),
+              (c0.z * p.x + c1.z * p.y) + (c2.z * p.z + c3.z));
 }
 RT_HD float3 xform_dir(const float* __restrict__ m, float3 d) {
-    return f3((RT_LDG(m + 0) * d.x + RT_LDG(m + 4) * d.y) + RT_LDG(m + 8) * d.z,
-              (RT_LDG(m + 1) * d.x + RT_LDG(m + 5) * d.y) + RT_LDG(m + 9) * d.z,
-              (RT_LDG(m + 2) * d.x + RT_LDG(m + 6) * d.y) + RT_LDG(m + 10) * d.z);
+    const float4 c0 = RT_COL(m, 0), c1 = RT_COL(m, 1), c2 = RT_COL(m, 2);
+    return f3((c0.x * d.x + c1.x * d.y) + c2.x * d.z,
+              (c0.y * d.x + c1.y * d.y) + c2.y * d.z,
+              (c0.z * d.x + c1.z * d.y) + c2.z * d.z);
 }
 // hierarchy.py:76: normalize(transpose(Minv) * vec4(n,0)).xyz -- the vec4 is normalised INCLUDING
 // its w = Minv[:,3] . n, so normals under translated nodes come out shorter than unit
 RT_HD float3 xform_normal(const float* __restrict__ mi, float3 n) {
-    float x = (RT_LDG(mi + 0) * n.x + RT_LDG(mi + 1) * n.y) + RT_LDG(mi + 2) * n.z;
-    float y = (RT_LDG(mi + 4) * n.x + RT_LDG(mi + 5) * n.y) + RT_LDG(mi + 6) * n.z;
-    float z = (RT_LDG(mi + 8) * n.x + RT_LDG(mi + 9) * n.y) + RT_LDG(mi + 10) * n.z;
-    float w = (RT_LDG(mi + 12) * n.x + RT_LDG(mi + 13) * n.y) + RT_LDG(mi + 14) * n.z;
+    const float4 c0 = RT_COL(mi, 0), c1 = RT_COL(mi, 1), c2 = RT_COL(mi, 2), c3 = RT_COL(mi, 3);
+    float x = (c0.x * n.x + c0.y * n.y) + c0.z * n.z;
+    float y = (c1.x * n.x + c1.y * n.y) + c1.z * n.z;
+    float z = (c2.x * n.x + c2.y * n.y) + c2.z * n.z;
+    float w = (c3.x * n.x + c3.y * n.y) + c3.z * n.z;
     float inv = 1.0f / sqrtf((x * x + y * y) + (z * z + w * w));
     return f3(x * inv, y * inv, z * inv);
 }

@@ -20,6 +20,7 @@ struct HostScene {
     std::vector<BvhNode4> tlas_nodes;  // object BVH over the bounded top-level objects (empty: none)
     std::vector<int> lin_objs;         // top-level objects tested one by one (no finite bounds)
     std::vector<int> sep_mesh;         // top-level meshes, traversed after the walk over the other objects
+    std::vector<float4> child_lo, child_hi;   // per object: padded bounds in the parent's space (SceneView::child_lo/hi)
     bool has_nodes = false, has_specular = false, has_mesh = false;
     SceneView view{};          // scalars filled; pointers are the caller's business
 };
@@ -148,19 +149,33 @@ inline int tlas_build(std::vector<TlasItem>& it, int b, int e, BinTree& bt, int 
     return idx;
 }
 
+inline float bound_pad(const ObjBound& b) {                  // fp32 slack of the exact tests (hit points a few ulp off the surface)
+    const float m = fmaxf(fmaxf(fabsf(b.lo.x), fabsf(b.hi.x)), fmaxf(fmaxf(fabsf(b.lo.y), fabsf(b.hi.y)), fmaxf(fabsf(b.lo.z), fabsf(b.hi.z))));
+    return 1e-4f * m + 1e-5f;
+}
+
 // splits the top-level objects into the object BVH (finite bounds) and the linear list (the rest, scene order)
 inline void build_tlas(const RtSceneDesc* d, HostScene& hs) {
     hs.tlas_nodes.clear(); hs.lin_objs.clear();
     float tlo = INFINITY, thi = -INFINITY;
     for (int t = 0; t < d->n_times; t++) { float v = (float)d->motion_times[t]; tlo = fminf(tlo, v); thi = fmaxf(thi, v); }
+    // bounds of the nodes' children, each in its parent's space
+    hs.child_lo.assign((size_t)d->n_objects, f4(-INFINITY, -INFINITY, -INFINITY, 0.0f));
+    hs.child_hi.assign((size_t)d->n_objects, f4(INFINITY, INFINITY, INFINITY, 0.0f));
+    for (int i = d->n_top; i < d->n_objects && std::isfinite(tlo) && std::isfinite(thi); i++) {
+        const ObjBound b = object_bound(d, i, tlo, thi);
+        if (!b.finite || !finite3(b.lo) || !finite3(b.hi)) continue;
+        const float pad = bound_pad(b);
+        hs.child_lo[i] = f4(b.lo.x - pad, b.lo.y - pad, b.lo.z - pad, 0.0f);
+        hs.child_hi[i] = f4(b.hi.x + pad, b.hi.y + pad, b.hi.z + pad, 0.0f);
+    }
     hs.sep_mesh.clear();
     std::vector<TlasItem> items;
     for (int i = 0; i < d->n_top; i++) {
         if (d->objects[i].kind == RT_KIND_MESH) { hs.sep_mesh.push_back(i); continue; }
         ObjBound b = (std::isfinite(tlo) && std::isfinite(thi)) ? object_bound(d, i, tlo, thi) : ObjBound{f3(0, 0, 0), f3(0, 0, 0), false};
         if (!b.finite) { hs.lin_objs.push_back(i); continue; }
-        const float m = fmaxf(fmaxf(fabsf(b.lo.x), fabsf(b.hi.x)), fmaxf(fmaxf(fabsf(b.lo.y), fabsf(b.hi.y)), fmaxf(fabsf(b.lo.z), fabsf(b.hi.z))));
-        const float pad = 1e-4f * m + 1e-5f;                 // fp32 slack of the exact tests (hit points a few ulp off the surface)
+        const float pad = bound_pad(b);
         TlasItem ti; ti.lo = b.lo - f3(pad, pad, pad); ti.hi = b.hi + f3(pad, pad, pad); ti.obj = i;
         const int kind = d->objects[i].kind;                  // mesh.py:121-153 and hierarchy.py:94-107 ignore t_max
         ti.flags = (kind == RT_KIND_MESH || kind == RT_KIND_NODE) ? RT_TLAS_NO_TMAX : 0;

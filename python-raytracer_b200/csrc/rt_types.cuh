@@ -45,7 +45,7 @@ struct __attribute__((aligned(16))) DevLight {
     float4 dir_norm;  // directional: normalize(-vector) (scene.py:173), precomputed
 };
 
-struct DevXform { float M[16]; float Minv[16]; };
+struct __attribute__((aligned(16))) DevXform { float M[16]; float Minv[16]; };   // columns are read as float4
 
 // Binary LBVH node as the builder emits it before the 4-wide collapse (build-time only), 64 B:
 //   q0 = (c0.min.xyz, c0.max.x)  q1 = (c0.max.yz, c1.min.xy)  q2 = (c1.min.z, c1.max.xyz)  q3 = (bits child0, bits child1, -, -)
@@ -91,6 +91,11 @@ struct SceneView {
     // of a warp enter the (long) LBVH traversal together instead of at whatever step their walk happens to reach the mesh
     const int* sep_mesh;
     int n_sep_mesh;
+    // conservative bounds of every object IN ITS PARENT'S SPACE (children of CSG / transform nodes; top-level objects and
+    // unbounded ones carry [-inf, +inf]): a ray or point outside them cannot hit / be inside that child, so whole subtrees
+    // of a node are skipped without transforming the ray into them.  NULL when the scene has no nodes.
+    const float4* child_lo;
+    const float4* child_hi;
     // sampling tables (scene.py:41-43,118-138 precomputed once per scene)
     const float* col_x;          // [W]  (float)x of pixel-centre column
     const float* row_y;          // [H]

@@ -111,6 +111,7 @@ static int make_sim(const RtSceneDesc* d, Sim& sim) {
     V.ray_origin = sim.hs.ray_origin.data(); V.times = sim.hs.times.data();
     V.tlas_nodes = sim.hs.tlas_nodes.empty() ? nullptr : sim.hs.tlas_nodes.data();
     V.lin_objs = sim.hs.lin_objs.data(); V.n_lin = (int)sim.hs.lin_objs.size();
+    V.child_lo = sim.hs.has_nodes ? sim.hs.child_lo.data() : nullptr; V.child_hi = sim.hs.has_nodes ? sim.hs.child_hi.data() : nullptr;
     V.sep_mesh = sim.hs.sep_mesh.data(); V.n_sep_mesh = (int)sim.hs.sep_mesh.size();
     return 0;
 }
