@@ -274,6 +274,37 @@ def test_synthetic_mesh_scene_sampled_parity_and_bvh_equivalence():
     assert frac >= PARITY_FRACTION, (frac, dmax)
 
 
+def test_config5_full_size_4k_64spp_1m_triangles():
+    """BASELINE.json configs[4] at FULL size (3840x2160 x 64 spp, 1 048 576 triangles + 64 spheres: the bench workload),
+    through size-independent properties: ray tallies, a sub-rectangle rendered alone == the same pixels of the frame
+    (counter-based jitter, tile/batch independence), LBVH + object BVH == the reference's own loops (brute force over
+    every face, in-order object list) on a 16x16-pixel window on the mesh, and 48 random pixels (all 64 samples each)
+    against the brute-force oracle."""
+    from python_raytracer_b200 import synthetic
+    sc = synthetic.make_scene(ingest="device")
+    W, H = 3840, 2160
+    assert (sc.vc.width, sc.vc.height, sc.samples) == (W, H, 64) and sc.objects[1].faces.shape[0] == 1048576
+    img = sc.render_region(0, W, 0, H)
+    c = dict(sc.last_counters)
+    assert c["rays_primary"] == W * H * 64 and c["error_flags"] == 0
+    assert c["rays_shadow"] == 3 * c["shaded_hits"] and c["rays_reflect"] > 0 and c["rays_refract"] > 0
+    assert np.isfinite(img).all() and img.min() >= 0.0 and img.max() <= 1.0
+    c0, r0, n = 1912, 1072, 16
+    win = sc.render_region(c0, n, r0, n, mesh_mode=0).copy()
+    assert np.array_equal(win, img[c0:c0 + n, r0:r0 + n])
+    assert sc.last_counters["tri_tests"] > 0                      # the window is on the mesh
+    brute = sc.render_region(c0, n, r0, n, mesh_mode=3)
+    assert sc.last_counters["tri_tests"] >= 1048576 * n * n * 64
+    assert np.array_equal(win, brute)
+    rng = np.random.default_rng(11)
+    cols, rows = rng.integers(0, W, 48), rng.integers(0, H, 48)
+    ref, _ = oracle.render_pixels(sc.flatten(), abi, cols, rows)
+    a = (np.asarray(img[cols, rows], dtype=np.float64) * 255).astype(np.uint8).astype(int)
+    b = (ref * 255).astype(np.uint8).astype(int)
+    bad = int((np.abs(a - b).max(axis=1) > 1).sum())
+    assert bad <= 1, (bad, np.abs(a - b).max())    # 48 pixels cannot resolve a 0.1 % residue: at most one edge pixel may differ
+
+
 @pytest.mark.parametrize("case,over", [
     ("DepthOfField", {"resolution": [1920, 1080], "DOF": {"samples": 64}, "AA": {"jitter": True, "samples": 1}}),
     ("MotionBlur", {"resolution": [1920, 1080], "motion": {"time": 2.0, "samples": 63, "final": 1}}),
