@@ -242,7 +242,19 @@ static int build_mesh_bvh(RtScene* sc, int mi, cudaStream_t st) {
     cudaError_t e = cudaSuccess;
     b.n_nodes4 = 0;
     if (n >= 2) {
-        k_lbvh_even<<<G, T, 0, st>>>(n, parent_node, even, remap);
+        // which binary nodes become 4-wide nodes: rounds of top-down marking from the root (arrive[] is free again: reused
+        // as the marks), a host look at the "changed" flag every 8 rounds
+        unsigned* mark = arrive;
+        unsigned* d_changed = (unsigned*)hist;
+        const unsigned one = 1u;
+        cudaMemsetAsync(mark, 0, sizeof(unsigned) * n, st);
+        cudaMemcpyAsync(mark, &one, sizeof(unsigned), cudaMemcpyHostToDevice, st);
+        for (unsigned round = 1, go = 1; go && round < 4096; ) {
+            cudaMemsetAsync(d_changed, 0, sizeof(unsigned), st);
+            for (int k = 0; k < 8; k++, round++) k_lbvh_mark<<<G, T, 0, st>>>(n, children, node_lo, node_hi, mark, round, d_changed);
+            if (cudaMemcpyAsync(&go, d_changed, sizeof(unsigned), cudaMemcpyDeviceToHost, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) break;
+        }
+        k_lbvh_flags<<<G, T, 0, st>>>(n, mark, even, remap);
         k_rs_scan<<<1, 1024, 0, st>>>(remap, n - 1);
         unsigned last_idx = 0, last_even = 0;
         e = cudaMemcpyAsync(&last_idx, remap + (n - 2), sizeof(unsigned), cudaMemcpyDeviceToHost, st);

@@ -195,14 +195,15 @@ inline void build_tlas(const RtSceneDesc* d, HostScene& hs) {
     }
     float3 lo, hi; int flags;
     tlas_build(items, 0, (int)items.size(), bt, 0, lo, hi, flags);
-    // 4-wide collapse: even-depth nodes survive, numbered in index order (rt_bvh.cuh)
+    // 4-wide collapse (rt_bvh.cuh: largest-area child opened first), nodes numbered in index order
     const int nb = (int)bt.children.size();
-    std::vector<unsigned> remap(nb, 0);
+    std::vector<unsigned> remap(nb, 0), wide(nb, 0);
+    wide_mark_host(bt.children.data(), bt.node_lo.data(), bt.node_hi.data(), nb, wide.data());
     unsigned n4 = 0;
-    for (int i = 0; i < nb; i++) if ((bt.depth[i] & 1) == 0) remap[i] = n4++;
+    for (int i = 0; i < nb; i++) if (wide[i]) remap[i] = n4++;
     hs.tlas_nodes.resize(n4);
     for (int i = 0; i < nb; i++)
-        if ((bt.depth[i] & 1) == 0)
+        if (wide[i])
             hs.tlas_nodes[remap[i]] = make_wide_node(bt.children.data(), i, remap.data(), bt.leaf_lo.data(), bt.leaf_hi.data(),
                                                      bt.node_lo.data(), bt.node_hi.data(), bt.leaf_flags.data(), bt.node_flags.data(), 0.0f);
 }

@@ -84,10 +84,12 @@ static void build_mesh(const RtMesh& m, HostMesh& hm, DevMesh& g) {
         refit(ch, 0, 0, leaf_lo, leaf_hi, nlo, nhi, dep, rl, rh);
         std::vector<unsigned> remap(n - 1, 0);
         unsigned n4 = 0;
-        for (int i = 0; i < n - 1; i++) if ((dep[i] & 1) == 0) remap[i] = n4++;
+        std::vector<unsigned> wide(n - 1, 0);
+        wide_mark_host(ch.data(), nlo.data(), nhi.data(), n - 1, wide.data());
+        for (int i = 0; i < n - 1; i++) if (wide[i]) remap[i] = n4++;
         hm.nodes.resize(n4);
         for (int i = 0; i < n - 1; i++)
-            if ((dep[i] & 1) == 0)
+            if (wide[i])
                 hm.nodes[remap[i]] = make_wide_node(ch.data(), i, remap.data(), leaf_lo.data(), leaf_hi.data(), nlo.data(), nhi.data(),
                                                     nullptr, nullptr, pad);
     }
