@@ -83,14 +83,18 @@ RT_HD float box_half_area(const float4& lo, const float4& hi) {
     const float dx = hi.x - lo.x, dy = hi.y - lo.y, dz = hi.z - lo.z;
     return dx * dy + dy * dz + dz * dx;
 }
-RT_HD int wide_children(const int2* children, const float4* node_lo, const float4* node_hi, int i, int out[4]) {
+// leaf_tris > 1 (mesh LBVH only): a binary node whose subtree holds at most that many triangles is not opened but becomes
+// ONE leaf slot over its (consecutive, Morton-ordered) triangle slots; the refit leaves (first slot, count) in the .w of
+// the node's box corners.
+RT_HD bool wide_openable(const float4* node_hi, int c, int leaf_tris) { return c >= 0 && (leaf_tris <= 1 || as_int(node_hi[c].w) > leaf_tris); }
+RT_HD int wide_children(const int2* children, const float4* node_lo, const float4* node_hi, int i, int leaf_tris, int out[4]) {
     const int2 ch = children[i];
     out[0] = ch.x; out[1] = ch.y;
     int n = 2;
     while (n < 4) {
         int pick = -1; float best = -1.0f;
         for (int k = 0; k < n; k++)
-            if (out[k] >= 0) { const float a = box_half_area(node_lo[out[k]], node_hi[out[k]]); if (a > best) { best = a; pick = k; } }
+            if (wide_openable(node_hi, out[k], leaf_tris)) { const float a = box_half_area(node_lo[out[k]], node_hi[out[k]]); if (a > best) { best = a; pick = k; } }
         if (pick < 0) break;
         const int2 g = children[out[pick]];
         for (int k = n; k > pick + 1; k--) out[k] = out[k - 1];
@@ -100,7 +104,7 @@ RT_HD int wide_children(const int2* children, const float4* node_lo, const float
     return n;
 }
 // which binary nodes become traversal nodes (host form: breadth-first from the root; the GPU does it in rounds, k_lbvh_mark)
-inline void wide_mark_host(const int2* children, const float4* node_lo, const float4* node_hi, int n_internal, unsigned* is_wide) {
+inline void wide_mark_host(const int2* children, const float4* node_lo, const float4* node_hi, int n_internal, int leaf_tris, unsigned* is_wide) {
     for (int i = 0; i < n_internal; i++) is_wide[i] = 0;
     if (n_internal <= 0) return;
     int* queue = new int[n_internal];
@@ -108,8 +112,8 @@ inline void wide_mark_host(const int2* children, const float4* node_lo, const fl
     queue[qt++] = 0; is_wide[0] = 1;
     while (qh < qt) {
         int c[4];
-        const int n = wide_children(children, node_lo, node_hi, queue[qh++], c);
-        for (int k = 0; k < n; k++) if (c[k] >= 0) { is_wide[c[k]] = 1; queue[qt++] = c[k]; }
+        const int n = wide_children(children, node_lo, node_hi, queue[qh++], leaf_tris, c);
+        for (int k = 0; k < n; k++) if (wide_openable(node_hi, c[k], leaf_tris)) { is_wide[c[k]] = 1; queue[qt++] = c[k]; }
     }
     delete[] queue;
 }
@@ -118,7 +122,8 @@ RT_HD void set4i(int4& v, int k, int x) { if (k == 0) v.x = x; else if (k == 1) 
 // one traversal node from the binary tree: boxes padded by `pad`; remap: binary index -> compact wide index;
 // leaf_flags may be NULL (mesh LBVH)
 RT_HD BvhNode4 make_wide_node(const int2* children, int i, const unsigned* remap, const float4* leaf_lo, const float4* leaf_hi,
-                              const float4* node_lo, const float4* node_hi, const int* leaf_flags, const int* node_flags, float pad) {
+                              const float4* node_lo, const float4* node_hi, const int* leaf_flags, const int* node_flags, float pad,
+                              int leaf_tris = 1) {
     BvhNode4 nd;
     const float inf = RT_INF;                  // empty slots: [+inf, -inf] boxes, missed by every ray (see RT_SLAB4)
     nd.lox = nd.loy = nd.loz = f4(inf, inf, inf, inf);
@@ -126,13 +131,16 @@ RT_HD BvhNode4 make_wide_node(const int2* children, int i, const unsigned* remap
     nd.link.x = nd.link.y = nd.link.z = nd.link.w = RT_LINK_NONE;
     nd.flags.x = nd.flags.y = nd.flags.z = nd.flags.w = 0;
     int c[4];
-    const int n = wide_children(children, node_lo, node_hi, i, c);
+    const int n = wide_children(children, node_lo, node_hi, i, leaf_tris, c);
     for (int k = 0; k < n; k++) {
         const bool leaf = c[k] < 0;
         const float4 lo = leaf ? leaf_lo[~c[k]] : node_lo[c[k]], hi = leaf ? leaf_hi[~c[k]] : node_hi[c[k]];
         set4(nd.lox, k, lo.x - pad); set4(nd.loy, k, lo.y - pad); set4(nd.loz, k, lo.z - pad);
         set4(nd.hix, k, hi.x + pad); set4(nd.hiy, k, hi.y + pad); set4(nd.hiz, k, hi.z + pad);
-        set4i(nd.link, k, leaf ? c[k] : (int)remap[c[k]]);
+        int link = leaf ? c[k] : (int)remap[c[k]];
+        if (!leaf && !wide_openable(node_hi, c[k], leaf_tris))      // small subtree folded into one multi-triangle leaf
+            link = ~(as_int(node_lo[c[k]].w) | ((as_int(node_hi[c[k]].w) - 1) << RT_LEAF_SLOT_BITS));
+        set4i(nd.link, k, link);
         if (leaf_flags) set4i(nd.flags, k, leaf ? leaf_flags[~c[k]] : node_flags[c[k]]);
     }
     return nd;
@@ -264,8 +272,11 @@ __global__ void k_lbvh_leaves_refit(const float* __restrict__ verts, const int* 
         float4 l0, h0, l1, h1;                             // L1 is not coherent: read the siblings' boxes from L2
         if (ch.x < 0) { l0 = __ldcg(leaf_lo + ~ch.x); h0 = __ldcg(leaf_hi + ~ch.x); } else { l0 = __ldcg(node_lo + ch.x); h0 = __ldcg(node_hi + ch.x); }
         if (ch.y < 0) { l1 = __ldcg(leaf_lo + ~ch.y); h1 = __ldcg(leaf_hi + ~ch.y); } else { l1 = __ldcg(node_lo + ch.y); h1 = __ldcg(node_hi + ch.y); }
-        node_lo[node] = f4(fminf(l0.x, l1.x), fminf(l0.y, l1.y), fminf(l0.z, l1.z), 0.0f);
-        node_hi[node] = f4(fmaxf(h0.x, h1.x), fmaxf(h0.y, h1.y), fmaxf(h0.z, h1.z), 0.0f);
+        // .w of the corners: first triangle slot and number of triangles under the node (bit patterns)
+        const int f0 = ch.x < 0 ? ~ch.x : __float_as_int(l0.w), f1 = ch.y < 0 ? ~ch.y : __float_as_int(l1.w);
+        const int n0 = ch.x < 0 ? 1 : __float_as_int(h0.w), n1 = ch.y < 0 ? 1 : __float_as_int(h1.w);
+        node_lo[node] = f4(fminf(l0.x, l1.x), fminf(l0.y, l1.y), fminf(l0.z, l1.z), __int_as_float(min(f0, f1)));
+        node_hi[node] = f4(fmaxf(h0.x, h1.x), fmaxf(h0.y, h1.y), fmaxf(h0.z, h1.z), __int_as_float(n0 + n1));
         __threadfence();
         node = parent_node[node];
     }
@@ -278,9 +289,9 @@ __global__ void k_lbvh_mark(int n, const int2* __restrict__ children, const floa
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n - 1 || mark[i] != round) return;
     int c[4];
-    const int nc = wide_children(children, node_lo, node_hi, i, c);
+    const int nc = wide_children(children, node_lo, node_hi, i, RT_LEAF_TRIS, c);
     bool any = false;
-    for (int k = 0; k < nc; k++) if (c[k] >= 0) { mark[c[k]] = round + 1; any = true; }
+    for (int k = 0; k < nc; k++) if (wide_openable(node_hi, c[k], RT_LEAF_TRIS)) { mark[c[k]] = round + 1; any = true; }
     if (any) *changed = 1u;
 }
 // marks -> 0/1 flags (`even` keeps its name from the depth-parity collapse it replaces) and the scan input
@@ -297,6 +308,6 @@ __global__ void k_lbvh_emit4(int n, const int2* __restrict__ children, const uns
                              const float4* __restrict__ node_lo, const float4* __restrict__ node_hi, float pad, BvhNode4* __restrict__ out) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n - 1 || !even[i]) return;
-    out[remap[i]] = make_wide_node(children, i, remap, leaf_lo, leaf_hi, node_lo, node_hi, nullptr, nullptr, pad);
+    out[remap[i]] = make_wide_node(children, i, remap, leaf_lo, leaf_hi, node_lo, node_hi, nullptr, nullptr, pad, RT_LEAF_TRIS);
 }
 #endif  // __CUDACC__

@@ -309,8 +309,12 @@ RT_HD void mesh_visit(TraceCtx& cx, const DevMesh* m, const RayInv& ri, float tm
             const int k = first_bit(lm);
             lm &= lm - 1u;
             if (ORDERED && sel4(n0, n1, n2, n3, k) > tmax) continue;        // an earlier leaf of this node already came closer
-            cx.tally.tris++;
-            if (onTri(~link_of(link, (unsigned)k), tmax)) return;
+            const int code = ~link_of(link, (unsigned)k);                    // first slot | (count - 1) << RT_LEAF_SLOT_BITS
+            const int first = code & ((1 << RT_LEAF_SLOT_BITS) - 1), last = first + (code >> RT_LEAF_SLOT_BITS);
+            for (int s = first; s <= last; s++) {
+                cx.tally.tris++;
+                if (onTri(s, tmax)) return;
+            }
         }
         if (ORDERED) {
             h0 = h0 && n0 <= tmax; h1 = h1 && n1 <= tmax; h2 = h2 && n2 <= tmax; h3 = h3 && n3 <= tmax;

@@ -198,7 +198,7 @@ inline void build_tlas(const RtSceneDesc* d, HostScene& hs) {
     // 4-wide collapse (rt_bvh.cuh: largest-area child opened first), nodes numbered in index order
     const int nb = (int)bt.children.size();
     std::vector<unsigned> remap(nb, 0), wide(nb, 0);
-    wide_mark_host(bt.children.data(), bt.node_lo.data(), bt.node_hi.data(), nb, wide.data());
+    wide_mark_host(bt.children.data(), bt.node_lo.data(), bt.node_hi.data(), nb, 1, wide.data());
     unsigned n4 = 0;
     for (int i = 0; i < nb; i++) if (wide[i]) remap[i] = n4++;
     hs.tlas_nodes.resize(n4);
@@ -213,6 +213,8 @@ inline int convert_scene(const RtSceneDesc* d, HostScene& hs, std::string& err) 
     auto bad = [&](int code, const char* m) { err = m; return code; };
     if (d->width <= 0 || d->height <= 0 || d->dof_samples <= 0 || d->aa_samples <= 0 || d->n_times <= 0)
         return bad(RT_ERR_INVALID, "resolution and sample counts must be positive");
+    for (int m = 0; m < d->n_meshes; m++)
+        if (d->meshes[m].n_faces >= (1 << RT_LEAF_SLOT_BITS)) return bad(RT_ERR_LIMIT, "a mesh may hold fewer than 2^28 faces (leaf link encoding)");
     if (d->max_depth < 0 || d->max_depth > 255) return bad(RT_ERR_LIMIT, "max_depth must be in [0, 255]");
     hs.objs.resize(d->n_objects);
     for (int i = 0; i < d->n_objects; i++) {

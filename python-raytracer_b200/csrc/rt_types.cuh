@@ -55,6 +55,11 @@ struct __attribute__((aligned(16))) BvhNode { float4 q0, q1, q2, q3; };
 // tests vectorise over registers; link >= 0: node index, < 0: ~leaf (triangle slot / object index),
 // RT_LINK_NONE: empty slot, box [+inf, -inf] (never hit).  The walk addresses the planes by byte offset (RayInv).  flags: per-child bits (object BVH only).
 #define RT_LINK_NONE 0x7fffffff
+// mesh LBVH leaves hold 1..RT_LEAF_TRIS consecutive triangle slots: link = ~(first_slot | (count - 1) << RT_LEAF_SLOT_BITS)
+#ifndef RT_LEAF_TRIS
+#define RT_LEAF_TRIS 2
+#endif
+#define RT_LEAF_SLOT_BITS 28
 struct __attribute__((aligned(16))) BvhNode4 { float4 lox, loy, loz, hix, hiy, hiz; int4 link; int4 flags; };
 
 struct DevMesh {

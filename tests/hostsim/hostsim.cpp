@@ -34,8 +34,10 @@ static void refit(const std::vector<int2>& ch, int c, int depth, const std::vect
     float4 l0, h0, l1, h1;
     refit(ch, ch[c].x, depth + 1, leaf_lo, leaf_hi, nlo, nhi, dep, l0, h0);
     refit(ch, ch[c].y, depth + 1, leaf_lo, leaf_hi, nlo, nhi, dep, l1, h1);
-    lo = f4(fminf(l0.x, l1.x), fminf(l0.y, l1.y), fminf(l0.z, l1.z), 0.0f);
-    hi = f4(fmaxf(h0.x, h1.x), fmaxf(h0.y, h1.y), fmaxf(h0.z, h1.z), 0.0f);
+    const int f0 = ch[c].x < 0 ? ~ch[c].x : as_int(l0.w), f1 = ch[c].y < 0 ? ~ch[c].y : as_int(l1.w);
+    const int n0 = ch[c].x < 0 ? 1 : as_int(h0.w), n1 = ch[c].y < 0 ? 1 : as_int(h1.w);
+    lo = f4(fminf(l0.x, l1.x), fminf(l0.y, l1.y), fminf(l0.z, l1.z), as_float(std::min(f0, f1)));
+    hi = f4(fmaxf(h0.x, h1.x), fmaxf(h0.y, h1.y), fmaxf(h0.z, h1.z), as_float(n0 + n1));
     nlo[c] = lo; nhi[c] = hi; dep[c] = depth;
 }
 
@@ -85,13 +87,13 @@ static void build_mesh(const RtMesh& m, HostMesh& hm, DevMesh& g) {
         std::vector<unsigned> remap(n - 1, 0);
         unsigned n4 = 0;
         std::vector<unsigned> wide(n - 1, 0);
-        wide_mark_host(ch.data(), nlo.data(), nhi.data(), n - 1, wide.data());
+        wide_mark_host(ch.data(), nlo.data(), nhi.data(), n - 1, RT_LEAF_TRIS, wide.data());
         for (int i = 0; i < n - 1; i++) if (wide[i]) remap[i] = n4++;
         hm.nodes.resize(n4);
         for (int i = 0; i < n - 1; i++)
             if (wide[i])
                 hm.nodes[remap[i]] = make_wide_node(ch.data(), i, remap.data(), leaf_lo.data(), leaf_hi.data(), nlo.data(), nhi.data(),
-                                                    nullptr, nullptr, pad);
+                                                    nullptr, nullptr, pad, RT_LEAF_TRIS);
     }
     g.tri = hm.tri.data(); g.nodes = n >= 2 ? hm.nodes.data() : nullptr; g.face_vidx = hm.vidx.data();
     g.vnormals = hm.vn.empty() ? nullptr : hm.vn.data();

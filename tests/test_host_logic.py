@@ -237,8 +237,9 @@ def test_traversal_stack_spill_gives_the_same_image():
 
 
 def test_lbvh_structure_is_a_valid_tree():
-    """4-wide nodes (BvhNode4: 6 float4 of child boxes, int4 links, int4 flags): every triangle slot is the leaf of
-    exactly one node, every node but the root has exactly one parent, child boxes contain their subtrees."""
+    """4-wide nodes (BvhNode4: 6 float4 of child boxes, int4 links, int4 flags): every triangle slot belongs to exactly one
+    leaf (a leaf link covers 1..RT_LEAF_TRIS consecutive slots: ~(first | (count-1) << 28)), every node but the root has
+    exactly one parent, child boxes contain their subtrees and leaf boxes their triangles."""
     sc = load_case("TorusMesh_flat")
     nodes, order = hostsim.bvh(sc.flatten())
     n, n4 = len(order), len(nodes)
@@ -250,7 +251,9 @@ def test_lbvh_structure_is_a_valid_tree():
         if c == NONE:
             continue
         if c < 0:
-            seen_leaf[~c] += 1
+            first, count = (~c) & ((1 << 28) - 1), ((~c) >> 28) + 1
+            assert 1 <= count <= 2
+            seen_leaf[first:first + count] += 1
         else:
             seen_node[c] += 1
     assert (seen_leaf == 1).all() and seen_node[0] == 0 and (seen_node[1:] == 1).all()
