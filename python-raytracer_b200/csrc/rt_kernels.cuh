@@ -159,9 +159,10 @@ __global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_HIT_CSG : 
 }
 
 // ---- stage 2: shadow rays (scene.py:148-167) -------------------------------------------------------------
-// light-major: a warp works on ONE light and 32 neighbouring hit points
+// a warp works on ONE light and 32 neighbouring hit points at a time
 // LIGHT_ROWS: gridDim.y = lights (small queues of the deeper levels: every (light, ray) pair gets its own thread);
-// otherwise the whole grid sweeps the rays once per light (big level-0 batches: all resident warps on one light).
+// otherwise a thread walks the lights of its ray one after the other (big level-0 batches: the 16-B hit position is read
+// once instead of once per light; measured 3 ms/frame faster than sweeping the rays once per light).
 template <bool HAS_NODES, bool LIGHT_ROWS>
 __global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_SHADOW_CSG : RT_MIN_BLOCKS_SHADOW) k_shadow(SceneView S, long long n_rays, const unsigned long long* n_dev,
                                                                            HitPlanes H, uint8_t* __restrict__ occ, RtCounters* counters) {
@@ -170,13 +171,13 @@ __global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_SHADOW_CSG
     const long long n = n_dev ? (long long)*n_dev : n_rays;
     const long long stride = (long long)gridDim.x * blockDim.x;
     const int li0 = LIGHT_ROWS ? (int)blockIdx.y : 0, li1 = LIGHT_ROWS ? li0 + 1 : S.n_lights;
-    for (int li = li0; li < li1; li++)                                     // light-major without an index division: the whole grid
-        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {   // sweeps the rays once per light
-            const float4 h0 = H.planes[0 * H.cap + i];
-            if (h0.w != h0.w) continue;                                   // no hit: no shadow rays
-            TraceCtx cx{S, h0.w, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill};
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const float4 h0 = H.planes[0 * H.cap + i];
+        if (h0.w != h0.w) continue;                                       // no hit: no shadow rays
+        TraceCtx cx{S, h0.w, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill};
+        for (int li = li0; li < li1; li++)                                // the lanes of a warp still work on ONE light at a time
             occ[(long long)li * H.cap + i] = light_occluded<HAS_NODES>(cx, f3(h0), li) ? 1 : 0;
-        }
+    }
     tally_flush(tally, 0, 0, counters);
 }
 
