@@ -14,7 +14,7 @@ cases = [(c, None) for c in ALL_CASES] + [
     ("NovelScene1_small", {"resolution": [2048, 1024], "AA": {"jitter": True, "samples": 32}}),
     ("NovelScene2_small", {"resolution": [1024, 512], "AA": {"jitter": True, "samples": 2}, "DOF": {"samples": 15},
                            "motion": {"time": 1.0, "final": 1, "samples": 15}})]
-if len(sys.argv) > 1:
+if len(sys.argv) > 1:     # e.g. `Novel`: only the big versions of the named cases
     cases = [c for c in cases if any(a in c[0] for a in sys.argv[1:]) and c[1]]
 man = manifest()
 for case, over in cases:
