@@ -53,6 +53,25 @@ def _torus_smooth():
     return {"objects": objs}
 
 
+# AABB.get_diffuse with a texture (simple_geometry.py:312-355) is used by none of the shipped scenes: this case puts the
+# shipped wall textures on boxes seen from outside on five of their faces (camera, and a mirror sphere behind them)
+BOX_TEXTURE = {
+    "resolution": [200, 150], "AA": {"jitter": False, "samples": 1},
+    "materials": [{"name": "blue", "ID": 0, "diffuse": [0.0, 0.0, 1.0], "specular": [0.5, 0.5, 0.5], "hardness": 16},
+                  {"name": "mirror", "ID": 1, "diffuse": [0.1, 0.1, 0.1], "specular": [0.3, 0.3, 0.3], "hardness": 50,
+                   "type": "mirror", "tint": 0.85},
+                  {"name": "black", "ID": 2, "diffuse": [0.0, 0.0, 0.0], "specular": [0.0, 0.0, 0.0], "hardness": 0},
+                  {"name": "white", "ID": 3, "diffuse": [1.0, 1.0, 1.0], "specular": [0.0, 0.0, 0.0], "hardness": 0}],
+    "objects": [{"name": "plane", "type": "plane", "normal": [0.0, 1.0, 0.0], "position": [0.0, 0.0, 0.0], "materials": [2, 3]},
+                {"name": "crate_l", "type": "box", "size": [1.6, 1.6, 1.6], "position": [-1.7, 0.8, 0.2], "materials": [0],
+                 "texture": "textures/wall1.png"},
+                {"name": "crate_r", "type": "box", "min": [1.0, 0.0, -0.6], "max": [2.4, 2.2, 0.9], "materials": [0],
+                 "texture": "textures/wall3.png"},
+                {"name": "lid", "type": "box", "size": [1.0, 0.3, 1.0], "position": [0.0, 2.6, -0.5], "materials": [0],
+                 "texture": "textures/wall2.png"},
+                {"name": "ball", "type": "sphere", "radius": 1.5, "position": [0.0, 1.5, -3.2], "materials": [1]}],
+}
+
 CASES = [  # (case, scene, overrides, author's render to cross-check or None)
     ("TwoSpheresPlane", "TwoSpheresPlane", None, "renders/TwoSpheresPlane.png"),
     ("MirrorRefraction", "MirrorRefraction", None, "renders/MirrorRefraction.png"),
@@ -60,6 +79,7 @@ CASES = [  # (case, scene, overrides, author's render to cross-check or None)
     ("TorusMesh_flat", "TorusMesh", None, "renders/TorusMesh_flat.png"),
     ("TorusMesh_smooth", "TorusMesh", "torus_smooth", "renders/TorusMesh.png"),
     ("DepthOfField", "DepthOfField", None, None),
+    ("BoxTexture", "TwoSpheresPlane", BOX_TEXTURE, None),
     ("NovelScene1_small", "NovelScene1", {"resolution": [256, 128], "AA": {"jitter": True, "samples": 2}}, None),
     ("NovelScene2_small", "NovelScene2", {"resolution": [128, 64], "AA": {"jitter": True, "samples": 2},
                                           "DOF": {"samples": 3}, "motion": {"samples": 3, "final": 1}}, None),
