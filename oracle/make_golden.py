@@ -72,6 +72,62 @@ BOX_TEXTURE = {
                 {"name": "ball", "type": "sphere", "radius": 1.5, "position": [0.0, 1.5, -3.2], "materials": [1]}],
 }
 
+# BoundingSphere (bounding_volumes.py:12-37) is chosen by Mesh.__init__ only when the sphere is smaller than the box
+# (mesh.py:45-51); the shipped torus gets the box.  An irregular octahedron (written by export_inputs, not a reference
+# file) gets the sphere; smooth shaded, translated and scaled, with a mirror ball so rays also arrive from behind.
+OCTA_OBJ = """# tests/golden fixture (authored for this repo): irregular octahedron
+v 1.1 0 0
+v -1 0 0
+v 0 1.2 0
+v 0 -0.9 0
+v 0 0 1
+v 0 0 -1.05
+f 1 3 5
+f 3 2 5
+f 2 4 5
+f 4 1 5
+f 3 1 6
+f 2 3 6
+f 4 2 6
+f 1 4 6
+"""
+SPHERE_GATE = {
+    "resolution": [200, 150], "AA": {"jitter": False, "samples": 1},
+    "materials": [{"name": "blue", "ID": 0, "diffuse": [0.1, 0.2, 0.9], "specular": [0.6, 0.6, 0.6], "hardness": 24},
+                  {"name": "mirror", "ID": 1, "diffuse": [0.1, 0.1, 0.1], "specular": [0.3, 0.3, 0.3], "hardness": 50,
+                   "type": "mirror", "tint": 0.85},
+                  {"name": "black", "ID": 2, "diffuse": [0.0, 0.0, 0.0], "specular": [0.0, 0.0, 0.0], "hardness": 0},
+                  {"name": "white", "ID": 3, "diffuse": [1.0, 1.0, 1.0], "specular": [0.0, 0.0, 0.0], "hardness": 0}],
+    "objects": [{"name": "plane", "type": "plane", "normal": [0.0, 1.0, 0.0], "position": [0.0, 0.0, 0.0], "materials": [2, 3]},
+                {"name": "octa", "type": "mesh", "filepath": "./meshes/octa.obj", "scale": 1.3, "position": [-0.4, 1.05, 0.2],
+                 "materials": [0], "flat_shaded": False},
+                {"name": "ball", "type": "sphere", "radius": 1.2, "position": [1.9, 1.2, -2.0], "materials": [1]}],
+}
+
+# Meshes as CHILDREN of transform / CSG nodes (scene_parser.py:262-275 allows it, no shipped scene does it): a rotated,
+# non-uniformly scaled union holding the torus, and a difference torus - sphere (Mesh.is_inside is the base class's False).
+MESH_IN_NODE = {
+    "resolution": [200, 150], "AA": {"jitter": False, "samples": 1},
+    "materials": [{"name": "blue", "ID": 0, "diffuse": [0.1, 0.2, 0.9], "specular": [0.6, 0.6, 0.6], "hardness": 24},
+                  {"name": "red", "ID": 1, "diffuse": [0.9, 0.15, 0.1], "specular": [0.5, 0.5, 0.5], "hardness": 40},
+                  {"name": "black", "ID": 2, "diffuse": [0.0, 0.0, 0.0], "specular": [0.0, 0.0, 0.0], "hardness": 0},
+                  {"name": "white", "ID": 3, "diffuse": [1.0, 1.0, 1.0], "specular": [0.0, 0.0, 0.0], "hardness": 0},
+                  {"name": "mirror", "ID": 4, "diffuse": [0.1, 0.1, 0.1], "specular": [0.3, 0.3, 0.3], "hardness": 50,
+                   "type": "mirror", "tint": 0.85}],
+    "objects": [{"name": "plane", "type": "plane", "normal": [0.0, 1.0, 0.0], "position": [0.0, 0.0, 0.0], "materials": [2, 3]},
+                {"name": "tilted", "type": "node", "hierarchy_type": "union", "position": [-1.5, 1.3, 0.0],
+                 "rotation": [35.0, 20.0, 10.0], "scale": [1.0, 1.4, 0.8], "materials": [1],
+                 "children": [{"name": "torus", "type": "mesh", "filepath": "./meshes/torus.obj", "scale": 1.0,
+                               "position": [0.0, 0.0, 0.0], "materials": [0], "flat_shaded": True},
+                              {"name": "hub", "type": "sphere", "radius": 0.35, "position": [0.0, 0.0, 0.0], "materials": []}]},
+                {"name": "bitten", "type": "node", "hierarchy_type": "difference", "position": [1.4, 0.9, 0.3],
+                 "rotation": [60.0, 0.0, 0.0], "materials": [1],
+                 "children": [{"name": "torus", "type": "mesh", "filepath": "./meshes/torus.obj", "scale": 1.1,
+                               "position": [0.0, 0.0, 0.0], "materials": [], "flat_shaded": False},
+                              {"name": "bite", "type": "sphere", "radius": 0.9, "position": [1.0, 0.0, 0.3], "materials": [0]}]},
+                {"name": "ball", "type": "sphere", "radius": 0.9, "position": [0.2, 0.9, -3.0], "materials": [4]}],
+}
+
 CASES = [  # (case, scene, overrides, author's render to cross-check or None)
     ("TwoSpheresPlane", "TwoSpheresPlane", None, "renders/TwoSpheresPlane.png"),
     ("MirrorRefraction", "MirrorRefraction", None, "renders/MirrorRefraction.png"),
@@ -80,6 +136,8 @@ CASES = [  # (case, scene, overrides, author's render to cross-check or None)
     ("TorusMesh_smooth", "TorusMesh", "torus_smooth", "renders/TorusMesh.png"),
     ("DepthOfField", "DepthOfField", None, None),
     ("BoxTexture", "TwoSpheresPlane", BOX_TEXTURE, None),
+    ("MeshSphereGate", "TwoSpheresPlane", SPHERE_GATE, None),
+    ("MeshInNode", "TwoSpheresPlane", MESH_IN_NODE, None),
     ("NovelScene1_small", "NovelScene1", {"resolution": [256, 128], "AA": {"jitter": True, "samples": 2}}, None),
     ("NovelScene2_small", "NovelScene2", {"resolution": [128, 64], "AA": {"jitter": True, "samples": 2},
                                           "DOF": {"samples": 3}, "motion": {"samples": 3, "final": 1}}, None),
@@ -108,6 +166,8 @@ def export_inputs():
         im = Image.open(os.path.join(REF, t))
         assert t.endswith(".png")
         im.save(os.path.join(OUT, t), optimize=True)   # same pixels and mode, re-encoded
+    with open(os.path.join(OUT, "meshes", "octa.obj"), "w") as out:
+        out.write(OCTA_OBJ)
     # torus: keep only v / f rows
     with open(os.path.join(REF, "meshes/torus.obj")) as fh, open(os.path.join(OUT, "meshes", "torus.obj"), "w") as out:
         out.write("# tests/golden fixture: v/f rows of the reference's meshes/torus.obj\n")
@@ -115,6 +175,18 @@ def export_inputs():
             p = line.split()
             if p and p[0] in ("v", "f"):
                 out.write(" ".join(p) + "\n")
+
+
+def _for_reference(overrides):
+    """The reference resolves mesh paths against its own (read-only) tree: fixtures authored here are given by absolute path."""
+    ov = json.loads(json.dumps(overrides)) if overrides else overrides
+    def walk(objs):
+        for o in objs:
+            if o.get("filepath") == "./meshes/octa.obj":
+                o["filepath"] = os.path.abspath(os.path.join(OUT, "meshes", "octa.obj"))
+            walk(o.get("children", []))
+    walk((ov or {}).get("objects", []))
+    return ov
 
 
 def main():
@@ -131,7 +203,7 @@ def main():
             continue
         overrides = _torus_smooth() if ov == "torus_smooth" else ov
         t0 = time.time()
-        img, cpu = ref_runner.render_reference(SCENES[scene], overrides=overrides, seed=a.seed)
+        img, cpu = ref_runner.render_reference(SCENES[scene], overrides=_for_reference(overrides), seed=a.seed)
         png = ref_runner.to_png_array(img)
         assert np.array_equal(img.astype(np.float32).astype(np.float64), img)
         Image.fromarray(png).save(os.path.join(OUT, "renders", case + ".png"), optimize=True)

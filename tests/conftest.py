@@ -81,4 +81,4 @@ def parity_stats(a_u8, b_u8):
 PARITY_FRACTION = 0.999
 
 ALL_CASES = ["TwoSpheresPlane", "MirrorRefraction", "MotionBlur", "TorusMesh_flat", "TorusMesh_smooth",
-             "DepthOfField", "BoxTexture", "NovelScene1_small", "NovelScene2_small"]
+             "DepthOfField", "BoxTexture", "MeshSphereGate", "MeshInNode", "NovelScene1_small", "NovelScene2_small"]
