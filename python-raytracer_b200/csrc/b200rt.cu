@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -14,6 +15,16 @@
 #include "rt_kernels.cuh"
 #include "rt_obj.hpp"
 #include "rt_scene_build.hpp"
+
+#ifndef RT_TAIL_BIG_BATCH
+#define RT_TAIL_BIG_BATCH (96ll << 20)
+#endif
+// first level handled by k_tail (0 = never: every level as three launches); developer override: B200RT_TAIL_LEVEL
+static int tail_level_for(long long n_rays) {
+    static const char* env = getenv("B200RT_TAIL_LEVEL");
+    if (env) return atoi(env);
+    return n_rays >= RT_TAIL_BIG_BATCH ? 3 : 1;
+}
 
 #define RT_PROF_CLASSES 5
 #define RT_COUNTER_CLASSES 4     // tallies kept apart for level-0 k_hit / k_shadow / k_shade and for the deeper levels
@@ -403,11 +414,17 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
             (*launches) += 2;
         }
         if (secondary) {
+            const int tail_level = tail_level_for(n_rays);
             for (int level = 1; level < V.max_depth; level++) {       // level L consumes the rays spawned by level L-1
                 RayQueue& qin = (level & 1) ? q0 : q1;
                 RayQueue& qout = (level & 1) ? q1 : q0;
                 const unsigned long long* n_in = sc->d_qcount + (level - 1);
                 ProfScope ps_(sc, 3, st);
+                if (tail_level > 0 && level >= tail_level) {          // the small remainder: every path to its end in one launch
+                    k_tail<HAS_NODES><<<max_grid, RT_BLOCK, smem, st>>>(V, qin, n_in, sc->d_samples, sc->d_counters + 3);
+                    (*launches)++;
+                    break;
+                }
                 k_hit<HAS_NODES, false><<<max_grid, RT_BLOCK, smem, st>>>(V, pmk, 0, 0, qin, n_in, H, sc->d_counters + 3);
                 if (V.n_lights > 0) { k_shadow<HAS_NODES, true><<<dim3((unsigned)std::max(1, max_grid / V.n_lights), (unsigned)V.n_lights), RT_BLOCK, smem, st>>>(V, 0, n_in, H, sc->d_occ, sc->d_counters + 3); (*launches)++; }
                 k_shade<false><<<max_grid, RT_BLOCK, 0, st>>>(V, 0, qin, n_in, H, sc->d_occ, sc->d_samples, qout, sc->d_qcount + level, sc->d_counters + 3);

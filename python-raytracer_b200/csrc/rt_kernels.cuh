@@ -219,6 +219,33 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS_SHADE) k_shade(SceneVi
     tally_flush(tally, 0, n_queued, counters);
 }
 
+// ---- the deep levels in one launch ----------------------------------------------------------------------------
+// After a few levels the queues hold a small fraction of a batch, and every further level costs three launches whose
+// time is the slowest warp's, not the ray count's.  From level RT_TAIL_LEVEL on, each queued path is followed to its end
+// by ONE thread (closest hit, shadow rays and shading in place, like the reference's recursion): same functions, same
+// results, one launch instead of 3 x (max_depth - RT_TAIL_LEVEL).
+#ifndef RT_MIN_BLOCKS_TAIL
+#define RT_MIN_BLOCKS_TAIL 4
+#endif
+template <bool HAS_NODES>
+__global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_HIT_CSG : RT_MIN_BLOCKS_TAIL) k_tail(SceneView S, RayQueue qin, const unsigned long long* qin_count,
+                                                                                          float4* __restrict__ samples, RtCounters* counters) {
+    Tally tally = tally_zero();
+    int spill[RT_STACK_SPILL];
+    unsigned long long n_queued = 0;
+    const long long n = (long long)*qin_count;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        PathState ps; float time; unsigned slot;
+        queue_load(qin, i, ps, time, slot);
+        TraceCtx cx{S, time, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill};
+        float3 sample;
+        while (trace_level<HAS_NODES>(cx, ps, sample)) n_queued++;      // counted like the rays the wavefront levels would have queued
+        samples[slot] = f4(sample.x, sample.y, sample.z, 0.0f);
+    }
+    tally_flush(tally, 0, n_queued, counters);
+}
+
 // ---- per-pixel average -------------------------------------------------------------------------------
 // colour accumulates in float32 in loop order (scene.py:69), then one float32 division (scene.py:73)
 __global__ void k_resolve(PixelMap pm, long long pixel_begin, int n_pixels, int N, const float4* __restrict__ samples,
