@@ -334,6 +334,9 @@ def run_ours(a):
                             "kernel_share_of_step": kernel_share,
                             "counts_rank0_per_frame": {"bvh_nodes": int(pc.bvh_nodes), "tri_tests": int(pc.tri_tests),
                                                        "queued_rays": int(pc.queued_rays)}},
+               "tallies_rank0_per_frame": {k: {n: v for n, v in c.as_dict().items() if v and n not in ("kernel_launches", "error_flags")}
+                                           for k, c in (("k_hit", prof.hit), ("k_shadow", prof.shadow), ("k_shade", prof.shade),
+                                                        ("levels>=1", prof.secondary))},
                "kernel_ms_per_frame": {"k_hit": prof.ms_hit / a.steps, "k_shadow": prof.ms_shadow / a.steps,
                                        "k_shade": prof.ms_shade / a.steps, "levels>=1 (hit+shadow+shade)": prof.ms_secondary / a.steps,
                                        "k_resolve": prof.ms_resolve / a.steps},

@@ -14,7 +14,6 @@
 #pragma once
 #include "rt_core.cuh"
 
-#define RT_BLOCK 128
 // resident blocks per SM each kernel's register allocation is held to (tuned on B200)
 #ifndef RT_MIN_BLOCKS_HIT
 #define RT_MIN_BLOCKS_HIT 6

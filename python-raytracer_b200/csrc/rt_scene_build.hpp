@@ -281,6 +281,11 @@ inline int convert_scene(const RtSceneDesc* d, HostScene& hs, std::string& err) 
     V.max_depth = d->max_depth;
     V.mesh_mode = 0;
     build_tlas(d, hs);
+    V.tlas_flagged = 0;
+    for (const BvhNode4& nd : hs.tlas_nodes) V.tlas_flagged |= (nd.flags.x | nd.flags.y | nd.flags.z | nd.flags.w) & RT_TLAS_NO_TMAX;
+    V.any_motion = 0;
+    for (int i = 0; i < d->n_objects; i++)
+        if (d->objects[i].speed[0] != 0.0f || d->objects[i].speed[1] != 0.0f || d->objects[i].speed[2] != 0.0f) V.any_motion = 1;
     V.tlas_nodes = nullptr; V.lin_objs = nullptr; V.n_lin = (int)hs.lin_objs.size();
     V.sep_mesh = nullptr; V.n_sep_mesh = (int)hs.sep_mesh.size();
     return RT_OK;

@@ -4,6 +4,7 @@
 #include "../../include/b200rt.h"
 
 #define RT_MAX_NEST 8        // CSG / transform nesting depth supported (NovelScene uses 5)
+#define RT_BLOCK 128         // threads per block of every ray kernel (the traversal stack layout depends on it)
 #ifndef RT_STACK_DEPTH
 #define RT_STACK_DEPTH 40    // BVH traversal stack entries per ray held in shared memory (object BVH + mesh LBVH share it)
 #endif
@@ -90,6 +91,8 @@ struct SceneView {
     // for everything that has a finite extent); same 4-wide node layout as the mesh LBVH, link < 0: ~object index,
     // flags = per-child bits (RT_TLAS_NO_TMAX: the subtree holds an object whose shadow test ignores t_max).
     const BvhNode4* tlas_nodes;  // NULL: no object BVH (fewer than 2 bounded objects) -> plain loop over n_top
+    int tlas_flagged;            // some child of the object BVH carries RT_TLAS_NO_TMAX (otherwise the walk skips the flag rows)
+    int any_motion;              // some object has a non-zero speed (otherwise primitive tests skip the speed loads)
     const int* lin_objs;         // top-level objects tested one by one, scene order: no finite bounds (planes, nodes holding
     int n_lin;                   // planes), or everything but the separate meshes when there is no object BVH
     // top-level meshes are kept OUT of that walk and traversed after it (gate test each, scene order), so that the lanes

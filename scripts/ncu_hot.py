@@ -41,7 +41,7 @@ def agg(keyf, title, top=25):
         print(f"{100*v/tot:6.2f}% samples {100*e[k]/tot_e:6.2f}% instr  {k}")
 agg(lambda ins, st: st[0] if st else None, "innermost line")
 agg(lambda ins, st: tuple(st[-3:-1]) if len(st) >= 3 else tuple(st), "outer frames (2 below the kernel)")
-agg(lambda ins, st: next((f for f in st if f[0] == "rt_core.cuh" and f[1] > 280), st[0] if st else None), "first rt_core frame past the walker")
+agg(lambda ins, st: next((f for f in st if f[0] == "rt_core.cuh" and f[1] > 280), st[0] if st else None), "first rt_core frame past the walker", int(os.environ.get("TOP", "25")))
 stall = collections.Counter()
 for r in body:
     for i in stall_cols: stall[h[i]] += int(r[i])
