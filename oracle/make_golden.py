@@ -128,6 +128,12 @@ MESH_IN_NODE = {
                 {"name": "ball", "type": "sphere", "radius": 0.9, "position": [0.2, 0.9, -3.0], "materials": [4]}],
 }
 
+# Random scenes (tests/fuzz_scenes.py): combinations of primitives, nested CSG / transform nodes, `ref` copies, meshes inside
+# nodes, moving objects, textures, all three material types and AA / DOF / motion sampling that no hand-written scene has.
+sys.path.insert(0, os.path.join(HERE, "..", "tests"))
+import fuzz_scenes  # noqa: E402
+FUZZ_SEEDS = (1, 8, 12, 18, 19)
+
 CASES = [  # (case, scene, overrides, author's render to cross-check or None)
     ("TwoSpheresPlane", "TwoSpheresPlane", None, "renders/TwoSpheresPlane.png"),
     ("MirrorRefraction", "MirrorRefraction", None, "renders/MirrorRefraction.png"),
@@ -141,7 +147,7 @@ CASES = [  # (case, scene, overrides, author's render to cross-check or None)
     ("NovelScene1_small", "NovelScene1", {"resolution": [256, 128], "AA": {"jitter": True, "samples": 2}}, None),
     ("NovelScene2_small", "NovelScene2", {"resolution": [128, 64], "AA": {"jitter": True, "samples": 2},
                                           "DOF": {"samples": 3}, "motion": {"samples": 3, "final": 1}}, None),
-]
+] + [(f"Fuzz{s}", "TwoSpheresPlane", fuzz_scenes.make(s, 128, 96), None) for s in FUZZ_SEEDS]
 
 
 def export_inputs():

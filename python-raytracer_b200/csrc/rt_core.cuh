@@ -566,6 +566,9 @@ RT_HD_NOINLINE bool difference_shadow(TraceCtx& cx, int c0, const Ray& mr);
 // boxes are padded, an unbounded or top-level object carries [-inf, +inf] and always passes.
 RT_HD float3 csg_ray_inv(const Ray& r) { return f3(safe_rcp(r.d.x), safe_rcp(r.d.y), safe_rcp(r.d.z)); }
 RT_HD bool child_may_hit(const SceneView& S, int oi, const Ray& r, float3 inv) {
+#ifdef RT_NO_CHILD_BOUNDS      // test aid (tests/hostsim variant): the pruning must not change any image
+    return true;
+#endif
     const float4 lo = ld4(S.child_lo + oi), hi = ld4(S.child_hi + oi);
     if (lo.x == -RT_INF) return true;
     const float ax = (lo.x - r.o.x) * inv.x, bx = (hi.x - r.o.x) * inv.x;
@@ -576,6 +579,9 @@ RT_HD bool child_may_hit(const SceneView& S, int oi, const Ray& r, float3 inv) {
     return entry <= exit_;
 }
 RT_HD bool child_may_contain(const SceneView& S, int oi, float3 p) {
+#ifdef RT_NO_CHILD_BOUNDS
+    return true;
+#endif
     const float4 lo = ld4(S.child_lo + oi), hi = ld4(S.child_hi + oi);
     return !(p.x < lo.x || p.x > hi.x || p.y < lo.y || p.y > hi.y || p.z < lo.z || p.z > hi.z);
 }

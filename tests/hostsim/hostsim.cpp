@@ -167,6 +167,59 @@ extern "C" int hostsim_render_pixels(const RtSceneDesc* d, const int32_t* cols, 
     return 0;
 }
 
+// the primary ray of (col, row, dof sample d, aa sample s): origin xyz, direction xyz
+extern "C" int hostsim_primary_ray(const RtSceneDesc* d, int col, int row, int dd, int s, float* out6) {
+    Sim sim;
+    int rc = make_sim(d, sim);
+    if (rc) return rc;
+    Ray r = generate_ray(sim.V, col, row, dd, s);
+    out6[0] = r.o.x; out6[1] = r.o.y; out6[2] = r.o.z; out6[3] = r.d.x; out6[4] = r.d.y; out6[5] = r.d.z;
+    return 0;
+}
+
+// explicit rays through the same functions (the host twins of rt_trace_rays / rt_occluded)
+extern "C" int hostsim_trace_rays(const RtSceneDesc* d, int64_t n, const float* org, const float* dir, const double* times,
+                                  float* rgb, float* hit_t, int32_t* hit_geom, float* hit_np /* n xyz, p xyz, mat */, int mesh_mode) {
+    Sim sim;
+    int rc = make_sim(d, sim);
+    if (rc) return rc;
+    SceneView V = sim.V; V.mesh_mode = mesh_mode;
+#pragma omp parallel for schedule(dynamic, 64)
+    for (int64_t i = 0; i < n; i++) {
+        int stack[RT_STACK_DEPTH], spill[RT_STACK_SPILL];
+        Tally tally{};
+        PathState ps;
+        ps.ray.o = f3(org[3 * i], org[3 * i + 1], org[3 * i + 2]); ps.ray.d = f3(dir[3 * i], dir[3 * i + 1], dir[3 * i + 2]);
+        TraceCtx cx{V, (float)times[i], tally, stack, 1, spill};
+        Hit h;
+        const bool hit = sim.hs.has_nodes ? closest_hit<true>(cx, ps.ray, h) : closest_hit<false>(cx, ps.ray, h);
+        hit_t[i] = hit ? h.t : INFINITY; hit_geom[i] = hit ? h.geom : -1;
+        if (hit_np && hit) { float* q = hit_np + 7 * i; q[0] = h.n.x; q[1] = h.n.y; q[2] = h.n.z; q[3] = h.p.x; q[4] = h.p.y; q[5] = h.p.z; q[6] = (float)h.mat; }
+        ps.fold = fold_identity(); ps.depth_left = V.max_depth; ps.in_shape = 0;
+        float3 sample;
+        while (sim.hs.has_nodes ? trace_level<true>(cx, ps, sample) : trace_level<false>(cx, ps, sample)) {}
+        rgb[3 * i] = sample.x; rgb[3 * i + 1] = sample.y; rgb[3 * i + 2] = sample.z;
+    }
+    return 0;
+}
+
+extern "C" int hostsim_occluded(const RtSceneDesc* d, int64_t n, const float* org, const float* dir, const double* times,
+                                const double* tmax, int32_t* occ, int mesh_mode) {
+    Sim sim;
+    int rc = make_sim(d, sim);
+    if (rc) return rc;
+    SceneView V = sim.V; V.mesh_mode = mesh_mode;
+#pragma omp parallel for schedule(dynamic, 64)
+    for (int64_t i = 0; i < n; i++) {
+        int stack[RT_STACK_DEPTH], spill[RT_STACK_SPILL];
+        Tally tally{};
+        Ray r; r.o = f3(org[3 * i], org[3 * i + 1], org[3 * i + 2]); r.d = f3(dir[3 * i], dir[3 * i + 1], dir[3 * i + 2]);
+        TraceCtx cx{V, (float)times[i], tally, stack, 1, spill};
+        occ[i] = (sim.hs.has_nodes ? occluded<true>(cx, r, (float)tmax[i]) : occluded<false>(cx, r, (float)tmax[i])) ? 1 : 0;
+    }
+    return 0;
+}
+
 // diagnostics: LBVH nodes visited by the first cast_ray level (closest hit + its shadow rays) of every (pixel, sample)
 // ray, to estimate how evenly the lanes of a warp are loaded (scripts/warp_balance.py)
 extern "C" int hostsim_node_counts(const RtSceneDesc* d, const int32_t* cols, const int32_t* rows, int64_t n, uint32_t* out) {

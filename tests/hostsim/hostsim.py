@@ -62,6 +62,37 @@ def render(flat, abi, mesh_mode=0, library=None):
     return out.reshape(W, H, 3), ctr
 
 
+def trace_rays(flat, origins, dirs, times=None, mesh_mode=0):
+    o = np.ascontiguousarray(origins, dtype=np.float32).reshape(-1, 3)
+    d = np.ascontiguousarray(dirs, dtype=np.float32).reshape(-1, 3)
+    n = o.shape[0]
+    t = np.zeros(n, dtype=np.float64) if times is None else np.ascontiguousarray(times, dtype=np.float64)
+    res = dict(rgb=np.empty((n, 3), np.float32), t=np.empty(n, np.float32), geom=np.empty(n, np.int32))
+    npm = np.zeros((n, 7), np.float32)
+    L = lib()
+    L.hostsim_trace_rays.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 7 + [C.c_int]
+    rc = L.hostsim_trace_rays(C.addressof(flat.desc), n, o.ctypes.data, d.ctypes.data, t.ctypes.data, res["rgb"].ctypes.data,
+                              res["t"].ctypes.data, res["geom"].ctypes.data, npm.ctypes.data, mesh_mode)
+    assert rc == 0, rc
+    res["n"], res["p"], res["mat"] = npm[:, 0:3].copy(), npm[:, 3:6].copy(), npm[:, 6].astype(np.int32)
+    return res
+
+
+def occluded(flat, origins, dirs, tmax, times=None, mesh_mode=0):
+    o = np.ascontiguousarray(origins, dtype=np.float32).reshape(-1, 3)
+    d = np.ascontiguousarray(dirs, dtype=np.float32).reshape(-1, 3)
+    n = o.shape[0]
+    t = np.zeros(n, dtype=np.float64) if times is None else np.ascontiguousarray(times, dtype=np.float64)
+    tm = np.ascontiguousarray(np.broadcast_to(np.asarray(tmax, dtype=np.float64), (n,)))
+    occ = np.empty(n, np.int32)
+    L = lib()
+    L.hostsim_occluded.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 5 + [C.c_int]
+    rc = L.hostsim_occluded(C.addressof(flat.desc), n, o.ctypes.data, d.ctypes.data, t.ctypes.data, tm.ctypes.data,
+                            occ.ctypes.data, mesh_mode)
+    assert rc == 0, rc
+    return occ
+
+
 def bvh(flat, mesh=0):
     n = C.cast(flat.desc.meshes, C.POINTER(type("M", (C.Structure,), {"_fields_": [("n_verts", C.c_int32), ("n_faces", C.c_int32)]})))[0].n_faces
     nodes = np.zeros((max(n - 1, 0), 32), dtype=np.float32)      # 4-wide nodes, 128 B each (BvhNode4)

@@ -11,7 +11,7 @@ import pytest
 
 import oracle
 import python_raytracer_b200 as rt
-from conftest import ALL_CASES, PARITY_FRACTION, golden_png, load_case, parity_stats, to_png_array
+from conftest import ALL_CASES, FUZZ_GPU_SEEDS, PARITY_FRACTION, golden_png, load_case, load_fuzz, parity_stats, to_png_array
 
 pytestmark = pytest.mark.gpu
 abi = rt._abi
@@ -38,6 +38,28 @@ def test_render_matches_reference_render(case):
     for k in ("rays_shadow", "rays_reflect", "rays_refract", "shaded_hits"):
         assert abs(c[k] - c_ref[k]) <= max(8, 5e-4 * c_ref[k]), (k, c[k], c_ref[k])
     assert c["error_flags"] == 0
+
+
+@pytest.mark.parametrize("seed", FUZZ_GPU_SEEDS)
+def test_random_scene_matches_oracle(seed):
+    """Fresh random scenes (tests/fuzz_scenes.py: nested CSG, `ref` copies, meshes in nodes, moving objects, textures, DOF /
+    motion / jitter) against the oracle, which reproduces the reference float-exactly on 43 + 5 scenes of the same generator
+    (oracle/fuzz_check.py, tests/golden Fuzz*).  Also: BVHs and child-bounds pruning leave the image bit-identical."""
+    sc = load_fuzz(seed)
+    img = sc.render()
+    ref, c_ref = oracle.render(sc.flatten(), abi)
+    frac, dmax, _ = parity_stats(to_png_array(img), to_png_array(ref))
+    assert frac >= PARITY_FRACTION, (seed, frac, dmax)
+    c = sc.last_counters
+    assert c["rays_primary"] == c_ref["rays_primary"] and c["error_flags"] == 0
+    for k in ("rays_shadow", "rays_reflect", "rays_refract", "shaded_hits"):
+        assert abs(c[k] - c_ref[k]) <= max(8, 1e-3 * c_ref[k]), (k, c[k], c_ref[k])
+    plain = sc.render_region(0, sc.vc.width, 0, sc.vc.height, mesh_mode=3)
+    # identical, except where a far-away ray (ground plane hit at the horizon, t ~ 1e4) makes a primitive's float32 test report
+    # a hit that is geometrically impossible (cancellation in the sphere discriminant): the conservative boxes skip that
+    # primitive, the plain loop evaluates it.  Seen on 4 of 12288 pixels of seed 123, colour difference 5e-5.
+    differ = np.abs(np.asarray(img, dtype=np.float32) - plain).max(axis=2) > 0
+    assert differ.mean() <= 1e-3 and np.abs(np.asarray(img, dtype=np.float32) - plain).max() < 1e-3
 
 
 def test_render_is_deterministic_and_strips_concatenate():
