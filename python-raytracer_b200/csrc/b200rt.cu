@@ -16,6 +16,12 @@
 #include "rt_obj.hpp"
 #include "rt_scene_build.hpp"
 
+#ifndef RT_GRID_WAVES
+#define RT_GRID_WAVES 48
+#endif
+#ifndef RT_GRID_WAVES_DEEP
+#define RT_GRID_WAVES_DEEP 8
+#endif
 #ifndef RT_TAIL_BIG_BATCH
 #define RT_TAIL_BIG_BATCH (96ll << 20)
 #endif
@@ -24,6 +30,18 @@ static int tail_level_for(long long n_rays) {
     static const char* env = getenv("B200RT_TAIL_LEVEL");
     if (env) return atoi(env);
     return n_rays >= RT_TAIL_BIG_BATCH ? 3 : 1;
+}
+
+// Persistent grid-stride grids: blocks = SMs x resident blocks per SM of THAT kernel (its __launch_bounds__) x waves.  Measured at
+// 4K x 64 spp (ms/frame): 1 wave 144.6, 2 139.0, 4 132.3, 8 128.3, 16 127.0, 32 126.1, 64 126.7, 256 134.4 (48 + 8 deep: 124.5) - blocks finish at
+// very different times (rays per block are equal, node visits are not), so small blocks even out the end of a launch; the small
+// queues of the deeper levels want fewer (18 ms at 8-16 waves, 19.4 at 64).  Developer overrides: B200RT_WAVES, B200RT_WAVES_DEEP.
+static int grid_waves(bool deep) {
+    static const char* env = getenv("B200RT_WAVES");
+    static const char* env_deep = getenv("B200RT_WAVES_DEEP");
+    const char* e = deep ? env_deep : env;
+    const int w = e ? atoi(e) : (deep ? RT_GRID_WAVES_DEEP : RT_GRID_WAVES);
+    return w > 0 ? w : 1;
 }
 
 #define RT_PROF_CLASSES 5
@@ -391,7 +409,13 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
         CU(cudaFuncSetAttribute(k_shadow<HAS_NODES, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     }
     const int direct = (job->direct && job->world == 1) ? 1 : 0;
-    const int max_grid = sc->sm_count * 16;
+    const int waves = grid_waves(false), waves_deep = grid_waves(true);
+    const int b_hit = sc->sm_count * (HAS_NODES ? RT_MIN_BLOCKS_HIT_CSG : RT_MIN_BLOCKS_HIT);
+    const int b_shadow = sc->sm_count * (HAS_NODES ? RT_MIN_BLOCKS_SHADOW_CSG : RT_MIN_BLOCKS_SHADOW);
+    const int b_shade = sc->sm_count * RT_MIN_BLOCKS_SHADE;
+    const int g_hit0 = b_hit * waves, g_shadow0 = b_shadow * waves, g_shade0 = b_shade * waves;              // level 0
+    const int g_hit = b_hit * waves_deep, g_shadow = b_shadow * waves_deep, g_shade = b_shade * waves_deep;   // queued levels
+    const int g_tail = sc->sm_count * waves_deep * (HAS_NODES ? RT_MIN_BLOCKS_HIT_CSG : RT_MIN_BLOCKS_TAIL);
     HitPlanes H{sc->d_hit, sc->hit_cap};
     PixelMap pmk = pm;                                   // + the sample-slot divisors of this scene
     pmk.fd_N = make_fastdiv((unsigned)N); pmk.fd_T = make_fastdiv((unsigned)V.T); pmk.fd_S = make_fastdiv((unsigned)V.S);
@@ -402,15 +426,14 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
         const long long n_rays = npx * N;
         CU(cudaMemsetAsync(sc->d_qcount, 0, sizeof(unsigned long long) * (size_t)(V.max_depth + 2), st));
         RayQueue q0{sc->d_queue[0], sc->queue_cap}, q1{sc->d_queue[1], sc->queue_cap};
-        const int grid = (int)std::min<long long>((n_rays + RT_BLOCK - 1) / RT_BLOCK, max_grid);
-        const int grid_sh = grid;
+        const long long need = (n_rays + RT_BLOCK - 1) / RT_BLOCK;
         {   // level 0: generated rays
             { ProfScope ps_(sc, 0, st);
-              k_hit<HAS_NODES, true><<<grid, RT_BLOCK, smem, st>>>(V, pmk, p0, n_rays, q0, nullptr, H, sc->d_counters + 0); }
+              k_hit<HAS_NODES, true><<<(int)std::min<long long>(need, g_hit0), RT_BLOCK, smem, st>>>(V, pmk, p0, n_rays, q0, nullptr, H, sc->d_counters + 0); }
             if (V.n_lights > 0) { ProfScope ps_(sc, 1, st);
-              k_shadow<HAS_NODES, false><<<grid_sh, RT_BLOCK, smem, st>>>(V, n_rays, nullptr, H, sc->d_occ, sc->d_counters + 1); (*launches)++; }
+              k_shadow<HAS_NODES, false><<<(int)std::min<long long>(need, g_shadow0), RT_BLOCK, smem, st>>>(V, n_rays, nullptr, H, sc->d_occ, sc->d_counters + 1); (*launches)++; }
             { ProfScope ps_(sc, 2, st);
-              k_shade<true><<<grid, RT_BLOCK, 0, st>>>(V, n_rays, q0, nullptr, H, sc->d_occ, sc->d_samples, q0, sc->d_qcount, sc->d_counters + 2); }
+              k_shade<true><<<(int)std::min<long long>(need, g_shade0), RT_BLOCK, 0, st>>>(V, n_rays, q0, nullptr, H, sc->d_occ, sc->d_samples, q0, sc->d_qcount, sc->d_counters + 2); }
             (*launches) += 2;
         }
         if (secondary) {
@@ -421,13 +444,13 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
                 const unsigned long long* n_in = sc->d_qcount + (level - 1);
                 ProfScope ps_(sc, 3, st);
                 if (tail_level > 0 && level >= tail_level) {          // the small remainder: every path to its end in one launch
-                    k_tail<HAS_NODES><<<max_grid, RT_BLOCK, smem, st>>>(V, qin, n_in, sc->d_samples, sc->d_counters + 3);
+                    k_tail<HAS_NODES><<<g_tail, RT_BLOCK, smem, st>>>(V, qin, n_in, sc->d_samples, sc->d_counters + 3);
                     (*launches)++;
                     break;
                 }
-                k_hit<HAS_NODES, false><<<max_grid, RT_BLOCK, smem, st>>>(V, pmk, 0, 0, qin, n_in, H, sc->d_counters + 3);
-                if (V.n_lights > 0) { k_shadow<HAS_NODES, true><<<dim3((unsigned)std::max(1, max_grid / V.n_lights), (unsigned)V.n_lights), RT_BLOCK, smem, st>>>(V, 0, n_in, H, sc->d_occ, sc->d_counters + 3); (*launches)++; }
-                k_shade<false><<<max_grid, RT_BLOCK, 0, st>>>(V, 0, qin, n_in, H, sc->d_occ, sc->d_samples, qout, sc->d_qcount + level, sc->d_counters + 3);
+                k_hit<HAS_NODES, false><<<g_hit, RT_BLOCK, smem, st>>>(V, pmk, 0, 0, qin, n_in, H, sc->d_counters + 3);
+                if (V.n_lights > 0) { k_shadow<HAS_NODES, true><<<dim3((unsigned)std::max(1, g_shadow / V.n_lights), (unsigned)V.n_lights), RT_BLOCK, smem, st>>>(V, 0, n_in, H, sc->d_occ, sc->d_counters + 3); (*launches)++; }
+                k_shade<false><<<g_shade, RT_BLOCK, 0, st>>>(V, 0, qin, n_in, H, sc->d_occ, sc->d_samples, qout, sc->d_qcount + level, sc->d_counters + 3);
                 (*launches) += 2;
             }
         }
