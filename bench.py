@@ -328,7 +328,7 @@ def run_ours(a):
                             "frac": (achieved / hbm_peak) if achieved else None, "traffic": traffic_of(dom, a), "peak_source": peak_src,
                             "note": "algorithmic bytes = BVH nodes/triangles the kernel fetches (tallies x record size); the 93 MB BVH "
                                     "is L1/L2 resident, so DRAM traffic is far below them and frac can exceed 1: the kernel is bound by "
-                                    "L1 register write-back (75 % of peak wavefronts) and issue slots (67 %) (profiles/r01q_final_4k64.txt), not by HBM",
+                                    "L1 register write-back (85 % of peak wavefronts) and issue slots (75 %) (profiles/r01w_final_4k64.txt), not by HBM",
                             "algorithmic_bytes_per_launch": alg_bytes_frame / launches_per_frame,
                             "launch_ms": ms_dom, "launches_per_frame": launches_per_frame,
                             "kernel_share_of_step": kernel_share,

@@ -26,9 +26,13 @@
 #define RT_TAIL_BIG_BATCH (96ll << 20)
 #endif
 // first level handled by k_tail (0 = never: every level as three launches); developer override: B200RT_TAIL_LEVEL
-static int tail_level_for(long long n_rays) {
+// Scenes with CSG / transform nodes: k_tail<true> is the whole node interpreter in one kernel (instruction-fetch bound, 4 blocks/SM),
+// so it only pays while launch overhead dominates.  NovelScene1 at 32 spp, ms/frame with k_tail from level 1 / from level 2 / never:
+// 1 Mi rays 3.9 / 3.7 / 4.6, 4 Mi 13.6 / 10.8 / 11.1, 16 Mi 52.4 / 40.6 / 36.5, 64 Mi 210 / 159 / 139.
+static int tail_level_for(long long n_rays, bool has_nodes) {
     static const char* env = getenv("B200RT_TAIL_LEVEL");
     if (env) return atoi(env);
+    if (has_nodes) return n_rays < (8ll << 20) ? 2 : 0;
     return n_rays >= RT_TAIL_BIG_BATCH ? 3 : 1;
 }
 
@@ -437,7 +441,7 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
             (*launches) += 2;
         }
         if (secondary) {
-            const int tail_level = tail_level_for(n_rays);
+            const int tail_level = tail_level_for(n_rays, HAS_NODES);
             for (int level = 1; level < V.max_depth; level++) {       // level L consumes the rays spawned by level L-1
                 RayQueue& qin = (level & 1) ? q0 : q1;
                 RayQueue& qout = (level & 1) ? q1 : q0;
