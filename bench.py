@@ -166,18 +166,23 @@ class ClockSampler:
         return out
 
 
-def traffic_of(kernel, a):
-    """dram__bytes_read+write of one launch of `kernel` from the committed ncu --set full capture of THIS workload
-    (profiles/traffic.json, written by profiles/summarize.py), or None when no capture matches."""
+def frame_metrics(a):
+    """Per-frame ncu sums per kernel for THIS workload (profiles/frame_metrics.json, written by profiles/summarize.py
+    --frame from a one-frame `ncu --metrics smsp__inst_executed.sum,l1tex__data_pipe_lsu_wavefronts.sum,dram__bytes_*`
+    capture at N=1): {kernel: {inst, lsu_wavefronts, dram_bytes, launches}} or {} when no capture matches."""
     try:
-        with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
-            t = json.load(fh)
-        return t.get(f"{kernel}@{a.width}x{a.height}x{a.spp}")
+        with open(os.path.join(ROOT, "profiles", "frame_metrics.json")) as fh:
+            return json.load(fh).get(f"{a.width}x{a.height}x{a.spp}", {})
     except Exception:
-        return None
+        return {}
+
+
+# reference-formulation flop counts (SURVEY 8d; FMA = 2): the whole-frame FP32 figure reported beside the issue-slot roofline
+FLOPS = {"raygen": 60, "node4": 4 * 30, "tri": 110, "prim": 35, "light": 45}
 
 
 def run_ours(a):
+    import hashlib
     import torch
     import torch.distributed as dist
     import python_raytracer_b200 as rt
@@ -220,6 +225,10 @@ def run_ours(a):
     sc.max_batch_rays = a.batch_rays
     sc.debug_mode_bits = a.mode_bits
 
+    # roofline denominators measured here and now on this GPU (hand-written micro-benchmarks, csrc/rt_peaks.cuh)
+    peaks = _abi.RtPeaks()
+    _abi.check(lib, lib.rt_measure_peaks(C.byref(peaks), torch.cuda.current_stream().cuda_stream), "rt_measure_peaks")
+
     sharder = TileSharder(sc, rank, world)
     W, H = a.width, a.height
 
@@ -235,17 +244,16 @@ def run_ours(a):
     for _ in range(max(0, a.warmup - 1)):
         sharder.render()
     tallies = torch.tensor([getattr(ctr, k) for k in RAY_KEYS] + [ctr.kernel_launches, ctr.bvh_nodes, ctr.tri_tests, ctr.queued_rays,
-                                                                  ctr.mesh_hits_smooth, ctr.shaded_hits],
+                                                                  ctr.mesh_hits_smooth, ctr.shaded_hits, ctr.prim_tests],
                            dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(tallies)
     tl = [int(x) for x in tallies.tolist()]
     rays_frame = sum(tl[:4])
-    launches_frame = tl[4] + (1 if world > 1 else 0)
+    launches_frame = tl[4] + (1 if world > 1 else 0)          # + rank 0's k_assemble
 
-    # ---- timed region 1: inputs resident in HBM, image left on the device (rank 0)
+    # ---- timed region 1: inputs resident in HBM, image left on the device (rank 0).  Profiling instrumentation is OFF.
     sampler = ClockSampler(local_rank) if rank == 0 else None
-    _abi.check(lib, lib.rt_scene_profile(h, 1), "rt_scene_profile")
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
@@ -257,97 +265,140 @@ def run_ours(a):
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_total = float(ms.item())
+
+    # ---- timed region 2 (e2e): the public call with HOST output; D2H of the frame inside the timed region
+    host_img = torch.empty(W * H * 3, dtype=torch.float32).pin_memory() if rank == 0 else None
+    host_u8 = torch.empty(W * H * 3, dtype=torch.uint8).pin_memory() if rank == 0 else None
+    dev_u8 = torch.empty(W * H * 3, dtype=torch.uint8, device="cuda") if rank == 0 else None
+    e2e_steps = a.steps
+
+    def e2e_frame(u8=False):
+        img = sharder.render()
+        if rank == 0:
+            if u8:   # main.py:31-33 on the device (rt_finalize_u8): a quarter of the bytes cross PCIe
+                _abi.check(lib, lib.rt_finalize_u8(img.data_ptr(), W, H, dev_u8.data_ptr(), torch.cuda.current_stream().cuda_stream), "rt_finalize_u8")
+                host_u8.copy_(dev_u8, non_blocking=True)
+            else:
+                host_img.copy_(img, non_blocking=True)
+        # every rank's caller waits for its call to finish (rank 0: owns the pixels) before the next frame starts
+        torch.cuda.current_stream().synchronize()
+
+    def timed_e2e(u8):
+        for _ in range(min(2, a.warmup)):       # warm-up of THIS path: first copy into the fresh pinned buffer, first per-frame waits
+            e2e_frame(u8)
+        barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        for _ in range(e2e_steps):
+            e2e_frame(u8)
+        f1.record()
+        barrier()
+        t = torch.tensor([f0.elapsed_time(f1)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    ms2_total = timed_e2e(False)
+    clocks = sampler.stop() if sampler else None
+    ms3_total = timed_e2e(True)
+
+    # ---- untimed: per-kernel split (CUDA-event pairs around every launch) and per-kernel tallies, from a separate pass
+    prof_frames = max(1, min(3, a.steps))
+    _abi.check(lib, lib.rt_scene_profile(h, 1), "rt_scene_profile")
+    for _ in range(prof_frames):
+        sharder.render()
+    torch.cuda.synchronize()
     prof = _abi.RtProfile()
     _abi.check(lib, lib.rt_scene_profile_read(h, C.byref(prof)), "rt_scene_profile_read")
     _abi.check(lib, lib.rt_scene_profile(h, 0), "rt_scene_profile")
 
-    # ---- timed region 2 (e2e): the public call with HOST output; D2H of the frame inside the timed region
-    host_img = torch.empty(W * H * 3, dtype=torch.float32).pin_memory() if rank == 0 else None
-    e2e_steps = a.steps
-
-    def e2e_frame():
-        img = sharder.render()
-        if rank == 0:
-            host_img.copy_(img, non_blocking=True)
-        # every rank's caller waits for its call to finish (rank 0: owns the pixels) before the next frame starts; with only
-        # rank 0 waiting, the other ranks queued whole frames ahead and the two-rank e2e time wandered between 65 and 93 ms
-        torch.cuda.current_stream().synchronize()
-
-    for _ in range(min(2, a.warmup)):       # warm-up of THIS path: first copy into the fresh pinned buffer, first per-frame waits
-        e2e_frame()
-    barrier()
-    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    f0.record()
-    for _ in range(e2e_steps):
-        e2e_frame()
-    f1.record()
-    barrier()
-    ms2 = torch.tensor([f0.elapsed_time(f1)], dtype=torch.float64, device="cuda")
+    # ---- untimed: the frame's checksum; N > 1: rank 0 also renders the whole frame alone and the two must be bit-identical
+    image_sha = None
+    equals_single = None
+    if rank == 0:
+        image_sha = hashlib.sha256(host_img.numpy().tobytes()).hexdigest()
     if world > 1:
-        dist.all_reduce(ms2, op=dist.ReduceOp.MAX)
-    ms2_total = float(ms2.item())
-    clocks = sampler.stop() if sampler else None
+        if rank == 0:
+            solo = TileSharder(sc, 0, 1)
+            ref = solo.render().cpu()
+            equals_single = bool(torch.equal(ref, host_img))
+            del solo, ref
+        dist.barrier()
 
     if rank == 0:
-        import json as _json
-        peaks = {}
+        hw = {}
         pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
         if os.path.exists(pk):
             with open(pk) as fh:
-                peaks = _json.load(fh)
-        hbm_peak, peak_src = (peaks.get("hbm_gbs"), "measured (MEASURED_PEAKS.json)") if peaks.get("hbm_gbs") else (6650.0, "fallback")
-        # roofline of the dominant kernel: algorithmic bytes per launch / mean launch time (DESIGN.md "Measurement").
-        # Bytes per unit: 128 B per 4-wide BVH node fetched, 48 B per triangle tested, 64 B of vertex ids + normals per
-        # smooth-shaded mesh hit, 48 B hit record per ray (k_hit writes, k_shade reads), 16 B hit position per shadow
-        # ray + 1 B flag, 16 B per finished sample, 80 B per queued secondary ray.
-        primary_rays_rank = W * H * a.spp / world
+                hw = json.load(fh)
+        hbm_peak, hbm_src = (hw.get("hbm_gbs"), "measured (MEASURED_PEAKS.json)") if hw.get("hbm_gbs") else (6650.0, "fallback")
+        per_frame = lambda x: x / prof_frames                                   # noqa: E731
+        kernel_ms = {"k_hit": per_frame(prof.ms_hit), "k_shadow": per_frame(prof.ms_shadow), "k_shade": per_frame(prof.ms_shade),
+                     "k_resolve": per_frame(prof.ms_resolve),
+                     "level1 k_hit": per_frame(prof.ms_l1_hit), "level1 k_shadow": per_frame(prof.ms_l1_shadow),
+                     "level1 k_shade": per_frame(prof.ms_l1_shade), "levels>=2 (hit+shadow+shade)": per_frame(prof.ms_deep),
+                     "k_tail": per_frame(prof.ms_tail)}
+        level0 = {"k_hit": (prof.ms_hit, prof.n_hit), "k_shadow": (prof.ms_shadow, prof.n_shadow), "k_shade": (prof.ms_shade, prof.n_shade)}
+        dom = max(level0, key=lambda k: level0[k][0])
+        ms_dom_frame = per_frame(level0[dom][0])
+        launches_dom = max(1, int(level0[dom][1]) // prof_frames)
+        ms_all = sum(kernel_ms.values())
+        fm = frame_metrics(a).get(dom, {}) if world == 1 else {}
+        # the dominant kernel is bound by the warp schedulers' issue slots (ncu: smsp__issue_active), not by HBM: its BVH is L1/L2
+        # resident.  achieved = warp instructions the kernel executes per frame (ncu smsp__inst_executed.sum of the SAME workload,
+        # committed under profiles/) / the kernel's time per frame measured live above; peak = issue rate measured live.
+        sec = ms_dom_frame * 1e-3
+        inst, lsu, dram = fm.get("inst"), fm.get("lsu_wavefronts"), fm.get("dram_bytes")
+        roof = {"bound": "issue", "kernel": dom, "unit": "Gwarp-inst/s",
+                "achieved": (inst / sec / 1e9) if inst and sec > 0 else None, "peak": peaks.issue_ginst,
+                "frac": (inst / sec / 1e9 / peaks.issue_ginst) if inst and sec > 0 else None,
+                "traffic": (dram / launches_dom) if dram else None,
+                "peak_source": "measured in this run by rt_measure_peaks (csrc/rt_peaks.cuh: FFMA/IADD3/LOP3 mix, 16 warps per scheduler)",
+                "count_source": "ncu smsp__inst_executed.sum / l1tex__data_pipe_lsu_wavefronts.sum / dram__bytes_* per frame of this "
+                                "workload at N=1 (profiles/frame_metrics.json); time = CUDA events around each launch, this run",
+                "kernel_ms_per_frame": ms_dom_frame, "launches_per_frame": launches_dom,
+                "kernel_share_of_step": ms_dom_frame / max(1e-9, ms_all),
+                "l1_lsu": {"achieved": (lsu / sec / 1e9) if lsu and sec > 0 else None, "peak": peaks.lsu_gwavefronts, "unit": "Gwavefronts/s (128 B)",
+                           "frac": (lsu / sec / 1e9 / peaks.lsu_gwavefronts) if lsu and sec > 0 else None},
+                "hbm": {"achieved": (dram / sec / 1e9) if dram and sec > 0 else None, "peak": hbm_peak, "unit": "GB/s", "peak_source": hbm_src,
+                        "frac": (dram / sec / 1e9 / hbm_peak) if dram and sec > 0 else None}}
+        if not fm:
+            roof["note"] = "no ncu capture of this workload at N=1 under profiles/frame_metrics.json: counts unavailable, fractions null"
+        # whole-frame FP32 figure from the device tallies x reference-formulation flop counts against the measured FMA peak
         n_lights = len(sc.lights)
-        kinds = {
-            "k_hit": (prof.ms_hit, prof.n_hit, prof.hit,
-                      lambda c: 128 * c.bvh_nodes + 48 * c.tri_tests + 64 * c.mesh_hits_smooth + 48 * primary_rays_rank),
-            "k_shadow": (prof.ms_shadow, prof.n_shadow, prof.shadow,
-                         lambda c: 128 * c.bvh_nodes + 48 * c.tri_tests + 16 * primary_rays_rank * n_lights + c.rays_shadow),
-            "k_shade": (prof.ms_shade, prof.n_shade, prof.shade,
-                        lambda c: (48 + n_lights) * c.shaded_hits + 16 * primary_rays_rank + 80 * c.queued_rays),
-        }
-        dom = max(kinds, key=lambda k: kinds[k][0])
-        ms_dom_total, n_launch, pc, bytes_of = kinds[dom]
-        n_launch = max(1, int(n_launch))
-        launches_per_frame = max(1, n_launch // max(1, a.steps))
-        alg_bytes_frame = bytes_of(pc)
-        ms_dom = ms_dom_total / n_launch
-        achieved = alg_bytes_frame / launches_per_frame / (ms_dom * 1e-3) / 1e9 if ms_dom > 0 else None
-        ms_all = prof.ms_hit + prof.ms_shadow + prof.ms_shade + prof.ms_secondary + prof.ms_resolve
-        kernel_share = ms_dom_total / max(1e-9, ms_all)
+        flops_frame = (FLOPS["raygen"] * tl[0] + FLOPS["node4"] * tl[5] + FLOPS["tri"] * tl[6] + FLOPS["prim"] * tl[10]
+                       + FLOPS["light"] * n_lights * tl[9])
+        step_s = ms_total / a.steps * 1e-3
         value = rays_frame * a.steps / (ms_total * 1e-3) / 1e6
         e2e_value = rays_frame * e2e_steps / (ms2_total * 1e-3) / 1e6
+        knobs = {k: v for k, v in os.environ.items() if k.startswith("B200RT_")}
         out = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
                "ms_per_step": ms_total / a.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                "dtype": "f32", "data": "synthetic",
                "config": {**workload_config(a), "tiles": f"{sc.tile[0]}x{sc.tile[1]} interleaved over ranks",
-                          "l2_policy": "working set (BVH nodes+triangles+sample/queue buffers) exceeds the 126 MB L2; no flush between frames"},
+                          "l2_policy": "working set (BVH nodes+triangles+sample/queue buffers) exceeds the 126 MB L2; no flush between frames",
+                          "env_knobs": knobs},
                "rays_per_frame": dict(zip(RAY_KEYS, tl[:4])),
                "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": ms2_total / e2e_steps,
                        "h2d_bytes_per_step": C.sizeof(_abi.RtRenderJob), "d2h_bytes_per_step": W * H * 3 * 4,
-                       "what": "frame rendered through the C ABI and copied to pinned HOST memory every step (scene resident: "
+                       "what": "frame rendered through the C ABI and copied to pinned HOST memory every step as float32 (scene resident: "
                                "uploaded once like the reference's load_scene)"},
+               "e2e_u8": {"value": rays_frame * e2e_steps / (ms3_total * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": ms3_total / e2e_steps,
+                          "d2h_bytes_per_step": W * H * 3,
+                          "what": "same, but main.py:31-33 (rot90, *255 truncation) done on the device and the uint8 PNG array copied"},
                "gpu_launches": launches_frame * a.steps,
-               "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                            "frac": (achieved / hbm_peak) if achieved else None, "traffic": traffic_of(dom, a), "peak_source": peak_src,
-                            "note": "algorithmic bytes = BVH nodes/triangles the kernel fetches (tallies x record size); the 93 MB BVH "
-                                    "is L1/L2 resident, so DRAM traffic is far below them and frac can exceed 1: the kernel is bound by "
-                                    "L1 register write-back (85 % of peak wavefronts) and issue slots (75 %) (profiles/r01w_final_4k64.txt), not by HBM",
-                            "algorithmic_bytes_per_launch": alg_bytes_frame / launches_per_frame,
-                            "launch_ms": ms_dom, "launches_per_frame": launches_per_frame,
-                            "kernel_share_of_step": kernel_share,
-                            "counts_rank0_per_frame": {"bvh_nodes": int(pc.bvh_nodes), "tri_tests": int(pc.tri_tests),
-                                                       "queued_rays": int(pc.queued_rays)}},
+               "image_sha256": image_sha, "image_equals_single_rank_render": equals_single,
+               "roofline": roof,
+               "fp32": {"achieved_tflops": flops_frame / step_s / 1e12, "peak_tflops": peaks.fp32_fma_tflops,
+                        "frac": flops_frame / step_s / 1e12 / peaks.fp32_fma_tflops,
+                        "flops_per_unit": FLOPS, "note": "whole frame; reference-formulation flop counts x device tallies"},
+               "peaks_measured": peaks.as_dict(),
+               "bytes_per_step_dram": sum(v.get("dram_bytes", 0) for v in frame_metrics(a).values()) or None,
                "tallies_rank0_per_frame": {k: {n: v for n, v in c.as_dict().items() if v and n not in ("kernel_launches", "error_flags")}
                                            for k, c in (("k_hit", prof.hit), ("k_shadow", prof.shadow), ("k_shade", prof.shade),
                                                         ("levels>=1", prof.secondary))},
-               "kernel_ms_per_frame": {"k_hit": prof.ms_hit / a.steps, "k_shadow": prof.ms_shadow / a.steps,
-                                       "k_shade": prof.ms_shade / a.steps, "levels>=1 (hit+shadow+shade)": prof.ms_secondary / a.steps,
-                                       "k_resolve": prof.ms_resolve / a.steps},
+               "kernel_ms_per_frame": kernel_ms,
+               "kernel_ms_note": f"separate untimed pass of {prof_frames} frames with per-launch CUDA events; `value` is timed with that instrumentation off",
                "setup_ms": {"scene_python": 1e3 * t_scene, **t_ingest, "upload": 1e3 * t_upload, "lbvh_build": 1e3 * t_bvh},
                "clocks": clocks}
         if not a.no_cpu_baseline and world == 1:

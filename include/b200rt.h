@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define RT_ABI_VERSION 2
+#define RT_ABI_VERSION 3
 
 /* ---- enums ------------------------------------------------------------------------- */
 enum RtKind { RT_KIND_SPHERE = 0, RT_KIND_PLANE = 1, RT_KIND_BOX = 2, RT_KIND_MESH = 3, RT_KIND_NODE = 4 };
@@ -198,7 +198,20 @@ typedef struct RtProfile {
     uint64_t n_hit, n_shadow, n_shade, n_secondary, n_resolve;   /* timed launches (n_secondary: levels) */
     RtCounters hit, shadow, shade;                 /* tallies of the level-0 kernels of the last rt_render */
     RtCounters secondary;                          /* tallies of all deeper-level kernels of the last rt_render */
+    /* the queued levels in detail (their sum is ms_secondary): level 1 per kernel, levels >= 2 as a whole, k_tail */
+    double ms_l1_hit, ms_l1_shadow, ms_l1_shade, ms_deep, ms_tail;
+    uint64_t n_l1_hit, n_deep, n_tail;
 } RtProfile;
+
+/* Roofline denominators MEASURED on the current device by hand-written micro-benchmarks (csrc/rt_peaks.cuh): FP32 FMA
+ * throughput of the CUDA cores, warp-instruction issue rate, L1 data-pipe wavefront rate (128 B each); *_nominal = SMs x
+ * per-SM rate x the device's reported SM clock, for comparison. */
+typedef struct RtPeaks {
+    double fp32_fma_tflops, issue_ginst, lsu_gwavefronts;
+    double fp32_fma_tflops_nominal, issue_ginst_nominal, lsu_gwavefronts_nominal;
+    double sm_clock_mhz;
+    int32_t sm_count, _pad;
+} RtPeaks;
 
 typedef struct RtScene RtScene;  /* opaque, device-resident */
 
@@ -215,7 +228,10 @@ int rt_scene_build_bvh(RtScene* scene, void* stream);
 
 /* Replaces Scene.render(subimage, tasks) (scene.py:35-79).  d_out is DEVICE memory:
  * job->direct ? (ncols, nrows, 3) : (n_local_tiles, tile_h, tile_w, 3), float32.
- * counters may be NULL; when given, the call synchronises the stream before returning. */
+ * counters may be NULL; when given, the call synchronises the stream before returning.
+ * The job rectangle must lie inside the frame (RT_ERR_INVALID otherwise).  ONE render call may be in flight per scene
+ * handle: the wavefront buffers (samples, hit records, ray queues, counters) belong to the handle and are re-used and
+ * re-grown by every call; use one handle per stream for concurrent renders.  The caller's current device is preserved. */
 int rt_render(RtScene* scene, const RtRenderJob* job, float* d_out, RtCounters* counters, void* stream);
 
 /* Same, HOST output buffer (pageable or pinned): device staging + D2H copy inside the call;
@@ -275,6 +291,8 @@ int rt_occluded(RtScene* scene, int64_t n, const float* h_origins, const float* 
 int rt_scene_profile(RtScene* scene, int32_t enable);
 /* synchronises the recorded events and returns the sums */
 int rt_scene_profile_read(RtScene* scene, RtProfile* out);
+/* runs the three micro-benchmarks on `stream` of the current device (a few ms each); synchronous */
+int rt_measure_peaks(RtPeaks* out, void* stream);
 const char* rt_last_error(void);
 int rt_abi_version(void);
 

@@ -33,6 +33,8 @@ def lib():
         L.oracle_trace_rays.argtypes = [vp, C.c_int64, vp, vp, vp, vp, vp, vp, vp, vp, vp]
         L.oracle_occluded.argtypes = [vp, C.c_int64, vp, vp, vp, vp, vp]
         L.oracle_philox.argtypes = [C.c_uint64, C.c_uint64, vp]
+        L.oracle_render_pixels_perturbed.argtypes = [vp, vp, vp, C.c_int64, vp, C.c_double, C.c_uint64, C.c_int]
+        L.oracle_pixel_features.argtypes = [vp, vp, vp, C.c_int64, vp, C.c_int]
         _lib = L
     return _lib
 
@@ -62,6 +64,41 @@ def render_pixels(flat, abi, cols, rows, threads=0):
                                     out.ctypes.data, C.addressof(ctr), threads)
     assert rc == 0, rc
     return out, ctr.as_dict()
+
+
+def render_pixels_perturbed(flat, cols, rows, eps=1e-6, seed=1, threads=0):
+    """Stability probe (NOT reference behaviour): the same pixels with every cast_ray input ray and closest-hit position
+    moved by a random vector of relative size `eps` (a few float32 ulp)."""
+    cols = np.ascontiguousarray(cols, dtype=np.int32)
+    rows = np.ascontiguousarray(rows, dtype=np.int32)
+    out = np.empty((len(cols), 3), dtype=np.float64)
+    rc = lib().oracle_render_pixels_perturbed(C.addressof(flat.desc), cols.ctypes.data, rows.ctypes.data, len(cols),
+                                              out.ctypes.data, float(eps), int(seed), threads)
+    assert rc == 0, rc
+    return out
+
+
+def unstable_pixels(flat, cols, rows, base_rgb, eps=1e-6, trials=6, threads=0):
+    """Which of the given pixels are REFERENCE-UNSTABLE: the oracle's own uint8 value moves by more than 1 when its rays
+    and hit points are perturbed by `eps` (relative).  `base_rgb` (n,3) float = the unperturbed oracle values.  A correct
+    float32 implementation cannot be expected to agree with the reference on such a pixel."""
+    base = (np.asarray(base_rgb, dtype=np.float64) * 255).astype(np.uint8).astype(int)
+    unstable = np.zeros(len(cols), dtype=bool)
+    for k in range(trials):
+        p = (render_pixels_perturbed(flat, cols, rows, eps, seed=1000 + k, threads=threads) * 255).astype(np.uint8).astype(int)
+        unstable |= np.abs(p - base).max(axis=1) > 1
+    return unstable
+
+
+def pixel_features(flat, cols, rows, threads=0):
+    """(n,4) int32 per pixel: leaf object of the first sample's closest hit, material index, shadowed-light bits,
+    material type (0 diffuse / 1 mirror / 2 refractive)."""
+    cols = np.ascontiguousarray(cols, dtype=np.int32)
+    rows = np.ascontiguousarray(rows, dtype=np.int32)
+    out = np.empty((len(cols), 4), dtype=np.int32)
+    rc = lib().oracle_pixel_features(C.addressof(flat.desc), cols.ctypes.data, rows.ctypes.data, len(cols), out.ctypes.data, threads)
+    assert rc == 0, rc
+    return out
 
 
 def trace_rays(flat, origins, dirs, times=None):

@@ -114,6 +114,11 @@ typedef struct {
     const RtSceneDesc* s;
     double time;          /* scene.current_time, scene.py:68 */
     RtCounters c;
+    /* stability probe (oracle_render_pixels_perturbed; NOT reference behaviour, 0 = off): every ray handed to cast_ray
+     * and every closest-hit position is moved by a random vector of relative length `perturb` (a few float32 ulp) before
+     * it is used, so that a pixel whose reference value hinges on sub-ulp coincidences shows up as unstable */
+    double perturb;
+    uint32_t pstate[4];
 } Ctx;
 
 #define EPSILON 1e-4          /* geometry/__init__.py:12 */
@@ -586,6 +591,17 @@ static int obj_get_material(Ctx* cx, int oi, v3 p) {
 /* ---------------------------------------------------------------- shading, scene.py:81-209 */
 static v3 cast_ray(Ctx* cx, const Ray* ray, int max_recursion, int in_shape);
 
+/* stability probe only: v + perturb * max(1, |v|_inf) * (random vector in [-1,1]^3) */
+static v3 probe_jiggle(Ctx* cx, v3 v, int relative_to_length) {
+    cx->pstate[0]++;
+    uint32_t c[4] = {cx->pstate[0], cx->pstate[1], 0x9e3779b9u, 0};
+    philox4x32_10(c, cx->pstate[2], cx->pstate[3]);
+    double m = fmax(fabs((double)v.x), fmax(fabs((double)v.y), fabs((double)v.z)));
+    double scale = cx->perturb * (relative_to_length ? m : fmax(1.0, m));
+    return V3((float)((double)v.x + scale * (c[0] * 0x1p-31 - 1.0)), (float)((double)v.y + scale * (c[1] * 0x1p-31 - 1.0)),
+              (float)((double)v.z + scale * (c[2] * 0x1p-31 - 1.0)));
+}
+
 static v3 regular_lighting(Ctx* cx, const Ray* ray, const Hit* hit) {
     const RtSceneDesc* s = cx->s;
     v3 colour = V3(0, 0, 0);
@@ -638,15 +654,19 @@ static v3 compute_refraction(Ctx* cx, const Ray* ray, Hit* hit, int in_shape, in
     return cast_ray(cx, &rr, max_recursion - 1, !in_shape);
 }
 
-static v3 cast_ray(Ctx* cx, const Ray* ray, int max_recursion, int in_shape) {
+static v3 cast_ray(Ctx* cx, const Ray* ray_in, int max_recursion, int in_shape) {
     if (max_recursion == 0) return V3(0, 0, 0);
     const RtSceneDesc* s = cx->s;
+    Ray jiggled;
+    const Ray* ray = ray_in;
+    if (cx->perturb > 0) { jiggled.o = probe_jiggle(cx, ray_in->o, 0); jiggled.d = probe_jiggle(cx, ray_in->d, 1); ray = &jiggled; }
     HitList hl = {0, 0, 0};
     for (int oi = 0; oi < s->n_top; oi++) obj_intersect(cx, oi, ray, &hl);
     if (hl.n == 0) { free(hl.v); return V3(0, 0, 0); }
     Hit first = hl.v[0];
     for (int i = 1; i < hl.n; i++) if (hl.v[i].t < first.t) first = hl.v[i];
     free(hl.v);
+    if (cx->perturb > 0) first.p = probe_jiggle(cx, first.p, 0);
     if (first.mat < 0) {   /* reference raises IndexError */
         cx->c.error_flags |= 1ull << RT_ERR_NO_MATERIAL;
         return V3(0, 0, 0);
@@ -765,6 +785,83 @@ int oracle_render_pixels(const RtSceneDesc* s, const int32_t* cols, const int32_
         free(dof_pts); free(aa_pts);
     }
     if (counters) *counters = total;
+    return RT_OK;
+}
+
+/* Stability probe (tests only; NOT reference behaviour): oracle_render_pixels with every cast_ray input ray and every
+ * closest-hit position moved by a random vector of relative size `eps` (see Ctx.perturb).  Deterministic in (seed, pixel). */
+int oracle_render_pixels_perturbed(const RtSceneDesc* s, const int32_t* cols, const int32_t* rows, int64_t n, double* out,
+                                   double eps, uint64_t seed, int n_threads) {
+    if (!s || s->abi_version != RT_ABI_VERSION) return RT_ERR_INVALID;
+#ifdef _OPENMP
+    if (n_threads > 0) omp_set_num_threads(n_threads);
+#else
+    (void)n_threads;
+#endif
+#pragma omp parallel
+    {
+        Ctx cx; memset(&cx, 0, sizeof cx); cx.s = s; cx.perturb = eps;
+        v3* dof_pts = (v3*)malloc(sizeof(v3) * (size_t)(s->dof_samples > 0 ? s->dof_samples : 1));
+        v3* aa_pts = (v3*)malloc(sizeof(v3) * (size_t)(s->aa_samples > 0 ? s->aa_samples : 1));
+#pragma omp for schedule(dynamic, 16)
+        for (int64_t i = 0; i < n; i++) {
+            cx.pstate[0] = 0; cx.pstate[1] = (uint32_t)(cols[i] * 65599u + rows[i]);
+            cx.pstate[2] = (uint32_t)seed; cx.pstate[3] = (uint32_t)(seed >> 32);
+            render_pixel(&cx, cols[i], rows[i], 0, out + 3 * i, dof_pts, aa_pts);
+        }
+        free(dof_pts); free(aa_pts);
+    }
+    return RT_OK;
+}
+
+/* What the FIRST sample of a pixel sees (dof 0, aa 0, time 0, no jitter): out[4*i..] = leaf object index of the closest hit
+ * (-1: none), material index, bit li set when light li is shadowed at the hit (scene.py:160-164), material type (RtMatType).
+ * Tests use it to say WHERE a residue pixel lies: silhouettes / material (checker) edges / shadow edges are the places where
+ * these values change between neighbouring pixels; mirror / refractive materials mark the reflection and refraction regions. */
+int oracle_pixel_features(const RtSceneDesc* s, const int32_t* cols, const int32_t* rows, int64_t n, int32_t* out, int n_threads) {
+    if (!s || s->abi_version != RT_ABI_VERSION) return RT_ERR_INVALID;
+#ifdef _OPENMP
+    if (n_threads > 0) omp_set_num_threads(n_threads);
+#else
+    (void)n_threads;
+#endif
+    double dx = (s->right - s->left) / s->width, dy = (s->top - s->bottom) / s->height;
+#pragma omp parallel
+    {
+        Ctx cx; memset(&cx, 0, sizeof cx); cx.s = s;
+#pragma omp for schedule(dynamic, 64)
+        for (int64_t i = 0; i < n; i++) {
+            double x = accum_coord(s->left, dx, 0, cols[i]), y = accum_coord(s->bottom, dy, 0, rows[i]);
+            v3 pos = v3p(s->cam_pos), u = v3p(s->cam_u), v = v3p(s->cam_v), w = v3p(s->cam_w);
+            v3 base_dir = vnormalize(vsub(vadd(vscaled(u, x), vscaled(v, y)), vscaled(w, s->cam_d)));
+            v3 focal_point = vadd(pos, vscaled(base_dir, s->focal_length));
+            v3 dof0, aa0;
+            sunflower(1, pos, s->dof_samples == 1 ? s->aperture : 0.0, &dof0);     /* centre of the lens when there are several */
+            if (s->dof_samples != 1) dof0 = pos;
+            aa0 = dof0;
+            Ray ray; ray.o = aa0; ray.d = vnormalize(vsub(focal_point, dof0));
+            cx.time = s->motion_times[0];
+            HitList hl = {0, 0, 0};
+            for (int oi = 0; oi < s->n_top; oi++) obj_intersect(&cx, oi, &ray, &hl);
+            int32_t* o = out + 4 * i;
+            o[0] = -1; o[1] = -1; o[2] = 0; o[3] = 0;
+            if (hl.n > 0) {
+                Hit first = hl.v[0];
+                for (int k = 1; k < hl.n; k++) if (hl.v[k].t < first.t) first = hl.v[k];
+                o[0] = first.geom; o[1] = first.mat;
+                if (first.mat >= 0) o[3] = s->materials[first.mat].type;
+                for (int li = 0; li < s->n_lights && li < 31; li++) {
+                    const RtLight* L = &s->lights[li];
+                    Ray sr; double tmax; v3 lv = v3p(L->vector);
+                    if (L->type == RT_LIGHT_POINT) { sr.o = first.p; sr.d = vsub(lv, first.p); tmax = 1.0; }
+                    else { sr.o = first.p; sr.d = vneg(lv); tmax = INFINITY; }
+                    for (int oi = 0; oi < s->n_top; oi++)
+                        if (obj_shadow(&cx, oi, &sr, tmax)) { o[2] |= 1 << li; break; }
+                }
+            }
+            free(hl.v);
+        }
+    }
     return RT_OK;
 }
 

@@ -79,7 +79,55 @@ def traffic(workload, paths):
     print(json.dumps(table, indent=1))
 
 
+def frame(workload, csv_path, tag):
+    """profiles/frame_metrics.json["<WxHxspp>"][kernel] = per-FRAME sums over the launches of one frame (ncu --metrics ... of
+    scripts/ncu_frame.sh): inst (smsp__inst_executed.sum), thread_inst, lsu_wavefronts, dram_bytes, launches, ncu_ms; plus a
+    text table under profiles/<tag>.txt."""
+    import json
+    import os
+    rows = [r for r in csv.reader(open(csv_path)) if len(r) > 10]
+    h = rows[0]
+    ki, vi, mi, ui, ii = h.index("Kernel Name"), h.index("Metric Value"), h.index("Metric Name"), h.index("Metric Unit"), h.index("ID")
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1e-6, "us": 1e-3, "ms": 1.0, "nsecond": 1e-6, "usecond": 1e-3, "msecond": 1.0}
+    per = defaultdict(lambda: defaultdict(float))
+    pct = defaultdict(lambda: defaultdict(list))
+    ids = defaultdict(set)
+    for r in rows[1:]:
+        k = r[ki].split("(")[0].split("<")[0].replace("void ", "").strip()
+        v = float(r[vi].replace(",", "")) * scale.get(r[ui], 1.0)
+        ids[k].add(r[ii])
+        if "pct" in r[mi]:
+            pct[k][r[mi]].append(v)
+        else:
+            per[k][r[mi]] += v
+    table = {}
+    for k, m in per.items():
+        table[k] = {"inst": m.get("smsp__inst_executed.sum", 0.0), "thread_inst": m.get("smsp__thread_inst_executed.sum", 0.0),
+                    "lsu_wavefronts": m.get("l1tex__data_pipe_lsu_wavefronts.sum", 0.0),
+                    "dram_bytes": m.get("dram__bytes_read.sum", 0.0) + m.get("dram__bytes_write.sum", 0.0),
+                    "launches": len(ids[k]), "ncu_ms": m.get("gpu__time_duration.sum", 0.0),
+                    "issue_active_pct_mean": sum(pct[k].get("smsp__issue_active.avg.pct_of_peak_sustained_active", [0])) / max(1, len(ids[k])),
+                    "lsu_pct_mean": sum(pct[k].get("l1tex__data_pipe_lsu_wavefronts.sum.pct_of_peak_sustained_elapsed", [0])) / max(1, len(ids[k])),
+                    "l1_hit_pct_mean": sum(pct[k].get("l1tex__t_sector_hit_rate.pct", [0])) / max(1, len(ids[k])),
+                    "l2_hit_pct_mean": sum(pct[k].get("lts__t_sector_hit_rate.pct", [0])) / max(1, len(ids[k]))}
+    dst = "profiles/frame_metrics.json"
+    allm = json.load(open(dst)) if os.path.exists(dst) else {}
+    allm[workload] = table
+    json.dump(allm, open(dst, "w"), indent=1, sort_keys=True)
+    with open(f"profiles/{tag}.txt", "w") as out:
+        out.write(f"# one frame of {workload}: per-kernel sums over its launches (ncu --metrics, --clock-control none; times are serialised, cold)\n")
+        out.write(f"{'kernel':12s} {'launches':>8s} {'ncu_ms':>9s} {'warp inst':>14s} {'lanes/inst':>10s} {'lsu wavefronts':>15s} {'dram GB':>9s} {'issue%':>7s} {'lsu%':>6s} {'L1hit%':>7s} {'L2hit%':>7s}\n")
+        for k, t in sorted(table.items(), key=lambda kv: -kv[1]["ncu_ms"]):
+            out.write(f"{k[:12]:12s} {t['launches']:8d} {t['ncu_ms']:9.3f} {t['inst']:14.4g} {t['thread_inst'] / max(1.0, t['inst']):10.2f} "
+                      f"{t['lsu_wavefronts']:15.4g} {t['dram_bytes'] / 1e9:9.3f} {t['issue_active_pct_mean']:7.1f} {t['lsu_pct_mean']:6.1f} "
+                      f"{t['l1_hit_pct_mean']:7.1f} {t['l2_hit_pct_mean']:7.1f}\n")
+    print(open(f"profiles/{tag}.txt").read())
+
+
 if __name__ == "__main__":
+    if sys.argv[1] == "--frame":     # python profiles/summarize.py --frame 3840x2160x64 gpurun_out/x_metrics.csv r02a_frame_4k64
+        frame(sys.argv[2], sys.argv[3], sys.argv[4])
+        sys.exit(0)
     if sys.argv[1] == "--traffic":   # python profiles/summarize.py --traffic 3840x2160x64 a.ncu-rep b.ncu-rep ...
         traffic(sys.argv[2], sys.argv[3:])
         sys.exit(0)

@@ -11,7 +11,7 @@ import numpy as np
 
 from . import geometry as geom
 
-RT_ABI_VERSION = 2
+RT_ABI_VERSION = 3
 KIND_SPHERE, KIND_PLANE, KIND_BOX, KIND_MESH, KIND_NODE = range(5)
 MAT_TYPES = {"mirror": 1, "refractive": 2}            # anything else shades as diffuse, scene.py:97-111
 LIGHT_TYPES = {"point": 0, "directional": 1}
@@ -93,7 +93,20 @@ class RtProfile(C.Structure):
                 ("ms_secondary", C.c_double), ("ms_resolve", C.c_double),
                 ("n_hit", C.c_uint64), ("n_shadow", C.c_uint64), ("n_shade", C.c_uint64),
                 ("n_secondary", C.c_uint64), ("n_resolve", C.c_uint64),
-                ("hit", RtCounters), ("shadow", RtCounters), ("shade", RtCounters), ("secondary", RtCounters)]
+                ("hit", RtCounters), ("shadow", RtCounters), ("shade", RtCounters), ("secondary", RtCounters),
+                ("ms_l1_hit", C.c_double), ("ms_l1_shadow", C.c_double), ("ms_l1_shade", C.c_double),
+                ("ms_deep", C.c_double), ("ms_tail", C.c_double),
+                ("n_l1_hit", C.c_uint64), ("n_deep", C.c_uint64), ("n_tail", C.c_uint64)]
+
+
+class RtPeaks(C.Structure):
+    _fields_ = [("fp32_fma_tflops", C.c_double), ("issue_ginst", C.c_double), ("lsu_gwavefronts", C.c_double),
+                ("fp32_fma_tflops_nominal", C.c_double), ("issue_ginst_nominal", C.c_double),
+                ("lsu_gwavefronts_nominal", C.c_double), ("sm_clock_mhz", C.c_double),
+                ("sm_count", C.c_int32), ("_pad", C.c_int32)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_ if n != "_pad"}
 
 
 DEFAULT_JITTER_SEED = 0x5EED
@@ -273,7 +286,7 @@ LIB_PATH = os.environ.get("B200RT_LIB") or os.path.join(os.path.dirname(os.path.
 ENTRY_POINTS = ["rt_scene_create", "rt_scene_build_bvh", "rt_render", "rt_render_host", "rt_render_u8_host", "rt_job_extent",
                 "rt_assemble_tiles", "rt_finalize_u8", "rt_scene_destroy", "rt_scene_bvh_stats",
                 "rt_scene_bvh_download", "rt_last_error", "rt_abi_version", "rt_trace_rays", "rt_occluded",
-                "rt_scene_profile", "rt_scene_profile_read", "rt_obj_load", "rt_obj_copy", "rt_obj_free", "rt_mesh_ingest"]
+                "rt_scene_profile", "rt_scene_profile_read", "rt_measure_peaks", "rt_obj_load", "rt_obj_copy", "rt_obj_free", "rt_mesh_ingest"]
 
 
 class B200RTError(RuntimeError):
@@ -307,6 +320,7 @@ def load_library(path=None):
     lib.rt_occluded.argtypes = [vp, C.c_int64, vp, vp, vp, vp, vp, i32, vp]
     lib.rt_scene_profile.argtypes = [vp, i32]
     lib.rt_scene_profile_read.argtypes = [vp, C.POINTER(RtProfile)]
+    lib.rt_measure_peaks.argtypes = [C.POINTER(RtPeaks), vp]
     lib.rt_last_error.restype = C.c_char_p
     lib.rt_last_error.argtypes = []
     lib.rt_abi_version.argtypes = []

@@ -14,6 +14,7 @@
 #include "rt_ingest.cuh"
 #include "rt_kernels.cuh"
 #include "rt_obj.hpp"
+#include "rt_peaks.cuh"
 #include "rt_scene_build.hpp"
 
 #ifndef RT_GRID_WAVES
@@ -48,7 +49,9 @@ static int grid_waves(bool deep) {
     return w > 0 ? w : 1;
 }
 
-#define RT_PROF_CLASSES 5
+// profiling classes (per-launch CUDA-event pairs when rt_scene_profile is on): level-0 k_hit / k_shadow / k_shade, k_resolve,
+// then the queued levels: level-1 k_hit / k_shadow / k_shade, all launches of levels >= 2, k_tail
+enum { PC_HIT0 = 0, PC_SHADOW0, PC_SHADE0, PC_RESOLVE, PC_HIT1, PC_SHADOW1, PC_SHADE1, PC_DEEP, PC_TAIL, RT_PROF_CLASSES };
 #define RT_COUNTER_CLASSES 4     // tallies kept apart for level-0 k_hit / k_shadow / k_shade and for the deeper levels
 static thread_local std::string g_last_error;
 
@@ -61,6 +64,13 @@ static int fail(int code, const std::string& msg) { g_last_error = msg; return c
             return fail(e_ == cudaErrorMemoryAllocation ? RT_ERR_NOMEM : RT_ERR_CUDA,                      \
                         std::string(#expr) + ": " + cudaGetErrorString(e_));                              \
     } while (0)
+
+// cudaSetDevice(scene's device) for the duration of a call, the caller's current device restored on return
+struct DeviceGuard {
+    int prev = -1; bool switched = false;
+    explicit DeviceGuard(int dev) { if (cudaGetDevice(&prev) == cudaSuccess && prev != dev) switched = cudaSetDevice(dev) == cudaSuccess; }
+    ~DeviceGuard() { if (switched) cudaSetDevice(prev); }
+};
 
 struct MeshBuild {
     int n_verts = 0, n_faces = 0;
@@ -97,17 +107,23 @@ struct RtScene {
     int device = 0;
     int sm_count = 148;
     unsigned long long last_launches = 0;
-    bool profiling = false;
-    // profiling classes: level-0 k_hit / k_shadow / k_shade, all kernels of the deeper levels, k_resolve
-    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev[RT_PROF_CLASSES];
-    double prof_ms[RT_PROF_CLASSES] = {0, 0, 0, 0, 0};
-    unsigned long long prof_n[RT_PROF_CLASSES] = {0, 0, 0, 0, 0};
+    bool profiling = false, l2_window_tried = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev[RT_PROF_CLASSES];     // recorded, not yet read
+    std::vector<cudaEvent_t> ev_pool;                                          // events ready for re-use (created once)
+    double prof_ms[RT_PROF_CLASSES] = {};
+    unsigned long long prof_n[RT_PROF_CLASSES] = {};
 };
 
-struct ProfScope {   // event pair around one launch when profiling is on
+struct ProfScope {   // event pair around one launch when profiling is on (events come from a pool: none is created per launch once warm)
     RtScene* sc; int cls; cudaStream_t st; cudaEvent_t a = nullptr, b = nullptr;
+    static cudaEvent_t take(RtScene* s) {
+        cudaEvent_t e = nullptr;
+        if (!s->ev_pool.empty()) { e = s->ev_pool.back(); s->ev_pool.pop_back(); }
+        else cudaEventCreate(&e);
+        return e;
+    }
     ProfScope(RtScene* s, int c, cudaStream_t t) : sc(s), cls(c), st(t) {
-        if (sc->profiling) { cudaEventCreate(&a); cudaEventCreate(&b); cudaEventRecord(a, st); }
+        if (sc->profiling) { a = take(sc); b = take(sc); cudaEventRecord(a, st); }
     }
     ~ProfScope() { if (a) { cudaEventRecord(b, st); sc->ev[cls].push_back({a, b}); } }
 };
@@ -120,7 +136,7 @@ static int upload(RtScene* sc, const T* host, size_t n, T** out) {
     CU(cudaMalloc(&p, alloc_n * sizeof(T)));
     sc->allocs.push_back(p);
     if (host && n) CU(cudaMemcpy(p, host, n * sizeof(T), cudaMemcpyHostToDevice));
-    else { CU(cudaMemset(p, 0, alloc_n * sizeof(T))); CU(cudaDeviceSynchronize()); }   // set-up time only: later kernels run on caller streams
+    else CU(cudaMemset(p, 0, alloc_n * sizeof(T)));       // the callers synchronise once before caller streams may touch the buffers
     *out = (T*)p;
     return RT_OK;
 }
@@ -199,6 +215,7 @@ static int scene_create_impl(const RtSceneDesc* d, RtScene* sc) {
     sc->samples_per_pixel = d->dof_samples * d->aa_samples * d->n_times;
     UP(upload(sc, (const unsigned long long*)nullptr, (size_t)d->max_depth + 2, &sc->d_qcount));
     UP(upload(sc, (const RtCounters*)nullptr, RT_COUNTER_CLASSES, &sc->d_counters));
+    CU(cudaDeviceSynchronize());     // the memsets above ran on the legacy stream; later kernels run on caller streams
     return RT_OK;
 }
 
@@ -214,6 +231,7 @@ extern "C" int rt_scene_destroy(RtScene* sc) {
     if (sc->d_stage) cudaFree(sc->d_stage);
     if (sc->d_stage_u8) cudaFree(sc->d_stage_u8);
     drain_events(sc);
+    for (cudaEvent_t e : sc->ev_pool) cudaEventDestroy(e);
     delete sc;
     return RT_OK;
 }
@@ -240,20 +258,23 @@ static int build_mesh_bvh(RtScene* sc, int mi, cudaStream_t st) {
     UP(upload(sc, (const int4*)nullptr, (size_t)n, &b.d_face_vidx));
     UP(upload(sc, (const int*)nullptr, (size_t)n, &b.d_order));
     // temporaries
-    uint64_t *keys[2]; int* vals[2]; unsigned* hist; int2* children; int *parent_node, *parent_leaf; unsigned *arrive, *even, *remap;
+    uint64_t *keys[2]; int* vals[2]; unsigned *hist, *scratch; int2* children; int *parent_node, *parent_leaf; unsigned *arrive, *even, *remap;
     float4 *leaf_lo, *leaf_hi, *node_lo, *node_hi;
     const int n_tiles = (n + RS_TILE - 1) / RS_TILE;
     std::vector<void*> tmp;
     auto talloc = [&](void** p, size_t bytes) { cudaError_t e = cudaMalloc(p, std::max<size_t>(bytes, 16)); if (e == cudaSuccess) tmp.push_back(*p); return e; };
     auto tfree = [&]() { for (void* p : tmp) cudaFree(p); };
 #define TA(ptr, bytes) do { cudaError_t e_ = talloc((void**)&(ptr), (bytes)); if (e_ != cudaSuccess) { tfree(); return fail(RT_ERR_NOMEM, cudaGetErrorString(e_)); } } while (0)
+    // every CUDA call of the build is checked: the first failure frees the temporaries and is reported with its call site
+#define TC(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { tfree(); return fail(RT_ERR_CUDA, std::string("LBVH build: " #expr ": ") + cudaGetErrorString(e_)); } } while (0)
     TA(keys[0], sizeof(uint64_t) * n); TA(keys[1], sizeof(uint64_t) * n);
     TA(vals[0], sizeof(int) * n); TA(vals[1], sizeof(int) * n);
     TA(hist, sizeof(unsigned) * 256 * n_tiles);
+    TA(scratch, sizeof(unsigned) * scan_scratch_elems(std::max<long long>(256ll * n_tiles, n)));
     TA(children, sizeof(int2) * n); TA(parent_node, sizeof(int) * n); TA(parent_leaf, sizeof(int) * n);
     TA(arrive, sizeof(unsigned) * n); TA(even, sizeof(unsigned) * n); TA(remap, sizeof(unsigned) * n);
     TA(leaf_lo, sizeof(float4) * n); TA(leaf_hi, sizeof(float4) * n); TA(node_lo, sizeof(float4) * n); TA(node_hi, sizeof(float4) * n);
-#undef TA
+    TC(cudaDeviceSynchronize());                     // the zero-fills of upload() ran on the legacy stream
     float3 ext = b.hi - b.lo;
     float3 inv_ext = f3(ext.x > 0 ? 1.0f / ext.x : 0.0f, ext.y > 0 ? 1.0f / ext.y : 0.0f, ext.z > 0 ? 1.0f / ext.z : 0.0f);
     const int T = 256, G = (n + T - 1) / T;
@@ -262,56 +283,84 @@ static int build_mesh_bvh(RtScene* sc, int mi, cudaStream_t st) {
     for (int pass = 0; pass < 8; pass++) {           // 63-bit keys: 8 digits of 8 bits, least significant first
         const int shift = pass * 8;
         k_rs_hist<<<n_tiles, RS_THREADS, 0, st>>>(keys[cur], n, shift, n_tiles, hist);
-        k_rs_scan<<<1, 1024, 0, st>>>(hist, 256 * n_tiles);
+        exclusive_scan_u32(hist, 256 * n_tiles, scratch, st);
         k_rs_scatter<<<n_tiles, RS_THREADS, 0, st>>>(keys[cur], vals[cur], n, shift, n_tiles, hist, keys[cur ^ 1], vals[cur ^ 1]);
         cur ^= 1;
     }
-    cudaMemcpyAsync(b.d_order, vals[cur], sizeof(int) * n, cudaMemcpyDeviceToDevice, st);
-    cudaMemsetAsync(arrive, 0, sizeof(unsigned) * n, st);
+    TC(cudaGetLastError());
+    TC(cudaMemcpyAsync(b.d_order, vals[cur], sizeof(int) * n, cudaMemcpyDeviceToDevice, st));
+    TC(cudaMemsetAsync(arrive, 0, sizeof(unsigned) * n, st));
     if (n >= 2) k_lbvh_hierarchy<<<G, T, 0, st>>>(keys[cur], n, children, parent_node, parent_leaf);
     k_lbvh_leaves_refit<<<G, T, 0, st>>>(b.d_verts, b.d_faces, vals[cur], n, children, parent_node, parent_leaf, b.d_tri, b.d_face_vidx,
                                         leaf_lo, leaf_hi, node_lo, node_hi, arrive);
-    // 4-wide collapse: even-depth nodes survive; exclusive scan of the flags = compact, deterministic node indices
-    cudaError_t e = cudaSuccess;
+    TC(cudaGetLastError());
+    // 4-wide collapse: which binary nodes survive as traversal nodes; exclusive scan of the flags = compact, deterministic node indices
     b.n_nodes4 = 0;
     if (n >= 2) {
-        // which binary nodes become 4-wide nodes: rounds of top-down marking from the root (arrive[] is free again: reused
-        // as the marks), a host look at the "changed" flag every 8 rounds
+        // rounds of top-down marking from the root (arrive[] is free again: reused as the marks), a host look at the
+        // "changed" flag every 8 rounds
         unsigned* mark = arrive;
         unsigned* d_changed = (unsigned*)hist;
         const unsigned one = 1u;
-        cudaMemsetAsync(mark, 0, sizeof(unsigned) * n, st);
-        cudaMemcpyAsync(mark, &one, sizeof(unsigned), cudaMemcpyHostToDevice, st);
+        TC(cudaMemsetAsync(mark, 0, sizeof(unsigned) * n, st));
+        TC(cudaMemcpyAsync(mark, &one, sizeof(unsigned), cudaMemcpyHostToDevice, st));
         for (unsigned round = 1, go = 1; go && round < 4096; ) {
-            cudaMemsetAsync(d_changed, 0, sizeof(unsigned), st);
+            TC(cudaMemsetAsync(d_changed, 0, sizeof(unsigned), st));
             for (int k = 0; k < 8; k++, round++) k_lbvh_mark<<<G, T, 0, st>>>(n, children, node_lo, node_hi, mark, round, d_changed);
-            if (cudaMemcpyAsync(&go, d_changed, sizeof(unsigned), cudaMemcpyDeviceToHost, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) break;
+            TC(cudaMemcpyAsync(&go, d_changed, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+            TC(cudaStreamSynchronize(st));
         }
         k_lbvh_flags<<<G, T, 0, st>>>(n, mark, even, remap);
-        k_rs_scan<<<1, 1024, 0, st>>>(remap, n - 1);
+        exclusive_scan_u32(remap, n - 1, scratch, st);
         unsigned last_idx = 0, last_even = 0;
-        e = cudaMemcpyAsync(&last_idx, remap + (n - 2), sizeof(unsigned), cudaMemcpyDeviceToHost, st);
-        if (e == cudaSuccess) e = cudaMemcpyAsync(&last_even, even + (n - 2), sizeof(unsigned), cudaMemcpyDeviceToHost, st);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-        if (e == cudaSuccess) {
-            b.n_nodes4 = (int)(last_idx + last_even);
-            int rc = upload(sc, (const BvhNode4*)nullptr, (size_t)std::max(1, b.n_nodes4), &b.d_nodes);
-            if (rc != RT_OK) { tfree(); return rc; }
-            k_lbvh_emit4<<<G, T, 0, st>>>(n, children, even, remap, leaf_lo, leaf_hi, node_lo, node_hi, b.pad, b.d_nodes);
-        }
+        TC(cudaMemcpyAsync(&last_idx, remap + (n - 2), sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+        TC(cudaMemcpyAsync(&last_even, even + (n - 2), sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+        TC(cudaStreamSynchronize(st));
+        b.n_nodes4 = (int)(last_idx + last_even);
+        int rc = upload(sc, (const BvhNode4*)nullptr, (size_t)std::max(1, b.n_nodes4), &b.d_nodes);
+        if (rc != RT_OK) { tfree(); return rc; }
+        TC(cudaDeviceSynchronize());
+        k_lbvh_emit4<<<G, T, 0, st>>>(n, children, even, remap, leaf_lo, leaf_hi, node_lo, node_hi, b.pad, b.d_nodes);
     }
-    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-    if (e == cudaSuccess) e = cudaGetLastError();
+    TC(cudaStreamSynchronize(st));
+    TC(cudaGetLastError());
+#undef TA
+#undef TC
     tfree();
-    if (e != cudaSuccess) return fail(RT_ERR_CUDA, std::string("LBVH build: ") + cudaGetErrorString(e));
     g.tri = b.d_tri; g.nodes = n >= 2 ? b.d_nodes : nullptr; g.face_vidx = b.d_face_vidx;
     b.built = true;
     return RT_OK;
 }
 
+// Developer experiment (B200RT_L2_PERSIST=<MiB>): pin the largest mesh's traversal nodes in a persisting L2 carve-out so the
+// per-ray record streams cannot evict them (B200: 126 MB L2).
+static void l2_persist_nodes(RtScene* sc, cudaStream_t st) {
+    static const char* env = getenv("B200RT_L2_PERSIST");
+    if (!env || sc->meshes.empty()) return;
+    const size_t want = (size_t)atoi(env) << 20;
+    const MeshBuild* big = nullptr;
+    for (const MeshBuild& b : sc->meshes) if (b.d_nodes && (!big || b.n_nodes4 > big->n_nodes4)) big = &b;
+    if (!big || want == 0) return;
+    int max_persist = 0, max_window = 0;
+    cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, sc->device);
+    cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, sc->device);
+    const size_t carve = std::min(want, (size_t)max_persist);
+    if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, carve) != cudaSuccess) { cudaGetLastError(); return; }
+    cudaStreamAttrValue av{};
+    const size_t bytes = std::min((size_t)big->n_nodes4 * sizeof(BvhNode4), (size_t)max_window);
+    av.accessPolicyWindow.base_ptr = (void*)big->d_nodes;
+    av.accessPolicyWindow.num_bytes = bytes;
+    av.accessPolicyWindow.hitRatio = bytes > carve ? (float)carve / (float)bytes : 1.0f;
+    av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+    av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    if (cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &av) != cudaSuccess) cudaGetLastError();
+    fprintf(stderr, "b200rt: L2 persisting window %zu MB over %zu MB of nodes (carve-out %zu MB, max %d MB)\n", bytes >> 20,
+            ((size_t)big->n_nodes4 * sizeof(BvhNode4)) >> 20, carve >> 20, max_persist >> 20);
+}
+
 extern "C" int rt_scene_build_bvh(RtScene* sc, void* stream) {
     if (!sc) return fail(RT_ERR_INVALID, "null scene");
-    CU(cudaSetDevice(sc->device));
+    DeviceGuard dg(sc->device);
     for (size_t i = 0; i < sc->meshes.size(); i++)
         if (!sc->meshes[i].built) UP(build_mesh_bvh(sc, (int)i, (cudaStream_t)stream));
     if (!sc->h_meshes.empty())
@@ -432,11 +481,11 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
         RayQueue q0{sc->d_queue[0], sc->queue_cap}, q1{sc->d_queue[1], sc->queue_cap};
         const long long need = (n_rays + RT_BLOCK - 1) / RT_BLOCK;
         {   // level 0: generated rays
-            { ProfScope ps_(sc, 0, st);
+            { ProfScope ps_(sc, PC_HIT0, st);
               k_hit<HAS_NODES, true><<<(int)std::min<long long>(need, g_hit0), RT_BLOCK, smem, st>>>(V, pmk, p0, n_rays, q0, nullptr, H, sc->d_counters + 0); }
-            if (V.n_lights > 0) { ProfScope ps_(sc, 1, st);
+            if (V.n_lights > 0) { ProfScope ps_(sc, PC_SHADOW0, st);
               k_shadow<HAS_NODES, false><<<(int)std::min<long long>(need, g_shadow0), RT_BLOCK, smem, st>>>(V, n_rays, nullptr, H, sc->d_occ, sc->d_counters + 1); (*launches)++; }
-            { ProfScope ps_(sc, 2, st);
+            { ProfScope ps_(sc, PC_SHADE0, st);
               k_shade<true><<<(int)std::min<long long>(need, g_shade0), RT_BLOCK, 0, st>>>(V, n_rays, q0, nullptr, H, sc->d_occ, sc->d_samples, q0, sc->d_qcount, sc->d_counters + 2); }
             (*launches) += 2;
         }
@@ -446,20 +495,23 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
                 RayQueue& qin = (level & 1) ? q0 : q1;
                 RayQueue& qout = (level & 1) ? q1 : q0;
                 const unsigned long long* n_in = sc->d_qcount + (level - 1);
-                ProfScope ps_(sc, 3, st);
                 if (tail_level > 0 && level >= tail_level) {          // the small remainder: every path to its end in one launch
+                    ProfScope ps_(sc, PC_TAIL, st);
                     k_tail<HAS_NODES><<<g_tail, RT_BLOCK, smem, st>>>(V, qin, n_in, sc->d_samples, sc->d_counters + 3);
                     (*launches)++;
                     break;
                 }
-                k_hit<HAS_NODES, false><<<g_hit, RT_BLOCK, smem, st>>>(V, pmk, 0, 0, qin, n_in, H, sc->d_counters + 3);
-                if (V.n_lights > 0) { k_shadow<HAS_NODES, true><<<dim3((unsigned)std::max(1, g_shadow / V.n_lights), (unsigned)V.n_lights), RT_BLOCK, smem, st>>>(V, 0, n_in, H, sc->d_occ, sc->d_counters + 3); (*launches)++; }
-                k_shade<false><<<g_shade, RT_BLOCK, 0, st>>>(V, 0, qin, n_in, H, sc->d_occ, sc->d_samples, qout, sc->d_qcount + level, sc->d_counters + 3);
+                { ProfScope ps_(sc, level == 1 ? PC_HIT1 : PC_DEEP, st);
+                  k_hit<HAS_NODES, false><<<g_hit, RT_BLOCK, smem, st>>>(V, pmk, 0, 0, qin, n_in, H, sc->d_counters + 3); }
+                if (V.n_lights > 0) { ProfScope ps_(sc, level == 1 ? PC_SHADOW1 : PC_DEEP, st);
+                  k_shadow<HAS_NODES, true><<<dim3((unsigned)std::max(1, g_shadow / V.n_lights), (unsigned)V.n_lights), RT_BLOCK, smem, st>>>(V, 0, n_in, H, sc->d_occ, sc->d_counters + 3); (*launches)++; }
+                { ProfScope ps_(sc, level == 1 ? PC_SHADE1 : PC_DEEP, st);
+                  k_shade<false><<<g_shade, RT_BLOCK, 0, st>>>(V, 0, qin, n_in, H, sc->d_occ, sc->d_samples, qout, sc->d_qcount + level, sc->d_counters + 3); }
                 (*launches) += 2;
             }
         }
         {
-            ProfScope ps_(sc, 4, st);
+            ProfScope ps_(sc, PC_RESOLVE, st);
             k_resolve<<<(int)((npx + 127) / 128), 128, 0, st>>>(pm, p0, (int)npx, N, sc->d_samples, d_out, direct);
         }
         (*launches)++;
@@ -473,8 +525,12 @@ extern "C" int rt_render(RtScene* sc, const RtRenderJob* job, float* d_out, RtCo
     for (auto& m : sc->meshes) if (!m.built) return fail(RT_ERR_INVALID, "rt_scene_build_bvh has not been called");
     PixelMap pm; long long nt;
     UP(make_pixel_map(job, pm, nt));
+    // the sampling tables (col_x[W], row_y[H]) are indexed by absolute pixel coordinates: the job must stay inside the frame
+    if (job->col0 < 0 || job->row0 < 0 || (long long)job->col0 + job->ncols > sc->view.width || (long long)job->row0 + job->nrows > sc->view.height)
+        return fail(RT_ERR_INVALID, "RtRenderJob rectangle leaves the frame [0,width) x [0,height)");
     cudaStream_t st = (cudaStream_t)stream;
-    CU(cudaSetDevice(sc->device));
+    DeviceGuard dg(sc->device);
+    if (!sc->l2_window_tried) { sc->l2_window_tried = true; l2_persist_nodes(sc, st); }
     CU(cudaMemsetAsync(sc->d_counters, 0, RT_COUNTER_CLASSES * sizeof(RtCounters), st));
     unsigned long long launches = 0;
     int rc = sc->has_nodes ? render_impl<true>(sc, job, pm, d_out, st, &launches) : render_impl<false>(sc, job, pm, d_out, st, &launches);
@@ -565,7 +621,7 @@ extern "C" int rt_trace_rays(RtScene* sc, int64_t n, const float* h_org, const f
     if (!sc || n < 0) return fail(RT_ERR_INVALID, "bad argument");
     for (auto& m : sc->meshes) if (!m.built) return fail(RT_ERR_INVALID, "rt_scene_build_bvh has not been called");
     if (n == 0) return RT_OK;
-    CU(cudaSetDevice(sc->device));
+    DeviceGuard dg(sc->device);
     cudaStream_t st = (cudaStream_t)stream;
     DevTmp tmp;
     float *org, *dir, *times, *rgb, *t, *nn, *pp; int *geom, *mat;
@@ -599,7 +655,7 @@ extern "C" int rt_occluded(RtScene* sc, int64_t n, const float* h_org, const flo
     if (!sc || n < 0) return fail(RT_ERR_INVALID, "bad argument");
     for (auto& m : sc->meshes) if (!m.built) return fail(RT_ERR_INVALID, "rt_scene_build_bvh has not been called");
     if (n == 0) return RT_OK;
-    CU(cudaSetDevice(sc->device));
+    DeviceGuard dg(sc->device);
     cudaStream_t st = (cudaStream_t)stream;
     DevTmp tmp;
     float *org, *dir, *times, *tmax; int* occ;
@@ -629,7 +685,7 @@ static void drain_events(RtScene* sc) {
             cudaEventSynchronize(pr.second);
             float ms = 0.0f;
             if (cudaEventElapsedTime(&ms, pr.first, pr.second) == cudaSuccess) { sc->prof_ms[c] += ms; sc->prof_n[c]++; }
-            cudaEventDestroy(pr.first); cudaEventDestroy(pr.second);
+            sc->ev_pool.push_back(pr.first); sc->ev_pool.push_back(pr.second);
         }
         sc->ev[c].clear();
     }
@@ -646,13 +702,68 @@ extern "C" int rt_scene_profile(RtScene* sc, int32_t enable) {
 extern "C" int rt_scene_profile_read(RtScene* sc, RtProfile* out) {
     if (!sc || !out) return fail(RT_ERR_INVALID, "null argument");
     drain_events(sc);
-    out->ms_hit = sc->prof_ms[0]; out->ms_shadow = sc->prof_ms[1]; out->ms_shade = sc->prof_ms[2];
-    out->ms_secondary = sc->prof_ms[3]; out->ms_resolve = sc->prof_ms[4];
-    out->n_hit = sc->prof_n[0]; out->n_shadow = sc->prof_n[1]; out->n_shade = sc->prof_n[2];
-    out->n_secondary = sc->prof_n[3]; out->n_resolve = sc->prof_n[4];
+    const double* ms = sc->prof_ms; const unsigned long long* nn = sc->prof_n;
+    out->ms_hit = ms[PC_HIT0]; out->ms_shadow = ms[PC_SHADOW0]; out->ms_shade = ms[PC_SHADE0]; out->ms_resolve = ms[PC_RESOLVE];
+    out->ms_secondary = ms[PC_HIT1] + ms[PC_SHADOW1] + ms[PC_SHADE1] + ms[PC_DEEP] + ms[PC_TAIL];
+    out->n_hit = nn[PC_HIT0]; out->n_shadow = nn[PC_SHADOW0]; out->n_shade = nn[PC_SHADE0]; out->n_resolve = nn[PC_RESOLVE];
+    out->n_secondary = nn[PC_HIT1] + nn[PC_SHADOW1] + nn[PC_SHADE1] + nn[PC_DEEP] + nn[PC_TAIL];
+    out->ms_l1_hit = ms[PC_HIT1]; out->ms_l1_shadow = ms[PC_SHADOW1]; out->ms_l1_shade = ms[PC_SHADE1];
+    out->ms_deep = ms[PC_DEEP]; out->ms_tail = ms[PC_TAIL];
+    out->n_l1_hit = nn[PC_HIT1]; out->n_deep = nn[PC_DEEP]; out->n_tail = nn[PC_TAIL];
     RtCounters cls[RT_COUNTER_CLASSES];
     CU(cudaMemcpy(cls, sc->d_counters, sizeof cls, cudaMemcpyDeviceToHost));
     out->hit = cls[0]; out->shadow = cls[1]; out->shade = cls[2]; out->secondary = cls[3];
+    return RT_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Roofline denominators measured on the current device (rt_peaks.cuh)
+extern "C" int rt_measure_peaks(RtPeaks* out, void* stream) {
+    if (!out) return fail(RT_ERR_INVALID, "null argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    int dev = 0, sms = 0, khz = 0;
+    CU(cudaGetDevice(&dev));
+    CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    CU(cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev));
+    float* d_out = nullptr; float4* d_table = nullptr;
+    CU(cudaMalloc((void**)&d_out, 16));
+    CU(cudaMalloc((void**)&d_table, PK_LSU_TABLE_BYTES));
+    CU(cudaMemset(d_table, 0, PK_LSU_TABLE_BYTES));
+    CU(cudaDeviceSynchronize());
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
+    const int grid = sms * PK_BLOCKS_PER_SM;
+    const double threads = (double)grid * PK_BLOCK, warps = threads / 32.0;
+    auto timed = [&](int which, int trips, float* ms_out) -> cudaError_t {
+        float best = 1e30f;
+        for (int rep = 0; rep < 4; rep++) {                    // rep 0 warms up (clocks, instruction cache); best of the other three
+            cudaEventRecord(e0, st);
+            if (which == 0) k_peak_fma<<<grid, PK_BLOCK, 0, st>>>(d_out, trips, 1.0000001f, 1e-9f);
+            else if (which == 1) k_peak_issue<<<grid, PK_BLOCK, 0, st>>>(d_out, trips, 1.0000001f, 1e-9f, 0x9e3779b9u);
+            else k_peak_lsu<<<grid, PK_BLOCK, 0, st>>>(d_table, d_out, trips);
+            cudaEventRecord(e1, st);
+            cudaError_t e = cudaEventSynchronize(e1);
+            if (e != cudaSuccess) return e;
+            float ms = 0.0f; cudaEventElapsedTime(&ms, e0, e1);
+            if (rep > 0 && ms < best) best = ms;
+        }
+        *ms_out = best;
+        return cudaGetLastError();
+    };
+    float ms_fma = 0, ms_issue = 0, ms_lsu = 0;
+    const int trips_fma = 4096, trips_issue = 4096, trips_lsu = 4096;
+    cudaError_t e = timed(0, trips_fma, &ms_fma);
+    if (e == cudaSuccess) e = timed(1, trips_issue, &ms_issue);
+    if (e == cudaSuccess) e = timed(2, trips_lsu, &ms_lsu);
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d_out); cudaFree(d_table);
+    if (e != cudaSuccess) return fail(RT_ERR_CUDA, std::string("rt_measure_peaks: ") + cudaGetErrorString(e));
+    out->fp32_fma_tflops = threads * trips_fma * (double)PK_FMA_PER_TRIP * 2.0 / (ms_fma * 1e-3) / 1e12;
+    out->issue_ginst = warps * trips_issue * (double)PK_INST_PER_TRIP / (ms_issue * 1e-3) / 1e9;
+    out->lsu_gwavefronts = warps * trips_lsu * (double)PK_LOADS_PER_TRIP * 4.0 / (ms_lsu * 1e-3) / 1e9;
+    out->sm_count = sms; out->sm_clock_mhz = khz / 1000.0;
+    out->fp32_fma_tflops_nominal = sms * 128.0 * 2.0 * (khz * 1e3) / 1e12;          // 128 FP32 lanes per SM, FMA = 2 flops
+    out->issue_ginst_nominal = sms * 4.0 * (khz * 1e3) / 1e9;                        // 4 schedulers per SM, 1 warp instruction per cycle
+    out->lsu_gwavefronts_nominal = sms * 1.0 * (khz * 1e3) / 1e9;                    // one 128-byte wavefront per cycle per SM
     return RT_OK;
 }
 
@@ -721,13 +832,14 @@ extern "C" int rt_mesh_ingest(int32_t n_verts, const double* h_raw_verts, int32_
     TC(cudaMemcpyAsync(ext + 6, d_ext + 6, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
     if (want_normals) {
         const int n_pairs = 3 * n_faces;
-        int* d_faces; float4* d_weighted; float* d_vn; uint64_t* keys[2]; int* vals[2]; unsigned* hist;
+        int* d_faces; float4* d_weighted; float* d_vn; uint64_t* keys[2]; int* vals[2]; unsigned *hist, *scratch;
         const int n_tiles = std::max(1, (n_pairs + RS_TILE - 1) / RS_TILE);
         TA(d_faces, sizeof(int) * (size_t)std::max(1, n_pairs)); TA(d_weighted, sizeof(float4) * (size_t)std::max(1, n_faces));
         TA(d_vn, sizeof(float) * 3 * (size_t)n_verts);
         TA(keys[0], sizeof(uint64_t) * (size_t)std::max(1, n_pairs)); TA(keys[1], sizeof(uint64_t) * (size_t)std::max(1, n_pairs));
         TA(vals[0], sizeof(int) * (size_t)std::max(1, n_pairs)); TA(vals[1], sizeof(int) * (size_t)std::max(1, n_pairs));
         TA(hist, sizeof(unsigned) * 256 * (size_t)n_tiles);
+        TA(scratch, sizeof(unsigned) * scan_scratch_elems(256ll * n_tiles));
         int cur = 0;
         if (n_faces > 0) {
             TC(cudaMemcpyAsync(d_faces, h_faces, sizeof(int) * (size_t)n_pairs, cudaMemcpyHostToDevice, st));
@@ -736,7 +848,7 @@ extern "C" int rt_mesh_ingest(int32_t n_verts, const double* h_raw_verts, int32_
             while (bits < 32 && (1u << bits) < (unsigned)n_verts) bits++;
             for (int shift = 0; shift < bits; shift += 8) {          // stable LSD passes over the digits a vertex index can occupy
                 k_rs_hist<<<n_tiles, RS_THREADS, 0, st>>>(keys[cur], n_pairs, shift, n_tiles, hist);
-                k_rs_scan<<<1, 1024, 0, st>>>(hist, 256 * n_tiles);
+                exclusive_scan_u32(hist, 256 * n_tiles, scratch, st);
                 k_rs_scatter<<<n_tiles, RS_THREADS, 0, st>>>(keys[cur], vals[cur], n_pairs, shift, n_tiles, hist, keys[cur ^ 1], vals[cur ^ 1]);
                 cur ^= 1;
             }

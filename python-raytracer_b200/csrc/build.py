@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, "libb200rt.so")
 SRCS = ["b200rt.cu"]
-DEPS = ["b200rt.cu", "rt_kernels.cuh", "rt_core.cuh", "rt_bvh.cuh", "rt_ingest.cuh", "rt_obj.hpp", "rt_types.cuh", "rt_math.cuh", "../../include/b200rt.h"]
+DEPS = sorted(f for f in os.listdir(HERE) if f.endswith((".cu", ".cuh", ".hpp", ".h"))) + ["../../include/b200rt.h"]      # every source the library includes
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-shared",
          "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr"]
 

@@ -32,6 +32,17 @@
 #define RT_MIN_BLOCKS_SHADE 8
 #endif
 
+// The per-ray wavefront records (hit planes, occlusion flags, samples, queue entries) are written once and read once, tens of
+// GB per frame, next to a ~100 MB BVH that every ray re-reads: with RT_STREAM_RECORDS they are accessed with the streaming
+// (evict-first) cache hints so they do not push BVH lines out of L1/L2.
+#ifdef RT_STREAM_RECORDS
+#define RT_ST_REC(ptr, val) __stcs((ptr), (val))
+#define RT_LD_REC(ptr) __ldcs(ptr)
+#else
+#define RT_ST_REC(ptr, val) (*(ptr) = (val))
+#define RT_LD_REC(ptr) (*(ptr))
+#endif
+
 // Compacted ray queue, SoA of float4 planes (coalesced 128-bit accesses):
 //   plane 0: origin.xyz, time           plane 1: dir.xyz, bits(sample slot)
 //   plane 2: fold.a.xyz, fold.w         plane 3: fold.lo.xyz, bits(depth_left | in_shape << 8)
@@ -147,11 +158,11 @@ __global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_HIT_CSG : 
             live = closest_hit<HAS_NODES>(cx, ray, hit);
         }
         if (live) {
-            H.planes[0 * H.cap + i] = f4(hit.p.x, hit.p.y, hit.p.z, time);
-            H.planes[1 * H.cap + i] = f4(hit.n.x, hit.n.y, hit.n.z, as_float(hit.mat));
-            H.planes[2 * H.cap + i] = f4(ray.d.x, ray.d.y, ray.d.z, as_float(hit.geom));
+            RT_ST_REC(&H.planes[0 * H.cap + i], f4(hit.p.x, hit.p.y, hit.p.z, time));
+            RT_ST_REC(&H.planes[1 * H.cap + i], f4(hit.n.x, hit.n.y, hit.n.z, as_float(hit.mat)));
+            RT_ST_REC(&H.planes[2 * H.cap + i], f4(ray.d.x, ray.d.y, ray.d.z, as_float(hit.geom)));
         } else {
-            H.planes[0 * H.cap + i] = f4(0.0f, 0.0f, 0.0f, as_float(0x7fc00000));
+            RT_ST_REC(&H.planes[0 * H.cap + i], f4(0.0f, 0.0f, 0.0f, as_float(0x7fc00000)));
         }
     }
     tally_flush(tally, n_primary, 0, counters);
@@ -171,11 +182,11 @@ __global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_SHADOW_CSG
     const long long stride = (long long)gridDim.x * blockDim.x;
     const int li0 = LIGHT_ROWS ? (int)blockIdx.y : 0, li1 = LIGHT_ROWS ? li0 + 1 : S.n_lights;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const float4 h0 = H.planes[0 * H.cap + i];
+        const float4 h0 = RT_LD_REC(&H.planes[0 * H.cap + i]);
         if (h0.w != h0.w) continue;                                       // no hit: no shadow rays
         TraceCtx cx{S, h0.w, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill};
         for (int li = li0; li < li1; li++)                                // the lanes of a warp still work on ONE light at a time
-            occ[(long long)li * H.cap + i] = light_occluded<HAS_NODES>(cx, f3(h0), li) ? 1 : 0;
+            RT_ST_REC(&occ[(long long)li * H.cap + i], (uint8_t)(light_occluded<HAS_NODES>(cx, f3(h0), li) ? 1 : 0));
     }
     tally_flush(tally, 0, 0, counters);
 }
@@ -197,10 +208,10 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS_SHADE) k_shade(SceneVi
             if (PRIMARY) { ps.fold = fold_identity(); ps.depth_left = S.max_depth; ps.in_shape = 0; ps.ray.o = f3(0, 0, 0); }
             else queue_load(qin, i, ps, time, slot);
             // every load of this ray issued up front (the kernel is latency-bound: hit planes + one flag byte per light)
-            const float4 h0 = H.planes[0 * H.cap + i], h1 = H.planes[1 * H.cap + i], h2 = H.planes[2 * H.cap + i];
+            const float4 h0 = RT_LD_REC(&H.planes[0 * H.cap + i]), h1 = RT_LD_REC(&H.planes[1 * H.cap + i]), h2 = RT_LD_REC(&H.planes[2 * H.cap + i]);
             unsigned lit_mask = 0;
             const int n_pre = S.n_lights < 32 ? S.n_lights : 32;
-            for (int li = 0; li < n_pre; li++) lit_mask |= (occ[(long long)li * H.cap + i] == 0 ? 1u : 0u) << li;
+            for (int li = 0; li < n_pre; li++) lit_mask |= (RT_LD_REC(&occ[(long long)li * H.cap + i]) == 0 ? 1u : 0u) << li;
             float3 sample;
             if (h0.w != h0.w) sample = fold_eval(ps.fold, f3(0, 0, 0));          // miss: cast_ray returns black (scene.py:91-92)
             else {
@@ -210,7 +221,7 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS_SHADE) k_shade(SceneVi
                 TraceCtx cx{S, time, tally, nullptr, 0, nullptr};
                 cont = shade_level(cx, ps, hit, [&](int li) { return li < 32 ? ((lit_mask >> li) & 1u) != 0 : occ[(long long)li * H.cap + i] == 0; }, sample);
             }
-            if (!cont) samples[slot] = f4(sample.x, sample.y, sample.z, 0.0f);
+            if (!cont) RT_ST_REC(&samples[slot], f4(sample.x, sample.y, sample.z, 0.0f));
         }
         long long qi = queue_reserve(qout_count, cont);
         if (cont) { queue_store(qout, qi, ps, time, slot); n_queued++; }
@@ -257,7 +268,7 @@ __global__ void k_resolve(PixelMap pm, long long pixel_begin, int n_pixels, int 
     float3 c = f3(0, 0, 0);
     if (valid) {
         const float4* sp = samples + (long long)p * N;
-        for (int k = 0; k < N; k++) { float4 v = sp[k]; c = c + f3(v); }
+        for (int k = 0; k < N; k++) { float4 v = RT_LD_REC(&sp[k]); c = c + f3(v); }
         const float n = (float)N;
         c = f3(c.x / n, c.y / n, c.z / n);
     }

@@ -58,6 +58,8 @@ inline float3 min3(float3 a, float3 b) { return f3(fminf(a.x, b.x), fminf(a.y, b
 inline float3 max3(float3 a, float3 b) { return f3(fmaxf(a.x, b.x), fmaxf(a.y, b.y), fmaxf(a.z, b.z)); }
 inline bool finite3(float3 a) { return std::isfinite(a.x) && std::isfinite(a.y) && std::isfinite(a.z); }
 
+inline float half_area(float3 lo, float3 hi) { float3 e = hi - lo; return e.x * e.y + e.y * e.z + e.z * e.x; }
+
 inline ObjBound object_bound(const RtSceneDesc* d, int oi, float tlo, float thi) {
     const RtObject& o = d->objects[oi];
     ObjBound b; b.finite = false; b.lo = f3(INFINITY, INFINITY, INFINITY); b.hi = f3(-INFINITY, -INFINITY, -INFINITY);
@@ -84,15 +86,32 @@ inline ObjBound object_bound(const RtSceneDesc* d, int oi, float tlo, float thi)
         }
         case RT_KIND_NODE: {                                   // hierarchy.py:42-78: hits of the children, mapped by M
             const int c0 = o.first_child, nc = o.n_children;
-            int use = 0;
-            if (o.csg == RT_CSG_UNION || o.csg == RT_CSG_INTERSECTION) use = nc;
-            else if (o.csg == RT_CSG_DIFFERENCE && nc >= 2) use = 1;   // A-hits, and B-hits inside A (is_inside(A) => within A's bound)
-            if (use == 0) break;
             float3 lo = b.lo, hi = b.hi;
-            for (int k = 0; k < use; k++) {
-                ObjBound cb = object_bound(d, c0 + k, tlo, thi);
-                if (!cb.finite) return b;
-                lo = min3(lo, cb.lo); hi = max3(hi, cb.hi);
+            if (o.csg == RT_CSG_INTERSECTION) {
+                // hierarchy.py:52-57: a hit of child k is kept iff every OTHER child contains it, so every kept hit lies on child
+                // k's surface and inside every other child: within the bound of EACH child.  hierarchy.py:87-93: the node shadows
+                // iff ALL children do, so a shadowing ray touches each child's bound (not necessarily at one common point: the
+                // intersection of the bounds would be wrong there).  Any ONE finite child bound is therefore valid for both
+                // queries; the smallest is taken, and unbounded children (planes) do not make the node unbounded:
+                // `intersection(plane, box)` - the walls of scenes/NovelScene1.json:83-160 - is bounded by its box.
+                float best = INFINITY; bool any = false;
+                for (int k = 0; k < nc; k++) {
+                    ObjBound cb = object_bound(d, c0 + k, tlo, thi);
+                    if (!cb.finite) continue;
+                    const float a = half_area(cb.lo, cb.hi);
+                    if (!any || a < best) { best = a; lo = cb.lo; hi = cb.hi; any = true; }
+                }
+                if (!any) break;                                   // also nc == 0: all([]) hits nothing that has an extent
+            } else {
+                int use = 0;
+                if (o.csg == RT_CSG_UNION) use = nc;
+                else if (o.csg == RT_CSG_DIFFERENCE && nc >= 2) use = 1;   // A-hits, and B-hits inside A (is_inside(A) => within A's bound)
+                if (use == 0) break;
+                for (int k = 0; k < use; k++) {
+                    ObjBound cb = object_bound(d, c0 + k, tlo, thi);
+                    if (!cb.finite) return b;
+                    lo = min3(lo, cb.lo); hi = max3(hi, cb.hi);
+                }
             }
             const float* M = d->xforms[o.xform].M;
             for (int c = 0; c < 8; c++) {
@@ -109,7 +128,6 @@ inline ObjBound object_bound(const RtSceneDesc* d, int oi, float tlo, float thi)
 }
 
 struct TlasItem { float3 lo, hi; int obj; int flags; };
-inline float half_area(float3 lo, float3 hi) { float3 e = hi - lo; return e.x * e.y + e.y * e.z + e.z * e.x; }
 
 // binary tree under construction (same shape as the GPU LBVH builder's arrays, so the 4-wide collapse is shared)
 struct BinTree {

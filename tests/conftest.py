@@ -85,14 +85,75 @@ ALL_CASES = ["TwoSpheresPlane", "MirrorRefraction", "MotionBlur", "TorusMesh_fla
              "Fuzz1", "Fuzz8", "Fuzz12", "Fuzz18", "Fuzz19"]     # Fuzz<seed>: tests/fuzz_scenes.py rendered by the reference
 
 
-# Fresh random scenes (tests/fuzz_scenes.py) compared with the oracle at test time.  The seeds are SCREENED: the reference's
-# CSG semantics are chaotic on some surfaces (e.g. the exit face of a box seen through a carved hole: Hierarchy.shadow_intersect
-# of a difference goes through AABB.intersect, which returns no hit at all when the un-offset shadow origin lies 1e-7 inside the
-# box and two hits when it lies 1e-7 outside, hierarchy.py:94-107 + simple_geometry.py:223), so there the shadow state is a coin
-# toss in the reference itself and two correct float implementations differ on whole patches.  Seeds whose host-twin render
-# differed from the oracle on more than 3 of 12288 pixels were left out (of 0..149: 10 15 25 26 28 109 121 130 132 134 140 148 149).
+# Fresh random scenes (tests/fuzz_scenes.py) compared with the oracle at test time.
 FUZZ_GPU_SEEDS = [100, 101, 102, 103, 104, 105, 106, 107, 108, 110, 111, 112, 113, 115, 116, 117]
 FUZZ_HOST_SEEDS = [118, 119, 120, 122, 123, 124]
+# Seeds of 0..149 on which a plain >= 99.9 % threshold fails or nearly fails (round 1 left them out): the reference's CSG
+# semantics are chaotic on some surfaces (e.g. the exit face of a box seen through a carved hole: Hierarchy.shadow_intersect of a
+# difference goes through AABB.intersect, which returns no hit at all when the un-offset shadow origin lies 1e-7 inside the box
+# and two hits when it lies 1e-7 outside, hierarchy.py:94-107 + simple_geometry.py:223), so there the shadow state is a coin
+# toss in the reference itself.  They are TESTED, not hidden: `residue_report` below classifies every out-of-tolerance pixel with
+# the oracle's stability probe and the tests require the statistic on the reference-stable pixels.
+FUZZ_CHAOTIC_SEEDS = [10, 15, 25, 26, 28, 109, 121, 130, 132, 134, 140, 148, 149]
+
+
+def u8_cr(image):
+    """(cols, rows, 3) float image -> the uint8 values main.py:33 writes, still indexed [col, row]."""
+    return (np.asarray(image, dtype=np.float64) * 255).astype(np.uint8).astype(int)
+
+
+def residue_report(flat, ref, got, eps=1e-6, trials=6):
+    """WHERE the pixels are that differ from the reference by more than 1/255 (SURVEY 8d "parity statistic", north_star
+    "residue confined to fp32-vs-fp64 edge and refraction pixels").  `ref` = oracle image, `got` = image under test, both
+    (W, H, 3).  Every residue pixel is
+      * `unstable`: the ORACLE's own uint8 value moves by more than 1 when its rays and hit points are perturbed by `eps`
+        relative (a few float32 ulp; oracle.unstable_pixels) - a reference-chaotic pixel;
+      * `edge`: the first sample's (leaf object, material, shadowed-light bits) differs from a 3x3 neighbour's: silhouette,
+        checker / material edge, shadow edge;
+      * `specular`: it or a neighbour sees a mirror / refractive material (reflection and refraction regions);
+    and `unexplained` counts the ones that are none of these.  `frac_stable` is the parity statistic over the
+    reference-stable pixels: 1 - (#residue pixels that are not unstable) / (#pixels)."""
+    import oracle
+    d = np.abs(u8_cr(ref) - u8_cr(got)).max(axis=2)
+    W, H = d.shape
+    bad = np.argwhere(d > 1)
+    rep = {"pixels": int(W * H), "residue": int(len(bad)), "frac": float((d <= 1).mean()), "max_delta": int(d.max()),
+           "unstable": 0, "edge": 0, "specular": 0, "unexplained": 0, "frac_stable": 1.0}
+    if len(bad) == 0:
+        return rep
+    cols, rows = bad[:, 0], bad[:, 1]
+    un = oracle.unstable_pixels(flat, cols, rows, np.asarray(ref)[cols, rows], eps=eps, trials=trials)
+    f0 = oracle.pixel_features(flat, cols, rows)
+    edge, spec = np.zeros(len(bad), bool), f0[:, 3] != 0
+    for dc in (-1, 0, 1):
+        for dr in (-1, 0, 1):
+            f = oracle.pixel_features(flat, np.clip(cols + dc, 0, W - 1), np.clip(rows + dr, 0, H - 1))
+            edge |= (f[:, :3] != f0[:, :3]).any(axis=1)
+            spec |= f[:, 3] != 0
+    rep.update(unstable=int(un.sum()), edge=int(edge.sum()), specular=int(spec.sum()),
+               unexplained=int((~un & ~edge & ~spec).sum()), frac_stable=float(1.0 - (~un).sum() / (W * H)))
+    return rep
+
+
+def unstable_fraction(flat, ref, n=2000, seed=0):
+    """Share of reference-unstable pixels in a random sample of the frame (keeps the probe honest: it must not call
+    everything unstable)."""
+    import oracle
+    W, H = np.asarray(ref).shape[:2]
+    rng = np.random.default_rng(seed)
+    cols, rows = rng.integers(0, W, n), rng.integers(0, H, n)
+    return float(oracle.unstable_pixels(flat, cols, rows, np.asarray(ref)[cols, rows]).mean())
+
+
+def load_bundled(name, overrides=None):
+    """A bundled scene (tests/golden/scenes copy of the reference's scenes/<name>.json) at its SHIPPED settings."""
+    import python_raytracer_b200 as rt
+    rt.scene_parser.VERBOSE = False
+    with open(os.path.join(GOLDEN, "scenes", name + ".json")) as fh:
+        data = _merge(json.load(fh), overrides)
+    sc = rt.scene_parser.load_scene_dict(data, os.path.join(GOLDEN, "scenes"))
+    sc.jitter_seed = 0x5EED
+    return sc
 
 
 def load_fuzz(seed, width=128, height=96):

@@ -11,7 +11,8 @@ import pytest
 
 import oracle
 import python_raytracer_b200 as rt
-from conftest import ALL_CASES, FUZZ_GPU_SEEDS, PARITY_FRACTION, golden_png, load_case, load_fuzz, parity_stats, to_png_array
+from conftest import (ALL_CASES, FUZZ_CHAOTIC_SEEDS, FUZZ_GPU_SEEDS, PARITY_FRACTION, golden_png, load_bundled, load_case, load_fuzz,
+                      parity_stats, residue_report, to_png_array, u8_cr, unstable_fraction)
 
 pytestmark = pytest.mark.gpu
 abi = rt._abi
@@ -300,8 +301,8 @@ def test_config5_full_size_4k_64spp_1m_triangles():
     """BASELINE.json configs[4] at FULL size (3840x2160 x 64 spp, 1 048 576 triangles + 64 spheres: the bench workload),
     through size-independent properties: ray tallies, a sub-rectangle rendered alone == the same pixels of the frame
     (counter-based jitter, tile/batch independence), LBVH + object BVH == the reference's own loops (brute force over
-    every face, in-order object list) on a 16x16-pixel window on the mesh, and 48 random pixels (all 64 samples each)
-    against the brute-force oracle."""
+    every face, in-order object list) on a 16x16-pixel window on the mesh, and 320 pixels (all 64 samples each; 200 of them
+    on the highest-contrast edges of the frame) against the brute-force oracle."""
     from python_raytracer_b200 import synthetic
     sc = synthetic.make_scene(ingest="device")
     W, H = 3840, 2160
@@ -318,13 +319,23 @@ def test_config5_full_size_4k_64spp_1m_triangles():
     brute = sc.render_region(c0, n, r0, n, mesh_mode=3)
     assert sc.last_counters["tri_tests"] >= 1048576 * n * n * 64
     assert np.array_equal(win, brute)
+    # oracle sample (brute force over 1 M faces per ray: ~0.5 s per pixel on 16 cores): 120 uniformly random pixels + 200 drawn
+    # from the 1 % of the frame with the largest local contrast (sphere rims, mesh silhouette, shadow and checker edges, the
+    # reflections in the spheres) - the places where a residue would be.  All 64 samples of each pixel.
+    u8 = u8_cr(img)
+    grad = np.zeros((W, H))
+    grad[1:-1, 1:-1] = np.maximum(np.abs(u8[2:, 1:-1] - u8[:-2, 1:-1]).max(axis=2), np.abs(u8[1:-1, 2:] - u8[1:-1, :-2]).max(axis=2))
     rng = np.random.default_rng(11)
-    cols, rows = rng.integers(0, W, 48), rng.integers(0, H, 48)
+    edge_px = np.argwhere(grad >= np.quantile(grad, 0.99))
+    pick = edge_px[rng.choice(len(edge_px), 200, replace=False)]
+    cols = np.concatenate([rng.integers(0, W, 120), pick[:, 0]])
+    rows = np.concatenate([rng.integers(0, H, 120), pick[:, 1]])
     ref, _ = oracle.render_pixels(sc.flatten(), abi, cols, rows)
-    a = (np.asarray(img[cols, rows], dtype=np.float64) * 255).astype(np.uint8).astype(int)
-    b = (ref * 255).astype(np.uint8).astype(int)
-    bad = int((np.abs(a - b).max(axis=1) > 1).sum())
-    assert bad <= 1, (bad, np.abs(a - b).max())    # 48 pixels cannot resolve a 0.1 % residue: at most one edge pixel may differ
+    a, b = u8_cr(img[cols, rows]), u8_cr(ref)
+    bad = np.abs(a - b).max(axis=1) > 1
+    print(f"config 5 oracle sample: random 120: {int(bad[:120].sum())} off, edge-biased 200: {int(bad[120:].sum())} off, max delta {np.abs(a - b).max()}")
+    assert bad[:120].sum() <= 1, (int(bad[:120].sum()), np.abs(a - b).max())     # uniformly random pixels: the 99.9 % statistic
+    assert bad[120:].sum() <= 4, (int(bad[120:].sum()), np.abs(a - b).max())     # edge pixels only: 98 % of them within 1/255
 
 
 @pytest.mark.parametrize("case,over", [
@@ -346,3 +357,84 @@ def test_config4_1080p_64spp_sampled_parity(case, over):
     b = (ref * 255).astype(np.uint8).astype(int)
     frac = float((np.abs(a - b).max(axis=1) <= 1).mean())
     assert frac >= PARITY_FRACTION, (case, frac)
+
+
+# ---- round 2: parity holes named by the round-1 review -------------------------------------------------------------------
+@pytest.mark.parametrize("name,n_px", [("NovelScene1", 20000), ("NovelScene2", 4000)])
+def test_bundled_csg_scenes_at_shipped_settings(name, n_px):
+    """The two bundled CSG scenes at their SHIPPED settings (scenes/NovelScene1.json:2-3: 2048x1024 x 32 spp, jitter;
+    NovelScene2.json:2-5: 1024x512 x AA 2 x DOF 15 x 16 motion times = 480 samples): nesting depth 6, `ref` copies, textures,
+    inverted boxes, moving CSG.  Full frame on the GPU; parity on random pixels (all samples each) against the oracle."""
+    sc = load_bundled(name)
+    W, H = sc.vc.width, sc.vc.height
+    N = sc.vc.dof_samples * sc.samples * len(sc.vc.motion_times)
+    assert (W, H, N) == ((2048, 1024, 32) if name == "NovelScene1" else (1024, 512, 480))
+    img = sc.render_region(0, W, 0, H)
+    c = dict(sc.last_counters)
+    assert c["rays_primary"] == W * H * N and c["error_flags"] == 0
+    rng = np.random.default_rng(5)
+    cols, rows = rng.integers(0, W, n_px), rng.integers(0, H, n_px)
+    ref, _ = oracle.render_pixels(sc.flatten(), abi, cols, rows)
+    d = np.abs(u8_cr(img[cols, rows]) - u8_cr(ref)).max(axis=1)
+    print(f"{name} shipped: {n_px} pixels, {(d > 1).sum()} off by more than 1/255, max {d.max()}")
+    assert (d <= 1).mean() >= PARITY_FRACTION, (name, (d <= 1).mean(), d.max())
+
+
+@pytest.mark.parametrize("seed", FUZZ_CHAOTIC_SEEDS)
+def test_chaotic_random_scenes_match_on_reference_stable_pixels(seed):
+    """The 13 random scenes round 1 screened out (the reference's CSG-difference shadows are a coin toss on some surfaces,
+    hierarchy.py:94-107 + simple_geometry.py:223; 6 of the 13 miss a plain 99.9 % threshold): every out-of-tolerance pixel is
+    classified with the oracle's stability probe (conftest.residue_report); the statistic over the reference-STABLE pixels
+    must meet the tolerance and no residue pixel may be unexplained."""
+    sc = load_fuzz(seed)
+    fs = sc.flatten()
+    img = sc.render()
+    ref, _ = oracle.render(fs, abi)
+    rep = residue_report(fs, ref, img)
+    print(f"seed {seed}: {rep}")
+    assert rep["frac_stable"] >= PARITY_FRACTION and rep["unexplained"] == 0, rep
+    assert unstable_fraction(fs, ref) <= 0.10      # the probe calls 0.5-6 % of these frames unstable, not everything
+
+
+@pytest.mark.parametrize("case", ALL_CASES)
+def test_residue_lies_on_edges_and_refraction_regions(case):
+    """SURVEY 8d parity statistic: the pixels outside 1/255 are reference-unstable, or on silhouettes / material edges /
+    shadow edges, or in mirror / refraction regions - never in the interior of a diffuse surface."""
+    sc = load_case(case)
+    fs = sc.flatten()
+    img = sc.render()
+    ref, _ = oracle.render(fs, abi)
+    rep = residue_report(fs, ref, img)
+    print(f"{case}: {rep}")
+    assert rep["frac"] >= PARITY_FRACTION and rep["unexplained"] == 0, rep
+
+
+def test_gpu_lbvh_equals_host_restatement_on_a_large_mesh_with_equal_keys(lib):
+    """The GPU build (63-bit Morton keys, 8-pass radix sort over 33 tiles, Karras hierarchy with the index tie-break, atomic
+    refit, 4-wide collapse) against the sequential host restatement on 135 168 triangles of which 4 096 are exact duplicates
+    (equal centroids -> equal Morton keys -> the stable sort and the index tie-break decide) and 128 are degenerate."""
+    import hostsim
+    from python_raytracer_b200 import geometry, synthetic
+    verts, faces = synthetic.displaced_torus(512, 128, 3)
+    assert faces.shape[0] == 131072
+    rng = np.random.default_rng(9)
+    dup = faces[rng.choice(len(faces), 4096, replace=False)]
+    dup[::2] = dup[::2][:, [1, 2, 0]]                                    # same triangle, rotated corner order: same centroid up to rounding
+    degenerate = np.repeat(rng.integers(0, len(verts), (128, 1)), 3, axis=1).astype(faces.dtype)   # zero-area: three times one vertex
+    faces = np.concatenate([faces, dup, degenerate])
+    mesh = geometry.Mesh("m", "mesh", [rt.helperclasses.Material("d", (0, 0, 0), (0.8, 0.8, 0.8), 0, 0)], (0.0, 0.0, 0.0), 1.0,
+                         (verts, faces), True, None)
+    sc = load_case("TorusMesh_flat", {"resolution": [64, 64]})
+    sc.objects[1] = mesh
+    sc.invalidate()
+    h = sc.upload()
+    nodes_ref, order_ref = hostsim.bvh(sc.flatten())
+    n4, nt, nb = C.c_int64(), C.c_int64(), C.c_int64()
+    abi.check(lib, lib.rt_scene_bvh_stats(h, 0, C.byref(n4), C.byref(nt), C.byref(nb)), "rt_scene_bvh_stats")
+    assert nt.value == len(faces) == len(order_ref) and n4.value == len(nodes_ref)
+    nodes = np.zeros_like(nodes_ref); order = np.zeros_like(order_ref)
+    abi.check(lib, lib.rt_scene_bvh_download(h, 0, nodes.ctypes.data, order.ctypes.data), "rt_scene_bvh_download")
+    assert np.array_equal(order, order_ref)
+    assert np.array_equal(nodes.view(np.int32), nodes_ref.view(np.int32))
+    img = sc.render_region(0, 64, 0, 64)                                 # and the tree is usable
+    assert sc.last_counters["error_flags"] == 0 and img.max() > 0
