@@ -343,7 +343,9 @@ def run_ours(a):
         ms_dom_frame = per_frame(level0[dom][0])
         launches_dom = max(1, int(level0[dom][1]) // prof_frames)
         ms_all = sum(kernel_ms.values())
-        fm = frame_metrics(a).get(dom, {}) if world == 1 else {}
+        # level-0 kernels of the bench scene (no CSG nodes) as ncu names them: template arguments <HAS_NODES, PRIMARY / LIGHT_ROWS>
+        ncu_name = {"k_hit": "k_hit<0, 1>", "k_shadow": "k_shadow<0, 0>", "k_shade": "k_shade<1>"}[dom]
+        fm = frame_metrics(a).get(ncu_name, {}) if world == 1 else {}
         # the dominant kernel is bound by the warp schedulers' issue slots (ncu: smsp__issue_active), not by HBM: its BVH is L1/L2
         # resident.  achieved = warp instructions the kernel executes per frame (ncu smsp__inst_executed.sum of the SAME workload,
         # committed under profiles/) / the kernel's time per frame measured live above; peak = issue rate measured live.

@@ -169,7 +169,8 @@ typedef struct RtRenderJob {
     int32_t rank, world;
     int32_t direct;
     int32_t mesh_mode;       /* test aids, bit field: 0 = accelerated; bit 0 = brute force over all faces (mesh.py:77);
-                              * bit 1 = plain in-order loop over the top-level objects (scene.py:87,160) instead of the object BVH */
+                              * bit 1 = plain in-order loop over the top-level objects (scene.py:87,160) instead of the object BVH;
+                              * bit 2 (rt_occluded only) = the warp-packet any-hit walks the level-0 shadow kernel uses */
     int64_t max_batch_rays;  /* 0 = default */
 } RtRenderJob;
 

@@ -93,7 +93,7 @@ def frame(workload, csv_path, tag):
     pct = defaultdict(lambda: defaultdict(list))
     ids = defaultdict(set)
     for r in rows[1:]:
-        k = r[ki].split("(")[0].split("<")[0].replace("void ", "").strip()
+        k = r[ki].split("(")[0].replace("void ", "").strip()          # template arguments kept: k_shadow<0, 0> is the level-0 kernel
         v = float(r[vi].replace(",", "")) * scale.get(r[ui], 1.0)
         ids[k].add(r[ii])
         if "pct" in r[mi]:
@@ -116,9 +116,9 @@ def frame(workload, csv_path, tag):
     json.dump(allm, open(dst, "w"), indent=1, sort_keys=True)
     with open(f"profiles/{tag}.txt", "w") as out:
         out.write(f"# one frame of {workload}: per-kernel sums over its launches (ncu --metrics, --clock-control none; times are serialised, cold)\n")
-        out.write(f"{'kernel':12s} {'launches':>8s} {'ncu_ms':>9s} {'warp inst':>14s} {'lanes/inst':>10s} {'lsu wavefronts':>15s} {'dram GB':>9s} {'issue%':>7s} {'lsu%':>6s} {'L1hit%':>7s} {'L2hit%':>7s}\n")
+        out.write(f"{'kernel':16s} {'launches':>8s} {'ncu_ms':>9s} {'warp inst':>14s} {'lanes/inst':>10s} {'lsu wavefronts':>15s} {'dram GB':>9s} {'issue%':>7s} {'lsu%':>6s} {'L1hit%':>7s} {'L2hit%':>7s}\n")
         for k, t in sorted(table.items(), key=lambda kv: -kv[1]["ncu_ms"]):
-            out.write(f"{k[:12]:12s} {t['launches']:8d} {t['ncu_ms']:9.3f} {t['inst']:14.4g} {t['thread_inst'] / max(1.0, t['inst']):10.2f} "
+            out.write(f"{k[:16]:16s} {t['launches']:8d} {t['ncu_ms']:9.3f} {t['inst']:14.4g} {t['thread_inst'] / max(1.0, t['inst']):10.2f} "
                       f"{t['lsu_wavefronts']:15.4g} {t['dram_bytes'] / 1e9:9.3f} {t['issue_active_pct_mean']:7.1f} {t['lsu_pct_mean']:6.1f} "
                       f"{t['l1_hit_pct_mean']:7.1f} {t['l2_hit_pct_mean']:7.1f}\n")
     print(open(f"profiles/{tag}.txt").read())

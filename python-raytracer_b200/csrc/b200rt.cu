@@ -454,12 +454,12 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
         }
         sc->queue_cap = batch_cap;
     }
-    const size_t smem = (sc->has_mesh || sc->has_tlas) ? sizeof(int) * RT_STACK_DEPTH * RT_BLOCK : 0;
+    const size_t smem = (sc->has_mesh || sc->has_tlas) ? sizeof(int) * RT_STACK_ROWS * RT_BLOCK : 0;
     if (smem) {
         CU(cudaFuncSetAttribute(k_hit<HAS_NODES, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         CU(cudaFuncSetAttribute(k_hit<HAS_NODES, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        CU(cudaFuncSetAttribute(k_shadow<HAS_NODES, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        CU(cudaFuncSetAttribute(k_shadow<HAS_NODES, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CU(cudaFuncSetAttribute(k_shadow<HAS_NODES, SHADOW_PACKET>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CU(cudaFuncSetAttribute(k_shadow<HAS_NODES, SHADOW_ROWS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     }
     const int direct = (job->direct && job->world == 1) ? 1 : 0;
     const int waves = grid_waves(false), waves_deep = grid_waves(true);
@@ -484,9 +484,12 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
             { ProfScope ps_(sc, PC_HIT0, st);
               k_hit<HAS_NODES, true><<<(int)std::min<long long>(need, g_hit0), RT_BLOCK, smem, st>>>(V, pmk, p0, n_rays, q0, nullptr, H, sc->d_counters + 0); }
             if (V.n_lights > 0) { ProfScope ps_(sc, PC_SHADOW0, st);
-              k_shadow<HAS_NODES, false><<<(int)std::min<long long>(need, g_shadow0), RT_BLOCK, smem, st>>>(V, n_rays, nullptr, H, sc->d_occ, sc->d_counters + 1); (*launches)++; }
+              // the packet walk needs the shared stack area (scenes with a BVH to walk); without one there is nothing to walk per warp
+              if (RT_PACKET_SHADOW && smem) k_shadow<HAS_NODES, SHADOW_PACKET><<<(int)std::min<long long>(need, g_shadow0), RT_BLOCK, smem, st>>>(V, n_rays, nullptr, H, sc->d_occ, sc->d_counters + 1);
+              else k_shadow<HAS_NODES, SHADOW_PER_RAY><<<(int)std::min<long long>(need, g_shadow0), RT_BLOCK, smem, st>>>(V, n_rays, nullptr, H, sc->d_occ, sc->d_counters + 1);
+              (*launches)++; }
             { ProfScope ps_(sc, PC_SHADE0, st);
-              k_shade<true><<<(int)std::min<long long>(need, g_shade0), RT_BLOCK, 0, st>>>(V, n_rays, q0, nullptr, H, sc->d_occ, sc->d_samples, q0, sc->d_qcount, sc->d_counters + 2); }
+              k_shade<true><<<(int)std::min<long long>(need, g_shade0), RT_BLOCK, 0, st>>>(V, pmk, p0, n_rays, q0, nullptr, H, sc->d_occ, sc->d_samples, q0, sc->d_qcount, sc->d_counters + 2); }
             (*launches) += 2;
         }
         if (secondary) {
@@ -504,9 +507,9 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
                 { ProfScope ps_(sc, level == 1 ? PC_HIT1 : PC_DEEP, st);
                   k_hit<HAS_NODES, false><<<g_hit, RT_BLOCK, smem, st>>>(V, pmk, 0, 0, qin, n_in, H, sc->d_counters + 3); }
                 if (V.n_lights > 0) { ProfScope ps_(sc, level == 1 ? PC_SHADOW1 : PC_DEEP, st);
-                  k_shadow<HAS_NODES, true><<<dim3((unsigned)std::max(1, g_shadow / V.n_lights), (unsigned)V.n_lights), RT_BLOCK, smem, st>>>(V, 0, n_in, H, sc->d_occ, sc->d_counters + 3); (*launches)++; }
+                  k_shadow<HAS_NODES, SHADOW_ROWS><<<dim3((unsigned)std::max(1, g_shadow / V.n_lights), (unsigned)V.n_lights), RT_BLOCK, smem, st>>>(V, 0, n_in, H, sc->d_occ, sc->d_counters + 3); (*launches)++; }
                 { ProfScope ps_(sc, level == 1 ? PC_SHADE1 : PC_DEEP, st);
-                  k_shade<false><<<g_shade, RT_BLOCK, 0, st>>>(V, 0, qin, n_in, H, sc->d_occ, sc->d_samples, qout, sc->d_qcount + level, sc->d_counters + 3); }
+                  k_shade<false><<<g_shade, RT_BLOCK, 0, st>>>(V, pmk, 0, 0, qin, n_in, H, sc->d_occ, sc->d_samples, qout, sc->d_qcount + level, sc->d_counters + 3); }
                 (*launches) += 2;
             }
         }
@@ -629,7 +632,7 @@ extern "C" int rt_trace_rays(RtScene* sc, int64_t n, const float* h_org, const f
     UP(tmp.get(&rgb, 3 * n)); UP(tmp.get(&t, n)); UP(tmp.get(&nn, 3 * n)); UP(tmp.get(&pp, 3 * n));
     UP(tmp.get(&geom, n)); UP(tmp.get(&mat, n));
     SceneView V = sc->view; V.mesh_mode = mesh_mode;
-    const size_t smem = (sc->has_mesh || sc->has_tlas) ? sizeof(int) * RT_STACK_DEPTH * RT_BLOCK : 0;
+    const size_t smem = (sc->has_mesh || sc->has_tlas) ? sizeof(int) * RT_STACK_ROWS * RT_BLOCK : 0;
     const int grid = (int)((n + RT_BLOCK - 1) / RT_BLOCK);
     CU(cudaMemsetAsync(sc->d_counters, 0, sizeof(RtCounters), st));
     if (sc->has_nodes) {
@@ -662,7 +665,7 @@ extern "C" int rt_occluded(RtScene* sc, int64_t n, const float* h_org, const flo
     UP(tmp.get(&org, 3 * n, h_org)); UP(tmp.get(&dir, 3 * n, h_dir)); UP(tmp.get(&times, n, h_times)); UP(tmp.get(&tmax, n, h_tmax));
     UP(tmp.get(&occ, n));
     SceneView V = sc->view; V.mesh_mode = mesh_mode;
-    const size_t smem = (sc->has_mesh || sc->has_tlas) ? sizeof(int) * RT_STACK_DEPTH * RT_BLOCK : 0;
+    const size_t smem = (sc->has_mesh || sc->has_tlas) ? sizeof(int) * RT_STACK_ROWS * RT_BLOCK : 0;
     const int grid = (int)((n + RT_BLOCK - 1) / RT_BLOCK);
     if (sc->has_nodes) {
         if (smem) CU(cudaFuncSetAttribute(k_occluded<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -18,10 +18,26 @@ RT_HD uint64_t expand21(uint64_t v) {   // spread the low 21 bits to every third
     v = (v | v << 2) & 0x1249249249249249ull;
     return v;
 }
+// explicitly rounded single operations: nvcc would contract `centroid * (1/3) - lo` into one FMA, the host restatement
+// (tests/hostsim, -ffp-contract=off) cannot, and keys one ulp apart order duplicate triangles differently
+#if defined(__CUDA_ARCH__)
+#define RT_SUB_RN(a, b) __fsub_rn((a), (b))
+#define RT_MUL_RN(a, b) __fmul_rn((a), (b))
+#define RT_ADD_RN(a, b) __fadd_rn((a), (b))
+#else
+#define RT_SUB_RN(a, b) ((a) - (b))
+#define RT_MUL_RN(a, b) ((a) * (b))
+#define RT_ADD_RN(a, b) ((a) + (b))
+#endif
+RT_HD float3 tri_centroid(float3 a, float3 b, float3 c) {
+    const float k = 1.0f / 3.0f;
+    return f3(RT_MUL_RN(RT_ADD_RN(RT_ADD_RN(a.x, b.x), c.x), k), RT_MUL_RN(RT_ADD_RN(RT_ADD_RN(a.y, b.y), c.y), k),
+              RT_MUL_RN(RT_ADD_RN(RT_ADD_RN(a.z, b.z), c.z), k));
+}
 RT_HD uint64_t morton63(float3 c, float3 lo, float3 inv_ext) {
-    float x = fminf(fmaxf((c.x - lo.x) * inv_ext.x, 0.0f), 1.0f);
-    float y = fminf(fmaxf((c.y - lo.y) * inv_ext.y, 0.0f), 1.0f);
-    float z = fminf(fmaxf((c.z - lo.z) * inv_ext.z, 0.0f), 1.0f);
+    float x = fminf(fmaxf(RT_MUL_RN(RT_SUB_RN(c.x, lo.x), inv_ext.x), 0.0f), 1.0f);
+    float y = fminf(fmaxf(RT_MUL_RN(RT_SUB_RN(c.y, lo.y), inv_ext.y), 0.0f), 1.0f);
+    float z = fminf(fmaxf(RT_MUL_RN(RT_SUB_RN(c.z, lo.z), inv_ext.z), 0.0f), 1.0f);
     uint64_t xi = (uint64_t)fminf(x * 2097152.0f, 2097151.0f);
     uint64_t yi = (uint64_t)fminf(y * 2097152.0f, 2097151.0f);
     uint64_t zi = (uint64_t)fminf(z * 2097152.0f, 2097151.0f);
@@ -153,8 +169,7 @@ __global__ void k_morton(const float* __restrict__ verts, const int* __restrict_
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float3 a = vert_at(verts, faces[3 * i]), b = vert_at(verts, faces[3 * i + 1]), c = vert_at(verts, faces[3 * i + 2]);
-    float3 cen = (a + b + c) * (1.0f / 3.0f);
-    keys[i] = morton63(cen, lo, inv_ext);
+    keys[i] = morton63(tri_centroid(a, b, c), lo, inv_ext);
     vals[i] = i;
 }
 

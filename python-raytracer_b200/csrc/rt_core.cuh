@@ -220,6 +220,15 @@ RT_HD bool mesh_gate_rcp(const DevMesh* m, const Ray& r, const RayInv& ri) {
     }
     return !(entry > exit_ || entry < 0.0f);
 }
+// does the segment [0, tmax] of the ray touch the scene's bounded part (SceneView::world_lo/hi)?  Only ever says "cannot": the box is padded
+RT_HD bool touches_world(const SceneView& S, const RayInv& ri, float tmax) {
+    const float ax = fmaf(S.world_lo.x, ri.inv.x, ri.oinv.x), bx = fmaf(S.world_hi.x, ri.inv.x, ri.oinv.x);
+    const float ay = fmaf(S.world_lo.y, ri.inv.y, ri.oinv.y), by = fmaf(S.world_hi.y, ri.inv.y, ri.oinv.y);
+    const float az = fmaf(S.world_lo.z, ri.inv.z, ri.oinv.z), bz = fmaf(S.world_hi.z, ri.inv.z, ri.oinv.z);
+    const float near_ = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
+    const float far_ = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), tmax));
+    return near_ <= far_;
+}
 RT_HD unsigned as_uint(float f) { return (unsigned)as_int(f); }
 RT_HD int link_of(const int4& l, unsigned slot) { return (slot & 2u) ? ((slot & 1u) ? l.w : l.z) : ((slot & 1u) ? l.y : l.x); }
 RT_HD void key_swap(unsigned& a, unsigned& b) { unsigned lo = a < b ? a : b, hi = a < b ? b : a; a = lo; b = hi; }
@@ -402,6 +411,8 @@ RT_HD void mesh_visit(TraceCtx& cx, const DevMesh* m, const RayInv& ri, float tm
 // consumer breaks equal-t ties by object index itself; the any-hit consumer is order-free.
 struct TopIter { int lin_i; int cur; int sp; };
 RT_HD TopIter top_begin() { TopIter it; it.lin_i = 0; it.cur = 0; it.sp = 0; return it; }
+// the object BVH is not entered at all (the ray misses the scene's bounded part): the walk ends after the linear list
+RT_HD void top_skip_bvh(TopIter& it) { it.cur = RT_LINK_NONE; }
 
 // SHADOW: subtrees holding a mesh / CSG node are walked without the t_max bound because their shadow tests
 // ignore it
@@ -855,6 +866,9 @@ RT_HD bool closest_hit(TraceCtx& cx, const Ray& r, Hit& out) {
     const float A = dot(r.d, r.d);
     const RayInv ri = ray_inv(r);
     TopIter it = top_begin();
+    // rays that miss the padded bound of everything bounded (object BVH + separate meshes) only see the linear list (planes)
+    const bool in_world = !S.has_world || (S.mesh_mode & RT_MODE_LINEAR_TOP) || touches_world(S, ri, RT_INF);
+    if (!in_world) top_skip_bvh(it);
     for (;;) {
         const int oi = top_next<false>(cx, it, ri, best);
         if (oi < 0) break;
@@ -887,7 +901,7 @@ RT_HD bool closest_hit(TraceCtx& cx, const Ray& r, Hit& out) {
         }
     }
     cx.sbase = 0;
-    for (int k = 0; k < S.n_sep_mesh; k++) {                          // top-level meshes: all lanes of the warp enter the LBVH together
+    for (int k = 0; k < S.n_sep_mesh && in_world; k++) {              // top-level meshes: all lanes of the warp enter the LBVH together
         {
             const int oi = RT_LDG(S.sep_mesh + k);
             cx.tally.prims++;
@@ -912,6 +926,23 @@ RT_HD bool closest_hit(TraceCtx& cx, const Ray& r, Hit& out) {
     return true;
 }
 
+// shadow_intersect of ONE top-level object (the body of the loop of scene.py:160-164); A = d.d
+template <bool HAS_NODES>
+RT_HD bool object_shadow(TraceCtx& cx, int oi, const Ray& r, float A, float tmax) {
+    const DevObject* o = cx.S.objects + oi;
+    const int kind = o->kind;
+    if (kind == RT_KIND_SPHERE) {
+        cx.tally.prims++;
+        float4 a = ld4(&o->a);
+        float t1, t2;
+        return sphere_roots(moved(cx, o, f3(a)), a.w, r, A, t1, t2) &&
+               ((RT_SHADOW_EPS_SPHERE < t1 && t1 < tmax) || (RT_SHADOW_EPS_SPHERE < t2 && t2 < tmax));
+    }
+    if (kind == RT_KIND_MESH) return false;                           // (linear test mode only) traversed after the walk
+    if (kind != RT_KIND_NODE) return leaf_shadow<false>(cx, oi, r, tmax);
+    return HAS_NODES ? csg_shadow(cx, oi, r, tmax) : false;
+}
+
 // Any-hit over the top-level objects (scene.py:160-164)
 template <bool HAS_NODES>
 RT_HD bool occluded(TraceCtx& cx, const Ray& r, float tmax) {
@@ -920,32 +951,145 @@ RT_HD bool occluded(TraceCtx& cx, const Ray& r, float tmax) {
     const RayInv ri = ray_inv(r);
     TopIter it = top_begin();
     bool occ = false;
+    // mesh and CSG-difference shadows ignore t_max, so the world test is made with the unbounded ray
+    const bool in_world = !S.has_world || (S.mesh_mode & RT_MODE_LINEAR_TOP) || touches_world(S, ri, RT_INF);
+    if (!in_world) top_skip_bvh(it);
     for (;;) {
         const int oi = top_next<true>(cx, it, ri, tmax);
         if (oi < 0) break;
         cx.sbase = it.sp;
-        const DevObject* o = S.objects + oi;
-        const int kind = o->kind;
-        if (kind == RT_KIND_SPHERE) {
-            cx.tally.prims++;
-            float4 a = ld4(&o->a);
-            float t1, t2;
-            if (sphere_roots(moved(cx, o, f3(a)), a.w, r, A, t1, t2) &&
-                ((RT_SHADOW_EPS_SPHERE < t1 && t1 < tmax) || (RT_SHADOW_EPS_SPHERE < t2 && t2 < tmax))) { occ = true; break; }
-        } else if (kind == RT_KIND_MESH) {                            // (linear test mode only) traversed after the walk, below
-        } else if (kind != RT_KIND_NODE) {
-            if (leaf_shadow<false>(cx, oi, r, tmax)) { occ = true; break; }
-        } else if (HAS_NODES) {
-            if (csg_shadow(cx, oi, r, tmax)) { occ = true; break; }
-        }
+        if (object_shadow<HAS_NODES>(cx, oi, r, A, tmax)) { occ = true; break; }
     }
     cx.sbase = 0;
-    for (int k = 0; k < S.n_sep_mesh && !occ; k++) {
+    for (int k = 0; k < S.n_sep_mesh && !occ && in_world; k++) {
         cx.tally.prims++;
         occ = mesh_shadow(cx, S.meshes + S.objects[RT_LDG(S.sep_mesh + k)].mesh, r, ri);
     }
     return occ;
 }
+
+#if defined(__CUDACC__)
+// ------------------------------------------------------------------------------------------------
+// PACKET any-hit walks (device only).  The 32 rays of a warp at level 0 are the samples of one pixel (or of neighbouring
+// pixels of a tile) towards ONE light: nearly the same ray.  Walked lane by lane they still drift apart - a lane whose ray
+// misses one child box pops a different node than its neighbours - and from then on every lane tests ITS leaves at its own
+// step (ncu: 5.4 of 32 lanes active in the triangle tests).  Here the WARP walks the tree: one node per step for all lanes,
+// every lane tests its own ray against the four child boxes, a child is entered when ANY lane's ray touches it (one REDUX),
+// the stack is one warp-uniform stack in shared memory, and a leaf's triangles are tested once per warp with all interested
+// lanes at the same time.  Any-hit results do not depend on the visiting order, and the boxes only prune (a ray that hits a
+// triangle touches every box around it), so every lane gets exactly the answer its own walk would have given.
+// All 32 lanes of the warp must call these functions together; `active`: this lane still wants an answer.
+#define RT_FULL_WARP 0xffffffffu
+__device__ __forceinline__ unsigned ws_addr(unsigned wbase, int e) { return wbase + (unsigned)(RT_STACK_DEPTH + (e >> 5)) * RT_STACK_PITCH + (unsigned)(e & 31) * 4u; }
+__device__ __forceinline__ void ws_push(TraceCtx& cx, unsigned wbase, int& sp, int v) {
+    if (sp >= RT_PACKET_ROWS * 32) { cx.tally.err |= 1u << RT_ERR_LIMIT; return; }
+    asm volatile("st.shared.b32 [%0], %1;" :: "r"(ws_addr(wbase, sp)), "r"(v) : "memory");
+    sp++;
+}
+__device__ __forceinline__ int ws_pop(unsigned wbase, int& sp) {
+    --sp;
+    int v;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(ws_addr(wbase, sp)) : "memory");
+    return v;
+}
+
+// onLeaf(leaf_code, mine): called by all lanes for every leaf some active lane's ray touches (mine: this lane's does);
+// it may clear `active`.  FLAGS: children flagged RT_TLAS_NO_TMAX are tested without the tmax bound (object BVH).
+template <bool FLAGS, class OnLeaf>
+__device__ __forceinline__ void bvh4_anyhit_packet(TraceCtx& cx, const BvhNode4* __restrict__ nodes, const RayInv& ri, const float tmin,
+                                                   const float tmax, bool& active, unsigned& visits, OnLeaf&& onLeaf) {
+#if defined(__CUDA_ARCH__)
+    const unsigned wbase = cx.saddr - (threadIdx.x & 31u) * 4u;       // lane 0's column of the block's shared stack area
+#else
+    const unsigned wbase = 0;                                          // (host pass of nvcc: never executed)
+#endif
+    int sp = 0, cur = 0;
+    for (;;) {
+        if (cur == RT_LINK_NONE) {
+            if (sp == 0) return;
+            cur = ws_pop(wbase, sp);
+        }
+        const BvhNode4* np = nodes + cur;
+        RT_LOAD_NODE4(np)
+        float t0 = tmax, t1 = tmax, t2 = tmax, t3 = tmax;
+        if (FLAGS && cx.S.tlas_flagged) {
+            const int4 fl = RT_LDG(&np->flags);
+            if (fl.x & RT_TLAS_NO_TMAX) t0 = RT_INF;
+            if (fl.y & RT_TLAS_NO_TMAX) t1 = RT_INF;
+            if (fl.z & RT_TLAS_NO_TMAX) t2 = RT_INF;
+            if (fl.w & RT_TLAS_NO_TMAX) t3 = RT_INF;
+        }
+        float n0, n1, n2, n3; bool h0, h1, h2, h3;
+        RT_SLAB4(pnx.x, pny.x, pnz.x, pfx.x, pfy.x, pfz.x, t0, n0, h0)
+        RT_SLAB4(pnx.y, pny.y, pnz.y, pfx.y, pfy.y, pfz.y, t1, n1, h1)
+        RT_SLAB4(pnx.z, pny.z, pnz.z, pfx.z, pfy.z, pfz.z, t2, n2, h2)
+        RT_SLAB4(pnx.w, pny.w, pnz.w, pfx.w, pfy.w, pfz.w, t3, n3, h3)
+        (void)n0; (void)n1; (void)n2; (void)n3;
+        const unsigned mine = active ? ((unsigned)h0 | (unsigned)h1 << 1 | (unsigned)h2 << 2 | (unsigned)h3 << 3) : 0u;
+        const unsigned any4 = __reduce_or_sync(RT_FULL_WARP, mine);
+        visits += active ? 1u : 0u;
+        int nxt = RT_LINK_NONE;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            if (!((any4 >> k) & 1u)) continue;
+            const int l = k == 0 ? link.x : k == 1 ? link.y : k == 2 ? link.z : link.w;
+            if (l < 0) onLeaf(~l, ((mine >> k) & 1u) != 0u);
+            else if (nxt == RT_LINK_NONE) nxt = l;
+            else ws_push(cx, wbase, sp, l);
+        }
+        if (!__any_sync(RT_FULL_WARP, active)) return;
+        cur = nxt;
+    }
+}
+
+// Mesh.shadow_intersect for a warp of rays and ONE mesh (same answer per lane as mesh_shadow)
+__device__ __forceinline__ bool mesh_shadow_packet(TraceCtx& cx, const DevMesh* m, const Ray& r, const RayInv& ri, bool want) {
+    bool active = want && mesh_gate_rcp(m, r, ri);
+    const int n = m->n_tris;
+    if (n <= 0 || !__any_sync(RT_FULL_WARP, active)) return false;
+    bool occ = false;
+    auto test = [&](int s, bool mine) {
+        float3 v0, v1, v2; int face;
+        tri_load(m, s, v0, v1, v2, face);                                   // one address for the whole warp
+        if (mine && active) { cx.tally.tris++; if (tri_shadow(v0, v1, v2, r)) { occ = true; active = false; } }
+    };
+    if ((cx.S.mesh_mode & RT_MODE_BRUTE_MESH) || n == 1) {
+        for (int s = 0; s < n && __any_sync(RT_FULL_WARP, active); s++) test(s, true);
+        return occ;
+    }
+    bvh4_anyhit_packet<false>(cx, m->nodes, ri, RT_SHADOW_EPS * 0.5f, RT_INF, active, cx.tally.nodes, [&](int code, bool mine) {
+        const int first = code & ((1 << RT_LEAF_SLOT_BITS) - 1), last = first + (code >> RT_LEAF_SLOT_BITS);
+        for (int s = first; s <= last; s++) test(s, mine);
+    });
+    return occ;
+}
+
+// the any-hit loop of scene.py:160-164 for a warp of rays (same answer per lane as occluded<>)
+template <bool HAS_NODES>
+__device__ __forceinline__ bool occluded_packet(TraceCtx& cx, const Ray& r, float tmax, bool want) {
+    const SceneView& S = cx.S;
+    if (S.mesh_mode & RT_MODE_LINEAR_TOP) return want ? occluded<HAS_NODES>(cx, r, tmax) : false;     // test aid: the plain loops
+    const float A = dot(r.d, r.d);
+    const RayInv ri = ray_inv(r);
+    bool occ = false, active = want;
+    cx.sbase = 0;
+    for (int k = 0; k < S.n_lin; k++) {                                      // unbounded objects: every lane, scene order
+        const int oi = RT_LDG(S.lin_objs + k);
+        if (active && object_shadow<HAS_NODES>(cx, oi, r, A, tmax)) { occ = true; active = false; }
+    }
+    active = active && (!S.has_world || touches_world(S, ri, RT_INF));       // lanes whose ray misses everything bounded are done
+    if (!__any_sync(RT_FULL_WARP, active)) return occ;
+    if (S.tlas_nodes != nullptr)
+        bvh4_anyhit_packet<true>(cx, S.tlas_nodes, ri, 0.0f, tmax, active, cx.tally.prims, [&](int oi, bool mine) {
+            if (mine && active && object_shadow<HAS_NODES>(cx, oi, r, A, tmax)) { occ = true; active = false; }
+        });
+    for (int k = 0; k < S.n_sep_mesh && __any_sync(RT_FULL_WARP, active); k++) {
+        if (active) cx.tally.prims++;
+        if (mesh_shadow_packet(cx, S.meshes + S.objects[RT_LDG(S.sep_mesh + k)].mesh, r, ri, active)) { occ = true; active = false; }
+    }
+    return occ;
+}
+#endif
 
 // ------------------------------------------------------------------------------------------------
 // Shadow ray of light `li` from hit point p (scene.py:148-167): un-offset origin, un-normalised direction (Q12)
@@ -958,6 +1102,18 @@ RT_HD bool light_occluded(TraceCtx& cx, float3 p, int li) {
     cx.tally.shadow++;
     return occluded<HAS_NODES>(cx, sr, point ? 1.0f : RT_INF);
 }
+#if defined(__CUDACC__)
+// the same for a warp of hit points and one light (all 32 lanes call; want: this lane has a hit point)
+template <bool HAS_NODES>
+__device__ __forceinline__ bool light_occluded_packet(TraceCtx& cx, float3 p, int li, bool want) {
+    const float4 lv = ld4(&cx.S.lights[li].vector);
+    const bool point = as_int(lv.w) == RT_LIGHT_POINT;
+    Ray sr; sr.o = p;
+    sr.d = point ? f3(lv) - p : -f3(lv);
+    if (want) cx.tally.shadow++;
+    return occluded_packet<HAS_NODES>(cx, sr, point ? 1.0f : RT_INF, want);
+}
+#endif
 
 // _compute_regular_lighting (scene.py:140-187): Blinn-Phong + ambient; lit(li) says whether light li reaches the
 // hit point (the shadow-ray results: traced in place by trace_level, read back from k_shadow's flags by k_shade)
@@ -1053,12 +1209,16 @@ RT_HD bool trace_level(TraceCtx& cx, PathState& ps, float3& sample) {
 
 // ------------------------------------------------------------------------------------------------
 // Sample generation (scene.py:47-69): primary ray of (col, row, dof d, aa s)
-RT_HD Ray generate_ray(const SceneView& S, int col, int row, int d, int s) {
+// direction of the primary rays of (col, row, dof sample d): the AA point and the jitter move only the origin (scene.py:58-65)
+RT_HD float3 primary_direction(const SceneView& S, int col, int row, int d) {
     float x = RT_LDG(S.col_x + col), y = RT_LDG(S.row_y + row);
     float3 base_dir = normalize((S.cam_u * x + S.cam_v * y) - S.cam_w);          // d = 1: d*w == w
     float3 focal_point = S.cam_pos + base_dir * S.focal_length;
+    return normalize(focal_point - f3(ld4(S.dof_origin + d)));
+}
+RT_HD Ray generate_ray(const SceneView& S, int col, int row, int d, int s) {
     Ray r;
-    r.d = normalize(focal_point - f3(ld4(S.dof_origin + d)));
+    r.d = primary_direction(S, col, row, d);
     r.o = f3(ld4(S.ray_origin + d * S.S + s));
     if (S.jitter) {
         uint64_t idx = (((uint64_t)col * (uint64_t)S.height + (uint64_t)row) * (uint64_t)S.D + (uint64_t)d) * (uint64_t)S.S + (uint64_t)s;

@@ -4,7 +4,7 @@
 // in the SM's instruction caches (a single fused kernel measured 94 % of the GPC instruction-fetch bandwidth and
 // a third of its issue slots stalled on "no instruction"):
 //   k_hit     : raygen (level 0) or queue load, closest hit over the scene -> hit record planes
-//   k_shadow  : one thread per (light, ray): any-hit shadow ray -> one occlusion byte
+//   k_shadow  : any-hit shadow rays -> one occlusion byte per (light, ray); level 0 walks the BVHs warp by warp (packets)
 //   k_shade   : Blinn-Phong with those flags, per-level clamp fold; finished samples go to the sample buffer,
 //               reflection/refraction rays are compacted (warp ballot + prefix popcount + one atomic per warp)
 //               into the next level's ray queue (replaces the recursion of scene.py:102,203,208)
@@ -33,9 +33,12 @@
 #endif
 
 // The per-ray wavefront records (hit planes, occlusion flags, samples, queue entries) are written once and read once, tens of
-// GB per frame, next to a ~100 MB BVH that every ray re-reads: with RT_STREAM_RECORDS they are accessed with the streaming
-// (evict-first) cache hints so they do not push BVH lines out of L1/L2.
-#ifdef RT_STREAM_RECORDS
+// GB per frame, next to a ~100 MB BVH that every ray re-reads: they are accessed with the streaming (evict-first) cache hints so
+// they do not push BVH lines out of L1/L2 (measured 0.5 ms of 124 per frame at 4K x 64; -DRT_STREAM_RECORDS=0 for plain accesses).
+#ifndef RT_STREAM_RECORDS
+#define RT_STREAM_RECORDS 1
+#endif
+#if RT_STREAM_RECORDS
 #define RT_ST_REC(ptr, val) __stcs((ptr), (val))
 #define RT_LD_REC(ptr) __ldcs(ptr)
 #else
@@ -114,14 +117,35 @@ __device__ __forceinline__ void tally_flush(const Tally& t, unsigned long long p
 
 __device__ __forceinline__ Tally tally_zero() { Tally t; t.shadow = t.reflect = t.refract = t.nodes = t.tris = t.prims = t.shaded = t.smooth = t.err = 0; return t; }
 
-extern __shared__ int rt_smem_stack[];   // RT_STACK_DEPTH * blockDim.x ints when the scene has a mesh or an object BVH
+extern __shared__ int rt_smem_stack[];   // RT_STACK_ROWS * blockDim.x ints when the scene has a mesh or an object BVH
+// the launches allocate the shared stack area only for scenes with something to walk (b200rt.cu: has_mesh || has_tlas)
+__device__ __forceinline__ bool rt_smem_stack_present(const SceneView& S) { return S.tlas_nodes != nullptr || S.n_sep_mesh > 0; }
 
-// Hit records of one level, SoA float4 planes of `cap` entries, indexed like the level's rays:
+// Hit records of one level, SoA float4 planes of `cap` entries, indexed like the level's rays: 32 bytes per ray
 //   plane 0: hit position xyz, w = ray time (NaN: the ray hit nothing / ended)
-//   plane 1: shading normal xyz, w = bits(material index)
-//   plane 2: ray direction xyz, w = bits(leaf object index)
+//   plane 1: shading normal xyz, w = bits((material index + 2) | leaf object index << RT_HIT_MAT_BITS)
+// The ray direction k_shade needs is NOT stored (it was a third plane: 17 GB of DRAM traffic per 4K x 64 frame): a queued ray's
+// direction is in its queue entry, a primary ray's is recomputed from its pixel (primary_direction: two table look-ups and two
+// normalisations; the jitter only moves the origin).
 struct HitPlanes { float4* planes; long long cap; };
-#define RT_HIT_PLANES 3
+#define RT_HIT_PLANES 2
+#define RT_HIT_MAT_BITS 12            // materials < 4094 (the two specials -1 / -2 included), objects < 2^20: checked by rt_scene_create
+__device__ __forceinline__ float hit_pack(int mat, int geom) { return as_float((mat + 2) | (geom << RT_HIT_MAT_BITS)); }
+__device__ __forceinline__ void hit_unpack(float w, int& mat, int& geom) {
+    const unsigned u = (unsigned)as_int(w);
+    mat = (int)(u & ((1u << RT_HIT_MAT_BITS) - 1u)) - 2; geom = (int)(u >> RT_HIT_MAT_BITS);
+}
+// ray i of a level-0 batch -> pixel and sample slot (loop order of scene.py:57-67: slot = (d*S + s)*T + t)
+struct PrimaryIndex { int col, row; unsigned d, s, t; bool live; };
+__device__ __forceinline__ PrimaryIndex primary_index(const SceneView& S, const PixelMap& pm, long long pixel_begin, unsigned iu, unsigned N) {
+    PrimaryIndex pi;
+    const unsigned px = fdiv(iu, pm.fd_N), slot = iu - px * N;
+    pi.live = pixel_of(pm, (unsigned)pixel_begin + px, pi.col, pi.row) && S.max_depth > 0;
+    const unsigned ds = fdiv(slot, pm.fd_T);
+    pi.t = slot - ds * (unsigned)S.T;
+    pi.d = fdiv(ds, pm.fd_S); pi.s = ds - pi.d * (unsigned)S.S;
+    return pi;
+}
 
 // ---- stage 1: closest hit ------------------------------------------------------------------------------
 // PRIMARY: ray i of the batch is generated here: pixel = pixel_begin + i / N, slot = i % N = (d*S + s)*T + t (loop
@@ -140,14 +164,10 @@ __global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_HIT_CSG : 
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         Ray ray; float time; bool live = true;
         if (PRIMARY) {
-            const unsigned iu = (unsigned)i;                                   // a batch holds < 2^30 rays
-            const unsigned px = fdiv(iu, pm.fd_N), slot = iu - px * (unsigned)N;
-            int col, row;
-            live = pixel_of(pm, (unsigned)pixel_begin + px, col, row) && S.max_depth > 0;
-            const unsigned ds = fdiv(slot, pm.fd_T), t = slot - ds * (unsigned)S.T;
-            const unsigned d = fdiv(ds, pm.fd_S), s = ds - d * (unsigned)S.S;
-            if (live) { ray = generate_ray(S, col, row, (int)d, (int)s); n_primary++; }
-            time = RT_LDG(S.times + t);
+            const PrimaryIndex pi = primary_index(S, pm, pixel_begin, (unsigned)i, (unsigned)N);      // a batch holds < 2^30 rays
+            live = pi.live;
+            if (live) { ray = generate_ray(S, pi.col, pi.row, (int)pi.d, (int)pi.s); n_primary++; }
+            time = RT_LDG(S.times + pi.t);
         } else {
             const float4 p0 = qin.planes[0 * qin.cap + i], p1 = qin.planes[1 * qin.cap + i];
             ray.o = f3(p0); ray.d = f3(p1); time = p0.w;
@@ -159,8 +179,7 @@ __global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_HIT_CSG : 
         }
         if (live) {
             RT_ST_REC(&H.planes[0 * H.cap + i], f4(hit.p.x, hit.p.y, hit.p.z, time));
-            RT_ST_REC(&H.planes[1 * H.cap + i], f4(hit.n.x, hit.n.y, hit.n.z, as_float(hit.mat)));
-            RT_ST_REC(&H.planes[2 * H.cap + i], f4(ray.d.x, ray.d.y, ray.d.z, as_float(hit.geom)));
+            RT_ST_REC(&H.planes[1 * H.cap + i], f4(hit.n.x, hit.n.y, hit.n.z, hit_pack(hit.mat, hit.geom)));
         } else {
             RT_ST_REC(&H.planes[0 * H.cap + i], f4(0.0f, 0.0f, 0.0f, as_float(0x7fc00000)));
         }
@@ -173,53 +192,102 @@ __global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_HIT_CSG : 
 // LIGHT_ROWS: gridDim.y = lights (small queues of the deeper levels: every (light, ray) pair gets its own thread);
 // otherwise a thread walks the lights of its ray one after the other (big level-0 batches: the 16-B hit position is read
 // once instead of once per light; measured 3 ms/frame faster than sweeping the rays once per light).
-template <bool HAS_NODES, bool LIGHT_ROWS>
+// MODE: how the (light, ray) pairs are laid over the threads
+//   SHADOW_PER_RAY : a thread walks the lights of its ray one after the other (big level-0 batches: the 16-B hit position is read once
+//                    instead of once per light; measured 3 ms/frame faster than sweeping the rays once per light)
+//   SHADOW_ROWS    : gridDim.y = lights (small queues of the deeper levels: every (light, ray) pair gets its own thread)
+//   SHADOW_PACKET  : like PER_RAY, but the BVHs are walked warp by warp (occluded_packet, rt_core.cuh): at level 0 the 32 lanes of a
+//                    warp hold samples of one pixel / neighbouring pixels and share the light, so their shadow rays are nearly the same.
+//                    Built, verified (rt_occluded mesh_mode bit 2, tests) and MEASURED at 4K x 64: the same 19.3 G warp instructions per
+//                    heavy launch as the per-ray walk (30.4 instead of 25.8 lanes per instruction, L1 data pipe 54 % instead of 84 %,
+//                    but the larger kernel is instruction-fetch bound: 98 % of the GPC fetch bandwidth) and 63.3 ms instead of 62.7
+//                    per frame: not the default (-DRT_PACKET_SHADOW=1 selects it).
+enum { SHADOW_PER_RAY = 0, SHADOW_ROWS = 1, SHADOW_PACKET = 2 };
+#ifndef RT_PACKET_SHADOW
+#define RT_PACKET_SHADOW 0
+#endif
+template <bool HAS_NODES, int MODE>
 __global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_SHADOW_CSG : RT_MIN_BLOCKS_SHADOW) k_shadow(SceneView S, long long n_rays, const unsigned long long* n_dev,
                                                                            HitPlanes H, uint8_t* __restrict__ occ, RtCounters* counters) {
     Tally tally = tally_zero();
     int spill[RT_STACK_SPILL];       // overflow of the shared-memory traversal stack (thread-local memory)
     const long long n = n_dev ? (long long)*n_dev : n_rays;
     const long long stride = (long long)gridDim.x * blockDim.x;
-    const int li0 = LIGHT_ROWS ? (int)blockIdx.y : 0, li1 = LIGHT_ROWS ? li0 + 1 : S.n_lights;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const float4 h0 = RT_LD_REC(&H.planes[0 * H.cap + i]);
-        if (h0.w != h0.w) continue;                                       // no hit: no shadow rays
-        TraceCtx cx{S, h0.w, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill};
-        for (int li = li0; li < li1; li++)                                // the lanes of a warp still work on ONE light at a time
-            RT_ST_REC(&occ[(long long)li * H.cap + i], (uint8_t)(light_occluded<HAS_NODES>(cx, f3(h0), li) ? 1 : 0));
+    if (MODE == SHADOW_PACKET) {
+        for (long long base = (long long)blockIdx.x * blockDim.x; base < n; base += stride) {     // whole warps stay together
+            const long long i = base + threadIdx.x;
+            const float4 h0 = i < n ? RT_LD_REC(&H.planes[0 * H.cap + i]) : f4(0.0f, 0.0f, 0.0f, as_float(0x7fc00000));
+            const bool live = !(h0.w != h0.w);                            // no hit: no shadow rays
+            if (!__any_sync(0xffffffffu, live)) continue;
+            TraceCtx cx{S, h0.w, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill};
+            unsigned bits = 0;
+            for (int li = 0; li < S.n_lights; li++) {
+                bits |= (light_occluded_packet<HAS_NODES>(cx, f3(h0), li, live) ? 1u : 0u) << (li & 7);
+                if ((li & 7) == 7 || li == S.n_lights - 1) { if (live) RT_ST_REC(&occ[(long long)(li >> 3) * H.cap + i], (uint8_t)bits); bits = 0; }
+            }
+        }
+    } else {
+        const int li0 = MODE == SHADOW_ROWS ? (int)blockIdx.y : 0, li1 = MODE == SHADOW_ROWS ? li0 + 1 : S.n_lights;
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+            const float4 h0 = RT_LD_REC(&H.planes[0 * H.cap + i]);
+            if (h0.w != h0.w) continue;                                       // no hit: no shadow rays
+            TraceCtx cx{S, h0.w, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill};
+            if (MODE == SHADOW_ROWS) {                                        // one byte per (light, ray)
+                RT_ST_REC(&occ[(long long)li0 * H.cap + i], (uint8_t)(light_occluded<HAS_NODES>(cx, f3(h0), li0) ? 1 : 0));
+            } else {                                                          // one BIT per (light, ray): byte plane li / 8; the lanes of a warp still work on ONE light at a time
+                unsigned bits = 0;
+                for (int li = li0; li < li1; li++) {
+                    bits |= (light_occluded<HAS_NODES>(cx, f3(h0), li) ? 1u : 0u) << (li & 7);
+                    if ((li & 7) == 7 || li == li1 - 1) { RT_ST_REC(&occ[(long long)(li >> 3) * H.cap + i], (uint8_t)bits); bits = 0; }
+                }
+            }
+        }
     }
     tally_flush(tally, 0, 0, counters);
 }
 
 // ---- stage 3: shading, fold, next ray ----------------------------------------------------------------------
+// PRIMARY (level 0): the occlusion flags are one BIT per (light, ray) (k_shadow SHADOW_PER_RAY / SHADOW_PACKET), the ray direction is
+// recomputed from the pixel; queued levels: one byte per (light, ray) (SHADOW_ROWS), direction from the queue entry.
 template <bool PRIMARY>
-__global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS_SHADE) k_shade(SceneView S, long long n_rays, RayQueue qin, const unsigned long long* qin_count,
+__global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS_SHADE) k_shade(SceneView S, PixelMap pm, long long pixel_begin, long long n_rays, RayQueue qin, const unsigned long long* qin_count,
                                                                          HitPlanes H, const uint8_t* __restrict__ occ, float4* __restrict__ samples,
                                                                          RayQueue qout, unsigned long long* qout_count, RtCounters* counters) {
     Tally tally = tally_zero();
     unsigned long long n_queued = 0;
     const long long n = PRIMARY ? n_rays : (long long)*qin_count;
     const long long stride = (long long)gridDim.x * blockDim.x;
+    const unsigned N = (unsigned)(S.D * S.S * S.T);
     for (long long base = (long long)blockIdx.x * blockDim.x; base < n; base += stride) {
         const long long i = base + threadIdx.x;
         bool cont = false;
         PathState ps; float time = 0.0f; unsigned slot = (unsigned)i;
         if (i < n) {
-            if (PRIMARY) { ps.fold = fold_identity(); ps.depth_left = S.max_depth; ps.in_shape = 0; ps.ray.o = f3(0, 0, 0); }
-            else queue_load(qin, i, ps, time, slot);
-            // every load of this ray issued up front (the kernel is latency-bound: hit planes + one flag byte per light)
-            const float4 h0 = RT_LD_REC(&H.planes[0 * H.cap + i]), h1 = RT_LD_REC(&H.planes[1 * H.cap + i]), h2 = RT_LD_REC(&H.planes[2 * H.cap + i]);
+            // every load of this ray issued up front (the kernel is latency-bound: hit planes + the flag bytes)
+            const float4 h0 = RT_LD_REC(&H.planes[0 * H.cap + i]), h1 = RT_LD_REC(&H.planes[1 * H.cap + i]);
             unsigned lit_mask = 0;
             const int n_pre = S.n_lights < 32 ? S.n_lights : 32;
-            for (int li = 0; li < n_pre; li++) lit_mask |= (RT_LD_REC(&occ[(long long)li * H.cap + i]) == 0 ? 1u : 0u) << li;
+            if (PRIMARY) {
+                for (int b = 0; b * 8 < n_pre; b++) lit_mask |= (unsigned)RT_LD_REC(&occ[(long long)b * H.cap + i]) << (8 * b);
+                lit_mask = ~lit_mask;
+                ps.fold = fold_identity(); ps.depth_left = S.max_depth; ps.in_shape = 0; ps.ray.o = f3(0, 0, 0);
+            } else {
+                for (int li = 0; li < n_pre; li++) lit_mask |= (RT_LD_REC(&occ[(long long)li * H.cap + i]) == 0 ? 1u : 0u) << li;
+                queue_load(qin, i, ps, time, slot);
+            }
             float3 sample;
             if (h0.w != h0.w) sample = fold_eval(ps.fold, f3(0, 0, 0));          // miss: cast_ray returns black (scene.py:91-92)
             else {
-                Hit hit; hit.p = f3(h0); hit.n = f3(h1); hit.mat = as_int(h1.w); hit.geom = as_int(h2.w); hit.t = 0.0f;
+                Hit hit; hit.p = f3(h0); hit.n = f3(h1); hit_unpack(h1.w, hit.mat, hit.geom); hit.t = 0.0f;
                 time = h0.w;
-                ps.ray.d = f3(h2);
+                if (PRIMARY) {
+                    const PrimaryIndex pi = primary_index(S, pm, pixel_begin, (unsigned)i, N);
+                    ps.ray.d = primary_direction(S, pi.col, pi.row, (int)pi.d);
+                }
                 TraceCtx cx{S, time, tally, nullptr, 0, nullptr};
-                cont = shade_level(cx, ps, hit, [&](int li) { return li < 32 ? ((lit_mask >> li) & 1u) != 0 : occ[(long long)li * H.cap + i] == 0; }, sample);
+                cont = shade_level(cx, ps, hit, [&](int li) {
+                    if (li < 32) return ((lit_mask >> li) & 1u) != 0;
+                    return PRIMARY ? ((occ[(long long)(li >> 3) * H.cap + i] >> (li & 7)) & 1) == 0 : occ[(long long)li * H.cap + i] == 0; }, sample);
             }
             if (!cont) RT_ST_REC(&samples[slot], f4(sample.x, sample.y, sample.z, 0.0f));
         }
@@ -340,10 +408,13 @@ __global__ void __launch_bounds__(RT_BLOCK) k_occluded(SceneView S, long long n,
     Tally tally = tally_zero();
     int spill[RT_STACK_SPILL];       // overflow of the shared-memory traversal stack (thread-local memory)
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) {
-        Ray r; r.o = f3(org[3 * i], org[3 * i + 1], org[3 * i + 2]); r.d = f3(dir[3 * i], dir[3 * i + 1], dir[3 * i + 2]);
-        TraceCtx cx{S, times[i], tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill};
-        occ[i] = occluded<HAS_NODES>(cx, r, tmax[i]) ? 1 : 0;
-    }
+    const bool valid = i < n;
+    const long long j = valid ? i : 0;
+    Ray r; r.o = f3(org[3 * j], org[3 * j + 1], org[3 * j + 2]); r.d = f3(dir[3 * j], dir[3 * j + 1], dir[3 * j + 2]);
+    TraceCtx cx{S, times[j], tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill};
+    bool o;
+    if ((S.mesh_mode & RT_MODE_PACKET_TEST) && rt_smem_stack_present(S)) o = occluded_packet<HAS_NODES>(cx, r, tmax[j], valid);   // the warp walks
+    else o = valid && occluded<HAS_NODES>(cx, r, tmax[j]);
+    if (valid) occ[i] = o ? 1 : 0;
     tally_flush(tally, 0, 0, counters);
 }

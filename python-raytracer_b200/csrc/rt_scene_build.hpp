@@ -234,6 +234,7 @@ inline int convert_scene(const RtSceneDesc* d, HostScene& hs, std::string& err) 
     for (int m = 0; m < d->n_meshes; m++)
         if (d->meshes[m].n_faces >= (1 << RT_LEAF_SLOT_BITS)) return bad(RT_ERR_LIMIT, "a mesh may hold fewer than 2^28 faces (leaf link encoding)");
     if (d->max_depth < 0 || d->max_depth > 255) return bad(RT_ERR_LIMIT, "max_depth must be in [0, 255]");
+    if (d->n_materials > 4093 || d->n_objects >= (1 << 20)) return bad(RT_ERR_LIMIT, "at most 4093 materials and 2^20 - 1 objects (packed hit record)");
     hs.objs.resize(d->n_objects);
     for (int i = 0; i < d->n_objects; i++) {
         const RtObject& o = d->objects[i];
@@ -299,6 +300,31 @@ inline int convert_scene(const RtSceneDesc* d, HostScene& hs, std::string& err) 
     V.max_depth = d->max_depth;
     V.mesh_mode = 0;
     build_tlas(d, hs);
+    {   // padded union of everything the object BVH and the separate meshes can report (SceneView::world_lo/hi)
+        float3 lo = f3(INFINITY, INFINITY, INFINITY), hi = f3(-INFINITY, -INFINITY, -INFINITY);
+        bool any = false, ok = true;
+        for (const BvhNode4& nd : hs.tlas_nodes) {
+            const float *lx = &nd.lox.x, *ly = &nd.loy.x, *lz = &nd.loz.x, *hx = &nd.hix.x, *hy = &nd.hiy.x, *hz = &nd.hiz.x;
+            const int* lk = &nd.link.x;
+            for (int k = 0; k < 4; k++)
+                if (lk[k] != RT_LINK_NONE) { lo = min3(lo, f3(lx[k], ly[k], lz[k])); hi = max3(hi, f3(hx[k], hy[k], hz[k])); any = true; }
+        }
+        for (int oi : hs.sep_mesh) {
+            const RtMesh& m = d->meshes[d->objects[oi].mesh];
+            if (m.n_faces <= 0) continue;
+            float3 glo, ghi;
+            if (m.gate == RT_GATE_SPHERE) { const float r = fabsf(m.gate_radius); glo = h3(m.gate_center) - f3(r, r, r); ghi = h3(m.gate_center) + f3(r, r, r); }
+            else { glo = min3(h3(m.gate_min), h3(m.gate_max)); ghi = max3(h3(m.gate_min), h3(m.gate_max)); }
+            lo = min3(lo, glo); hi = max3(hi, ghi); any = true;
+        }
+        ok = any && finite3(lo) && finite3(hi);
+        V.has_world = ok ? 1 : 0;
+        if (ok) {
+            ObjBound wb{lo, hi, true};
+            const float pad = 4.0f * bound_pad(wb);
+            V.world_lo = lo - f3(pad, pad, pad); V.world_hi = hi + f3(pad, pad, pad);
+        } else { V.world_lo = f3(-INFINITY, -INFINITY, -INFINITY); V.world_hi = f3(INFINITY, INFINITY, INFINITY); }
+    }
     V.tlas_flagged = 0;
     for (const BvhNode4& nd : hs.tlas_nodes) V.tlas_flagged |= (nd.flags.x | nd.flags.y | nd.flags.z | nd.flags.w) & RT_TLAS_NO_TMAX;
     V.any_motion = 0;

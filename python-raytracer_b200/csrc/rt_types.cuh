@@ -6,8 +6,12 @@
 #define RT_MAX_NEST 8        // CSG / transform nesting depth supported (NovelScene uses 5)
 #define RT_BLOCK 128         // threads per block of every ray kernel (the traversal stack layout depends on it)
 #ifndef RT_STACK_DEPTH
-#define RT_STACK_DEPTH 40    // BVH traversal stack entries per ray held in shared memory (object BVH + mesh LBVH share it)
+#define RT_STACK_DEPTH 32    // BVH traversal stack entries per ray held in shared memory (object BVH + mesh LBVH share it)
 #endif
+// further rows of the block's shared stack area that belong to the WARP as a whole: the warp-uniform stack of the packet
+// walks (bvh4_anyhit_packet), RT_PACKET_ROWS * 32 entries per warp
+#define RT_PACKET_ROWS 8
+#define RT_STACK_ROWS (RT_STACK_DEPTH + RT_PACKET_ROWS)
 #ifndef RT_STACK_SPILL
 #define RT_STACK_SPILL 88
 #endif
@@ -15,6 +19,7 @@
 #define RT_TLAS_NO_TMAX 1    // object-BVH child flag
 #define RT_MODE_BRUTE_MESH 1
 #define RT_MODE_LINEAR_TOP 2
+#define RT_MODE_PACKET_TEST 4   // rt_occluded only: answer through the warp-packet walks (occluded_packet) instead of the per-lane ones
 
 // One geometry object, 16-byte aligned so fields load as 128-bit vectors (warp-uniform index
 // -> one broadcast transaction).  Meaning of a/b per kind as in RtObject (include/b200rt.h).
@@ -99,6 +104,10 @@ struct SceneView {
     // of a warp enter the (long) LBVH traversal together instead of at whatever step their walk happens to reach the mesh
     const int* sep_mesh;
     int n_sep_mesh;
+    // padded union of the object BVH's root boxes and the separate meshes' gate volumes: a ray that misses it needs neither
+    // walk (most rays of an open scene: ground-plane hits whose shadow rays leave upwards).  Lives in the kernel parameter bank.
+    int has_world;
+    float3 world_lo, world_hi;
     // conservative bounds of every object IN ITS PARENT'S SPACE (children of CSG / transform nodes; top-level objects and
     // unbounded ones carry [-inf, +inf]): a ray or point outside them cannot hit / be inside that child, so whole subtrees
     // of a node are skipped without transforming the ray into them.  NULL when the scene has no nodes.

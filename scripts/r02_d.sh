@@ -1,0 +1,14 @@
+set -x
+python -m pytest tests -m gpu -q 2>&1 | tail -30 > gpurun_out/r02d_pytest.log; tail -6 gpurun_out/r02d_pytest.log
+L=$PWD/python-raytracer_b200/csrc
+python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/r02d_bench_sh8.json 2> gpurun_out/r02d_bench.err
+for v in sh7 sh6; do B200RT_LIB=$L/libb200rt_$v.so python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/r02d_bench_$v.json 2>> gpurun_out/r02d_bench.err; done
+for f in gpurun_out/r02d_bench*.json; do python - "$f" <<'PY'
+import json,sys
+try:
+    d=json.loads(open(sys.argv[1]).read().strip().splitlines()[-1])
+    print(sys.argv[1], round(d["ms_per_step"],2), round(d["e2e"]["ms_per_step"],2), round(d["e2e_u8"]["ms_per_step"],2), {k:round(v,2) for k,v in d["kernel_ms_per_frame"].items()}, d["image_sha256"][:12])
+except Exception as e: print(sys.argv[1], "ERR", e)
+PY
+done
+tail -5 gpurun_out/r02d_bench.err

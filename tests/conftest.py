@@ -163,3 +163,22 @@ def load_fuzz(seed, width=128, height=96):
     sc = rt.scene_parser.load_scene_dict(fuzz_scenes.make(seed, width, height), os.path.join(GOLDEN, "scenes"))
     sc.jitter_seed = 0x5EED
     return sc
+
+
+def morton63_keys(verts_f32, faces):
+    """numpy restatement of csrc/rt_bvh.cuh morton63 over triangle centroids (float32 arithmetic in the same order)."""
+    v = np.asarray(verts_f32, dtype=np.float32)
+    lo, hi = v.min(0), v.max(0)
+    ext = hi - lo
+    inv = np.where(ext > 0, np.float32(1) / np.where(ext > 0, ext, 1).astype(np.float32), 0).astype(np.float32)
+    a, b, c = v[faces[:, 0]], v[faces[:, 1]], v[faces[:, 2]]
+    cen = ((a + b) + c) * np.float32(1.0 / 3.0)
+    x = np.clip((cen - lo) * inv, 0, 1).astype(np.float32)
+    q = np.minimum(x * np.float32(2097152.0), np.float32(2097151.0)).astype(np.uint64)
+
+    def expand(u):
+        u = u & np.uint64(0x1fffff)
+        for sh, mask in ((32, 0x1f00000000ffff), (16, 0x1f0000ff0000ff), (8, 0x100f00f00f00f00f), (4, 0x10c30c30c30c30c3), (2, 0x1249249249249249)):
+            u = (u | u << np.uint64(sh)) & np.uint64(mask)
+        return u
+    return (expand(q[:, 0]) << np.uint64(2)) | (expand(q[:, 1]) << np.uint64(1)) | expand(q[:, 2])

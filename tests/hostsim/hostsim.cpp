@@ -52,7 +52,7 @@ static void build_mesh(const RtMesh& m, HostMesh& hm, DevMesh& g) {
     hm.order.resize(n);
     for (int i = 0; i < n; i++) {
         float3 a = vert_at(m.verts, m.faces[3 * i]), b = vert_at(m.verts, m.faces[3 * i + 1]), c = vert_at(m.verts, m.faces[3 * i + 2]);
-        keys[i] = morton63((a + b + c) * (1.0f / 3.0f), lo, inv_ext);
+        keys[i] = morton63(tri_centroid(a, b, c), lo, inv_ext);
         hm.order[i] = i;
     }
     std::stable_sort(hm.order.begin(), hm.order.end(), [&](int a, int b) { return keys[a] < keys[b]; });

@@ -434,7 +434,35 @@ def test_gpu_lbvh_equals_host_restatement_on_a_large_mesh_with_equal_keys(lib):
     assert nt.value == len(faces) == len(order_ref) and n4.value == len(nodes_ref)
     nodes = np.zeros_like(nodes_ref); order = np.zeros_like(order_ref)
     abi.check(lib, lib.rt_scene_bvh_download(h, 0, nodes.ctypes.data, order.ctypes.data), "rt_scene_bvh_download")
-    assert np.array_equal(order, order_ref)
+    from conftest import morton63_keys
+    keys = morton63_keys(mesh.verts, mesh.faces)
+    assert np.array_equal(np.argsort(keys, kind="stable"), order_ref)     # the host restatement sorts these keys, stably
+    assert sorted(order.tolist()) == list(range(len(faces))), "GPU leaf order is not a permutation"
+    wrong = np.flatnonzero(order != order_ref)
+    assert len(wrong) == 0, (f"{len(wrong)} of {len(order)} leaf slots differ; GPU order sorted by key: {bool((np.diff(keys[order].astype(np.int64)) >= 0).all())}; "
+                             f"differing slots hold tied keys only: {bool((keys[order[wrong]] == keys[order_ref[wrong]]).all())}; first: {wrong[:8]}, "
+                             f"gpu {order[wrong[:8]]}, host {order_ref[wrong[:8]]}")
     assert np.array_equal(nodes.view(np.int32), nodes_ref.view(np.int32))
     img = sc.render_region(0, 64, 0, 64)                                 # and the tree is usable
     assert sc.last_counters["error_flags"] == 0 and img.max() > 0
+
+
+@pytest.mark.parametrize("case,centre", [("TwoSpheresPlane", (0, 1, -0.5)), ("TorusMesh_flat", (0, 0, 0)), ("TorusMesh_smooth", (0, 0, 0)),
+                                         ("MeshInNode", (0, 1, 0)), ("NovelScene2_small", (0, 1, 0)), ("Fuzz12", (0, 1, 0))])
+def test_packet_any_hit_walk_equals_per_ray_walk(case, centre):
+    """The level-0 shadow kernel walks the object BVH and the mesh LBVHs WARP by warp (occluded_packet: one node per step for
+    all 32 lanes, a child is entered when any lane's ray touches it, leaves are tested once per warp).  Any-hit answers do not
+    depend on the visiting order, so every ray must get exactly the answer of its own walk - also for rays that have nothing
+    in common (random rays here; in the renderer the 32 rays of a warp are nearly the same ray)."""
+    sc = load_case(case)
+    rng = np.random.default_rng(77)
+    n = 30000 + 17                                                     # a ragged last warp
+    o, d = _random_rays(rng, n, np.array(centre, dtype=np.float64))
+    tmax = np.where(rng.random(n) < 0.5, 1.0, np.inf).astype(np.float32)
+    times = rng.choice(np.asarray(sc.vc.motion_times, dtype=np.float64), size=n).astype(np.float32)
+    per_ray = sc.occluded(o, d, tmax, times)
+    packet = sc.occluded(o, d, tmax, times, mesh_mode=4)
+    assert np.array_equal(per_ray, packet)
+    assert 0 < per_ray.sum() < n
+    if sc.flatten().desc.n_meshes:                                     # and with the brute-force face loop inside the packet walk
+        assert np.array_equal(per_ray, sc.occluded(o, d, tmax, times, mesh_mode=5))
