@@ -43,6 +43,9 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--batch-rays", type=int, default=0, help="rays per wavefront batch (0 = library default)")
+    ap.add_argument("--fan-in", default=None, choices=["shared", "gather"],
+                    help="N > 1: 'shared' = every rank's k_resolve stores its tiles into rank 0's frame over NVLink peer access (default); "
+                         "'gather' = NCCL gather of compact tile buffers + scatter kernel")
     ap.add_argument("--mode-bits", type=int, default=0, help="RtRenderJob.mesh_mode test-aid bits OR-ed into every job (tuning experiments)")
     return ap.parse_args()
 
@@ -229,7 +232,7 @@ def run_ours(a):
     peaks = _abi.RtPeaks()
     _abi.check(lib, lib.rt_measure_peaks(C.byref(peaks), torch.cuda.current_stream().cuda_stream), "rt_measure_peaks")
 
-    sharder = TileSharder(sc, rank, world)
+    sharder = TileSharder(sc, rank, world, fan_in=a.fan_in)
     W, H = a.width, a.height
 
     def barrier():
@@ -250,7 +253,7 @@ def run_ours(a):
         dist.all_reduce(tallies)
     tl = [int(x) for x in tallies.tolist()]
     rays_frame = sum(tl[:4])
-    launches_frame = tl[4] + (1 if world > 1 else 0)          # + rank 0's k_assemble
+    launches_frame = tl[4] + sharder.extra_launches_per_frame          # + rank 0's k_assemble in 'gather' mode
 
     # ---- timed region 1: inputs resident in HBM, image left on the device (rank 0).  Profiling instrumentation is OFF.
     sampler = ClockSampler(local_rank) if rank == 0 else None
@@ -377,7 +380,7 @@ def run_ours(a):
         out = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
                "ms_per_step": ms_total / a.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                "dtype": "f32", "data": "synthetic",
-               "config": {**workload_config(a), "tiles": f"{sc.tile[0]}x{sc.tile[1]} interleaved over ranks",
+               "config": {**workload_config(a), "tiles": f"{sc.tile[0]}x{sc.tile[1]} interleaved over ranks", "fan_in": sharder.fan_in,
                           "l2_policy": "working set (BVH nodes+triangles+sample/queue buffers) exceeds the 126 MB L2; no flush between frames",
                           "env_knobs": knobs},
                "rays_per_frame": dict(zip(RAY_KEYS, tl[:4])),
@@ -406,6 +409,7 @@ def run_ours(a):
         if not a.no_cpu_baseline and world == 1:
             out["cpu_baseline"] = cpu_sample(sc, a.cpu_seconds)
         print(json.dumps(out), flush=True)
+    sharder.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -167,12 +167,15 @@ typedef struct RtRenderJob {
     int32_t col0, ncols, row0, nrows;
     int32_t tile_w, tile_h;
     int32_t rank, world;
-    int32_t direct;
+    int32_t direct;          /* 0 = compact tile buffer; 1 = reference layout (world must be 1); RT_DIRECT_SHARED_FRAME = reference
+                              * layout of the WHOLE region with world > 1: every rank writes its own tiles into one shared frame */
     int32_t mesh_mode;       /* test aids, bit field: 0 = accelerated; bit 0 = brute force over all faces (mesh.py:77);
                               * bit 1 = plain in-order loop over the top-level objects (scene.py:87,160) instead of the object BVH;
                               * bit 2 (rt_occluded only) = the warp-packet any-hit walks the level-0 shadow kernel uses */
     int64_t max_batch_rays;  /* 0 = default */
 } RtRenderJob;
+
+#define RT_DIRECT_SHARED_FRAME 2
 
 /* Device-side tallies of one rt_render call */
 typedef struct RtCounters {
@@ -246,6 +249,17 @@ int rt_job_extent(const RtRenderJob* job, int64_t* n_local_tiles, int64_t* n_flo
  * each rank's buffer starting at rank_offsets_floats[r]) into the reference layout (ncols, nrows, 3). */
 int rt_assemble_tiles(const RtRenderJob* job, const float* d_gathered, const int64_t* rank_offsets_floats,
                       float* d_out, void* stream);
+
+/* Fan-in without a gather (render.nu:10-15 + glue.py:19-22 fused into the render): one process per GPU of an NVLink/NVSwitch
+ * box.  Rank 0 allocates the frame with rt_shared_alloc and hands the 64-byte handle to the other ranks (any transport:
+ * torch.distributed broadcast); they map it with rt_shared_open (CUDA IPC, peer access enabled on first use) and pass the
+ * mapped pointer as d_out of rt_render with job.direct = RT_DIRECT_SHARED_FRAME: k_resolve then stores every finished pixel of
+ * their tiles straight into rank 0's HBM.  The caller orders the readers after the writers (one stream-ordered barrier). */
+typedef struct RtIpcHandle { unsigned char bytes[64]; } RtIpcHandle;
+int rt_shared_alloc(int64_t bytes, void** d_ptr, RtIpcHandle* handle);
+int rt_shared_free(void* d_ptr);
+int rt_shared_open(const RtIpcHandle* handle, void** d_ptr);
+int rt_shared_close(void* d_ptr);
 
 /* Replaces main.py:31-33 / glue.py:23-25: rot90 + (image*255) truncation, (ncols,nrows,3) f32 -> (nrows,ncols,3) u8 */
 int rt_finalize_u8(const float* d_image, int32_t ncols, int32_t nrows, uint8_t* d_out_u8, void* stream);

@@ -99,6 +99,13 @@ class RtProfile(C.Structure):
                 ("n_l1_hit", C.c_uint64), ("n_deep", C.c_uint64), ("n_tail", C.c_uint64)]
 
 
+class RtIpcHandle(C.Structure):
+    _fields_ = [("bytes", C.c_ubyte * 64)]
+
+
+DIRECT_SHARED_FRAME = 2
+
+
 class RtPeaks(C.Structure):
     _fields_ = [("fp32_fma_tflops", C.c_double), ("issue_ginst", C.c_double), ("lsu_gwavefronts", C.c_double),
                 ("fp32_fma_tflops_nominal", C.c_double), ("issue_ginst_nominal", C.c_double),
@@ -286,7 +293,8 @@ LIB_PATH = os.environ.get("B200RT_LIB") or os.path.join(os.path.dirname(os.path.
 ENTRY_POINTS = ["rt_scene_create", "rt_scene_build_bvh", "rt_render", "rt_render_host", "rt_render_u8_host", "rt_job_extent",
                 "rt_assemble_tiles", "rt_finalize_u8", "rt_scene_destroy", "rt_scene_bvh_stats",
                 "rt_scene_bvh_download", "rt_last_error", "rt_abi_version", "rt_trace_rays", "rt_occluded",
-                "rt_scene_profile", "rt_scene_profile_read", "rt_measure_peaks", "rt_obj_load", "rt_obj_copy", "rt_obj_free", "rt_mesh_ingest"]
+                "rt_scene_profile", "rt_scene_profile_read", "rt_measure_peaks",
+                "rt_shared_alloc", "rt_shared_free", "rt_shared_open", "rt_shared_close", "rt_obj_load", "rt_obj_copy", "rt_obj_free", "rt_mesh_ingest"]
 
 
 class B200RTError(RuntimeError):
@@ -321,6 +329,10 @@ def load_library(path=None):
     lib.rt_scene_profile.argtypes = [vp, i32]
     lib.rt_scene_profile_read.argtypes = [vp, C.POINTER(RtProfile)]
     lib.rt_measure_peaks.argtypes = [C.POINTER(RtPeaks), vp]
+    lib.rt_shared_alloc.argtypes = [C.c_int64, C.POINTER(vp), C.POINTER(RtIpcHandle)]
+    lib.rt_shared_free.argtypes = [vp]
+    lib.rt_shared_open.argtypes = [C.POINTER(RtIpcHandle), C.POINTER(vp)]
+    lib.rt_shared_close.argtypes = [vp]
     lib.rt_last_error.restype = C.c_char_p
     lib.rt_last_error.argtypes = []
     lib.rt_abi_version.argtypes = []

@@ -397,7 +397,7 @@ extern "C" int rt_job_extent(const RtRenderJob* job, int64_t* n_local_tiles, int
     PixelMap pm; long long nt;
     UP(make_pixel_map(job, pm, nt));
     if (n_local_tiles) *n_local_tiles = nt;
-    if (n_floats) *n_floats = (job->direct && job->world == 1) ? (int64_t)job->ncols * job->nrows * 3 : pm.n_local_pixels * 3;
+    if (n_floats) *n_floats = ((job->direct && job->world == 1) || job->direct == RT_DIRECT_SHARED_FRAME) ? (int64_t)job->ncols * job->nrows * 3 : pm.n_local_pixels * 3;
     return RT_OK;
 }
 
@@ -461,7 +461,10 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
         CU(cudaFuncSetAttribute(k_shadow<HAS_NODES, SHADOW_PACKET>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         CU(cudaFuncSetAttribute(k_shadow<HAS_NODES, SHADOW_ROWS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     }
-    const int direct = (job->direct && job->world == 1) ? 1 : 0;
+    // direct: k_resolve writes the reference layout (ncols, nrows, 3) instead of the compact tile buffer.  With world > 1 only for
+    // RT_DIRECT_SHARED_FRAME: d_out is then the WHOLE frame (typically rank 0's buffer mapped through NVLink peer access) and
+    // this rank fills in its own tiles - the fan-in of glue.py:19-22 fused into the last kernel of the render.
+    const int direct = ((job->direct && job->world == 1) || job->direct == RT_DIRECT_SHARED_FRAME) ? 1 : 0;
     const int waves = grid_waves(false), waves_deep = grid_waves(true);
     const int b_hit = sc->sm_count * (HAS_NODES ? RT_MIN_BLOCKS_HIT_CSG : RT_MIN_BLOCKS_HIT);
     const int b_shadow = sc->sm_count * (HAS_NODES ? RT_MIN_BLOCKS_SHADOW_CSG : RT_MIN_BLOCKS_SHADOW);
@@ -585,17 +588,42 @@ extern "C" int rt_render_u8_host(RtScene* sc, const RtRenderJob* job, uint8_t* h
 extern "C" int rt_assemble_tiles(const RtRenderJob* job, const float* d_gathered, const int64_t* rank_offsets_floats, float* d_out, void* stream) {
     PixelMap pm; long long nt;
     UP(make_pixel_map(job, pm, nt));
-    if (job->world > 64) return fail(RT_ERR_LIMIT, "world > 64");
+    if (job->world > RT_MAX_WORLD) return fail(RT_ERR_LIMIT, "world > 64");
     cudaStream_t st = (cudaStream_t)stream;
-    long long* d_off = nullptr;
-    CU(cudaMallocAsync((void**)&d_off, sizeof(long long) * job->world, st));
-    CU(cudaMemcpyAsync(d_off, rank_offsets_floats, sizeof(long long) * job->world, cudaMemcpyHostToDevice, st));
+    RankOffsets off;                                     // by value in the kernel's parameter bank: no allocation, no copy per frame
+    for (int r = 0; r < job->world; r++) off.v[r] = rank_offsets_floats[r];
     const long long n = (long long)job->ncols * job->nrows;
-    if (n > 0) k_assemble<<<(int)((n + 255) / 256), 256, 0, st>>>(pm, d_gathered, d_off, d_out);
-    CU(cudaFreeAsync(d_off, st));
+    if (n > 0) k_assemble<<<(int)((n + 255) / 256), 256, 0, st>>>(pm, d_gathered, off, d_out);
     CU(cudaGetLastError());
     return RT_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------
+// Frame buffers shared between the ranks of one box (one process per GPU): rank 0 allocates and exports, the others open the
+// handle and get a pointer into rank 0's HBM through NVLink peer access (cudaIpc*).  rt_render with RT_DIRECT_SHARED_FRAME
+// then writes every rank's tiles straight into it.
+extern "C" int rt_shared_alloc(int64_t bytes, void** d_ptr, RtIpcHandle* handle) {
+    if (!d_ptr || !handle || bytes <= 0) return fail(RT_ERR_INVALID, "rt_shared_alloc: bad argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) <= sizeof(handle->bytes), "RtIpcHandle too small");
+    void* p = nullptr;
+    CU(cudaMalloc(&p, (size_t)bytes));                    // a plain allocation of its own: the IPC handle maps exactly this range
+    cudaIpcMemHandle_t h;
+    cudaError_t e = cudaIpcGetMemHandle(&h, p);
+    if (e != cudaSuccess) { cudaFree(p); return fail(RT_ERR_CUDA, std::string("cudaIpcGetMemHandle: ") + cudaGetErrorString(e)); }
+    memset(handle->bytes, 0, sizeof handle->bytes);
+    memcpy(handle->bytes, &h, sizeof h);
+    *d_ptr = p;
+    return RT_OK;
+}
+extern "C" int rt_shared_free(void* d_ptr) { if (d_ptr) CU(cudaFree(d_ptr)); return RT_OK; }
+extern "C" int rt_shared_open(const RtIpcHandle* handle, void** d_ptr) {
+    if (!d_ptr || !handle) return fail(RT_ERR_INVALID, "rt_shared_open: bad argument");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle->bytes, sizeof h);
+    CU(cudaIpcOpenMemHandle(d_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return RT_OK;
+}
+extern "C" int rt_shared_close(void* d_ptr) { if (d_ptr) CU(cudaIpcCloseMemHandle(d_ptr)); return RT_OK; }
 
 extern "C" int rt_finalize_u8(const float* d_image, int32_t ncols, int32_t nrows, uint8_t* d_out_u8, void* stream) {
     const long long n = (long long)ncols * nrows;

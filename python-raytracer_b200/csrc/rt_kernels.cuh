@@ -347,7 +347,9 @@ __global__ void k_resolve(PixelMap pm, long long pixel_begin, int n_pixels, int 
 }
 
 // ---- fan-in (glue.py:19-22) ----------------------------------------------------------------------------
-__global__ void k_assemble(PixelMap pm, const float* __restrict__ gathered, const long long* __restrict__ rank_off,
+#define RT_MAX_WORLD 64
+struct RankOffsets { long long v[RT_MAX_WORLD]; };      // first float of every rank's compact buffer inside `gathered`
+__global__ void k_assemble(PixelMap pm, const float* __restrict__ gathered, const RankOffsets rank_off,
                            float* __restrict__ out) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (long long)pm.ncols * pm.nrows) return;
@@ -357,7 +359,7 @@ __global__ void k_assemble(PixelMap pm, const float* __restrict__ gathered, cons
     const int rank = (int)(gt % pm.world);
     const long long lt = gt / pm.world;
     const int q = (r - trow * pm.tile_h) * pm.tile_w + (c - tcol * pm.tile_w);
-    const float* src = gathered + rank_off[rank] + (lt * pm.tile_px + q) * 3;
+    const float* src = gathered + rank_off.v[rank] + (lt * pm.tile_px + q) * 3;
     out[i * 3] = src[0]; out[i * 3 + 1] = src[1]; out[i * 3 + 2] = src[2];
 }
 

@@ -77,7 +77,7 @@ class Scene:
         job.row0, job.nrows = int(row0), int(self.vc.height if nrows is None else nrows)
         job.tile_w, job.tile_h = self.tile
         job.rank, job.world = int(rank), int(world)
-        job.direct = 1 if direct else 0
+        job.direct = int(direct) if not isinstance(direct, bool) else (1 if direct else 0)    # 2 = _abi.DIRECT_SHARED_FRAME
         job.mesh_mode = int(mesh_mode) | int(getattr(self, "debug_mode_bits", 0))
         job.max_batch_rays = int(max_batch_rays or getattr(self, "max_batch_rays", 0))
         return job

@@ -22,14 +22,20 @@ res = {}
 scenes = {"MirrorRefraction": load_case("MirrorRefraction"),
           "synthetic_640x360x4": synthetic.make_scene(width=640, height=360, aa_samples=4, grid=(256, 128))}
 for name, sc in scenes.items():
-    sh = TileSharder(sc, rank, world)
-    img = sh.render()
-    torch.cuda.synchronize()
-    if rank == 0:
-        got = img.cpu().numpy().reshape(sc.vc.width, sc.vc.height, 3)
-        ref = sc.render_region(0, sc.vc.width, 0, sc.vc.height)
-        res[name] = {"bit_identical": bool(np.array_equal(got, ref)), "max_abs_diff": float(np.abs(got - ref).max())}
-    dist.barrier()
+    for fan_in in ("shared", "gather"):      # NVLink peer stores from k_resolve into rank 0's frame / NCCL gather + scatter kernel
+        sh = TileSharder(sc, rank, world, fan_in=fan_in)
+        for frame in range(3):               # the shared frame is double-buffered: three frames touch both buffers
+            img = sh.render()
+            torch.cuda.synchronize()
+            if rank == 0:
+                got = img.cpu().numpy().reshape(sc.vc.width, sc.vc.height, 3)
+                ref = sc.render_region(0, sc.vc.width, 0, sc.vc.height)
+                ok = bool(np.array_equal(got, ref))
+                prev = res.get(f"{name}/{fan_in}", {"bit_identical": True, "max_abs_diff": 0.0})
+                res[f"{name}/{fan_in}"] = {"bit_identical": ok and prev["bit_identical"],
+                                           "max_abs_diff": max(prev["max_abs_diff"], float(np.abs(got - ref).max()))}
+            dist.barrier()
+        sh.close()
 if rank == 0:
     print(json.dumps({"world": world, "results": res}))
     assert all(v["bit_identical"] for v in res.values())
