@@ -147,7 +147,9 @@ typedef struct RtSceneDesc {
     int32_t n_xforms;
     int32_t n_meshes;
     int32_t n_textures;
-    int32_t _pad;
+    int32_t mesh_motion;     /* EXTENSION, 0 = reference behaviour: the reference stores a mesh's `speed` (scene_parser.py:255) and never
+                              * uses it (mesh.py:72-153: meshes stand still).  Non-zero: mesh objects translate by speed * time exactly
+                              * like spheres / planes / boxes do (simple_geometry.py:21-24), tested against the oracle extended the same way */
     const RtLight* lights;
     const RtMaterial* materials;
     const RtObject* objects;

@@ -356,9 +356,15 @@ static v3 box_get_diffuse(Ctx* cx, int oi, v3 point, int* err) {
 }
 
 /* ---------------------------------------------------------------- bounding volumes, bounding_volumes.py */
-static int gate_intersect(const RtMesh* m, const Ray* r) {
+/* `shift`: (0,0,0) in the reference (meshes stand still, mesh.py:72-153).  EXTENSION (RtSceneDesc.mesh_motion, not reference
+ * behaviour): speed * current_time, added to the bounding volume and to every vertex the way simple_geometry.py:21-24 moves
+ * the primitives (float32 vec3 + vec3 * float). */
+static inline v3 mesh_shift(const Ctx* cx, const RtObject* o) {
+    return cx->s->mesh_motion ? vscaled(v3p(o->speed), cx->time) : V3(0, 0, 0);
+}
+static int gate_intersect(const RtMesh* m, const Ray* r, v3 shift) {
     if (m->gate == RT_GATE_SPHERE) {  /* bounding_volumes.py:18-37 */
-        v3 center = v3p(m->gate_center);
+        v3 center = vadd(v3p(m->gate_center), shift);
         v3 oc = vsub(r->o, center);
         double a = (double)vdot(r->d, r->d);
         double b = 2.0 * (double)vdot(r->d, oc);
@@ -371,7 +377,7 @@ static int gate_intersect(const RtMesh* m, const Ray* r) {
         return t > 0;
     }
     Interval e, x;   /* bounding_volumes.py:49-83 */
-    if (!slab_intervals(v3p(m->gate_min), v3p(m->gate_max), r, &e, &x)) return 0;
+    if (!slab_intervals(vadd(v3p(m->gate_min), shift), vadd(v3p(m->gate_max), shift), r, &e, &x)) return 0;
     if (e.start > x.end || e.start < 0) return 0;
     return 1;
 }
@@ -389,10 +395,12 @@ static void mesh_intersect(Ctx* cx, int oi, const Ray* r, HitList* out) {
     const RtObject* o = &cx->s->objects[oi];
     const RtMesh* m = &cx->s->meshes[o->mesh];
     cx->c.prim_tests++;
-    if (!gate_intersect(m, r)) return;
+    const v3 shift = mesh_shift(cx, o);
+    if (!gate_intersect(m, r, shift)) return;
     for (int f = 0; f < m->n_faces; f++) {
         const int32_t* fc = m->faces + 3 * (size_t)f;
         v3 v0 = v3p(m->verts + 3 * (size_t)fc[0]), v1 = v3p(m->verts + 3 * (size_t)fc[1]), v2 = v3p(m->verts + 3 * (size_t)fc[2]);
+        if (cx->s->mesh_motion) { v0 = vadd(v0, shift); v1 = vadd(v1, shift); v2 = vadd(v2, shift); }
         cx->c.tri_tests++;
         v3 e1 = vsub(v1, v0), e2 = vsub(v2, v0);
         v3 normal = vnormalize(vcross(e1, e2));
@@ -424,10 +432,12 @@ static int mesh_shadow(Ctx* cx, int oi, const Ray* r, double tmax) {
     const RtObject* o = &cx->s->objects[oi];
     const RtMesh* m = &cx->s->meshes[o->mesh];
     cx->c.prim_tests++;
-    if (!gate_intersect(m, r)) return 0;
+    const v3 shift = mesh_shift(cx, o);
+    if (!gate_intersect(m, r, shift)) return 0;
     for (int f = 0; f < m->n_faces; f++) {
         const int32_t* fc = m->faces + 3 * (size_t)f;
         v3 v0 = v3p(m->verts + 3 * (size_t)fc[0]), v1 = v3p(m->verts + 3 * (size_t)fc[1]), v2 = v3p(m->verts + 3 * (size_t)fc[2]);
+        if (cx->s->mesh_motion) { v0 = vadd(v0, shift); v1 = vadd(v1, shift); v2 = vadd(v2, shift); }
         cx->c.tri_tests++;
         v3 normal = vcross(vsub(v1, v0), vsub(v2, v0));   /* un-normalised */
         double denom = (double)vdot(r->d, normal);

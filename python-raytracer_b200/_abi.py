@@ -68,7 +68,7 @@ class RtSceneDesc(C.Structure):
                 ("ambient", f3), ("max_depth", C.c_int32), ("jitter_seed", C.c_uint64),
                 ("n_lights", C.c_int32), ("n_materials", C.c_int32), ("n_objects", C.c_int32),
                 ("n_top", C.c_int32), ("n_xforms", C.c_int32), ("n_meshes", C.c_int32),
-                ("n_textures", C.c_int32), ("_pad", C.c_int32),
+                ("n_textures", C.c_int32), ("mesh_motion", C.c_int32),
                 ("lights", C.c_void_p), ("materials", C.c_void_p), ("objects", C.c_void_p),
                 ("xforms", C.c_void_p), ("meshes", C.c_void_p), ("textures", C.c_void_p)]
 
@@ -172,7 +172,7 @@ def flatten(scene, jitter_seed=DEFAULT_JITTER_SEED, max_depth=DEFAULT_MAX_DEPTH)
 
     objs_py = list(scene.objects)
     recs = [None] * len(objs_py)
-    xforms, meshes = [], []
+    xforms, meshes, mesh_index = [], [], {}
     i = 0
     while i < len(objs_py):
         o = objs_py[i]
@@ -201,8 +201,12 @@ def flatten(scene, jitter_seed=DEFAULT_JITTER_SEED, max_depth=DEFAULT_MAX_DEPTH)
             r.tex = tex_id(o.texture)
         elif isinstance(o, geom.Mesh):
             r.kind = KIND_MESH
-            r.mesh = len(meshes)
-            meshes.append(o)
+            # instances (deep copies made for `ref` nodes share their arrays, geometry.Mesh.__deepcopy__) -> ONE RtMesh, one LBVH
+            key = (id(o.verts), id(o.faces), id(o.norms), bool(o.flat_shaded), id(o.bounding_volume))
+            if key not in mesh_index:
+                mesh_index[key] = len(meshes)
+                meshes.append(o)
+            r.mesh = mesh_index[key]
         elif isinstance(o, geom.Hierarchy):
             r.kind = KIND_NODE
             r.csg = CSG_TYPES.get(o.hierarchy_type, 3)
@@ -273,6 +277,7 @@ def flatten(scene, jitter_seed=DEFAULT_JITTER_SEED, max_depth=DEFAULT_MAX_DEPTH)
     d.jitter_seed = int(jitter_seed)
     d.n_lights, d.n_materials, d.n_objects = len(scene.lights), len(mats), len(recs)
     d.n_top, d.n_xforms, d.n_meshes, d.n_textures = len(scene.objects), len(xforms), len(meshes), len(texs)
+    d.mesh_motion = 1 if getattr(scene, "mesh_motion", False) else 0
     d.lights = C.cast(light_arr, C.c_void_p)
     d.materials = C.cast(mat_arr, C.c_void_p)
     d.objects = C.cast(obj_arr, C.c_void_p)

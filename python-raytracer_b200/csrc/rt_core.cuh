@@ -70,6 +70,14 @@ RT_HD float3 moved(const DevObject* o, float3 base, float time) { return base + 
 // (base + 0 * time == base for every finite time, so the result is identical)
 RT_HD float3 moved(const TraceCtx& cx, const DevObject* o, float3 base) { return cx.S.any_motion ? moved(o, base, cx.time) : base; }
 
+// Moving meshes (EXTENSION, off unless SceneView::mesh_motion: the reference stores a mesh's `speed` and never uses it,
+// mesh.py:72-153).  A mesh that translates by speed * time is met in ITS rest frame: the ray origin moves by -speed * time,
+// direction and hit times stay, so the one LBVH built over the rest pose serves every motion time (no swept node boxes,
+// no refit); positions go back with +shift, normals are unchanged.
+RT_HD float3 mesh_shift(const TraceCtx& cx, int oi) {
+    return cx.S.mesh_motion ? f3(ld4(&cx.S.objects[oi].speed)) * cx.time : f3(0.0f, 0.0f, 0.0f);
+}
+
 // ------------------------------------------------------------------------------------------------
 // Sphere (simple_geometry.py:20-80).  A = d.d is ray-constant and passed in.
 RT_HD bool sphere_roots(float3 center, float radius, const Ray& r, float A, float& t1, float& t2) {
@@ -561,7 +569,11 @@ RT_HD bool leaf_shadow(TraceCtx& cx, int oi, const Ray& r, float tmax) {
         if (en > ex) return false;
         return RT_SHADOW_EPS < en && en < tmax;
     }
-    case RT_KIND_MESH: return WITH_MESH ? mesh_shadow_cold(cx, cx.S.meshes + o->mesh, r) : false;   // top-level meshes: see occluded()
+    case RT_KIND_MESH: {                                       // top-level meshes: see occluded()
+        if (!WITH_MESH) return false;
+        Ray mr = r; mr.o = r.o - mesh_shift(cx, oi);
+        return mesh_shadow_cold(cx, cx.S.meshes + o->mesh, mr);
+    }
             default: return false;
     }
 }
@@ -721,15 +733,17 @@ template <class Want, class Cand>
 RT_HD_NOINLINE void mesh_leaf_hits(TraceCtx& cx, int oi, const Ray& r, Want& want, Cand& cand) {
     const DevObject* o = cx.S.objects + oi;
     const DevMesh* m = cx.S.meshes + o->mesh;
-    if (!mesh_gate(m, r)) return;
+    const float3 shift = mesh_shift(cx, oi);
+    Ray mr = r; mr.o = r.o - shift;                                 // the mesh's rest frame (== r unless the mesh moves)
+    if (!mesh_gate(m, mr)) return;
     float tmax = RT_INF;
     const int mat = o->n_mats > 0 ? o->mat0 : -2;
-    const RayInv ri = ray_inv(r);
+    const RayInv ri = ray_inv(mr);
     mesh_visit<true>(cx, m, ri, 0.0f, tmax, [&](int slot, float&) {
         float3 v0, v1, v2; int face; float t;
         tri_load(m, slot, v0, v1, v2, face);
-        if (tri_hit(v0, v1, v2, r, t) && want(t)) {
-            Hit h; h.t = t; h.p = r.o + r.d * t; h.n = tri_normal(cx, m, slot, h.p); h.mat = mat; h.geom = oi;
+        if (tri_hit(v0, v1, v2, mr, t) && want(t)) {
+            Hit h; h.t = t; h.p = r.o + r.d * t; h.n = tri_normal(cx, m, slot, mr.o + mr.d * t); h.mat = mat; h.geom = oi;
             cand(h);
         }
         return false;
@@ -906,7 +920,9 @@ RT_HD bool closest_hit(TraceCtx& cx, const Ray& r, Hit& out) {
             const int oi = RT_LDG(S.sep_mesh + k);
             cx.tally.prims++;
             float t; int slot;
-            mesh_closest(cx, S.meshes + S.objects[oi].mesh, r, ri, best, [&](float tt) { return RT_BETTER(tt); }, t, slot);
+            Ray mr = r; RayInv mri = ri;
+            if (S.mesh_motion) { mr.o = r.o - mesh_shift(cx, oi); mri = ray_inv(mr); }
+            mesh_closest(cx, S.meshes + S.objects[oi].mesh, mr, mri, best, [&](float tt) { return RT_BETTER(tt); }, t, slot);
             if (slot >= 0) { best = t; best_obj = oi; best_aux = slot; }
         }
     }
@@ -921,7 +937,7 @@ RT_HD bool closest_hit(TraceCtx& cx, const Ray& r, Hit& out) {
         case RT_KIND_SPHERE: out.n = normalize(out.p - moved(cx, o, f3(ld4(&o->a)))); break;
         case RT_KIND_PLANE: out.n = f3(ld4(&o->b)); out.mat = plane_material(o, out.p, cx.time); break;
         case RT_KIND_BOX: out.n = box_normal(r, best_aux); break;
-        default: out.n = tri_normal(cx, S.meshes + o->mesh, best_aux, out.p); break;
+        default: out.n = tri_normal(cx, S.meshes + o->mesh, best_aux, S.mesh_motion ? (r.o - mesh_shift(cx, best_obj)) + r.d * best : out.p); break;
     }
     return true;
 }
@@ -963,7 +979,9 @@ RT_HD bool occluded(TraceCtx& cx, const Ray& r, float tmax) {
     cx.sbase = 0;
     for (int k = 0; k < S.n_sep_mesh && !occ && in_world; k++) {
         cx.tally.prims++;
-        occ = mesh_shadow(cx, S.meshes + S.objects[RT_LDG(S.sep_mesh + k)].mesh, r, ri);
+        const int oi = RT_LDG(S.sep_mesh + k);
+        if (S.mesh_motion) { Ray mr = r; mr.o = r.o - mesh_shift(cx, oi); occ = mesh_shadow(cx, S.meshes + S.objects[oi].mesh, mr, ray_inv(mr)); }
+        else occ = mesh_shadow(cx, S.meshes + S.objects[oi].mesh, r, ri);
     }
     return occ;
 }
@@ -1085,7 +1103,10 @@ __device__ __forceinline__ bool occluded_packet(TraceCtx& cx, const Ray& r, floa
         });
     for (int k = 0; k < S.n_sep_mesh && __any_sync(RT_FULL_WARP, active); k++) {
         if (active) cx.tally.prims++;
-        if (mesh_shadow_packet(cx, S.meshes + S.objects[RT_LDG(S.sep_mesh + k)].mesh, r, ri, active)) { occ = true; active = false; }
+        const int oi = RT_LDG(S.sep_mesh + k);
+        Ray mr = r; RayInv mri = ri;
+        if (S.mesh_motion) { mr.o = r.o - mesh_shift(cx, oi); mri = ray_inv(mr); }
+        if (mesh_shadow_packet(cx, S.meshes + S.objects[oi].mesh, mr, mri, active)) { occ = true; active = false; }
     }
     return occ;
 }

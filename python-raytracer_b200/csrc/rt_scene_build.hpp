@@ -78,10 +78,14 @@ inline ObjBound object_bound(const RtSceneDesc* d, int oi, float tlo, float thi)
                 b.lo = min3(b.lo, min3(p, q)); b.hi = max3(b.hi, max3(p, q));
             }
             b.finite = true; break;
-        case RT_KIND_MESH: {                                   // meshes do not move
+        case RT_KIND_MESH: {                                   // meshes do not move unless the mesh_motion extension is on
             const RtMesh& m = d->meshes[o.mesh];
             if (m.n_faces <= 0 || m.n_verts <= 0) break;
-            float pad; mesh_bounds(m, b.lo, b.hi, pad);
+            float pad; float3 lo, hi; mesh_bounds(m, lo, hi, pad);
+            for (int k = 0; k < 2; k++) {
+                const float3 sh = d->mesh_motion ? sp * ts[k] : f3(0, 0, 0);
+                b.lo = min3(b.lo, lo + sh); b.hi = max3(b.hi, hi + sh);
+            }
             b.finite = true; break;
         }
         case RT_KIND_NODE: {                                   // hierarchy.py:42-78: hits of the children, mapped by M
@@ -315,6 +319,11 @@ inline int convert_scene(const RtSceneDesc* d, HostScene& hs, std::string& err) 
             float3 glo, ghi;
             if (m.gate == RT_GATE_SPHERE) { const float r = fabsf(m.gate_radius); glo = h3(m.gate_center) - f3(r, r, r); ghi = h3(m.gate_center) + f3(r, r, r); }
             else { glo = min3(h3(m.gate_min), h3(m.gate_max)); ghi = max3(h3(m.gate_min), h3(m.gate_max)); }
+            if (d->mesh_motion)                                  // the gate volume moves with the mesh: sweep it over the motion times
+                for (int t = 0; t < d->n_times; t++) {
+                    const float3 sh = h3(d->objects[oi].speed) * (float)d->motion_times[t];
+                    lo = min3(lo, glo + sh); hi = max3(hi, ghi + sh);
+                }
             lo = min3(lo, glo); hi = max3(hi, ghi); any = true;
         }
         ok = any && finite3(lo) && finite3(hi);
@@ -327,6 +336,7 @@ inline int convert_scene(const RtSceneDesc* d, HostScene& hs, std::string& err) 
     }
     V.tlas_flagged = 0;
     for (const BvhNode4& nd : hs.tlas_nodes) V.tlas_flagged |= (nd.flags.x | nd.flags.y | nd.flags.z | nd.flags.w) & RT_TLAS_NO_TMAX;
+    V.mesh_motion = d->mesh_motion ? 1 : 0;
     V.any_motion = 0;
     for (int i = 0; i < d->n_objects; i++)
         if (d->objects[i].speed[0] != 0.0f || d->objects[i].speed[1] != 0.0f || d->objects[i].speed[2] != 0.0f) V.any_motion = 1;

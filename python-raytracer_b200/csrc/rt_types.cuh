@@ -98,6 +98,7 @@ struct SceneView {
     const BvhNode4* tlas_nodes;  // NULL: no object BVH (fewer than 2 bounded objects) -> plain loop over n_top
     int tlas_flagged;            // some child of the object BVH carries RT_TLAS_NO_TMAX (otherwise the walk skips the flag rows)
     int any_motion;              // some object has a non-zero speed (otherwise primitive tests skip the speed loads)
+    int mesh_motion;             // EXTENSION (RtSceneDesc::mesh_motion): meshes translate by speed * time like the primitives do
     const int* lin_objs;         // top-level objects tested one by one, scene order: no finite bounds (planes, nodes holding
     int n_lin;                   // planes), or everything but the separate meshes when there is no object BVH
     // top-level meshes are kept OUT of that walk and traversed after it (gate test each, scene order), so that the lanes

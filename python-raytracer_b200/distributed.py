@@ -35,6 +35,11 @@ class TileSharder:
         self.gathered = None
         self._shared_ptr = None          # rank 0: the allocation; others: the peer mapping
         self.extra_launches_per_frame = 0
+        self.ops = None
+        if self.device.type == "cuda":   # the render / scatter calls go through torch.ops.b200rt.* (current stream, tensors)
+            from . import torch_ext
+            self.ops = torch_ext.load()
+            self._torch_ext = torch_ext
         if self.fan_in == "shared":
             self._init_shared()
             return
@@ -79,8 +84,10 @@ class TileSharder:
         self._shared_ptr = ptr
         self.job = self.scene.make_job(0, W, 0, H, rank=self.rank, world=self.world, direct=_abi.DIRECT_SHARED_FRAME)
         self._flag = torch.zeros(1, dtype=torch.int32, device=self.device)
-        if self.rank == 0:          # tensor views of the two frames for the caller (no copy): rank 0's own allocation
-            self._images = [_device_tensor_from_ptr(ptr.value + k * self._frame_bytes, W * H * 3, self.device) for k in (0, 1)]
+        # tensor views of the two frames (no copy): rank 0's own allocation / the peer mapping of it on the other ranks
+        self._images = [_device_tensor_from_ptr(ptr.value + k * self._frame_bytes, W * H * 3, self.device) for k in (0, 1)]
+        self._job_t = self._torch_ext.job_tensor(self.job)
+        if self.rank == 0:
             self.image = self._images[0]
 
     def close(self):
@@ -88,8 +95,8 @@ class TileSharder:
             torch.cuda.synchronize()
             if self.world > 1:
                 dist.barrier(group=self.group)             # nobody unmaps / frees while another rank may still store
+            self.image = self._images = None
             if self.rank == 0:
-                self.image = self._images = None
                 self.lib.rt_shared_free(self._shared_ptr)
             else:
                 self.lib.rt_shared_close(self._shared_ptr)
@@ -121,13 +128,21 @@ class TileSharder:
         if self.fan_in == "shared":
             k = self._frame_no & 1
             self._frame_no += 1
-            self.scene.render_device(C.c_void_p(self._shared_ptr.value + k * self._frame_bytes), self.job, counters=counters, stream=stream)
+            if counters is None:
+                self.ops.render_into(self._images[k], self._torch_ext.scene_handle(self.scene), self._job_t)
+            else:       # the tallies come back through the C ABI call (it synchronises the stream)
+                self.scene.render_device(C.c_void_p(self._shared_ptr.value + k * self._frame_bytes), self.job, counters=counters, stream=stream)
             # stream-ordered on every rank after its own stores; rank 0's later work (copies, conversions) waits for all of them
             dist.all_reduce(self._flag, group=self.group)
             if self.rank == 0:
                 self.image = self._images[k]
             return self.image if self.rank == 0 else None
-        self.scene.render_device(self.local.data_ptr(), self.job, counters=counters, stream=stream)
+        if counters is None and self.ops is not None:
+            if not hasattr(self, "_job_t"):
+                self._job_t = self._torch_ext.job_tensor(self.job)
+            self.ops.render_into(self.local, self._torch_ext.scene_handle(self.scene), self._job_t)
+        else:           # the tallies come back through the C ABI call (it synchronises the stream)
+            self.scene.render_device(self.local.data_ptr(), self.job, counters=counters, stream=stream)
         if self.world == 1:
             return self.image
         self.gather()

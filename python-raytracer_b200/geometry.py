@@ -180,6 +180,32 @@ class Mesh(Geometry):
         else:
             self.bounding_volume = BoundingSphere(center, max_dist, None)
 
+    SHARE_ON_COPY = True
+
+    def __deepcopy__(self, memo):
+        """`ref` nodes are `copy.deepcopy` of a whole subtree in the reference (scene_parser.py:199), which duplicates every
+        vertex of every mesh below it.  Here a copy is an INSTANCE: its own name / materials / speed (they change per copy:
+        set_fallback_material, hierarchy.py:21-28), but the SAME vertex, face and normal arrays and bounding volume (read-only
+        after construction), so `_abi.flatten` hands the device one RtMesh - one LBVH - for all copies.  Results are identical
+        to duplicating the data (tests/test_host_logic.py)."""
+        import copy
+        if not Mesh.SHARE_ON_COPY:
+            cls = self.__class__
+            dup = cls.__new__(cls)
+            memo[id(self)] = dup
+            for k, v in self.__dict__.items():
+                setattr(dup, k, copy.deepcopy(v, memo))
+            return dup
+        cls = self.__class__
+        inst = cls.__new__(cls)
+        memo[id(self)] = inst
+        for k, v in self.__dict__.items():
+            if k in ("verts", "faces", "norms", "bounding_volume", "scene"):
+                setattr(inst, k, v)
+            else:
+                setattr(inst, k, copy.deepcopy(v, memo))
+        return inst
+
     def _compute_normals(self):
         """Area-weighted vertex normals, mesh.py:53-70, accumulated per vertex in face order."""
         v, f = self.verts, self.faces

@@ -26,6 +26,9 @@ class Scene:
         self.jitter_seed = _abi.DEFAULT_JITTER_SEED
         self.max_recursion = _abi.DEFAULT_MAX_DEPTH   # cast_ray default, scene.py:81
         self.tile = (8, 8)          # interleaved tile size used for load balance (kernel-side order only)
+        # EXTENSION, off = reference behaviour (the reference stores a mesh's speed and never uses it, mesh.py:72-153):
+        # when True, mesh objects translate by speed * time like the primitives do (JSON: top-level "mesh_motion": true)
+        self.mesh_motion = False
         self.last_counters = None
         self._flat = None
         self._handle = None
@@ -125,6 +128,18 @@ class Scene:
         self.last_counters = ctr.as_dict()
         self._raise_flags(ctr)
         return out
+
+    def render_tensor(self, subimage: int = 0, tasks: int = 1):
+        """`render()` that stays on the GPU: float32 CUDA tensor (W_sub, H, 3) in the reference orientation, produced by
+        `torch.ops.b200rt.render` on the current torch stream (no host copy, no synchronisation)."""
+        from . import torch_ext
+        ops = torch_ext.load()
+        width = self.strip_columns(subimage, tasks)
+        if len(width) == 0:
+            import torch
+            return torch.empty((0, self.vc.height, 3), dtype=torch.float32, device="cuda")
+        job = self.make_job(int(width[0]), len(width), 0, self.vc.height)
+        return ops.render(torch_ext.scene_handle(self), torch_ext.job_tensor(job))
 
     def render_device(self, d_out_ptr, job, counters=None, stream=None):
         """Raw device-buffer call (`rt_render`) for callers that own device memory (bench, multi-GPU)."""

@@ -161,6 +161,8 @@ def load_scene_dict(data, base_dir=None, ingest=None):
 
     _say("Parsing complete")
     sc = scene_mod.Scene(vc, jitter, samples, ambient, lights, materials, objects)
+    # extension key (absent from the reference's schema, which ignores unknown keys): meshes move like the primitives do
+    sc.mesh_motion = bool(data.get("mesh_motion", False))
     for obj in objects:
         obj.set_scene(sc)
     return sc

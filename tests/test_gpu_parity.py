@@ -466,3 +466,67 @@ def test_packet_any_hit_walk_equals_per_ray_walk(case, centre):
     assert 0 < per_ray.sum() < n
     if sc.flatten().desc.n_meshes:                                     # and with the brute-force face loop inside the packet walk
         assert np.array_equal(per_ray, sc.occluded(o, d, tmax, times, mesh_mode=5))
+
+
+def test_ref_instances_share_one_lbvh_and_moving_meshes_extension():
+    """SURVEY 8f rank 3 on the device: (a) the three instances of a `ref`-copied node share ONE RtMesh / LBVH and render exactly
+    like real deep copies; (b) with "mesh_motion": true the meshes translate by speed * time (ray taken into the mesh's rest
+    frame; the oracle moves the vertices), off by default = reference behaviour (meshes stand still)."""
+    import os
+    from conftest import GOLDEN
+    from test_host_logic import _instancing_scene, _moving_mesh_scene
+    base = os.path.join(GOLDEN, "scenes")
+    sc = rt.scene_parser.load_scene_dict(_instancing_scene(192, 128), base)
+    assert sc.flatten().desc.n_meshes == 1
+    img = sc.render()
+    rt.geometry.Mesh.SHARE_ON_COPY = False
+    try:
+        dup = rt.scene_parser.load_scene_dict(_instancing_scene(192, 128), base)
+    finally:
+        rt.geometry.Mesh.SHARE_ON_COPY = True
+    assert dup.flatten().desc.n_meshes == 3
+    assert np.array_equal(img, dup.render())
+    ref, _ = oracle.render(sc.flatten(), abi)
+    assert parity_stats(to_png_array(img), to_png_array(ref))[0] >= PARITY_FRACTION
+    for on in (False, True):
+        mv = rt.scene_parser.load_scene_dict(_moving_mesh_scene(on), base)
+        got = mv.render()
+        assert mv.last_counters["error_flags"] == 0
+        want, c_ref = oracle.render(mv.flatten(), abi)
+        frac, dmax, _ = parity_stats(to_png_array(got), to_png_array(want))
+        assert frac >= PARITY_FRACTION, (on, frac, dmax)
+        assert np.array_equal(np.asarray(got, dtype=np.float32), mv.render_region(0, mv.vc.width, 0, mv.vc.height, mesh_mode=3))
+
+
+def test_torch_ops_boundary_equals_the_ctypes_boundary():
+    """torch.ops.b200rt.* (thin PyTorch extension over the C ABI): tensors on the current stream, same pixels."""
+    import torch
+    from python_raytracer_b200 import torch_ext
+    ops = torch_ext.load()
+    sc = load_case("MirrorRefraction", {"resolution": [225, 128]})
+    want = sc.render()
+    t = sc.render_tensor()
+    assert t.is_cuda and t.dtype == torch.float32 and tuple(t.shape) == (225, 128, 3)
+    assert np.array_equal(t.cpu().numpy().astype(np.float64), want)
+    strips = torch.cat([sc.render_tensor(n, 4) for n in range(4)], dim=0)
+    assert torch.equal(strips, t)
+    assert np.array_equal(ops.finalize_u8(t).cpu().numpy(), to_png_array(want))
+    with torch.cuda.stream(torch.cuda.Stream()):                      # a non-default current stream
+        t2 = sc.render_tensor()
+    torch.cuda.synchronize()
+    assert torch.equal(t2, t)
+    # compact tile buffers of 3 emulated ranks -> render_into + assemble_tiles
+    h = torch_ext.scene_handle(sc)
+    bufs, offs, total = [], [], 0
+    for rank in range(3):
+        job = sc.make_job(0, 225, 0, 128, rank=rank, world=3, direct=False)
+        nt, nf = C.c_int64(), C.c_int64()
+        abi.check(sc._lib, sc._lib.rt_job_extent(C.byref(job), C.byref(nt), C.byref(nf)), "rt_job_extent")
+        buf = torch.zeros(nf.value, dtype=torch.float32, device="cuda")
+        ops.render_into(buf, h, torch_ext.job_tensor(job))
+        bufs.append(buf); offs.append(total); total += nf.value
+    job = sc.make_job(0, 225, 0, 128, rank=0, world=3, direct=False)
+    img = ops.assemble_tiles(torch.cat(bufs), torch.tensor(offs, dtype=torch.int64), torch_ext.job_tensor(job))
+    assert torch.equal(img, t)
+    with pytest.raises(RuntimeError):
+        ops.render_into(torch.zeros(10, device="cuda"), h, torch_ext.job_tensor(job))

@@ -333,3 +333,108 @@ def test_tile_interleave_partitions_the_region():
             assert len(cols) % (tw * th) == 0
             np.add.at(seen, (cols[valid] - 3, rows[valid] - 2), 1)
         assert (seen == 1).all()
+
+
+# ---- instancing of `ref` nodes and moving meshes ---------------------------------------------------------
+def _instancing_scene(width=96, height=64):
+    mesh = {"name": "t", "type": "mesh", "filepath": "./meshes/torus.obj", "scale": 0.8, "position": [0.0, 0.3, 0.0], "materials": []}
+    ball = {"name": "b", "type": "sphere", "radius": 0.45, "position": [0.0, 0.3, 0.0], "materials": [1]}
+    return {"resolution": [width, height], "AA": {"jitter": False, "samples": 1},
+            "camera": {"position": [0, 3.0, 7.0], "lookAt": [0, 0.6, 0], "up": [0, 1, 0], "fov": 45.0}, "ambient": [0.1, 0.1, 0.1],
+            "materials": [{"name": "a", "ID": 0, "diffuse": [0.8, 0.3, 0.2], "specular": [0.4, 0.4, 0.4], "hardness": 16},
+                          {"name": "b", "ID": 1, "diffuse": [0.2, 0.6, 0.9], "specular": [0, 0, 0], "hardness": 0},
+                          {"name": "c", "ID": 2, "diffuse": [0.9, 0.9, 0.3], "specular": [0.5, 0.5, 0.5], "hardness": 32, "type": "mirror", "tint": 0.5}],
+            "lights": [{"name": "l", "type": "point", "colour": [1, 1, 1], "power": 0.9, "position": [3, 6, 5]},
+                       {"name": "s", "type": "directional", "colour": [0.6, 0.6, 0.7], "power": 1.0, "direction": [-0.4, -1.0, -0.3]}],
+            "objects": [{"name": "ground", "type": "plane", "normal": [0, 1, 0], "position": [0, -0.5, 0], "materials": [1, 2]},
+                        {"name": "thing", "type": "node", "hierarchy_type": "union", "position": [-1.6, 0.8, 0.0], "rotation": [20, 30, 0],
+                         "scale": [1, 1, 1], "materials": [0], "children": [mesh, ball]},
+                        {"name": "copy1", "type": "node", "ref": "thing", "position": [1.7, 0.9, -0.5], "rotation": [-40, 10, 25],
+                         "scale": [0.8, 1.1, 0.9], "materials": [2]},
+                        {"name": "copy2", "type": "node", "ref": "thing", "position": [0.2, 2.2, -1.5], "rotation": [70, 0, 0],
+                         "scale": [0.7, 0.7, 0.7], "materials": [1]}]}
+
+
+def test_ref_nodes_are_instances_sharing_one_mesh_and_render_like_deep_copies():
+    """scene_parser.py:190-203 deep-copies a whole subtree per `ref`; here the copies of a mesh share its arrays
+    (geometry.Mesh.__deepcopy__) and `flatten` emits ONE RtMesh (one LBVH on the device) with a transform and materials per
+    instance.  The image is bit-identical to the one rendered from real deep copies, and equals the oracle's."""
+    rt.scene_parser.VERBOSE = False
+    base = os.path.join(GOLDEN, "scenes")
+    sc = rt.scene_parser.load_scene_dict(_instancing_scene(), base)
+    m0, m1, m2 = (sc.objects[k].children[0] for k in (1, 2, 3))
+    assert m0 is not m1 and m1.verts is m0.verts and m2.faces is m0.faces and m1.bounding_volume is m0.bounding_volume
+    assert [m.name for m in m0.materials] == ["a"] and [m.name for m in m1.materials] == ["c"] and [m.name for m in m2.materials] == ["b"]
+    fs = sc.flatten()
+    assert fs.desc.n_meshes == 1 and fs.desc.n_objects == 4 + 3 * 2 and fs.desc.n_xforms == 3
+    objs = C.cast(fs.desc.objects, C.POINTER(abi.RtObject))
+    assert [objs[i].mesh for i in range(fs.desc.n_objects) if objs[i].kind == abi.KIND_MESH] == [0, 0, 0]
+    rt.geometry.Mesh.SHARE_ON_COPY = False
+    try:
+        dup = rt.scene_parser.load_scene_dict(_instancing_scene(), base)
+    finally:
+        rt.geometry.Mesh.SHARE_ON_COPY = True
+    fd = dup.flatten()
+    assert fd.desc.n_meshes == 3 and dup.objects[2].children[0].verts is not dup.objects[1].children[0].verts
+    a, ca = hostsim.render(fs, abi)
+    b, cb = hostsim.render(fd, abi)
+    assert np.array_equal(a, b) and ca["rays_shadow"] == cb["rays_shadow"]
+    ref, _ = oracle.render(fs, abi)
+    assert parity_stats(to_png_array(ref), to_png_array(a))[0] >= PARITY_FRACTION
+    assert len(np.unique(to_png_array(a).reshape(-1, 3), axis=0)) > 50          # three visible instances, not an empty frame
+
+
+def _moving_mesh_scene(mesh_motion):
+    d = _instancing_scene(120, 80)
+    d["motion"] = {"time": 1.0, "samples": 3, "final": 1}
+    d["mesh_motion"] = mesh_motion
+    d["objects"][1]["speed"] = [0.5, 0.0, 0.3]                      # a moving node: the speed reaches its mesh and its sphere
+    d["objects"] = d["objects"][:2] + [{"name": "free", "type": "mesh", "filepath": "./meshes/torus.obj", "scale": 0.9, "flat_shaded": True,
+                                        "position": [1.5, 0.8, 0.5], "materials": [0], "speed": [-0.8, 0.4, 0.0]}]
+    return d
+
+
+def test_moving_meshes_extension_matches_the_extended_oracle_and_is_off_by_default():
+    """Reference behaviour (default): a mesh's `speed` is stored and never used (scene_parser.py:255, mesh.py:72-153), so the
+    meshes stand still while the primitives beside them move.  With the extension key "mesh_motion": true they translate by
+    speed * time like the primitives (simple_geometry.py:21-24): the device functions meet the mesh in its rest frame (ray
+    origin shifted), the oracle moves every vertex - two formulations, same image within the tolerance."""
+    rt.scene_parser.VERBOSE = False
+    base = os.path.join(GOLDEN, "scenes")
+    still = rt.scene_parser.load_scene_dict(_moving_mesh_scene(False), base)
+    moving = rt.scene_parser.load_scene_dict(_moving_mesh_scene(True), base)
+    assert still.mesh_motion is False and moving.mesh_motion is True and len(moving.vc.motion_times) == 4
+    imgs = {}
+    for name, sc in (("still", still), ("moving", moving)):
+        fs = sc.flatten()
+        assert fs.desc.mesh_motion == (1 if name == "moving" else 0)
+        ref, c_ref = oracle.render(fs, abi)
+        img, c_sim = hostsim.render(fs, abi)
+        frac, dmax, _ = parity_stats(to_png_array(ref), to_png_array(img))
+        assert frac >= PARITY_FRACTION, (name, frac, dmax)
+        assert c_sim["error_flags"] == 0 and c_ref["rays_primary"] == c_sim["rays_primary"]
+        plain, _ = hostsim.render(fs, abi, mesh_mode=3)               # brute-force faces + plain object loop: the BVHs only prune
+        assert np.array_equal(img, plain)
+        imgs[name] = to_png_array(img).astype(int)
+    assert (np.abs(imgs["still"] - imgs["moving"]).max(axis=2) > 8).mean() > 0.01      # the motion is visible
+    # switched off, the speeds on the meshes change nothing: same image as the scene without them
+    d = _moving_mesh_scene(False)
+    d["objects"][2].pop("speed")
+    nospeed = rt.scene_parser.load_scene_dict(d, base)
+    a, _ = hostsim.render(still.flatten(), abi)
+    b, _ = hostsim.render(nospeed.flatten(), abi)
+    assert np.array_equal(a, b)
+
+
+def test_torch_extension_registers_the_boundary_ops():
+    """The thin PyTorch extension (csrc/torch_ops.cpp): built in-tree, loads without a GPU, registers torch.ops.b200rt.*."""
+    import torch
+    from python_raytracer_b200 import torch_ext
+    assert os.path.exists(torch_ext.LIB_PATH), "build with `python __graft_entry__.py`"
+    ops = torch_ext.load()
+    for name in ("render", "render_into", "finalize_u8", "assemble_tiles"):
+        assert hasattr(ops, name)
+    job = abi.RtRenderJob(col0=1, ncols=2, row0=3, nrows=4, tile_w=8, tile_h=8, rank=0, world=1, direct=1, mesh_mode=0, max_batch_rays=5)
+    assert torch_ext.job_tensor(job).tolist() == [1, 2, 3, 4, 8, 8, 0, 1, 1, 0, 5]
+    with pytest.raises(RuntimeError):             # argument checks happen before any device work
+        ops.finalize_u8(torch.zeros(4, 4, 3))
