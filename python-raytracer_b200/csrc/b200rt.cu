@@ -23,18 +23,25 @@
 #ifndef RT_GRID_WAVES_DEEP
 #define RT_GRID_WAVES_DEEP 8
 #endif
-#ifndef RT_TAIL_BIG_BATCH
-#define RT_TAIL_BIG_BATCH (96ll << 20)
+// First level handled by k_tail (0 = never: every level as three launches).  The level is FIXED per kernel family, not chosen from
+// the batch size: the same per-ray functions compiled into k_tail and into k_hit / k_shadow / k_shade round a few products
+// differently (nvcc contracts across the stages k_tail inlines into one loop), so a path's last bits depend on where k_tail takes
+// over - measured: up to 1.6e-4 on deep refraction chains of scenes/MirrorRefraction.json between take-over levels 1 and 3.  A
+// take-over level that moved with the batch size made the image depend on the batch size, i.e. on the number of ranks a frame is
+// split over (SURVEY 8e wants N-rank == 1-rank bit for bit).  Measured at 4K x 64 (ms/frame) for levels never / 1 / 2 / 3 / 4:
+// 121.2 / 119.6 / 120.1 / 119.0 / 119.3.  Scenes with CSG / transform nodes: k_tail<true> is the whole node interpreter in one
+// kernel (instruction-fetch bound, 4 blocks/SM); NovelScene1 at its shipped 2048x1024x32 took 159 ms with k_tail from level 2
+// against 139 ms without.  Developer override for experiments: B200RT_TAIL_LEVEL (echoed by bench.py).
+#ifndef RT_TAIL_LEVEL_PLAIN
+#define RT_TAIL_LEVEL_PLAIN 3
 #endif
-// first level handled by k_tail (0 = never: every level as three launches); developer override: B200RT_TAIL_LEVEL
-// Scenes with CSG / transform nodes: k_tail<true> is the whole node interpreter in one kernel (instruction-fetch bound, 4 blocks/SM),
-// so it only pays while launch overhead dominates.  NovelScene1 at 32 spp, ms/frame with k_tail from level 1 / from level 2 / never:
-// 1 Mi rays 3.9 / 3.7 / 4.6, 4 Mi 13.6 / 10.8 / 11.1, 16 Mi 52.4 / 40.6 / 36.5, 64 Mi 210 / 159 / 139.
-static int tail_level_for(long long n_rays, bool has_nodes) {
+#ifndef RT_TAIL_LEVEL_NODES
+#define RT_TAIL_LEVEL_NODES 0
+#endif
+static int tail_level_for(bool has_nodes) {
     static const char* env = getenv("B200RT_TAIL_LEVEL");
     if (env) return atoi(env);
-    if (has_nodes) return n_rays < (8ll << 20) ? 2 : 0;
-    return n_rays >= RT_TAIL_BIG_BATCH ? 3 : 1;
+    return has_nodes ? RT_TAIL_LEVEL_NODES : RT_TAIL_LEVEL_PLAIN;
 }
 
 // Persistent grid-stride grids: blocks = SMs x resident blocks per SM of THAT kernel (its __launch_bounds__) x waves.  Measured at
@@ -496,7 +503,7 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
             (*launches) += 2;
         }
         if (secondary) {
-            const int tail_level = tail_level_for(n_rays, HAS_NODES);
+            const int tail_level = tail_level_for(HAS_NODES);
             for (int level = 1; level < V.max_depth; level++) {       // level L consumes the rays spawned by level L-1
                 RayQueue& qin = (level & 1) ? q0 : q1;
                 RayQueue& qout = (level & 1) ? q1 : q0;

@@ -197,7 +197,9 @@ RT_HD bool tri_shadow(float3 v0, float3 v1, float3 v2, const Ray& r) {
 struct RayInv { float3 inv, oinv; int nx, ny, nz; };
 // the reciprocal only scales conservative (padded) box tests: the 1-ulp MUFU.RCP is enough on the device
 #if defined(__CUDA_ARCH__)
-#define RT_RCP(x) __fdividef(1.0f, (x))
+// one MUFU.RCP: the callers keep |x| >= 2^-60, so none of the range handling of __fdividef / IEEE division is needed
+__device__ __forceinline__ float rt_rcp_approx(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+#define RT_RCP(x) rt_rcp_approx(x)
 #else
 #define RT_RCP(x) (1.0f / (x))
 #endif
@@ -208,6 +210,12 @@ RT_HD RayInv ray_inv(const Ray& r) {
     ri.oinv = f3(-r.o.x * ri.inv.x, -r.o.y * ri.inv.y, -r.o.z * ri.inv.z);
     ri.nx = ri.inv.x < 0.0f ? 48 : 0; ri.ny = ri.inv.y < 0.0f ? 64 : 16; ri.nz = ri.inv.z < 0.0f ? 80 : 32;
     return ri;
+}
+// the same ray with another origin (moving meshes: the ray in the mesh's rest frame): only the origin terms change
+RT_HD RayInv ray_inv_moved(const RayInv& ri, float3 o) {
+    RayInv m = ri;
+    m.oinv = f3(-o.x * ri.inv.x, -o.y * ri.inv.y, -o.z * ri.inv.z);
+    return m;
 }
 // Mesh gate for rays whose reciprocal direction is at hand (top-level meshes): same decisions as mesh_gate up to the
 // last ulp of the slab distances ((lo - o) * (1/d) instead of (lo - o) / d; six IEEE divisions saved per ray)
@@ -920,9 +928,11 @@ RT_HD bool closest_hit(TraceCtx& cx, const Ray& r, Hit& out) {
             const int oi = RT_LDG(S.sep_mesh + k);
             cx.tally.prims++;
             float t; int slot;
-            Ray mr = r; RayInv mri = ri;
-            if (S.mesh_motion) { mr.o = r.o - mesh_shift(cx, oi); mri = ray_inv(mr); }
-            mesh_closest(cx, S.meshes + S.objects[oi].mesh, mr, mri, best, [&](float tt) { return RT_BETTER(tt); }, t, slot);
+            // (moving meshes run on the GENERAL kernels only - HAS_NODES, see convert_scene - so the lean ones carry none of this)
+            if (HAS_NODES && S.mesh_motion) {
+                Ray mr = r; mr.o = r.o - mesh_shift(cx, oi);
+                mesh_closest(cx, S.meshes + S.objects[oi].mesh, mr, ray_inv_moved(ri, mr.o), best, [&](float tt) { return RT_BETTER(tt); }, t, slot);
+            } else mesh_closest(cx, S.meshes + S.objects[oi].mesh, r, ri, best, [&](float tt) { return RT_BETTER(tt); }, t, slot);
             if (slot >= 0) { best = t; best_obj = oi; best_aux = slot; }
         }
     }
@@ -937,7 +947,7 @@ RT_HD bool closest_hit(TraceCtx& cx, const Ray& r, Hit& out) {
         case RT_KIND_SPHERE: out.n = normalize(out.p - moved(cx, o, f3(ld4(&o->a)))); break;
         case RT_KIND_PLANE: out.n = f3(ld4(&o->b)); out.mat = plane_material(o, out.p, cx.time); break;
         case RT_KIND_BOX: out.n = box_normal(r, best_aux); break;
-        default: out.n = tri_normal(cx, S.meshes + o->mesh, best_aux, S.mesh_motion ? (r.o - mesh_shift(cx, best_obj)) + r.d * best : out.p); break;
+        default: out.n = tri_normal(cx, S.meshes + o->mesh, best_aux, (HAS_NODES && S.mesh_motion) ? (r.o - mesh_shift(cx, best_obj)) + r.d * best : out.p); break;
     }
     return true;
 }
@@ -980,7 +990,7 @@ RT_HD bool occluded(TraceCtx& cx, const Ray& r, float tmax) {
     for (int k = 0; k < S.n_sep_mesh && !occ && in_world; k++) {
         cx.tally.prims++;
         const int oi = RT_LDG(S.sep_mesh + k);
-        if (S.mesh_motion) { Ray mr = r; mr.o = r.o - mesh_shift(cx, oi); occ = mesh_shadow(cx, S.meshes + S.objects[oi].mesh, mr, ray_inv(mr)); }
+        if (HAS_NODES && S.mesh_motion) { Ray mr = r; mr.o = r.o - mesh_shift(cx, oi); occ = mesh_shadow(cx, S.meshes + S.objects[oi].mesh, mr, ray_inv_moved(ri, mr.o)); }
         else occ = mesh_shadow(cx, S.meshes + S.objects[oi].mesh, r, ri);
     }
     return occ;
@@ -1105,7 +1115,7 @@ __device__ __forceinline__ bool occluded_packet(TraceCtx& cx, const Ray& r, floa
         if (active) cx.tally.prims++;
         const int oi = RT_LDG(S.sep_mesh + k);
         Ray mr = r; RayInv mri = ri;
-        if (S.mesh_motion) { mr.o = r.o - mesh_shift(cx, oi); mri = ray_inv(mr); }
+        if (HAS_NODES && S.mesh_motion) { mr.o = r.o - mesh_shift(cx, oi); mri = ray_inv_moved(ri, mr.o); }
         if (mesh_shadow_packet(cx, S.meshes + S.objects[oi].mesh, mr, mri, active)) { occ = true; active = false; }
     }
     return occ;

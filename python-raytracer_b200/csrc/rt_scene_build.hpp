@@ -261,6 +261,9 @@ inline int convert_scene(const RtSceneDesc* d, HostScene& hs, std::string& err) 
         if (o.kind == RT_KIND_NODE) hs.has_nodes = true;
         if (o.kind == RT_KIND_MESH) hs.has_mesh = true;
     }
+    // moving meshes (extension) are handled by the GENERAL kernels only (the HAS_NODES instantiations: CSG / transform nodes), so
+    // that the lean kernels of node-free scenes carry neither the code nor the registers for it
+    if (d->mesh_motion && hs.has_mesh) hs.has_nodes = true;
     if (d->n_top < 0 || d->n_top > d->n_objects) return bad(RT_ERR_INVALID, "n_top out of range");
     for (int i = 0; i < d->n_top; i++)
         if (nest_depth(d, i, 0) > RT_MAX_NEST) return bad(RT_ERR_LIMIT, "CSG/transform nesting deeper than RT_MAX_NEST");

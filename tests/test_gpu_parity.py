@@ -91,6 +91,23 @@ def test_small_batches_equal_one_batch():
     assert ctr.kernel_launches > 20
 
 
+def test_batch_size_does_not_change_a_bit_with_recursive_materials():
+    """Mirror / refraction chains of depth 10 (queued levels 1-2, k_tail from level 3): the frame must not depend on how it is
+    cut into wavefront batches - the property that makes an N-rank render equal the 1-rank render (smaller batches per rank)."""
+    sc = load_case("MirrorRefraction")
+    full = sc.render_region(0, 900, 0, 512).copy()
+    assert sc.last_counters["rays_refract"] > 0 and sc.last_counters["rays_reflect"] > 0
+    h = sc.upload()
+    for batch in (150_000, 20_000, 1_000):
+        out = np.empty((900, 512, 3), np.float32)
+        job = sc.make_job(0, 900, 0, 512, max_batch_rays=batch)
+        ctr = abi.RtCounters()
+        abi.check(sc._lib, sc._lib.rt_render_host(h, C.byref(job), out.ctypes.data, C.byref(ctr), None), "rt_render_host")
+        assert np.array_equal(out, full), batch
+    win = sc.render_region(300, 64, 200, 48)                       # a window rendered alone == the same pixels of the frame
+    assert np.array_equal(win, full[300:364, 200:248])
+
+
 @pytest.mark.parametrize("world", [2, 3, 8])
 def test_tile_sharded_render_assembles_to_the_single_rank_image(world, lib):
     """Multi-GPU split emulated on one device: every rank's compact tile buffer, concatenated as the
