@@ -244,6 +244,20 @@ int rt_render(RtScene* scene, const RtRenderJob* job, float* d_out, RtCounters* 
  * synchronous.  This is the end-to-end call Scene.render() uses. */
 int rt_render_host(RtScene* scene, const RtRenderJob* job, float* h_out, RtCounters* counters, void* stream);
 
+/* rt_render for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  No counterpart in the reference.  Same arguments, same output (bit for bit)
+ * and same tallies as rt_render, but the call allocates nothing - no cudaMalloc / cudaFree / allocating library routine: the
+ * wavefront scratch (sample buffer, hit planes, occlusion planes, both ray queues: 216 bytes per ray) is a file-scope device array
+ * of RT_STATIC_MAX_RAYS rays = 13.5 MiB that every GPU which loads the library holds until the process exits, and the frame is
+ * worked through in batches of at most RT_STATIC_MAX_RAYS rays (any frame size; slower than rt_render for big frames).
+ * RT_ERR_LIMIT when the scene's samples per pixel (dof * aa * times) exceed RT_STATIC_MAX_RAYS or its lights exceed
+ * RT_STATIC_MAX_LIGHTS.  job->max_batch_rays is ignored.  ALL calls on one device share the array, whatever the scene handle
+ * or stream: calls that overlap on the GPU race (order them on one stream or with events).  The array keeps the last call's
+ * contents; nothing in it needs clearing (every record read was written by an earlier kernel of the same batch). */
+#define RT_STATIC_MAX_RAYS 65536
+#define RT_STATIC_MAX_LIGHTS 8
+int rt_render_static(RtScene* scene, const RtRenderJob* job, float* d_out, RtCounters* counters, void* stream);
+
 /* Number of pixels / tiles a job writes for (rank, world): sizes the compact buffer. */
 int rt_job_extent(const RtRenderJob* job, int64_t* n_local_tiles, int64_t* n_floats);
 

@@ -295,7 +295,7 @@ def flatten(scene, jitter_seed=DEFAULT_JITTER_SEED, max_depth=DEFAULT_MAX_DEPTH)
 _LIB = None
 LIB_PATH = os.environ.get("B200RT_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "libb200rt.so")
 
-ENTRY_POINTS = ["rt_scene_create", "rt_scene_build_bvh", "rt_render", "rt_render_host", "rt_render_u8_host", "rt_job_extent",
+ENTRY_POINTS = ["rt_scene_create", "rt_scene_build_bvh", "rt_render", "rt_render_static", "rt_render_host", "rt_render_u8_host", "rt_job_extent",
                 "rt_assemble_tiles", "rt_finalize_u8", "rt_scene_destroy", "rt_scene_bvh_stats",
                 "rt_scene_bvh_download", "rt_last_error", "rt_abi_version", "rt_trace_rays", "rt_occluded",
                 "rt_scene_profile", "rt_scene_profile_read", "rt_measure_peaks",
@@ -322,6 +322,7 @@ def load_library(path=None):
     lib.rt_scene_build_bvh.argtypes = [vp, vp]
     lib.rt_render.argtypes = [vp, C.POINTER(RtRenderJob), vp, C.POINTER(RtCounters), vp]
     lib.rt_render_host.argtypes = [vp, C.POINTER(RtRenderJob), vp, C.POINTER(RtCounters), vp]
+    lib.rt_render_static.argtypes = [vp, C.POINTER(RtRenderJob), vp, C.POINTER(RtCounters), vp]
     lib.rt_render_u8_host.argtypes = [vp, C.POINTER(RtRenderJob), vp, C.POINTER(RtCounters), vp]
     lib.rt_job_extent.argtypes = [C.POINTER(RtRenderJob), i64p, i64p]
     lib.rt_assemble_tiles.argtypes = [C.POINTER(RtRenderJob), vp, i64p, vp, vp]

@@ -559,6 +559,89 @@ extern "C" int rt_render(RtScene* sc, const RtRenderJob* job, float* d_out, RtCo
     return RT_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// rt_render without any allocation (no counterpart in the reference; added for callers
+// that cannot call cudaMalloc: CUDA graph capture, tight serving loops, harnesses that forbid it).  The wavefront scratch of the
+// render (sample buffer, hit planes, occlusion planes, both ray queues) lives in ONE file-scope device array instead of the
+// handle's grown buffers; the frame is worked through in batches of <= RT_STATIC_MAX_RAYS rays.  Every GPU that loads the
+// library holds the array until the process exits; every call on a device shares it (calls that overlap on the GPU race).
+// Nothing in it has to start at zero: every record a kernel reads was written by an earlier kernel of the same batch.
+#define RT_STATIC_ALIGN(x) (((size_t)(x) + 255) & ~(size_t)255)
+#define RT_STATIC_OFF_SAMPLES 0
+#define RT_STATIC_OFF_HIT (RT_STATIC_OFF_SAMPLES + RT_STATIC_ALIGN(sizeof(float4) * RT_STATIC_MAX_RAYS))
+#define RT_STATIC_OFF_OCC (RT_STATIC_OFF_HIT + RT_STATIC_ALIGN(sizeof(float4) * RT_HIT_PLANES * RT_STATIC_MAX_RAYS))
+#define RT_STATIC_OFF_Q0 (RT_STATIC_OFF_OCC + RT_STATIC_ALIGN((size_t)RT_STATIC_MAX_LIGHTS * RT_STATIC_MAX_RAYS))
+#define RT_STATIC_OFF_Q1 (RT_STATIC_OFF_Q0 + RT_STATIC_ALIGN(sizeof(float4) * RT_QUEUE_PLANES * RT_STATIC_MAX_RAYS))
+#define RT_STATIC_BYTES (RT_STATIC_OFF_Q1 + RT_STATIC_ALIGN(sizeof(float4) * RT_QUEUE_PLANES * RT_STATIC_MAX_RAYS))
+static __device__ __align__(256) unsigned char g_static_scratch[RT_STATIC_BYTES];      // 216 B per ray: 13.5 MiB
+// In host code `g_static_scratch` is only a stand-in for the symbol: the device address is asked for once per device, with
+// that device current, and kept here.
+#define RT_STATIC_MAX_DEVICES 64
+static unsigned char* g_static_ptr[RT_STATIC_MAX_DEVICES];
+
+static int static_scratch(int device, unsigned char** out) {
+    if (device < 0 || device >= RT_STATIC_MAX_DEVICES) return fail(RT_ERR_LIMIT, "rt_render_static: device ordinal >= 64");
+    if (!g_static_ptr[device]) {
+        void* p = nullptr;
+        CU(cudaGetSymbolAddress(&p, g_static_scratch));       // the caller made `device` current
+        g_static_ptr[device] = (unsigned char*)p;
+    }
+    *out = g_static_ptr[device];
+    return RT_OK;
+}
+
+extern "C" int rt_render_static(RtScene* sc, const RtRenderJob* job, float* d_out, RtCounters* counters, void* stream) {
+    if (!sc || !job || !d_out) return fail(RT_ERR_INVALID, "null argument");
+    for (auto& m : sc->meshes) if (!m.built) return fail(RT_ERR_INVALID, "rt_scene_build_bvh has not been called");
+    if (sc->samples_per_pixel > RT_STATIC_MAX_RAYS)
+        return fail(RT_ERR_LIMIT, "rt_render_static: " + std::to_string(sc->samples_per_pixel) + " samples per pixel exceed the static scratch ("
+                                  + std::to_string(RT_STATIC_MAX_RAYS) + " rays per batch); use rt_render");
+    if (sc->view.n_lights > RT_STATIC_MAX_LIGHTS)
+        return fail(RT_ERR_LIMIT, "rt_render_static: " + std::to_string(sc->view.n_lights) + " lights exceed the static scratch ("
+                                  + std::to_string(RT_STATIC_MAX_LIGHTS) + "); use rt_render");
+    PixelMap pm; long long nt;
+    UP(make_pixel_map(job, pm, nt));
+    if (job->col0 < 0 || job->row0 < 0 || (long long)job->col0 + job->ncols > sc->view.width || (long long)job->row0 + job->nrows > sc->view.height)
+        return fail(RT_ERR_INVALID, "RtRenderJob rectangle leaves the frame [0,width) x [0,height)");
+    cudaStream_t st = (cudaStream_t)stream;
+    DeviceGuard dg(sc->device);
+    unsigned char* base = nullptr;
+    UP(static_scratch(sc->device, &base));
+    // the handle's own work buffers step aside for the duration of the call (render_impl sizes its batches from max_batch_rays and
+    // never grows a buffer whose capacity already covers a batch); event pairs of the profiler are not recorded here either
+    struct Saved { float4* samples; long long samples_cap; float4* q0; float4* q1; long long queue_cap; float4* hit; long long hit_cap;
+                   uint8_t* occ; long long occ_cap; bool profiling; };
+    const Saved keep{sc->d_samples, sc->samples_cap, sc->d_queue[0], sc->d_queue[1], sc->queue_cap, sc->d_hit, sc->hit_cap, sc->d_occ, sc->occ_cap, sc->profiling};
+    sc->d_samples = (float4*)(base + RT_STATIC_OFF_SAMPLES); sc->samples_cap = RT_STATIC_MAX_RAYS;
+    sc->d_hit = (float4*)(base + RT_STATIC_OFF_HIT); sc->hit_cap = RT_STATIC_MAX_RAYS;
+    sc->d_occ = (uint8_t*)(base + RT_STATIC_OFF_OCC); sc->occ_cap = (long long)RT_STATIC_MAX_LIGHTS * RT_STATIC_MAX_RAYS;
+    sc->d_queue[0] = (float4*)(base + RT_STATIC_OFF_Q0); sc->d_queue[1] = (float4*)(base + RT_STATIC_OFF_Q1); sc->queue_cap = RT_STATIC_MAX_RAYS;
+    sc->profiling = false;
+    RtRenderJob j = *job;
+    j.max_batch_rays = RT_STATIC_MAX_RAYS;
+    unsigned long long launches = 0;
+    int rc = RT_OK;
+    cudaError_t e = cudaMemsetAsync(sc->d_counters, 0, RT_COUNTER_CLASSES * sizeof(RtCounters), st);
+    if (e != cudaSuccess) rc = fail(RT_ERR_CUDA, std::string("rt_render_static: cudaMemsetAsync: ") + cudaGetErrorString(e));
+    if (rc == RT_OK) rc = sc->has_nodes ? render_impl<true>(sc, &j, pm, d_out, st, &launches) : render_impl<false>(sc, &j, pm, d_out, st, &launches);
+    const bool intact = sc->d_samples == (float4*)(base + RT_STATIC_OFF_SAMPLES) && sc->d_hit == (float4*)(base + RT_STATIC_OFF_HIT) &&
+                        sc->d_occ == (uint8_t*)(base + RT_STATIC_OFF_OCC) && sc->d_queue[0] == (float4*)(base + RT_STATIC_OFF_Q0) &&
+                        sc->d_queue[1] == (float4*)(base + RT_STATIC_OFF_Q1);
+    sc->d_samples = keep.samples; sc->samples_cap = keep.samples_cap; sc->d_queue[0] = keep.q0; sc->d_queue[1] = keep.q1; sc->queue_cap = keep.queue_cap;
+    sc->d_hit = keep.hit; sc->hit_cap = keep.hit_cap; sc->d_occ = keep.occ; sc->occ_cap = keep.occ_cap; sc->profiling = keep.profiling;
+    if (rc != RT_OK) return rc;
+    if (!intact) return fail(RT_ERR_LIMIT, "rt_render_static: a batch outgrew the static scratch");
+    sc->last_launches = launches;
+    if (counters) {
+        RtCounters cls[RT_COUNTER_CLASSES];
+        CU(cudaMemcpyAsync(cls, sc->d_counters, sizeof cls, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        sum_counters(cls, counters);
+        counters->kernel_launches = launches;
+    }
+    return RT_OK;
+}
+
 extern "C" int rt_render_host(RtScene* sc, const RtRenderJob* job, float* h_out, RtCounters* counters, void* stream) {
     if (!sc || !h_out) return fail(RT_ERR_INVALID, "null argument");
     int64_t n_floats = 0;

@@ -147,6 +147,13 @@ class Scene:
         rc = self._lib.rt_render(h, C.byref(job), d_out_ptr, None if counters is None else C.byref(counters), stream)
         _abi.check(self._lib, rc, "rt_render")
 
+    def render_device_static(self, d_out_ptr, job, counters=None, stream=None):
+        """`rt_render_static`: the same render with its scratch in the library's static device array - the call allocates
+        nothing (callers under CUDA graph capture / serving loops); limits RT_STATIC_MAX_RAYS samples per pixel, RT_STATIC_MAX_LIGHTS."""
+        h = self.upload(stream)
+        rc = self._lib.rt_render_static(h, C.byref(job), d_out_ptr, None if counters is None else C.byref(counters), stream)
+        _abi.check(self._lib, rc, "rt_render_static")
+
     # ------------------------------------------------------------------ debugging / unit-test aids
     def trace_rays(self, origins, dirs, times=None, mesh_mode=0):
         """cast_ray (scene.py:81) for explicit rays: returns dict(rgb, t, n, p, geom, mat)."""
