@@ -382,6 +382,8 @@ def run_ours(a):
                "dtype": "f32", "data": "synthetic",
                "config": {**workload_config(a), "tiles": f"{sc.tile[0]}x{sc.tile[1]} interleaved over ranks", "fan_in": sharder.fan_in,
                           "l2_policy": "working set (BVH nodes+triangles+sample/queue buffers) exceeds the 126 MB L2; no flush between frames",
+                          "wavefront": "batches of <= 64 Mi rays; level 0 of every batch on the caller's stream, the deeper levels + resolve of batch b on a "
+                                       "high-priority side stream under level 0 of batch b + 1 (two work-buffer sets)",
                           "env_knobs": knobs},
                "rays_per_frame": dict(zip(RAY_KEYS, tl[:4])),
                "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": ms2_total / e2e_steps,
@@ -403,7 +405,8 @@ def run_ours(a):
                                            for k, c in (("k_hit", prof.hit), ("k_shadow", prof.shadow), ("k_shade", prof.shade),
                                                         ("levels>=1", prof.secondary))},
                "kernel_ms_per_frame": kernel_ms,
-               "kernel_ms_note": f"separate untimed pass of {prof_frames} frames with per-launch CUDA events; `value` is timed with that instrumentation off",
+               "kernel_ms_note": f"separate untimed pass of {prof_frames} frames with per-launch CUDA events, ONE launch at a time on one stream; `value` is timed with that "
+                                 "instrumentation off and with the deeper levels overlapped (their sum here exceeds ms_per_step by what the overlap hides)",
                "setup_ms": {"scene_python": 1e3 * t_scene, **t_ingest, "upload": 1e3 * t_upload, "lbvh_build": 1e3 * t_bvh},
                "clocks": clocks}
         if not a.no_cpu_baseline and world == 1:

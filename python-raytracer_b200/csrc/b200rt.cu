@@ -94,6 +94,15 @@ struct MeshBuild {
     bool built = false;
 };
 
+// the per-batch wavefront buffers of a render
+struct WorkSet {
+    float4* d_samples = nullptr; long long samples_cap = 0;
+    float4* d_queue[2] = {nullptr, nullptr}; long long queue_cap = 0;
+    float4* d_hit = nullptr; long long hit_cap = 0;          // hit record planes of the level in flight
+    uint8_t* d_occ = nullptr; long long occ_cap = 0;         // n_lights planes of occlusion flags
+    unsigned long long* d_qcount = nullptr;                  // [max_depth + 2]
+};
+
 struct RtScene {
     SceneView view{};
     std::vector<void*> allocs;
@@ -102,12 +111,14 @@ struct RtScene {
     DevMesh* d_meshes = nullptr;
     bool has_nodes = false, has_specular = false, has_mesh = false, has_tlas = false;
     int samples_per_pixel = 1;
-    // work buffers of rt_render, grown on demand
-    float4* d_samples = nullptr; long long samples_cap = 0;
-    float4* d_queue[2] = {nullptr, nullptr}; long long queue_cap = 0;
-    float4* d_hit = nullptr; long long hit_cap = 0;          // hit record planes of the level in flight
-    uint8_t* d_occ = nullptr; long long occ_cap = 0;         // n_lights planes of occlusion flags
-    unsigned long long* d_qcount = nullptr;   // [max_depth + 1]
+    // work buffers of rt_render, grown on demand.  TWO sets: consecutive wavefront batches of a frame alternate between them and
+    // between two streams (the caller's and `side`), so that one batch's tails and latency-bound kernels (the small launches of the
+    // deeper levels, k_shade, the last blocks of every launch) run under the other batch's issue-bound kernels.
+    WorkSet ws[2];
+    cudaStream_t side = nullptr;               // created by the first render that has two batches
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaEvent_t ev_l0[2] = {nullptr, nullptr}, ev_deep[2] = {nullptr, nullptr};   // pipeline mode: level 0 of a set done / its deeper levels + resolve done
+    bool serial_only = false;                  // rt_render_static: one set (the static array), one stream
     RtCounters* d_counters = nullptr;
     float* d_stage = nullptr; long long stage_cap = 0;   // rt_render_host staging
     uint8_t* d_stage_u8 = nullptr; long long stage_u8_cap = 0;
@@ -220,7 +231,7 @@ static int scene_create_impl(const RtSceneDesc* d, RtScene* sc) {
     UP(upload(sc, hs.times.data(), hs.times.size(), &d_times));
     V.col_x = d_colx; V.row_y = d_rowy; V.dof_origin = d_dof; V.ray_origin = d_org; V.times = d_times;
     sc->samples_per_pixel = d->dof_samples * d->aa_samples * d->n_times;
-    UP(upload(sc, (const unsigned long long*)nullptr, (size_t)d->max_depth + 2, &sc->d_qcount));
+    for (int k = 0; k < 2; k++) UP(upload(sc, (const unsigned long long*)nullptr, (size_t)d->max_depth + 2, &sc->ws[k].d_qcount));
     UP(upload(sc, (const RtCounters*)nullptr, RT_COUNTER_CLASSES, &sc->d_counters));
     CU(cudaDeviceSynchronize());     // the memsets above ran on the legacy stream; later kernels run on caller streams
     return RT_OK;
@@ -231,10 +242,16 @@ static void drain_events(RtScene* sc);
 extern "C" int rt_scene_destroy(RtScene* sc) {
     if (!sc) return RT_OK;
     for (void* p : sc->allocs) cudaFree(p);
-    if (sc->d_samples) cudaFree(sc->d_samples);
-    for (int k = 0; k < 2; k++) if (sc->d_queue[k]) cudaFree(sc->d_queue[k]);
-    if (sc->d_hit) cudaFree(sc->d_hit);
-    if (sc->d_occ) cudaFree(sc->d_occ);
+    for (WorkSet& w : sc->ws) {
+        if (w.d_samples) cudaFree(w.d_samples);
+        for (int k = 0; k < 2; k++) if (w.d_queue[k]) cudaFree(w.d_queue[k]);
+        if (w.d_hit) cudaFree(w.d_hit);
+        if (w.d_occ) cudaFree(w.d_occ);
+    }
+    if (sc->ev_fork) cudaEventDestroy(sc->ev_fork);
+    if (sc->ev_join) cudaEventDestroy(sc->ev_join);
+    for (int k = 0; k < 2; k++) { if (sc->ev_l0[k]) cudaEventDestroy(sc->ev_l0[k]); if (sc->ev_deep[k]) cudaEventDestroy(sc->ev_deep[k]); }
+    if (sc->side) cudaStreamDestroy(sc->side);
     if (sc->d_stage) cudaFree(sc->d_stage);
     if (sc->d_stage_u8) cudaFree(sc->d_stage_u8);
     drain_events(sc);
@@ -429,37 +446,72 @@ static void sum_counters(const RtCounters* cls, RtCounters* out) {
     for (int c = 0; c < RT_COUNTER_CLASSES; c++) out->error_flags |= cls[c].error_flags;
 }
 
+// Batch size of a frame when the job does not name one.  Two work sets of 64 Mi rays (samples 1 + hit planes 2 + occlusion 0.2 + queues
+// 2 x 5 GiB each) cost what one set of 128 Mi rays did.  Frames above RT_SPLIT_RAYS are cut into at least two batches so that the two
+// streams have something to overlap; smaller frames are launch-latency bound and stay one batch on the caller's stream.
+#ifndef RT_DEFAULT_BATCH_RAYS
+#define RT_DEFAULT_BATCH_RAYS (64ll << 20)
+#endif
+#ifndef RT_SPLIT_RAYS
+#define RT_SPLIT_RAYS (16ll << 20)
+#endif
+// developer override for experiments: B200RT_STREAMS=1 keeps every batch on the caller's stream (echoed by bench.py)
+// 1 = every batch on the caller's stream; 2 = whole batches alternate between two streams; 3 = pipeline: level 0 of every batch on
+// the caller's stream, the deeper levels + resolve of batch b on a high-priority side stream under level 0 of batch b + 1
+#ifndef RT_STREAM_MODE
+#define RT_STREAM_MODE 3
+#endif
+static int max_streams() {
+    static const char* env = getenv("B200RT_STREAMS");
+    return env ? std::max(1, std::min(3, atoi(env))) : RT_STREAM_MODE;
+}
+
+static int grow_set(RtScene* sc, WorkSet& w, long long batch_cap, int L, bool secondary) {
+    UP(grow(&w.d_samples, &w.samples_cap, batch_cap));
+    UP(grow(&w.d_hit, &w.hit_cap, batch_cap, RT_HIT_PLANES));
+    if (w.hit_cap * L > w.occ_cap) {                          // occlusion planes share the hit planes' stride
+        if (w.d_occ) { cudaFree(w.d_occ); w.d_occ = nullptr; w.occ_cap = 0; }
+        CU(cudaMalloc((void**)&w.d_occ, (size_t)w.hit_cap * L));
+        w.occ_cap = w.hit_cap * L;
+    }
+    if (secondary && batch_cap > w.queue_cap) {
+        for (int k = 0; k < 2; k++) {
+            if (w.d_queue[k]) { cudaFree(w.d_queue[k]); w.d_queue[k] = nullptr; }
+            w.queue_cap = 0;
+            CU(cudaMalloc((void**)&w.d_queue[k], sizeof(float4) * RT_QUEUE_PLANES * (size_t)batch_cap));
+        }
+        w.queue_cap = batch_cap;
+    }
+    (void)sc;
+    return RT_OK;
+}
+
 template <bool HAS_NODES>
 static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, float* d_out, cudaStream_t st, unsigned long long* launches) {
     SceneView V = sc->view;
     V.mesh_mode = job->mesh_mode;
     const int N = sc->samples_per_pixel;
-    // batch = as many whole pixels as fit in max_batch_rays (default 128 Mi rays: 2 GiB of samples + 2 x 10 GiB of
-    // queue planes out of 180 GB), evened out over the batches so the last one is not a sliver
-    long long max_rays = job->max_batch_rays > 0 ? job->max_batch_rays : (128ll << 20);
+    // batch = as many whole pixels as fit in max_batch_rays, evened out over the batches so the last one is not a sliver
+    long long max_rays = job->max_batch_rays > 0 ? job->max_batch_rays : RT_DEFAULT_BATCH_RAYS;
     max_rays = std::min(max_rays, 1ll << 30);
     long long px_per_batch = std::max(1ll, max_rays / N);
-    if (pm.n_local_pixels > px_per_batch) {
-        const long long n_batches = (pm.n_local_pixels + px_per_batch - 1) / px_per_batch;
-        px_per_batch = std::min(px_per_batch, (pm.n_local_pixels + n_batches - 1) / n_batches);
-    }
+    long long n_batches = std::max(1ll, (pm.n_local_pixels + px_per_batch - 1) / px_per_batch);
+    if (job->max_batch_rays <= 0 && n_batches == 1 && pm.n_local_pixels * N > RT_SPLIT_RAYS && !sc->serial_only) n_batches = 2;
+    if (pm.n_local_pixels > 0) px_per_batch = std::min(px_per_batch, (pm.n_local_pixels + n_batches - 1) / n_batches);
     const long long batch_cap = std::min(px_per_batch, std::max(1ll, pm.n_local_pixels)) * N;
-    UP(grow(&sc->d_samples, &sc->samples_cap, batch_cap));
-    UP(grow(&sc->d_hit, &sc->hit_cap, batch_cap, RT_HIT_PLANES));
+    // two streams when there are two batches to overlap; the per-launch event pairs of the profiler want one launch at a time
+    const bool two = n_batches >= 2 && !sc->serial_only && !sc->profiling && max_streams() >= 2;
     const int L = std::max(1, V.n_lights);
-    if (sc->hit_cap * L > sc->occ_cap) {                      // occlusion planes share the hit planes' stride
-        if (sc->d_occ) { cudaFree(sc->d_occ); sc->d_occ = nullptr; sc->occ_cap = 0; }
-        CU(cudaMalloc((void**)&sc->d_occ, (size_t)sc->hit_cap * L));
-        sc->occ_cap = sc->hit_cap * L;
-    }
     const bool secondary = sc->has_specular && V.max_depth > 1;
-    if (secondary && batch_cap > sc->queue_cap) {
-        for (int k = 0; k < 2; k++) {
-            if (sc->d_queue[k]) { cudaFree(sc->d_queue[k]); sc->d_queue[k] = nullptr; }
-            sc->queue_cap = 0;
-            CU(cudaMalloc((void**)&sc->d_queue[k], sizeof(float4) * RT_QUEUE_PLANES * (size_t)batch_cap));
-        }
-        sc->queue_cap = batch_cap;
+    for (int k = 0; k < (two ? 2 : 1); k++) UP(grow_set(sc, sc->ws[k], batch_cap, L, secondary));
+    const bool pipe = two && max_streams() >= 3;
+    if (two && !sc->side) {
+        int lo_prio = 0, hi_prio = 0;
+        CU(cudaDeviceGetStreamPriorityRange(&lo_prio, &hi_prio));
+        CU(cudaStreamCreateWithPriority(&sc->side, cudaStreamNonBlocking, hi_prio));      // its (small) launches go first when blocks retire
+        CU(cudaEventCreateWithFlags(&sc->ev_fork, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&sc->ev_join, cudaEventDisableTiming));
+        for (int k = 0; k < 2; k++) { CU(cudaEventCreateWithFlags(&sc->ev_l0[k], cudaEventDisableTiming)); CU(cudaEventCreateWithFlags(&sc->ev_deep[k], cudaEventDisableTiming)); }
     }
     const size_t smem = (sc->has_mesh || sc->has_tlas) ? sizeof(int) * RT_STACK_ROWS * RT_BLOCK : 0;
     if (smem) {
@@ -479,55 +531,73 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
     const int g_hit0 = b_hit * waves, g_shadow0 = b_shadow * waves, g_shade0 = b_shade * waves;              // level 0
     const int g_hit = b_hit * waves_deep, g_shadow = b_shadow * waves_deep, g_shade = b_shade * waves_deep;   // queued levels
     const int g_tail = sc->sm_count * waves_deep * (HAS_NODES ? RT_MIN_BLOCKS_HIT_CSG : RT_MIN_BLOCKS_TAIL);
-    HitPlanes H{sc->d_hit, sc->hit_cap};
     PixelMap pmk = pm;                                   // + the sample-slot divisors of this scene
     pmk.fd_N = make_fastdiv((unsigned)N); pmk.fd_T = make_fastdiv((unsigned)V.T); pmk.fd_S = make_fastdiv((unsigned)V.S);
+    if (two) {                                           // the side stream starts after everything the caller queued before this call
+        CU(cudaEventRecord(sc->ev_fork, st));
+        CU(cudaStreamWaitEvent(sc->side, sc->ev_fork, 0));
+    }
 
     // the hit/occlusion planes are indexed with the stride of their allocation; occ planes use H.cap as stride
-    for (long long p0 = 0; p0 < pm.n_local_pixels; p0 += px_per_batch) {
+    long long bi = 0;
+    for (long long p0 = 0; p0 < pm.n_local_pixels; p0 += px_per_batch, bi++) {
         const long long npx = std::min(px_per_batch, pm.n_local_pixels - p0);
         const long long n_rays = npx * N;
-        CU(cudaMemsetAsync(sc->d_qcount, 0, sizeof(unsigned long long) * (size_t)(V.max_depth + 2), st));
-        RayQueue q0{sc->d_queue[0], sc->queue_cap}, q1{sc->d_queue[1], sc->queue_cap};
+        WorkSet& w = sc->ws[two ? (bi & 1) : 0];
+        cudaStream_t s = (two && !pipe && (bi & 1)) ? sc->side : st;      // a stream's batches run in order, so its set is free again when the next one starts
+        HitPlanes H{w.d_hit, w.hit_cap};
+        if (pipe && bi >= 2) CU(cudaStreamWaitEvent(st, sc->ev_deep[bi & 1], 0));      // the set is free when the deeper levels of batch bi - 2 are done
+        CU(cudaMemsetAsync(w.d_qcount, 0, sizeof(unsigned long long) * (size_t)(V.max_depth + 2), s));
+        RayQueue q0{w.d_queue[0], w.queue_cap}, q1{w.d_queue[1], w.queue_cap};
         const long long need = (n_rays + RT_BLOCK - 1) / RT_BLOCK;
         {   // level 0: generated rays
-            { ProfScope ps_(sc, PC_HIT0, st);
-              k_hit<HAS_NODES, true><<<(int)std::min<long long>(need, g_hit0), RT_BLOCK, smem, st>>>(V, pmk, p0, n_rays, q0, nullptr, H, sc->d_counters + 0); }
-            if (V.n_lights > 0) { ProfScope ps_(sc, PC_SHADOW0, st);
+            { ProfScope ps_(sc, PC_HIT0, s);
+              k_hit<HAS_NODES, true><<<(int)std::min<long long>(need, g_hit0), RT_BLOCK, smem, s>>>(V, pmk, p0, n_rays, q0, nullptr, H, sc->d_counters + 0); }
+            if (V.n_lights > 0) { ProfScope ps_(sc, PC_SHADOW0, s);
               // the packet walk needs the shared stack area (scenes with a BVH to walk); without one there is nothing to walk per warp
-              if (RT_PACKET_SHADOW && smem) k_shadow<HAS_NODES, SHADOW_PACKET><<<(int)std::min<long long>(need, g_shadow0), RT_BLOCK, smem, st>>>(V, n_rays, nullptr, H, sc->d_occ, sc->d_counters + 1);
-              else k_shadow<HAS_NODES, SHADOW_PER_RAY><<<(int)std::min<long long>(need, g_shadow0), RT_BLOCK, smem, st>>>(V, n_rays, nullptr, H, sc->d_occ, sc->d_counters + 1);
+              if (RT_PACKET_SHADOW && smem) k_shadow<HAS_NODES, SHADOW_PACKET><<<(int)std::min<long long>(need, g_shadow0), RT_BLOCK, smem, s>>>(V, n_rays, nullptr, H, w.d_occ, sc->d_counters + 1);
+              else k_shadow<HAS_NODES, SHADOW_PER_RAY><<<(int)std::min<long long>(need, g_shadow0), RT_BLOCK, smem, s>>>(V, n_rays, nullptr, H, w.d_occ, sc->d_counters + 1);
               (*launches)++; }
-            { ProfScope ps_(sc, PC_SHADE0, st);
-              k_shade<true><<<(int)std::min<long long>(need, g_shade0), RT_BLOCK, 0, st>>>(V, pmk, p0, n_rays, q0, nullptr, H, sc->d_occ, sc->d_samples, q0, sc->d_qcount, sc->d_counters + 2); }
+            { ProfScope ps_(sc, PC_SHADE0, s);
+              k_shade<true><<<(int)std::min<long long>(need, g_shade0), RT_BLOCK, 0, s>>>(V, pmk, p0, n_rays, q0, nullptr, H, w.d_occ, w.d_samples, q0, w.d_qcount, sc->d_counters + 2); }
             (*launches) += 2;
+        }
+        if (pipe) {                                      // the rest of this batch runs on the side stream, under level 0 of the next batch
+            CU(cudaEventRecord(sc->ev_l0[bi & 1], st));
+            CU(cudaStreamWaitEvent(sc->side, sc->ev_l0[bi & 1], 0));
+            s = sc->side;
         }
         if (secondary) {
             const int tail_level = tail_level_for(HAS_NODES);
             for (int level = 1; level < V.max_depth; level++) {       // level L consumes the rays spawned by level L-1
                 RayQueue& qin = (level & 1) ? q0 : q1;
                 RayQueue& qout = (level & 1) ? q1 : q0;
-                const unsigned long long* n_in = sc->d_qcount + (level - 1);
+                const unsigned long long* n_in = w.d_qcount + (level - 1);
                 if (tail_level > 0 && level >= tail_level) {          // the small remainder: every path to its end in one launch
-                    ProfScope ps_(sc, PC_TAIL, st);
-                    k_tail<HAS_NODES><<<g_tail, RT_BLOCK, smem, st>>>(V, qin, n_in, sc->d_samples, sc->d_counters + 3);
+                    ProfScope ps_(sc, PC_TAIL, s);
+                    k_tail<HAS_NODES><<<g_tail, RT_BLOCK, smem, s>>>(V, qin, n_in, w.d_samples, sc->d_counters + 3);
                     (*launches)++;
                     break;
                 }
-                { ProfScope ps_(sc, level == 1 ? PC_HIT1 : PC_DEEP, st);
-                  k_hit<HAS_NODES, false><<<g_hit, RT_BLOCK, smem, st>>>(V, pmk, 0, 0, qin, n_in, H, sc->d_counters + 3); }
-                if (V.n_lights > 0) { ProfScope ps_(sc, level == 1 ? PC_SHADOW1 : PC_DEEP, st);
-                  k_shadow<HAS_NODES, SHADOW_ROWS><<<dim3((unsigned)std::max(1, g_shadow / V.n_lights), (unsigned)V.n_lights), RT_BLOCK, smem, st>>>(V, 0, n_in, H, sc->d_occ, sc->d_counters + 3); (*launches)++; }
-                { ProfScope ps_(sc, level == 1 ? PC_SHADE1 : PC_DEEP, st);
-                  k_shade<false><<<g_shade, RT_BLOCK, 0, st>>>(V, pmk, 0, 0, qin, n_in, H, sc->d_occ, sc->d_samples, qout, sc->d_qcount + level, sc->d_counters + 3); }
+                { ProfScope ps_(sc, level == 1 ? PC_HIT1 : PC_DEEP, s);
+                  k_hit<HAS_NODES, false><<<g_hit, RT_BLOCK, smem, s>>>(V, pmk, 0, 0, qin, n_in, H, sc->d_counters + 3); }
+                if (V.n_lights > 0) { ProfScope ps_(sc, level == 1 ? PC_SHADOW1 : PC_DEEP, s);
+                  k_shadow<HAS_NODES, SHADOW_ROWS><<<dim3((unsigned)std::max(1, g_shadow / V.n_lights), (unsigned)V.n_lights), RT_BLOCK, smem, s>>>(V, 0, n_in, H, w.d_occ, sc->d_counters + 3); (*launches)++; }
+                { ProfScope ps_(sc, level == 1 ? PC_SHADE1 : PC_DEEP, s);
+                  k_shade<false><<<g_shade, RT_BLOCK, 0, s>>>(V, pmk, 0, 0, qin, n_in, H, w.d_occ, w.d_samples, qout, w.d_qcount + level, sc->d_counters + 3); }
                 (*launches) += 2;
             }
         }
         {
-            ProfScope ps_(sc, PC_RESOLVE, st);
-            k_resolve<<<(int)((npx + 127) / 128), 128, 0, st>>>(pm, p0, (int)npx, N, sc->d_samples, d_out, direct);
+            ProfScope ps_(sc, PC_RESOLVE, s);
+            k_resolve<<<(int)((npx + 127) / 128), 128, 0, s>>>(pm, p0, (int)npx, N, w.d_samples, d_out, direct);
         }
         (*launches)++;
+        if (pipe) CU(cudaEventRecord(sc->ev_deep[bi & 1], sc->side));
+    }
+    if (two) {                                           // the caller's stream continues when the side stream's batches are done too
+        CU(cudaEventRecord(sc->ev_join, sc->side));
+        CU(cudaStreamWaitEvent(st, sc->ev_join, 0));
     }
     CU(cudaGetLastError());
     return RT_OK;
@@ -609,14 +679,15 @@ extern "C" int rt_render_static(RtScene* sc, const RtRenderJob* job, float* d_ou
     UP(static_scratch(sc->device, &base));
     // the handle's own work buffers step aside for the duration of the call (render_impl sizes its batches from max_batch_rays and
     // never grows a buffer whose capacity already covers a batch); event pairs of the profiler are not recorded here either
-    struct Saved { float4* samples; long long samples_cap; float4* q0; float4* q1; long long queue_cap; float4* hit; long long hit_cap;
-                   uint8_t* occ; long long occ_cap; bool profiling; };
-    const Saved keep{sc->d_samples, sc->samples_cap, sc->d_queue[0], sc->d_queue[1], sc->queue_cap, sc->d_hit, sc->hit_cap, sc->d_occ, sc->occ_cap, sc->profiling};
-    sc->d_samples = (float4*)(base + RT_STATIC_OFF_SAMPLES); sc->samples_cap = RT_STATIC_MAX_RAYS;
-    sc->d_hit = (float4*)(base + RT_STATIC_OFF_HIT); sc->hit_cap = RT_STATIC_MAX_RAYS;
-    sc->d_occ = (uint8_t*)(base + RT_STATIC_OFF_OCC); sc->occ_cap = (long long)RT_STATIC_MAX_LIGHTS * RT_STATIC_MAX_RAYS;
-    sc->d_queue[0] = (float4*)(base + RT_STATIC_OFF_Q0); sc->d_queue[1] = (float4*)(base + RT_STATIC_OFF_Q1); sc->queue_cap = RT_STATIC_MAX_RAYS;
+    const WorkSet keep = sc->ws[0];
+    const bool keep_profiling = sc->profiling;
+    WorkSet& w = sc->ws[0];
+    w.d_samples = (float4*)(base + RT_STATIC_OFF_SAMPLES); w.samples_cap = RT_STATIC_MAX_RAYS;
+    w.d_hit = (float4*)(base + RT_STATIC_OFF_HIT); w.hit_cap = RT_STATIC_MAX_RAYS;
+    w.d_occ = (uint8_t*)(base + RT_STATIC_OFF_OCC); w.occ_cap = (long long)RT_STATIC_MAX_LIGHTS * RT_STATIC_MAX_RAYS;
+    w.d_queue[0] = (float4*)(base + RT_STATIC_OFF_Q0); w.d_queue[1] = (float4*)(base + RT_STATIC_OFF_Q1); w.queue_cap = RT_STATIC_MAX_RAYS;
     sc->profiling = false;
+    sc->serial_only = true;                 // one work set (the static array) on the caller's stream: no second stream, no events
     RtRenderJob j = *job;
     j.max_batch_rays = RT_STATIC_MAX_RAYS;
     unsigned long long launches = 0;
@@ -624,11 +695,11 @@ extern "C" int rt_render_static(RtScene* sc, const RtRenderJob* job, float* d_ou
     cudaError_t e = cudaMemsetAsync(sc->d_counters, 0, RT_COUNTER_CLASSES * sizeof(RtCounters), st);
     if (e != cudaSuccess) rc = fail(RT_ERR_CUDA, std::string("rt_render_static: cudaMemsetAsync: ") + cudaGetErrorString(e));
     if (rc == RT_OK) rc = sc->has_nodes ? render_impl<true>(sc, &j, pm, d_out, st, &launches) : render_impl<false>(sc, &j, pm, d_out, st, &launches);
-    const bool intact = sc->d_samples == (float4*)(base + RT_STATIC_OFF_SAMPLES) && sc->d_hit == (float4*)(base + RT_STATIC_OFF_HIT) &&
-                        sc->d_occ == (uint8_t*)(base + RT_STATIC_OFF_OCC) && sc->d_queue[0] == (float4*)(base + RT_STATIC_OFF_Q0) &&
-                        sc->d_queue[1] == (float4*)(base + RT_STATIC_OFF_Q1);
-    sc->d_samples = keep.samples; sc->samples_cap = keep.samples_cap; sc->d_queue[0] = keep.q0; sc->d_queue[1] = keep.q1; sc->queue_cap = keep.queue_cap;
-    sc->d_hit = keep.hit; sc->hit_cap = keep.hit_cap; sc->d_occ = keep.occ; sc->occ_cap = keep.occ_cap; sc->profiling = keep.profiling;
+    const bool intact = w.d_samples == (float4*)(base + RT_STATIC_OFF_SAMPLES) && w.d_hit == (float4*)(base + RT_STATIC_OFF_HIT) &&
+                        w.d_occ == (uint8_t*)(base + RT_STATIC_OFF_OCC) && w.d_queue[0] == (float4*)(base + RT_STATIC_OFF_Q0) &&
+                        w.d_queue[1] == (float4*)(base + RT_STATIC_OFF_Q1);
+    sc->ws[0] = keep;
+    sc->profiling = keep_profiling; sc->serial_only = false;
     if (rc != RT_OK) return rc;
     if (!intact) return fail(RT_ERR_LIMIT, "rt_render_static: a batch outgrew the static scratch");
     sc->last_launches = launches;

@@ -249,14 +249,51 @@ RT_HD unsigned as_uint(float f) { return (unsigned)as_int(f); }
 RT_HD int link_of(const int4& l, unsigned slot) { return (slot & 2u) ? ((slot & 1u) ? l.w : l.z) : ((slot & 1u) ? l.y : l.x); }
 RT_HD void key_swap(unsigned& a, unsigned& b) { unsigned lo = a < b ? a : b, hi = a < b ? b : a; a = lo; b = hi; }
 
-// entry/exit distances of one child box from its entry planes (NX,NY,NZ) and exit planes (FX,FY,FZ); an empty slot
-// holds [+inf, -inf] boxes: its entry distance is +inf and its exit distance -inf for every direction sign
-#define RT_SLAB4(NX, NY, NZ, FX, FY, FZ, TMAXK, NEAR, HIT)                                                                      \
-    {                                                                                                                          \
-        NEAR = fmaxf(fmaxf(fmaf(NX, ri.inv.x, ri.oinv.x), fmaf(NY, ri.inv.y, ri.oinv.y)), fmaxf(fmaf(NZ, ri.inv.z, ri.oinv.z), tmin));          \
-        const float far_ = fminf(fminf(fmaf(FX, ri.inv.x, ri.oinv.x), fmaf(FY, ri.inv.y, ri.oinv.y)), fminf(fmaf(FZ, ri.inv.z, ri.oinv.z), TMAXK)); \
-        HIT = NEAR <= far_;                                                                                                    \
+// Entry/exit distances of the four child boxes of a node from its entry planes (pnx, pny, pnz) and exit planes (pfx, pfy, pfz);
+// an empty slot holds [+inf, -inf] boxes: its entry distance is +inf and its exit distance -inf for every direction sign.
+// On the device the 24 plane * (1/d) + (-o/d) products are 12 FFMA2: Blackwell's packed FP32 FMA (fma.rn.f32x2, sm_100+) takes the
+// two plane values of a child pair as one 64-bit register pair - exactly how LDG.128 delivers them - and broadcasts the scalar
+// reciprocal and offset (SASS: FFMA2 R, R.F32x2.HI_LO, R.F32, R.F32).  Each half is an IEEE fused multiply-add, so the
+// distances are bit-identical to the scalar form; the walkers are issue-bound, and this removes 12 issue slots per node.
+struct Slab4 { float n0, n1, n2, n3; bool h0, h1, h2, h3; };
+#if defined(__CUDA_ARCH__)
+__device__ __forceinline__ float2 rt_fma2(float a0, float a1, float b, float c) {
+    unsigned long long va, vb, vc, r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(va) : "f"(a0), "f"(a1));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(vb) : "f"(b));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(vc) : "f"(c));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(va), "l"(vb), "l"(vc));
+    float2 o;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(o.x), "=f"(o.y) : "l"(r));
+    return o;
+}
+#else
+inline float2 rt_fma2(float a0, float a1, float b, float c) { float2 o; o.x = fmaf(a0, b, c); o.y = fmaf(a1, b, c); return o; }
+#endif
+// USE_TMAX = false: the far distances are not clipped at all (walks whose tmax is +inf by construction: mesh shadows ignore t_max)
+template <bool USE_TMAX>
+RT_HD Slab4 slab4(const float4& pnx, const float4& pny, const float4& pnz, const float4& pfx, const float4& pfy, const float4& pfz,
+                  const float3 inv, const float3 oinv, const float tmin, const float t0, const float t1, const float t2, const float t3) {
+    const float2 nx01 = rt_fma2(pnx.x, pnx.y, inv.x, oinv.x), nx23 = rt_fma2(pnx.z, pnx.w, inv.x, oinv.x);
+    const float2 ny01 = rt_fma2(pny.x, pny.y, inv.y, oinv.y), ny23 = rt_fma2(pny.z, pny.w, inv.y, oinv.y);
+    const float2 nz01 = rt_fma2(pnz.x, pnz.y, inv.z, oinv.z), nz23 = rt_fma2(pnz.z, pnz.w, inv.z, oinv.z);
+    const float2 fx01 = rt_fma2(pfx.x, pfx.y, inv.x, oinv.x), fx23 = rt_fma2(pfx.z, pfx.w, inv.x, oinv.x);
+    const float2 fy01 = rt_fma2(pfy.x, pfy.y, inv.y, oinv.y), fy23 = rt_fma2(pfy.z, pfy.w, inv.y, oinv.y);
+    const float2 fz01 = rt_fma2(pfz.x, pfz.y, inv.z, oinv.z), fz23 = rt_fma2(pfz.z, pfz.w, inv.z, oinv.z);
+    Slab4 r;
+    r.n0 = fmaxf(fmaxf(nx01.x, ny01.x), fmaxf(nz01.x, tmin)); r.n1 = fmaxf(fmaxf(nx01.y, ny01.y), fmaxf(nz01.y, tmin));
+    r.n2 = fmaxf(fmaxf(nx23.x, ny23.x), fmaxf(nz23.x, tmin)); r.n3 = fmaxf(fmaxf(nx23.y, ny23.y), fmaxf(nz23.y, tmin));
+    float f0, f1, f2, f3_;
+    if (USE_TMAX) {
+        f0 = fminf(fminf(fx01.x, fy01.x), fminf(fz01.x, t0)); f1 = fminf(fminf(fx01.y, fy01.y), fminf(fz01.y, t1));
+        f2 = fminf(fminf(fx23.x, fy23.x), fminf(fz23.x, t2)); f3_ = fminf(fminf(fx23.y, fy23.y), fminf(fz23.y, t3));
+    } else {
+        f0 = fminf(fminf(fx01.x, fy01.x), fz01.x); f1 = fminf(fminf(fx01.y, fy01.y), fz01.y);
+        f2 = fminf(fminf(fx23.x, fy23.x), fz23.x); f3_ = fminf(fminf(fx23.y, fy23.y), fz23.y);
     }
+    r.h0 = r.n0 <= f0; r.h1 = r.n1 <= f1; r.h2 = r.n2 <= f2; r.h3 = r.n3 <= f3_;
+    return r;
+}
 #define RT_PLANE_AT(NB, OFF) ld4((const float4*)((NB) + (OFF)))
 #define RT_NODE_BASE(NP) const char* nb_ = (const char*)(NP);
 #define RT_LOAD_NODE4(NP)                                                                                                       \
@@ -320,11 +357,8 @@ RT_HD int bvh4_next(TraceCtx& cx, const BvhNode4* __restrict__ nodes, int& cur, 
             if (fl.z & RT_TLAS_NO_TMAX) t2 = RT_INF;
             if (fl.w & RT_TLAS_NO_TMAX) t3 = RT_INF;
         }
-        float n0, n1, n2, n3; bool h0, h1, h2, h3;
-        RT_SLAB4(pnx.x, pny.x, pnz.x, pfx.x, pfy.x, pfz.x, t0, n0, h0)
-        RT_SLAB4(pnx.y, pny.y, pnz.y, pfx.y, pfy.y, pfz.y, t1, n1, h1)
-        RT_SLAB4(pnx.z, pny.z, pnz.z, pfx.z, pfy.z, pfz.z, t2, n2, h2)
-        RT_SLAB4(pnx.w, pny.w, pnz.w, pfx.w, pfy.w, pfz.w, t3, n3, h3)
+        const Slab4 sl = slab4<true>(pnx, pny, pnz, pfx, pfy, pfz, ri.inv, ri.oinv, tmin, t0, t1, t2, t3);
+        const float n0 = sl.n0, n1 = sl.n1, n2 = sl.n2, n3 = sl.n3; const bool h0 = sl.h0, h1 = sl.h1, h2 = sl.h2, h3 = sl.h3;
         if (ORDERED) {
             // sort (entry distance, slot) keys: entry distances are >= tmin >= 0, so their bit patterns order as integers
             unsigned k0 = h0 ? ((as_uint(n0) & 0x7ffffffcu) | 0u) : 0xffffffffu;
@@ -382,11 +416,9 @@ RT_HD void mesh_visit(TraceCtx& cx, const DevMesh* m, const RayInv& ri, float tm
         const BvhNode4* np = nodes + cur;
         RT_LOAD_NODE4(np)
         cx.tally.nodes++;
-        float n0, n1, n2, n3; bool h0, h1, h2, h3;
-        RT_SLAB4(pnx.x, pny.x, pnz.x, pfx.x, pfy.x, pfz.x, tmax, n0, h0)
-        RT_SLAB4(pnx.y, pny.y, pnz.y, pfx.y, pfy.y, pfz.y, tmax, n1, h1)
-        RT_SLAB4(pnx.z, pny.z, pnz.z, pfx.z, pfy.z, pfz.z, tmax, n2, h2)
-        RT_SLAB4(pnx.w, pny.w, pnz.w, pfx.w, pfy.w, pfz.w, tmax, n3, h3)
+        // (the unordered walk is the mesh shadow test, which ignores t_max: its tmax is +inf and stays +inf, no far clip needed)
+        const Slab4 sl = slab4<ORDERED>(pnx, pny, pnz, pfx, pfy, pfz, ri.inv, ri.oinv, tmin, tmax, tmax, tmax, tmax);
+        const float n0 = sl.n0, n1 = sl.n1, n2 = sl.n2, n3 = sl.n3; bool h0 = sl.h0, h1 = sl.h1, h2 = sl.h2, h3 = sl.h3;
         // the links of the children whose boxes the ray touches (RT_LINK_NONE otherwise)
         const int l0 = h0 ? link.x : RT_LINK_NONE, l1 = h1 ? link.y : RT_LINK_NONE, l2 = h2 ? link.z : RT_LINK_NONE, l3 = h3 ? link.w : RT_LINK_NONE;
         // leaf children (negative links): their triangles are tested here and now
@@ -1047,12 +1079,8 @@ __device__ __forceinline__ void bvh4_anyhit_packet(TraceCtx& cx, const BvhNode4*
             if (fl.z & RT_TLAS_NO_TMAX) t2 = RT_INF;
             if (fl.w & RT_TLAS_NO_TMAX) t3 = RT_INF;
         }
-        float n0, n1, n2, n3; bool h0, h1, h2, h3;
-        RT_SLAB4(pnx.x, pny.x, pnz.x, pfx.x, pfy.x, pfz.x, t0, n0, h0)
-        RT_SLAB4(pnx.y, pny.y, pnz.y, pfx.y, pfy.y, pfz.y, t1, n1, h1)
-        RT_SLAB4(pnx.z, pny.z, pnz.z, pfx.z, pfy.z, pfz.z, t2, n2, h2)
-        RT_SLAB4(pnx.w, pny.w, pnz.w, pfx.w, pfy.w, pfz.w, t3, n3, h3)
-        (void)n0; (void)n1; (void)n2; (void)n3;
+        const Slab4 sl = slab4<true>(pnx, pny, pnz, pfx, pfy, pfz, ri.inv, ri.oinv, tmin, t0, t1, t2, t3);
+        const bool h0 = sl.h0, h1 = sl.h1, h2 = sl.h2, h3 = sl.h3;
         const unsigned mine = active ? ((unsigned)h0 | (unsigned)h1 << 1 | (unsigned)h2 << 2 | (unsigned)h3 << 3) : 0u;
         const unsigned any4 = __reduce_or_sync(RT_FULL_WARP, mine);
         visits += active ? 1u : 0u;

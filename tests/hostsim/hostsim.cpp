@@ -244,6 +244,38 @@ extern "C" int hostsim_node_counts(const RtSceneDesc* d, const int32_t* cols, co
     return 0;
 }
 
+// diagnostics: per (pixel, sample slot, light) of the FIRST level: kind of the hit object (-1: miss), occluded, mesh nodes visited,
+// triangles tested, object-BVH nodes + primitive tests, of that one shadow ray (scripts/shadow_stats.py)
+extern "C" int hostsim_shadow_stats(const RtSceneDesc* d, const int32_t* cols, const int32_t* rows, int64_t n, int32_t* out) {
+    Sim sim;
+    int rc = make_sim(d, sim);
+    if (rc) return rc;
+    const SceneView& V = sim.V;
+    const int N = V.D * V.S * V.T, L = V.n_lights;
+#pragma omp parallel for schedule(dynamic, 16)
+    for (int64_t i = 0; i < n; i++) {
+        int stack[RT_STACK_DEPTH], spill[RT_STACK_SPILL];
+        for (int slot = 0; slot < N; slot++) {
+            const int t = slot % V.T, ds = slot / V.T, s = ds % V.S, dd = ds / V.S;
+            Tally tally{};
+            Ray ray = generate_ray(V, cols[i], rows[i], dd, s);
+            TraceCtx cx{V, V.times[t], tally, stack, 1, spill};
+            Hit h;
+            const bool hit = sim.hs.has_nodes ? closest_hit<true>(cx, ray, h) : closest_hit<false>(cx, ray, h);
+            for (int li = 0; li < L; li++) {
+                int32_t* o = out + ((i * N + slot) * L + li) * 5;
+                o[0] = hit ? V.objects[h.geom].kind : -1; o[1] = o[2] = o[3] = o[4] = 0;
+                if (!hit) continue;
+                Tally t2{};
+                TraceCtx c2{V, V.times[t], t2, stack, 1, spill};
+                o[1] = (sim.hs.has_nodes ? light_occluded<true>(c2, h.p, li) : light_occluded<false>(c2, h.p, li)) ? 1 : 0;
+                o[2] = (int)t2.nodes; o[3] = (int)t2.tris; o[4] = (int)t2.prims;
+            }
+        }
+    }
+    return 0;
+}
+
 // returns the number of 4-wide nodes (>= 0) or -(status); nodes_out holds up to n_faces-1 nodes of 32 floats
 extern "C" int hostsim_bvh(const RtSceneDesc* d, int mesh, float* nodes_out, int32_t* order_out) {
     Sim sim;
