@@ -108,6 +108,7 @@ struct RtScene {
     std::vector<void*> allocs;
     std::vector<MeshBuild> meshes;
     std::vector<DevMesh> h_meshes;
+    std::vector<DevObject> h_objs;             // host copy of the object records (which mesh a top-level mesh object uses)
     DevMesh* d_meshes = nullptr;
     bool has_nodes = false, has_specular = false, has_mesh = false, has_tlas = false;
     int samples_per_pixel = 1;
@@ -120,6 +121,9 @@ struct RtScene {
     cudaEvent_t ev_l0[2] = {nullptr, nullptr}, ev_deep[2] = {nullptr, nullptr};   // pipeline mode: level 0 of a set done / its deeper levels + resolve done
     bool serial_only = false;                  // rt_render_static: one set (the static array), one stream
     RtCounters* d_counters = nullptr;
+    SceneView* d_view = nullptr;               // the scene as the general kernels read it (ViewArg<true>): one copy in global memory
+    SceneView h_view_dev{};                    // what d_view holds
+    bool view_dev_valid = false;
     float* d_stage = nullptr; long long stage_cap = 0;   // rt_render_host staging
     uint8_t* d_stage_u8 = nullptr; long long stage_u8_cap = 0;
     int device = 0;
@@ -177,6 +181,7 @@ static int scene_create_impl(const RtSceneDesc* d, RtScene* sc) {
     sc->view = hs.view;
     SceneView& V = sc->view;
     DevObject* d_objs; UP(upload(sc, hs.objs.data(), hs.objs.size(), &d_objs));
+    sc->h_objs = hs.objs;
     DevMaterial* d_mats; UP(upload(sc, hs.mats.data(), hs.mats.size(), &d_mats));
     DevLight* d_lights; UP(upload(sc, hs.lights.data(), hs.lights.size(), &d_lights));
     static_assert(sizeof(DevXform) == sizeof(RtXform), "xform layout");
@@ -233,6 +238,7 @@ static int scene_create_impl(const RtSceneDesc* d, RtScene* sc) {
     sc->samples_per_pixel = d->dof_samples * d->aa_samples * d->n_times;
     for (int k = 0; k < 2; k++) UP(upload(sc, (const unsigned long long*)nullptr, (size_t)d->max_depth + 2, &sc->ws[k].d_qcount));
     UP(upload(sc, (const RtCounters*)nullptr, RT_COUNTER_CLASSES, &sc->d_counters));
+    UP(upload(sc, (const SceneView*)nullptr, 1, &sc->d_view));
     CU(cudaDeviceSynchronize());     // the memsets above ran on the legacy stream; later kernels run on caller streams
     return RT_OK;
 }
@@ -389,6 +395,8 @@ extern "C" int rt_scene_build_bvh(RtScene* sc, void* stream) {
         if (!sc->meshes[i].built) UP(build_mesh_bvh(sc, (int)i, (cudaStream_t)stream));
     if (!sc->h_meshes.empty())
         CU(cudaMemcpy(sc->d_meshes, sc->h_meshes.data(), sizeof(DevMesh) * sc->h_meshes.size(), cudaMemcpyHostToDevice));
+    rtb::fill_const_meshes(sc->view, sc->h_objs, sc->h_meshes.data());
+    sc->view_dev_valid = false;
     return RT_OK;
 }
 
@@ -435,6 +443,20 @@ static int grow(T** buf, long long* cap, long long need, size_t elems_per_unit =
     return RT_OK;
 }
 
+// The scene argument of the HAS_NODES-templated kernels: by value, or the pointer to the device copy, which is brought up to date
+// first (it changes only with the job's mesh_mode test bits and when the LBVHs are built; a plain render copies nothing).
+static int sync_device_view(RtScene* sc, const SceneView& V, cudaStream_t st) {
+    if (sc->view_dev_valid && memcmp(&sc->h_view_dev, &V, sizeof V) == 0) return RT_OK;
+    if (sc->view_dev_valid) CU(cudaStreamSynchronize(st));     // (kernels of an earlier call on another stream may still read the old copy: callers keep one call in flight)
+    memcpy(&sc->h_view_dev, &V, sizeof V);
+    CU(cudaMemcpyAsync(sc->d_view, &sc->h_view_dev, sizeof V, cudaMemcpyHostToDevice, st));
+    sc->view_dev_valid = true;
+    return RT_OK;
+}
+template <bool HAS_NODES> static ViewArg<HAS_NODES> view_arg(RtScene* sc, const SceneView& V);
+template <> ViewArg<false> view_arg<false>(RtScene*, const SceneView& V) { return ViewArg<false>{V}; }
+template <> ViewArg<true> view_arg<true>(RtScene* sc, const SceneView&) { return ViewArg<true>{sc->d_view}; }
+
 static void sum_counters(const RtCounters* cls, RtCounters* out) {
     memset(out, 0, sizeof *out);
     uint64_t* o = (uint64_t*)out;
@@ -447,13 +469,16 @@ static void sum_counters(const RtCounters* cls, RtCounters* out) {
 }
 
 // Batch size of a frame when the job does not name one.  Two work sets of 64 Mi rays (samples 1 + hit planes 2 + occlusion 0.2 + queues
-// 2 x 5 GiB each) cost what one set of 128 Mi rays did.  Frames above RT_SPLIT_RAYS are cut into at least two batches so that the two
-// streams have something to overlap; smaller frames are launch-latency bound and stay one batch on the caller's stream.
+// 2 x 5 GiB each) cost what one set of 128 Mi rays did.  A frame that fits one batch stays one batch on the caller's stream: cutting
+// a rank's 66 M-ray share of the 4K frame in two to have something to overlap measured 15.97 instead of 15.30 ms.  Scenes with CSG /
+// transform nodes are the exception: their kernels are latency-bound at 4 blocks/SM, two batches in flight fill the machine better
+// (NovelScene1 at its shipped 2048x1024x32 = 64 Mi primary rays: 60.0 ms in two batches, 66.6 in one), so above RT_SPLIT_RAYS_NODES
+// rays such a frame is cut in at least two.
 #ifndef RT_DEFAULT_BATCH_RAYS
 #define RT_DEFAULT_BATCH_RAYS (64ll << 20)
 #endif
-#ifndef RT_SPLIT_RAYS
-#define RT_SPLIT_RAYS (16ll << 20)
+#ifndef RT_SPLIT_RAYS_NODES
+#define RT_SPLIT_RAYS_NODES (16ll << 20)
 #endif
 // developer override for experiments: B200RT_STREAMS=1 keeps every batch on the caller's stream (echoed by bench.py)
 // 1 = every batch on the caller's stream; 2 = whole batches alternate between two streams; 3 = pipeline: level 0 of every batch on
@@ -496,7 +521,7 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
     max_rays = std::min(max_rays, 1ll << 30);
     long long px_per_batch = std::max(1ll, max_rays / N);
     long long n_batches = std::max(1ll, (pm.n_local_pixels + px_per_batch - 1) / px_per_batch);
-    if (job->max_batch_rays <= 0 && n_batches == 1 && pm.n_local_pixels * N > RT_SPLIT_RAYS && !sc->serial_only) n_batches = 2;
+    if (HAS_NODES && job->max_batch_rays <= 0 && n_batches == 1 && pm.n_local_pixels * N > RT_SPLIT_RAYS_NODES && !sc->serial_only) n_batches = 2;
     if (pm.n_local_pixels > 0) px_per_batch = std::min(px_per_batch, (pm.n_local_pixels + n_batches - 1) / n_batches);
     const long long batch_cap = std::min(px_per_batch, std::max(1ll, pm.n_local_pixels)) * N;
     // two streams when there are two batches to overlap; the per-launch event pairs of the profiler want one launch at a time
@@ -533,6 +558,8 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
     const int g_tail = sc->sm_count * waves_deep * (HAS_NODES ? RT_MIN_BLOCKS_HIT_CSG : RT_MIN_BLOCKS_TAIL);
     PixelMap pmk = pm;                                   // + the sample-slot divisors of this scene
     pmk.fd_N = make_fastdiv((unsigned)N); pmk.fd_T = make_fastdiv((unsigned)V.T); pmk.fd_S = make_fastdiv((unsigned)V.S);
+    if (HAS_NODES) UP(sync_device_view(sc, V, st));
+    const ViewArg<HAS_NODES> VA = view_arg<HAS_NODES>(sc, V);
     if (two) {                                           // the side stream starts after everything the caller queued before this call
         CU(cudaEventRecord(sc->ev_fork, st));
         CU(cudaStreamWaitEvent(sc->side, sc->ev_fork, 0));
@@ -552,11 +579,11 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
         const long long need = (n_rays + RT_BLOCK - 1) / RT_BLOCK;
         {   // level 0: generated rays
             { ProfScope ps_(sc, PC_HIT0, s);
-              k_hit<HAS_NODES, true><<<(int)std::min<long long>(need, g_hit0), RT_BLOCK, smem, s>>>(V, pmk, p0, n_rays, q0, nullptr, H, sc->d_counters + 0); }
+              k_hit<HAS_NODES, true><<<(int)std::min<long long>(need, g_hit0), RT_BLOCK, smem, s>>>(VA, pmk, p0, n_rays, q0, nullptr, H, sc->d_counters + 0); }
             if (V.n_lights > 0) { ProfScope ps_(sc, PC_SHADOW0, s);
               // the packet walk needs the shared stack area (scenes with a BVH to walk); without one there is nothing to walk per warp
-              if (RT_PACKET_SHADOW && smem) k_shadow<HAS_NODES, SHADOW_PACKET><<<(int)std::min<long long>(need, g_shadow0), RT_BLOCK, smem, s>>>(V, n_rays, nullptr, H, w.d_occ, sc->d_counters + 1);
-              else k_shadow<HAS_NODES, SHADOW_PER_RAY><<<(int)std::min<long long>(need, g_shadow0), RT_BLOCK, smem, s>>>(V, n_rays, nullptr, H, w.d_occ, sc->d_counters + 1);
+              if (RT_PACKET_SHADOW && smem) k_shadow<HAS_NODES, SHADOW_PACKET><<<(int)std::min<long long>(need, g_shadow0), RT_BLOCK, smem, s>>>(VA, n_rays, nullptr, H, w.d_occ, sc->d_counters + 1);
+              else k_shadow<HAS_NODES, SHADOW_PER_RAY><<<(int)std::min<long long>(need, g_shadow0), RT_BLOCK, smem, s>>>(VA, n_rays, nullptr, H, w.d_occ, sc->d_counters + 1);
               (*launches)++; }
             { ProfScope ps_(sc, PC_SHADE0, s);
               k_shade<true><<<(int)std::min<long long>(need, g_shade0), RT_BLOCK, 0, s>>>(V, pmk, p0, n_rays, q0, nullptr, H, w.d_occ, w.d_samples, q0, w.d_qcount, sc->d_counters + 2); }
@@ -575,14 +602,14 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
                 const unsigned long long* n_in = w.d_qcount + (level - 1);
                 if (tail_level > 0 && level >= tail_level) {          // the small remainder: every path to its end in one launch
                     ProfScope ps_(sc, PC_TAIL, s);
-                    k_tail<HAS_NODES><<<g_tail, RT_BLOCK, smem, s>>>(V, qin, n_in, w.d_samples, sc->d_counters + 3);
+                    k_tail<HAS_NODES><<<g_tail, RT_BLOCK, smem, s>>>(VA, qin, n_in, w.d_samples, sc->d_counters + 3);
                     (*launches)++;
                     break;
                 }
                 { ProfScope ps_(sc, level == 1 ? PC_HIT1 : PC_DEEP, s);
-                  k_hit<HAS_NODES, false><<<g_hit, RT_BLOCK, smem, s>>>(V, pmk, 0, 0, qin, n_in, H, sc->d_counters + 3); }
+                  k_hit<HAS_NODES, false><<<g_hit, RT_BLOCK, smem, s>>>(VA, pmk, 0, 0, qin, n_in, H, sc->d_counters + 3); }
                 if (V.n_lights > 0) { ProfScope ps_(sc, level == 1 ? PC_SHADOW1 : PC_DEEP, s);
-                  k_shadow<HAS_NODES, SHADOW_ROWS><<<dim3((unsigned)std::max(1, g_shadow / V.n_lights), (unsigned)V.n_lights), RT_BLOCK, smem, s>>>(V, 0, n_in, H, w.d_occ, sc->d_counters + 3); (*launches)++; }
+                  k_shadow<HAS_NODES, SHADOW_ROWS><<<dim3((unsigned)std::max(1, g_shadow / V.n_lights), (unsigned)V.n_lights), RT_BLOCK, smem, s>>>(VA, 0, n_in, H, w.d_occ, sc->d_counters + 3); (*launches)++; }
                 { ProfScope ps_(sc, level == 1 ? PC_SHADE1 : PC_DEEP, s);
                   k_shade<false><<<g_shade, RT_BLOCK, 0, s>>>(V, pmk, 0, 0, qin, n_in, H, w.d_occ, w.d_samples, qout, w.d_qcount + level, sc->d_counters + 3); }
                 (*launches) += 2;
@@ -826,10 +853,11 @@ extern "C" int rt_trace_rays(RtScene* sc, int64_t n, const float* h_org, const f
     CU(cudaMemsetAsync(sc->d_counters, 0, sizeof(RtCounters), st));
     if (sc->has_nodes) {
         if (smem) CU(cudaFuncSetAttribute(k_trace<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_trace<true><<<grid, RT_BLOCK, smem, st>>>(V, n, org, dir, times, rgb, t, nn, pp, geom, mat, sc->d_counters);
+        UP(sync_device_view(sc, V, st));
+        k_trace<true><<<grid, RT_BLOCK, smem, st>>>(view_arg<true>(sc, V), n, org, dir, times, rgb, t, nn, pp, geom, mat, sc->d_counters);
     } else {
         if (smem) CU(cudaFuncSetAttribute(k_trace<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_trace<false><<<grid, RT_BLOCK, smem, st>>>(V, n, org, dir, times, rgb, t, nn, pp, geom, mat, sc->d_counters);
+        k_trace<false><<<grid, RT_BLOCK, smem, st>>>(view_arg<false>(sc, V), n, org, dir, times, rgb, t, nn, pp, geom, mat, sc->d_counters);
     }
     CU(cudaGetLastError());
     CU(cudaStreamSynchronize(st));
@@ -858,10 +886,11 @@ extern "C" int rt_occluded(RtScene* sc, int64_t n, const float* h_org, const flo
     const int grid = (int)((n + RT_BLOCK - 1) / RT_BLOCK);
     if (sc->has_nodes) {
         if (smem) CU(cudaFuncSetAttribute(k_occluded<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_occluded<true><<<grid, RT_BLOCK, smem, st>>>(V, n, org, dir, times, tmax, occ, sc->d_counters);
+        UP(sync_device_view(sc, V, st));
+        k_occluded<true><<<grid, RT_BLOCK, smem, st>>>(view_arg<true>(sc, V), n, org, dir, times, tmax, occ, sc->d_counters);
     } else {
         if (smem) CU(cudaFuncSetAttribute(k_occluded<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_occluded<false><<<grid, RT_BLOCK, smem, st>>>(V, n, org, dir, times, tmax, occ, sc->d_counters);
+        k_occluded<false><<<grid, RT_BLOCK, smem, st>>>(view_arg<false>(sc, V), n, org, dir, times, tmax, occ, sc->d_counters);
     }
     CU(cudaGetLastError());
     CU(cudaStreamSynchronize(st));

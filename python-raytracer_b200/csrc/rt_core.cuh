@@ -147,15 +147,51 @@ RT_HD float3 box_normal(const Ray& r, int label) {     // simple_geometry.py:231
 }
 
 // ------------------------------------------------------------------------------------------------
+// How the mesh functions below read a mesh header (DevMesh).  MeshG: through a pointer into the header array in global memory
+// (meshes under CSG / transform nodes, the general kernels).  MeshC: field by field out of SceneConst in the kernel parameter bank
+// (the k-th top-level mesh, lean kernels): every access is a constant-bank operand or an LDC, nothing is held in registers across
+// the walk and nothing goes through the L1 data pipe.  (A POINTER to the parameter copy would make the compiler move the whole
+// SceneView to local memory; hence the accessors.)
+struct MeshG {
+    const DevMesh* m;
+    RT_HD const float4* tri() const { return m->tri; }
+    RT_HD const BvhNode4* nodes() const { return m->nodes; }
+    RT_HD const int4* face_vidx() const { return m->face_vidx; }
+    RT_HD const float4* vnormals() const { return m->vnormals; }
+    RT_HD int n_tris() const { return m->n_tris; }
+    RT_HD int flat_shaded() const { return m->flat_shaded; }
+    RT_HD int gate() const { return m->gate; }
+    RT_HD float gate_radius() const { return m->gate_radius; }
+    RT_HD float4 gate_min() const { return ld4(&m->gate_min); }
+    RT_HD float4 gate_max() const { return ld4(&m->gate_max); }
+    RT_HD float4 gate_center() const { return ld4(&m->gate_center); }
+};
+struct MeshC {
+    const SceneView& S; int k;
+    RT_HD const float4* tri() const { return S.c.sep_mesh[k].tri; }
+    RT_HD const BvhNode4* nodes() const { return S.c.sep_mesh[k].nodes; }
+    RT_HD const int4* face_vidx() const { return S.c.sep_mesh[k].face_vidx; }
+    RT_HD const float4* vnormals() const { return S.c.sep_mesh[k].vnormals; }
+    RT_HD int n_tris() const { return S.c.sep_mesh[k].n_tris; }
+    RT_HD int flat_shaded() const { return S.c.sep_mesh[k].flat_shaded; }
+    RT_HD int gate() const { return S.c.sep_mesh[k].gate; }
+    RT_HD float gate_radius() const { return S.c.sep_mesh[k].gate_radius; }
+    RT_HD float4 gate_min() const { return S.c.sep_mesh[k].gate_min; }
+    RT_HD float4 gate_max() const { return S.c.sep_mesh[k].gate_max; }
+    RT_HD float4 gate_center() const { return S.c.sep_mesh[k].gate_center; }
+};
+
+// ------------------------------------------------------------------------------------------------
 // Mesh gate (bounding_volumes.py:18-37,49-83; SURVEY Q11: a ray starting inside the AABB never hits the mesh)
-RT_HD bool mesh_gate(const DevMesh* m, const Ray& r) {
-    if (m->gate == RT_GATE_SPHERE) {
+template <class M>
+RT_HD bool mesh_gate(const M& m, const Ray& r) {
+    if (m.gate() == RT_GATE_SPHERE) {
         float t1, t2;
-        if (!sphere_roots(f3(ld4(&m->gate_center)), m->gate_radius, r, dot(r.d, r.d), t1, t2)) return false;
+        if (!sphere_roots(f3(m.gate_center()), m.gate_radius(), r, dot(r.d, r.d), t1, t2)) return false;
         return t1 > 0.0f || t2 > 0.0f;
     }
     float en, ex; int label;
-    if (!box_slabs(f3(ld4(&m->gate_min)), f3(ld4(&m->gate_max)), r, en, ex, label)) return false;
+    if (!box_slabs(f3(m.gate_min()), f3(m.gate_max()), r, en, ex, label)) return false;
     return !(en > ex || en < 0.0f);
 }
 
@@ -219,9 +255,10 @@ RT_HD RayInv ray_inv_moved(const RayInv& ri, float3 o) {
 }
 // Mesh gate for rays whose reciprocal direction is at hand (top-level meshes): same decisions as mesh_gate up to the
 // last ulp of the slab distances ((lo - o) * (1/d) instead of (lo - o) / d; six IEEE divisions saved per ray)
-RT_HD bool mesh_gate_rcp(const DevMesh* m, const Ray& r, const RayInv& ri) {
-    if (m->gate == RT_GATE_SPHERE) return mesh_gate(m, r);
-    const float3 mn = f3(ld4(&m->gate_min)), mx = f3(ld4(&m->gate_max));
+template <class M>
+RT_HD bool mesh_gate_rcp(const M& m, const Ray& r, const RayInv& ri) {
+    if (m.gate() == RT_GATE_SPHERE) return mesh_gate(m, r);
+    const float3 mn = f3(m.gate_min()), mx = f3(m.gate_max());
     float entry = -RT_INF, exit_ = RT_INF;
 #if defined(__CUDA_ARCH__)
 #pragma unroll
@@ -397,15 +434,15 @@ RT_HD float sel4(float a, float b, float c, float d, int k) { return (k & 2) ? (
 // ONE loop level: every iteration is a node step (four slab tests) followed by the triangle tests of that node's leaf
 // children, so the lanes of a warp advance node by node in lock-step; an iterator that returns to the caller at every
 // leaf makes each lane wait for the slowest lane's walk to ITS next leaf (measured: 12 of 32 lanes active).
-template <bool ORDERED, class OnTri>
-RT_HD void mesh_visit(TraceCtx& cx, const DevMesh* m, const RayInv& ri, float tmin, float& tmax, OnTri&& onTri) {
-    const int n = m->n_tris;
+template <bool ORDERED, class M, class OnTri>
+RT_HD void mesh_visit(TraceCtx& cx, const M& m, const RayInv& ri, float tmin, float& tmax, OnTri&& onTri) {
+    const int n = m.n_tris();
     if (n <= 0) return;
     if ((cx.S.mesh_mode & RT_MODE_BRUTE_MESH) || n == 1) {
         for (int s = 0; s < n; s++) { cx.tally.tris++; if (onTri(s, tmax)) return; }
         return;
     }
-    const BvhNode4* __restrict__ nodes = m->nodes;
+    const BvhNode4* __restrict__ nodes = m.nodes();
     const int sbase = cx.sbase;
     int cur = 0, sp = sbase;
     for (;;) {
@@ -473,16 +510,18 @@ RT_HD int top_next(TraceCtx& cx, TopIter& it, const RayInv& ri, float tmax) {
     return bvh4_next<!SHADOW, SHADOW>(cx, S.tlas_nodes, it.cur, it.sp, 0, ri, 0.0f, tmax, cx.tally.prims);
 }
 
-RT_HD void tri_load(const DevMesh* m, int slot, float3& v0, float3& v1, float3& v2, int& face) {
-    float4 a = ld4(m->tri + 3 * (size_t)slot), b = ld4(m->tri + 3 * (size_t)slot + 1), c = ld4(m->tri + 3 * (size_t)slot + 2);
+template <class M>
+RT_HD void tri_load(const M& m, int slot, float3& v0, float3& v1, float3& v2, int& face) {
+    float4 a = ld4(m.tri() + 3 * (size_t)slot), b = ld4(m.tri() + 3 * (size_t)slot + 1), c = ld4(m.tri() + 3 * (size_t)slot + 2);
     v0 = f3(a); v1 = f3(b); v2 = f3(c); face = as_int(a.w);
 }
 
 // Shading normal of an accepted triangle hit (mesh.py:84,103-113); barycentrics as libigl computes them
-RT_HD float3 tri_normal(TraceCtx& cx, const DevMesh* m, int slot, float3 p) {
+template <class M>
+RT_HD float3 tri_normal(TraceCtx& cx, const M& m, int slot, float3 p) {
     float3 v0, v1, v2; int face;
     tri_load(m, slot, v0, v1, v2, face);
-    if (m->flat_shaded || m->vnormals == nullptr) return normalize(cross(v1 - v0, v2 - v0));
+    if (m.flat_shaded() || m.vnormals() == nullptr) return normalize(cross(v1 - v0, v2 - v0));
     cx.tally.smooth++;
     float3 e0 = v1 - v0, e1 = v2 - v0, e2 = p - v0;
     float d00 = dot(e0, e0), d01 = dot(e0, e1), d11 = dot(e1, e1), d20 = dot(e2, e0), d21 = dot(e2, e1);
@@ -490,13 +529,14 @@ RT_HD float3 tri_normal(TraceCtx& cx, const DevMesh* m, int slot, float3 p) {
     float l1 = (d11 * d20 - d01 * d21) / denom;
     float l2 = (d00 * d21 - d01 * d20) / denom;
     float l0 = 1.0f - (l1 + l2);
-    int4 vi = RT_LDG(m->face_vidx + slot);
-    float3 n0 = f3(ld4(m->vnormals + vi.x)), n1 = f3(ld4(m->vnormals + vi.y)), n2 = f3(ld4(m->vnormals + vi.z));
+    int4 vi = RT_LDG(m.face_vidx() + slot);
+    float3 n0 = f3(ld4(m.vnormals() + vi.x)), n1 = f3(ld4(m.vnormals() + vi.y)), n2 = f3(ld4(m.vnormals() + vi.z));
     return normalize((n0 * l0 + n1 * l1) + n2 * l2);
 }
 
 // Mesh.shadow_intersect (mesh.py:121-153): gate, then any accepted face; t_max is ignored by the reference
-RT_HD bool mesh_shadow(TraceCtx& cx, const DevMesh* m, const Ray& r, const RayInv& ri) {
+template <class M>
+RT_HD bool mesh_shadow(TraceCtx& cx, const M& m, const Ray& r, const RayInv& ri) {
     if (!mesh_gate_rcp(m, r, ri)) return false;
     bool occ = false;
     float tmax = RT_INF;
@@ -509,13 +549,13 @@ RT_HD bool mesh_shadow(TraceCtx& cx, const DevMesh* m, const Ray& r, const RayIn
     return occ;
 }
 // out-of-line copy for meshes under CSG nodes: keeps that traversal code out of the hot instruction stream
-RT_HD_NOINLINE bool mesh_shadow_cold(TraceCtx& cx, const DevMesh* m, const Ray& r) { return mesh_shadow(cx, m, r, ray_inv(r)); }
+RT_HD_NOINLINE bool mesh_shadow_cold(TraceCtx& cx, const DevMesh* m, const Ray& r) { return mesh_shadow(cx, MeshG{m}, r, ray_inv(r)); }
 
 // Closest accepted face of one top-level mesh against the running best (mesh.py:72-119 + scene.py:94).
 // better(t): would a hit at t replace the current best of OTHER objects; among this mesh's own faces an equal t
 // goes to the lower face index (list order).
-template <class Better>
-RT_HD void mesh_closest(TraceCtx& cx, const DevMesh* m, const Ray& r, const RayInv& ri, float best, Better&& better, float& t_out, int& slot_out) {
+template <class M, class Better>
+RT_HD void mesh_closest(TraceCtx& cx, const M& m, const Ray& r, const RayInv& ri, float best, Better&& better, float& t_out, int& slot_out) {
     slot_out = -1; t_out = best;
     if (!mesh_gate_rcp(m, r, ri)) return;
     float tmax = best;
@@ -772,7 +812,7 @@ RT_HD_NOINLINE bool csg_shadow(TraceCtx& cx, int root, const Ray& r, float tmax)
 template <class Want, class Cand>
 RT_HD_NOINLINE void mesh_leaf_hits(TraceCtx& cx, int oi, const Ray& r, Want& want, Cand& cand) {
     const DevObject* o = cx.S.objects + oi;
-    const DevMesh* m = cx.S.meshes + o->mesh;
+    const MeshG m{cx.S.meshes + o->mesh};
     const float3 shift = mesh_shift(cx, oi);
     Ray mr = r; mr.o = r.o - shift;                                 // the mesh's rest frame (== r unless the mesh moves)
     if (!mesh_gate(m, mr)) return;
@@ -908,6 +948,16 @@ RT_HD_NOINLINE bool difference_shadow(TraceCtx& cx, int c0, const Ray& mr) {
     return occ;
 }
 
+// Header of the k-th top-level mesh (the meshes traversed after the object walk).  The lean kernels (no CSG / transform nodes)
+// read it from the parameter bank: the pointer chase sep_mesh[k] -> objects[oi].mesh -> meshes[] -> nodes / triangles (four dependent
+// L1 round trips in front of every mesh walk, and the triangle array's address again at every leaf) becomes constant-bank operands.
+// Scenes with more than RT_CONST_MESH top-level meshes run on the general kernels (convert_scene).
+template <bool HAS_NODES>
+RT_HD int top_mesh_obj(const SceneView& S, int k) { return HAS_NODES ? RT_LDG(S.sep_mesh + k) : S.c.sep_obj[k]; }
+template <bool HAS_NODES> struct TopMesh;
+template <> struct TopMesh<true> { typedef MeshG type; static RT_HD MeshG get(const SceneView& S, int, int oi) { return MeshG{S.meshes + S.objects[oi].mesh}; } };
+template <> struct TopMesh<false> { typedef MeshC type; static RT_HD MeshC get(const SceneView& S, int k, int) { return MeshC{S, k}; } };
+
 // ------------------------------------------------------------------------------------------------
 // Closest hit over the top-level objects (scene.py:85-94): min by time, ties -> first in list order.
 // Leaves are resolved lazily (only t while scanning; position/normal/material for the winner).
@@ -915,7 +965,7 @@ template <bool HAS_NODES>
 RT_HD bool closest_hit(TraceCtx& cx, const Ray& r, Hit& out) {
     const SceneView& S = cx.S;
     float best = RT_INF;
-    int best_obj = 0x7fffffff, best_aux = 0;
+    int best_obj = 0x7fffffff, best_aux = 0, best_k = 0;
     Hit node_hit; node_hit.t = RT_INF; node_hit.mat = -1; node_hit.geom = -1; node_hit.n = f3(0, 0, 0); node_hit.p = f3(0, 0, 0);
     const float A = dot(r.d, r.d);
     const RayInv ri = ray_inv(r);
@@ -923,14 +973,25 @@ RT_HD bool closest_hit(TraceCtx& cx, const Ray& r, Hit& out) {
     // rays that miss the padded bound of everything bounded (object BVH + separate meshes) only see the linear list (planes)
     const bool in_world = !S.has_world || (S.mesh_mode & RT_MODE_LINEAR_TOP) || touches_world(S, ri, RT_INF);
     if (!in_world) top_skip_bvh(it);
+    // a candidate at time t replaces the current best iff it is earlier, or equally early and earlier in scene.objects
+    #define RT_BETTER(t) ((t) < best || ((t) == best && oi < best_obj))
+    if (!HAS_NODES && S.c.n_lin_planes >= 0 && !(S.mesh_mode & RT_MODE_LINEAR_TOP)) {      // the linear list is all planes: point / normal / speed from the parameter bank
+        for (int k = 0; k < S.c.n_lin_planes; k++) {
+            const int oi = S.c.lin_obj[k];
+            cx.tally.prims++;
+            float3 pt = f3(S.c.lin_point[k]);
+            if (S.any_motion) pt = pt + f3(S.c.lin_speed[k]) * cx.time;
+            float t;
+            if (plane_t(pt, f3(S.c.lin_normal[k]), r, t) && t >= 0.0f && RT_BETTER(t)) { best = t; best_obj = oi; }
+        }
+        it.lin_i = S.n_lin;
+    }
     for (;;) {
         const int oi = top_next<false>(cx, it, ri, best);
         if (oi < 0) break;
         cx.sbase = it.sp;
         const DevObject* o = S.objects + oi;
         const int kind = o->kind;
-        // a candidate at time t replaces the current best iff it is earlier, or equally early and earlier in scene.objects
-        #define RT_BETTER(t) ((t) < best || ((t) == best && oi < best_obj))
         if (kind == RT_KIND_SPHERE) {
             cx.tally.prims++;
             float4 a = ld4(&o->a);
@@ -957,15 +1018,15 @@ RT_HD bool closest_hit(TraceCtx& cx, const Ray& r, Hit& out) {
     cx.sbase = 0;
     for (int k = 0; k < S.n_sep_mesh && in_world; k++) {              // top-level meshes: all lanes of the warp enter the LBVH together
         {
-            const int oi = RT_LDG(S.sep_mesh + k);
+            const int oi = top_mesh_obj<HAS_NODES>(S, k);
+            const typename TopMesh<HAS_NODES>::type m = TopMesh<HAS_NODES>::get(S, k, oi);
             cx.tally.prims++;
             float t; int slot;
             // (moving meshes run on the GENERAL kernels only - HAS_NODES, see convert_scene - so the lean ones carry none of this)
-            if (HAS_NODES && S.mesh_motion) {
-                Ray mr = r; mr.o = r.o - mesh_shift(cx, oi);
-                mesh_closest(cx, S.meshes + S.objects[oi].mesh, mr, ray_inv_moved(ri, mr.o), best, [&](float tt) { return RT_BETTER(tt); }, t, slot);
-            } else mesh_closest(cx, S.meshes + S.objects[oi].mesh, r, ri, best, [&](float tt) { return RT_BETTER(tt); }, t, slot);
-            if (slot >= 0) { best = t; best_obj = oi; best_aux = slot; }
+            Ray mr = r; RayInv mri = ri;
+            if (HAS_NODES && S.mesh_motion) { mr.o = r.o - mesh_shift(cx, oi); mri = ray_inv_moved(ri, mr.o); }
+            mesh_closest(cx, m, mr, mri, best, [&](float tt) { return RT_BETTER(tt); }, t, slot);
+            if (slot >= 0) { best = t; best_obj = oi; best_aux = slot; best_k = k; }
         }
     }
     #undef RT_BETTER
@@ -979,7 +1040,7 @@ RT_HD bool closest_hit(TraceCtx& cx, const Ray& r, Hit& out) {
         case RT_KIND_SPHERE: out.n = normalize(out.p - moved(cx, o, f3(ld4(&o->a)))); break;
         case RT_KIND_PLANE: out.n = f3(ld4(&o->b)); out.mat = plane_material(o, out.p, cx.time); break;
         case RT_KIND_BOX: out.n = box_normal(r, best_aux); break;
-        default: out.n = tri_normal(cx, S.meshes + o->mesh, best_aux, (HAS_NODES && S.mesh_motion) ? (r.o - mesh_shift(cx, best_obj)) + r.d * best : out.p); break;
+        default: out.n = tri_normal(cx, TopMesh<HAS_NODES>::get(S, best_k, best_obj), best_aux, (HAS_NODES && S.mesh_motion) ? (r.o - mesh_shift(cx, best_obj)) + r.d * best : out.p); break;
     }
     return true;
 }
@@ -1012,6 +1073,16 @@ RT_HD bool occluded(TraceCtx& cx, const Ray& r, float tmax) {
     // mesh and CSG-difference shadows ignore t_max, so the world test is made with the unbounded ray
     const bool in_world = !S.has_world || (S.mesh_mode & RT_MODE_LINEAR_TOP) || touches_world(S, ri, RT_INF);
     if (!in_world) top_skip_bvh(it);
+    if (!HAS_NODES && S.c.n_lin_planes >= 0 && !(S.mesh_mode & RT_MODE_LINEAR_TOP)) {      // the linear list is all planes (simple_geometry.py:122-131 from the parameter bank)
+        for (int k = 0; k < S.c.n_lin_planes; k++) {
+            cx.tally.prims++;
+            float3 pt = f3(S.c.lin_point[k]);
+            if (S.any_motion) pt = pt + f3(S.c.lin_speed[k]) * cx.time;
+            float t;
+            if (plane_t(pt, f3(S.c.lin_normal[k]), r, t) && RT_SHADOW_EPS < t && t < tmax) return true;
+        }
+        it.lin_i = S.n_lin;
+    }
     for (;;) {
         const int oi = top_next<true>(cx, it, ri, tmax);
         if (oi < 0) break;
@@ -1021,9 +1092,10 @@ RT_HD bool occluded(TraceCtx& cx, const Ray& r, float tmax) {
     cx.sbase = 0;
     for (int k = 0; k < S.n_sep_mesh && !occ && in_world; k++) {
         cx.tally.prims++;
-        const int oi = RT_LDG(S.sep_mesh + k);
-        if (HAS_NODES && S.mesh_motion) { Ray mr = r; mr.o = r.o - mesh_shift(cx, oi); occ = mesh_shadow(cx, S.meshes + S.objects[oi].mesh, mr, ray_inv_moved(ri, mr.o)); }
-        else occ = mesh_shadow(cx, S.meshes + S.objects[oi].mesh, r, ri);
+        const int oi = top_mesh_obj<HAS_NODES>(S, k);
+        Ray mr = r; RayInv mri = ri;
+        if (HAS_NODES && S.mesh_motion) { mr.o = r.o - mesh_shift(cx, oi); mri = ray_inv_moved(ri, mr.o); }
+        occ = mesh_shadow(cx, TopMesh<HAS_NODES>::get(S, k, oi), mr, mri);
     }
     return occ;
 }
@@ -1099,9 +1171,10 @@ __device__ __forceinline__ void bvh4_anyhit_packet(TraceCtx& cx, const BvhNode4*
 }
 
 // Mesh.shadow_intersect for a warp of rays and ONE mesh (same answer per lane as mesh_shadow)
-__device__ __forceinline__ bool mesh_shadow_packet(TraceCtx& cx, const DevMesh* m, const Ray& r, const RayInv& ri, bool want) {
+template <class M>
+__device__ __forceinline__ bool mesh_shadow_packet(TraceCtx& cx, const M& m, const Ray& r, const RayInv& ri, bool want) {
     bool active = want && mesh_gate_rcp(m, r, ri);
-    const int n = m->n_tris;
+    const int n = m.n_tris();
     if (n <= 0 || !__any_sync(RT_FULL_WARP, active)) return false;
     bool occ = false;
     auto test = [&](int s, bool mine) {
@@ -1113,7 +1186,7 @@ __device__ __forceinline__ bool mesh_shadow_packet(TraceCtx& cx, const DevMesh* 
         for (int s = 0; s < n && __any_sync(RT_FULL_WARP, active); s++) test(s, true);
         return occ;
     }
-    bvh4_anyhit_packet<false>(cx, m->nodes, ri, RT_SHADOW_EPS * 0.5f, RT_INF, active, cx.tally.nodes, [&](int code, bool mine) {
+    bvh4_anyhit_packet<false>(cx, m.nodes(), ri, RT_SHADOW_EPS * 0.5f, RT_INF, active, cx.tally.nodes, [&](int code, bool mine) {
         const int first = code & ((1 << RT_LEAF_SLOT_BITS) - 1), last = first + (code >> RT_LEAF_SLOT_BITS);
         for (int s = first; s <= last; s++) test(s, mine);
     });
@@ -1141,10 +1214,10 @@ __device__ __forceinline__ bool occluded_packet(TraceCtx& cx, const Ray& r, floa
         });
     for (int k = 0; k < S.n_sep_mesh && __any_sync(RT_FULL_WARP, active); k++) {
         if (active) cx.tally.prims++;
-        const int oi = RT_LDG(S.sep_mesh + k);
+        const int oi = top_mesh_obj<HAS_NODES>(S, k);
         Ray mr = r; RayInv mri = ri;
         if (HAS_NODES && S.mesh_motion) { mr.o = r.o - mesh_shift(cx, oi); mri = ray_inv_moved(ri, mr.o); }
-        if (mesh_shadow_packet(cx, S.meshes + S.objects[oi].mesh, mr, mri, active)) { occ = true; active = false; }
+        if (mesh_shadow_packet(cx, TopMesh<HAS_NODES>::get(S, k, oi), mr, mri, active)) { occ = true; active = false; }
     }
     return occ;
 }
@@ -1152,9 +1225,16 @@ __device__ __forceinline__ bool occluded_packet(TraceCtx& cx, const Ray& r, floa
 
 // ------------------------------------------------------------------------------------------------
 // Shadow ray of light `li` from hit point p (scene.py:148-167): un-offset origin, un-normalised direction (Q12)
+// DevLight fields of light `li`: the first RT_CONST_LIGHTS from the parameter bank (SceneConst)
+// (CONST = false: always the global record - the general kernels are instruction-fetch bound and take no second code path)
+template <bool CONST = true>
+RT_HD float4 light_vector(const SceneView& S, int li) { return (CONST && li < RT_CONST_LIGHTS) ? S.c.light_vec[li] : ld4(&S.lights[li].vector); }
+RT_HD float4 light_colour_power(const SceneView& S, int li) { return li < RT_CONST_LIGHTS ? S.c.light_colour[li] : ld4(&S.lights[li].colour_power); }
+RT_HD float4 light_dir_norm(const SceneView& S, int li) { return li < RT_CONST_LIGHTS ? S.c.light_dirn[li] : ld4(&S.lights[li].dir_norm); }
+
 template <bool HAS_NODES>
 RT_HD bool light_occluded(TraceCtx& cx, float3 p, int li) {
-    const float4 lv = ld4(&cx.S.lights[li].vector);
+    const float4 lv = light_vector<!HAS_NODES>(cx.S, li);
     const bool point = as_int(lv.w) == RT_LIGHT_POINT;
     Ray sr; sr.o = p;
     sr.d = point ? f3(lv) - p : -f3(lv);
@@ -1165,7 +1245,7 @@ RT_HD bool light_occluded(TraceCtx& cx, float3 p, int li) {
 // the same for a warp of hit points and one light (all 32 lanes call; want: this lane has a hit point)
 template <bool HAS_NODES>
 __device__ __forceinline__ bool light_occluded_packet(TraceCtx& cx, float3 p, int li, bool want) {
-    const float4 lv = ld4(&cx.S.lights[li].vector);
+    const float4 lv = light_vector<!HAS_NODES>(cx.S, li);
     const bool point = as_int(lv.w) == RT_LIGHT_POINT;
     Ray sr; sr.o = p;
     sr.d = point ? f3(lv) - p : -f3(lv);
@@ -1190,14 +1270,13 @@ RT_HD float3 shade_local(TraceCtx& cx, const Ray& ray, const Hit& hit, Lit&& lit
     float3 colour = f3(0, 0, 0);
     for (int li = 0; li < S.n_lights; li++) {
         if (!lit(li)) continue;
-        const DevLight* L = S.lights + li;
-        float4 lv = ld4(&L->vector);
+        float4 lv = light_vector(S, li);
         const bool point = as_int(lv.w) == RT_LIGHT_POINT;
-        float3 light_dir = point ? normalize(f3(lv) - hit.p) : f3(ld4(&L->dir_norm));
+        float3 light_dir = point ? normalize(f3(lv) - hit.p) : f3(light_dir_norm(S, li));
         float3 lambert = diffuse * fmaxf(0.0f, dot(hit.n, light_dir));
         float3 half_vect = normalize(light_dir - ray.d);
         float3 specular = f3(ms) * powf(fmaxf(0.0f, dot(hit.n, half_vect)), md.w);   // 0**0 == 1 both sides
-        colour = colour + f3(ld4(&L->colour_power)) * (lambert + specular);
+        colour = colour + f3(light_colour_power(S, li)) * (lambert + specular);
     }
     return colour + S.ambient * diffuse;
 }

@@ -117,6 +117,15 @@ __device__ __forceinline__ void tally_flush(const Tally& t, unsigned long long p
 
 __device__ __forceinline__ Tally tally_zero() { Tally t; t.shadow = t.reflect = t.refract = t.nodes = t.tris = t.prims = t.shaded = t.smooth = t.err = 0; return t; }
 
+// How a kernel receives the scene.  Lean kernels (no CSG / transform nodes): SceneView BY VALUE in the parameter bank - everything
+// is inlined, every field is a constant-bank operand.  General kernels: a pointer to ONE copy in global memory.  Their out-of-line
+// node functions (csg_inside, csg_shadow, ...) take the scene by reference; for a by-value parameter that made every THREAD copy the
+// whole SceneView into its local-memory stack frame at kernel entry and read it back from there (ptxas: 2.0 - 3.2 KB frames,
+// 512 threads per SM): one shared read-only copy stays in L1 instead.
+template <bool GLOBAL> struct ViewArg;
+template <> struct ViewArg<false> { SceneView v; __device__ __forceinline__ const SceneView& get() const { return v; } };
+template <> struct ViewArg<true> { const SceneView* __restrict__ p; __device__ __forceinline__ const SceneView& get() const { return *p; } };
+
 extern __shared__ int rt_smem_stack[];   // RT_STACK_ROWS * blockDim.x ints when the scene has a mesh or an object BVH
 // the launches allocate the shared stack area only for scenes with something to walk (b200rt.cu: has_mesh || has_tlas)
 __device__ __forceinline__ bool rt_smem_stack_present(const SceneView& S) { return S.tlas_nodes != nullptr || S.n_sep_mesh > 0; }
@@ -151,9 +160,10 @@ __device__ __forceinline__ PrimaryIndex primary_index(const SceneView& S, const 
 // PRIMARY: ray i of the batch is generated here: pixel = pixel_begin + i / N, slot = i % N = (d*S + s)*T + t (loop
 // order of scene.py:57-67).  Otherwise ray i is entry i of the compacted queue `qin` (count on the device).
 template <bool HAS_NODES, bool PRIMARY>
-__global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_HIT_CSG : RT_MIN_BLOCKS_HIT) k_hit(SceneView S, PixelMap pm, long long pixel_begin, long long n_rays,
+__global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_HIT_CSG : RT_MIN_BLOCKS_HIT) k_hit(const ViewArg<HAS_NODES> SA, PixelMap pm, long long pixel_begin, long long n_rays,
                                                                      RayQueue qin, const unsigned long long* qin_count,
                                                                      HitPlanes H, RtCounters* counters) {
+    const SceneView& S = SA.get();
     Tally tally = tally_zero();
     int spill[RT_STACK_SPILL];       // overflow of the shared-memory traversal stack (thread-local memory)
     unsigned long long n_primary = 0;
@@ -207,8 +217,9 @@ enum { SHADOW_PER_RAY = 0, SHADOW_ROWS = 1, SHADOW_PACKET = 2 };
 #define RT_PACKET_SHADOW 0
 #endif
 template <bool HAS_NODES, int MODE>
-__global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_SHADOW_CSG : RT_MIN_BLOCKS_SHADOW) k_shadow(SceneView S, long long n_rays, const unsigned long long* n_dev,
+__global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_SHADOW_CSG : RT_MIN_BLOCKS_SHADOW) k_shadow(const ViewArg<HAS_NODES> SA, long long n_rays, const unsigned long long* n_dev,
                                                                            HitPlanes H, uint8_t* __restrict__ occ, RtCounters* counters) {
+    const SceneView& S = SA.get();
     Tally tally = tally_zero();
     int spill[RT_STACK_SPILL];       // overflow of the shared-memory traversal stack (thread-local memory)
     const long long n = n_dev ? (long long)*n_dev : n_rays;
@@ -306,8 +317,9 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS_SHADE) k_shade(SceneVi
 #define RT_MIN_BLOCKS_TAIL 4
 #endif
 template <bool HAS_NODES>
-__global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_HIT_CSG : RT_MIN_BLOCKS_TAIL) k_tail(SceneView S, RayQueue qin, const unsigned long long* qin_count,
+__global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_HIT_CSG : RT_MIN_BLOCKS_TAIL) k_tail(const ViewArg<HAS_NODES> SA, RayQueue qin, const unsigned long long* qin_count,
                                                                                           float4* __restrict__ samples, RtCounters* counters) {
+    const SceneView& S = SA.get();
     Tally tally = tally_zero();
     int spill[RT_STACK_SPILL];
     unsigned long long n_queued = 0;
@@ -375,9 +387,10 @@ __global__ void k_finalize_u8(const float* __restrict__ img, int ncols, int nrow
 
 // ---- unit-test aids: explicit rays through the same device functions ---------------------------------------
 template <bool HAS_NODES>
-__global__ void __launch_bounds__(RT_BLOCK) k_trace(SceneView S, long long n, const float* __restrict__ org, const float* __restrict__ dir,
+__global__ void __launch_bounds__(RT_BLOCK) k_trace(const ViewArg<HAS_NODES> SA, long long n, const float* __restrict__ org, const float* __restrict__ dir,
                                                      const float* __restrict__ times, float* rgb, float* hit_t, float* hit_n, float* hit_p,
                                                      int* hit_geom, int* hit_mat, RtCounters* counters) {
+    const SceneView& S = SA.get();
     Tally tally = tally_zero();
     int spill[RT_STACK_SPILL];       // overflow of the shared-memory traversal stack (thread-local memory)
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -404,9 +417,10 @@ __global__ void __launch_bounds__(RT_BLOCK) k_trace(SceneView S, long long n, co
 }
 
 template <bool HAS_NODES>
-__global__ void __launch_bounds__(RT_BLOCK) k_occluded(SceneView S, long long n, const float* __restrict__ org, const float* __restrict__ dir,
+__global__ void __launch_bounds__(RT_BLOCK) k_occluded(const ViewArg<HAS_NODES> SA, long long n, const float* __restrict__ org, const float* __restrict__ dir,
                                                         const float* __restrict__ times, const float* __restrict__ tmax, int* occ,
                                                         RtCounters* counters) {
+    const SceneView& S = SA.get();
     Tally tally = tally_zero();
     int spill[RT_STACK_SPILL];       // overflow of the shared-memory traversal stack (thread-local memory)
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;

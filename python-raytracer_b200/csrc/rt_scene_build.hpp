@@ -345,7 +345,34 @@ inline int convert_scene(const RtSceneDesc* d, HostScene& hs, std::string& err) 
         if (d->objects[i].speed[0] != 0.0f || d->objects[i].speed[1] != 0.0f || d->objects[i].speed[2] != 0.0f) V.any_motion = 1;
     V.tlas_nodes = nullptr; V.lin_objs = nullptr; V.n_lin = (int)hs.lin_objs.size();
     V.sep_mesh = nullptr; V.n_sep_mesh = (int)hs.sep_mesh.size();
+    // the parameter-bank copies (SceneConst); the mesh headers follow once the LBVHs exist (fill_const_meshes)
+    SceneConst& c = V.c;
+    memset(&c, 0, sizeof c);
+    for (int i = 0; i < d->n_lights && i < RT_CONST_LIGHTS; i++) {
+        c.light_vec[i] = hs.lights[i].vector; c.light_colour[i] = hs.lights[i].colour_power; c.light_dirn[i] = hs.lights[i].dir_norm;
+    }
+    c.n_lin_planes = -1;
+    if ((int)hs.lin_objs.size() <= RT_CONST_LIN) {
+        bool planes = true;
+        for (int oi : hs.lin_objs) planes = planes && hs.objs[oi].kind == RT_KIND_PLANE;
+        if (planes) {
+            c.n_lin_planes = (int)hs.lin_objs.size();
+            for (int k = 0; k < c.n_lin_planes; k++) {
+                const DevObject& o = hs.objs[hs.lin_objs[k]];
+                c.lin_obj[k] = hs.lin_objs[k]; c.lin_point[k] = o.a; c.lin_normal[k] = o.b; c.lin_speed[k] = o.speed;
+            }
+        }
+    }
+    // the lean kernels take the top-level mesh headers from the parameter bank: more meshes than it holds -> the general kernels
+    if ((int)hs.sep_mesh.size() > RT_CONST_MESH) hs.has_nodes = true;
+    c.n_sep_mesh = (int)hs.sep_mesh.size() <= RT_CONST_MESH ? (int)hs.sep_mesh.size() : -1;
+    for (int k = 0; k < c.n_sep_mesh; k++) c.sep_obj[k] = hs.sep_mesh[k];
     return RT_OK;
+}
+
+// SceneConst::sep_mesh: copies of the top-level meshes' headers, once their pointers are final (device LBVH built / host arrays laid out)
+inline void fill_const_meshes(SceneView& V, const std::vector<DevObject>& objs, const DevMesh* headers) {
+    for (int k = 0; k < V.c.n_sep_mesh; k++) V.c.sep_mesh[k] = headers[objs[V.c.sep_obj[k]].mesh];
 }
 
 // mesh bounds + the padding used for the conservative LBVH boxes

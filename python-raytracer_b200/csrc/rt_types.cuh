@@ -82,6 +82,21 @@ struct DevMesh {
 
 struct DevTexture { const uint8_t* rgb; int width, height; };
 
+// Copies of the small per-scene records that EVERY ray reads, held in the kernel parameter bank (SceneView is passed by value):
+// constant-bank operands / LDC instead of global loads through the L1 data pipe, which is what bounds the walkers.
+#define RT_CONST_LIGHTS 4      // the first lights
+#define RT_CONST_LIN 4         // the linearly tested top-level objects when they are all planes (the usual case: ground, walls)
+#define RT_CONST_MESH 8        // the headers of the top-level meshes (scenes with more run on the general kernels)
+struct SceneConst {
+    int n_lin_planes;          // == n_lin when every linearly tested object is a plane and n_lin <= RT_CONST_LIN, else -1
+    int n_sep_mesh;            // == n_sep_mesh when <= RT_CONST_MESH, else -1
+    int lin_obj[RT_CONST_LIN];
+    int sep_obj[RT_CONST_MESH];
+    float4 light_vec[RT_CONST_LIGHTS], light_colour[RT_CONST_LIGHTS], light_dirn[RT_CONST_LIGHTS];    // DevLight fields
+    float4 lin_point[RT_CONST_LIN], lin_normal[RT_CONST_LIN], lin_speed[RT_CONST_LIN];
+    DevMesh sep_mesh[RT_CONST_MESH];
+};
+
 struct SceneView {
     const DevObject* objects; int n_objects, n_top;
     const DevMaterial* materials; int n_materials;
@@ -124,6 +139,7 @@ struct SceneView {
     float focal_length, noise_scale;
     int width, height, D, S, T, jitter;
     uint32_t seed_lo, seed_hi;
+    SceneConst c;
 };
 
 struct Ray { float3 o, d; };

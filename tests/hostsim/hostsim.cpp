@@ -117,6 +117,7 @@ static int make_sim(const RtSceneDesc* d, Sim& sim) {
     V.lin_objs = sim.hs.lin_objs.data(); V.n_lin = (int)sim.hs.lin_objs.size();
     V.child_lo = sim.hs.has_nodes ? sim.hs.child_lo.data() : nullptr; V.child_hi = sim.hs.has_nodes ? sim.hs.child_hi.data() : nullptr;
     V.sep_mesh = sim.hs.sep_mesh.data(); V.n_sep_mesh = (int)sim.hs.sep_mesh.size();
+    rtb::fill_const_meshes(V, sim.hs.objs, sim.mesh_hdr.data());
     return 0;
 }
 
