@@ -602,7 +602,7 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
                 const unsigned long long* n_in = w.d_qcount + (level - 1);
                 if (tail_level > 0 && level >= tail_level) {          // the small remainder: every path to its end in one launch
                     ProfScope ps_(sc, PC_TAIL, s);
-                    k_tail<HAS_NODES><<<g_tail, RT_BLOCK, smem, s>>>(VA, qin, n_in, w.d_samples, sc->d_counters + 3);
+                    k_tail<HAS_NODES><<<g_tail, RT_BLOCK, smem, s>>>(VA, qin, n_in, w.d_qcount + level, w.d_samples, sc->d_counters + 3);   // d_qcount[level]: zero, unused from here on: the fetch counter
                     (*launches)++;
                     break;
                 }

@@ -316,22 +316,41 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS_SHADE) k_shade(SceneVi
 #ifndef RT_MIN_BLOCKS_TAIL
 #define RT_MIN_BLOCKS_TAIL 4
 #endif
+// Paths end at different depths, so a thread that walked "its" path to the end in an inner loop left its lane idle until the
+// longest of the warp's 32 paths was done (ncu: 9 of 32 lanes active).  Here every lane runs ONE level of whatever path it holds
+// per iteration, and a lane whose path has ended fetches the next queued path right away (warp-aggregated atomic on `next`, a
+// zeroed counter): the lanes of a warp stay together at the granularity of a level.
 template <bool HAS_NODES>
 __global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_HIT_CSG : RT_MIN_BLOCKS_TAIL) k_tail(const ViewArg<HAS_NODES> SA, RayQueue qin, const unsigned long long* qin_count,
-                                                                                          float4* __restrict__ samples, RtCounters* counters) {
+                                                                                          unsigned long long* next, float4* __restrict__ samples, RtCounters* counters) {
     const SceneView& S = SA.get();
     Tally tally = tally_zero();
     int spill[RT_STACK_SPILL];
     unsigned long long n_queued = 0;
     const long long n = (long long)*qin_count;
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        PathState ps; float time; unsigned slot;
-        queue_load(qin, i, ps, time, slot);
-        TraceCtx cx{S, time, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill};
-        float3 sample;
-        while (trace_level<HAS_NODES>(cx, ps, sample)) n_queued++;      // counted like the rays the wavefront levels would have queued
-        samples[slot] = f4(sample.x, sample.y, sample.z, 0.0f);
+    const unsigned lane = threadIdx.x & 31u;
+    PathState ps; float time = 0.0f; unsigned slot = 0;
+    bool have = false, exhausted = false;
+    for (;;) {
+        const unsigned want = __ballot_sync(0xffffffffu, !have && !exhausted);
+        if (want) {
+            const int leader = __ffs(want) - 1;
+            unsigned long long base = 0;
+            if ((int)lane == leader) base = atomicAdd(next, (unsigned long long)__popc(want));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (!have && !exhausted) {
+                const long long i = (long long)(base + __popc(want & ((1u << lane) - 1u)));
+                if (i < n) { queue_load(qin, i, ps, time, slot); have = true; }
+                else exhausted = true;
+            }
+        }
+        if (!__any_sync(0xffffffffu, have)) break;
+        if (have) {
+            TraceCtx cx{S, time, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill};
+            float3 sample;
+            if (trace_level<HAS_NODES>(cx, ps, sample)) n_queued++;      // counted like the rays the wavefront levels would have queued
+            else { samples[slot] = f4(sample.x, sample.y, sample.z, 0.0f); have = false; }
+        }
     }
     tally_flush(tally, 0, n_queued, counters);
 }
