@@ -318,12 +318,47 @@ static int build_mesh_bvh(RtScene* sc, int mi, cudaStream_t st) {
         cur ^= 1;
     }
     TC(cudaGetLastError());
+    if (RT_PLOC_RADIUS > 0 && n >= 2) {
+        // PLOC (rt_bvh.cuh): clusters = the Morton-ordered leaves, merged round by round; every array of the radix-tree path that is
+        // free at this point doubles as a PLOC buffer
+        int *cid[2], *nn = parent_node, *first = parent_leaf, *slot_of; float4 *clo[2], *chi[2]; unsigned *merge = arrive, *keep = even, *merge_scan = remap, *keep_scan;
+        TA(cid[0], sizeof(int) * n); TA(cid[1], sizeof(int) * n); TA(slot_of, sizeof(int) * n); TA(keep_scan, sizeof(unsigned) * n);
+        TA(clo[0], sizeof(float4) * n); TA(clo[1], sizeof(float4) * n); TA(chi[0], sizeof(float4) * n); TA(chi[1], sizeof(float4) * n);
+        k_ploc_leaf_boxes<<<G, T, 0, st>>>(b.d_verts, b.d_faces, vals[cur], n, cid[0], clo[0], chi[0]);
+        std::vector<int> round_end;
+        int m = n, created = 0, pc = 0;
+        while (m > 1) {
+            const int Gm = (m + T - 1) / T;
+            k_ploc_nn<<<Gm, T, 0, st>>>(clo[pc], chi[pc], m, RT_PLOC_RADIUS, nn);
+            k_ploc_flags<<<Gm, T, 0, st>>>(nn, m, merge, keep, merge_scan, keep_scan);
+            exclusive_scan_u32(merge_scan, m, scratch, st);
+            exclusive_scan_u32(keep_scan, m, scratch, st);
+            k_ploc_apply<<<Gm, T, 0, st>>>(n, m, created, nn, merge, keep, merge_scan, keep_scan, cid[pc], clo[pc], chi[pc], cid[pc ^ 1], clo[pc ^ 1], chi[pc ^ 1],
+                                          children, node_lo, node_hi);
+            unsigned last_scan = 0, last_flag = 0;
+            TC(cudaMemcpyAsync(&last_scan, merge_scan + (m - 1), sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+            TC(cudaMemcpyAsync(&last_flag, merge + (m - 1), sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+            TC(cudaStreamSynchronize(st));
+            const int merged = (int)(last_scan + last_flag);
+            if (merged <= 0) { tfree(); return fail(RT_ERR_CUDA, "LBVH build: a PLOC round merged nothing"); }    // (cannot happen: the closest pair is always mutual)
+            created += merged; m -= merged; pc ^= 1;
+            round_end.push_back(created);
+        }
+        TC(cudaMemsetAsync(first, 0, sizeof(int), st));               // the root's first slot
+        for (int t = (int)round_end.size() - 1; t >= 0; t--) {
+            const int k0 = t ? round_end[t - 1] : 0, k1 = round_end[t];
+            k_ploc_place<<<(k1 - k0 + T - 1) / T, T, 0, st>>>(n, k0, k1, children, node_lo, node_hi, first, slot_of);
+        }
+        k_ploc_emit_leaves<<<G, T, 0, st>>>(b.d_verts, b.d_faces, vals[cur], slot_of, n, b.d_tri, b.d_face_vidx, leaf_lo, leaf_hi, b.d_order);
+        TC(cudaGetLastError());
+    } else {
     TC(cudaMemcpyAsync(b.d_order, vals[cur], sizeof(int) * n, cudaMemcpyDeviceToDevice, st));
     TC(cudaMemsetAsync(arrive, 0, sizeof(unsigned) * n, st));
     if (n >= 2) k_lbvh_hierarchy<<<G, T, 0, st>>>(keys[cur], n, children, parent_node, parent_leaf);
     k_lbvh_leaves_refit<<<G, T, 0, st>>>(b.d_verts, b.d_faces, vals[cur], n, children, parent_node, parent_leaf, b.d_tri, b.d_face_vidx,
                                         leaf_lo, leaf_hi, node_lo, node_hi, arrive);
     TC(cudaGetLastError());
+    }
     // 4-wide collapse: which binary nodes survive as traversal nodes; exclusive scan of the flags = compact, deterministic node indices
     b.n_nodes4 = 0;
     if (n >= 2) {

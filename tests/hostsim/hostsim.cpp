@@ -57,33 +57,45 @@ static void build_mesh(const RtMesh& m, HostMesh& hm, DevMesh& g) {
     }
     std::stable_sort(hm.order.begin(), hm.order.end(), [&](int a, int b) { return keys[a] < keys[b]; });
     std::vector<uint64_t> sk(n);
+    for (int s = 0; s < n; s++) sk[s] = keys[hm.order[s]];
+    auto tri_box = [&](int f, float4& blo, float4& bhi) {
+        float3 a = vert_at(m.verts, m.faces[3 * f]), b = vert_at(m.verts, m.faces[3 * f + 1]), d = vert_at(m.verts, m.faces[3 * f + 2]);
+        blo = f4(fminf(a.x, fminf(b.x, d.x)), fminf(a.y, fminf(b.y, d.y)), fminf(a.z, fminf(b.z, d.z)), 0.0f);
+        bhi = f4(fmaxf(a.x, fmaxf(b.x, d.x)), fmaxf(a.y, fmaxf(b.y, d.y)), fmaxf(a.z, fmaxf(b.z, d.z)), 0.0f);
+    };
+    std::vector<int2> ch(std::max(n - 1, 0));
+    std::vector<float4> leaf_lo(n), leaf_hi(n), nlo(std::max(n - 1, 0)), nhi(std::max(n - 1, 0));
+    const bool ploc = RT_PLOC_RADIUS > 0 && n >= 2;
+    if (ploc) {                                     // PLOC: the tree decides the triangle slots (depth-first order), not the sort alone
+        std::vector<float4> mlo(n), mhi(n);
+        for (int p = 0; p < n; p++) tri_box(hm.order[p], mlo[p], mhi[p]);
+        std::vector<int> slot_of(n), order2(n);
+        ploc_build_host(n, mlo.data(), mhi.data(), RT_PLOC_RADIUS, ch.data(), nlo.data(), nhi.data(), slot_of.data());
+        for (int p = 0; p < n; p++) order2[slot_of[p]] = hm.order[p];
+        hm.order.swap(order2);
+    }
     hm.tri.resize(3 * (size_t)n); hm.vidx.resize(n);
     for (int s = 0; s < n; s++) {
         int f = hm.order[s];
-        sk[s] = keys[f];
         int i0 = m.faces[3 * f], i1 = m.faces[3 * f + 1], i2 = m.faces[3 * f + 2];
         float3 a = vert_at(m.verts, i0), b = vert_at(m.verts, i1), c = vert_at(m.verts, i2);
         hm.tri[3 * s] = f4(a.x, a.y, a.z, as_float(f));
         hm.tri[3 * s + 1] = f4(b.x, b.y, b.z, 0);
         hm.tri[3 * s + 2] = f4(c.x, c.y, c.z, 0);
         hm.vidx[s].x = i0; hm.vidx[s].y = i1; hm.vidx[s].z = i2; hm.vidx[s].w = f;
+        tri_box(f, leaf_lo[s], leaf_hi[s]);
     }
     if (m.vnormals && !m.flat_shaded) {
         hm.vn.resize(m.n_verts);
         for (int k = 0; k < m.n_verts; k++) hm.vn[k] = rtb::h4(m.vnormals + 3 * (size_t)k);
     }
     if (n >= 2) {
-        std::vector<int2> ch(n - 1);
-        for (int i = 0; i < n - 1; i++) lbvh_node(sk.data(), n, i, ch[i].x, ch[i].y);
-        std::vector<float4> leaf_lo(n), leaf_hi(n), nlo(n - 1), nhi(n - 1);
-        std::vector<int> dep(n - 1, 0);
-        for (int s = 0; s < n; s++) {
-            float3 a = f3(hm.tri[3 * s]), b = f3(hm.tri[3 * s + 1]), d = f3(hm.tri[3 * s + 2]);
-            leaf_lo[s] = f4(fminf(a.x, fminf(b.x, d.x)), fminf(a.y, fminf(b.y, d.y)), fminf(a.z, fminf(b.z, d.z)), 0.0f);
-            leaf_hi[s] = f4(fmaxf(a.x, fmaxf(b.x, d.x)), fmaxf(a.y, fmaxf(b.y, d.y)), fmaxf(a.z, fmaxf(b.z, d.z)), 0.0f);
+        if (!ploc) {
+            for (int i = 0; i < n - 1; i++) lbvh_node(sk.data(), n, i, ch[i].x, ch[i].y);
+            std::vector<int> dep(n - 1, 0);
+            float4 rl, rh;
+            refit(ch, 0, 0, leaf_lo, leaf_hi, nlo, nhi, dep, rl, rh);
         }
-        float4 rl, rh;
-        refit(ch, 0, 0, leaf_lo, leaf_hi, nlo, nhi, dep, rl, rh);
         std::vector<unsigned> remap(n - 1, 0);
         unsigned n4 = 0;
         std::vector<unsigned> wide(n - 1, 0);
