@@ -275,7 +275,14 @@ def run_ours(a):
     dev_u8 = torch.empty(W * H * 3, dtype=torch.uint8, device="cuda") if rank == 0 else None
     e2e_steps = a.steps
 
+    job_all = sc.make_job(0, W, 0, H)
+
     def e2e_frame(u8=False):
+        if world == 1 and not u8:
+            # the reference-facing C-ABI call with a HOST buffer: rt_render_host (pinned destination: the part of the frame a batch
+            # completes is copied while the next batches render); synchronous
+            _abi.check(lib, lib.rt_render_host(h, C.byref(job_all), host_img.data_ptr(), None, torch.cuda.current_stream().cuda_stream), "rt_render_host")
+            return
         img = sharder.render()
         if rank == 0:
             if u8:   # main.py:31-33 on the device (rt_finalize_u8): a quarter of the bytes cross PCIe
@@ -388,8 +395,8 @@ def run_ours(a):
                "rays_per_frame": dict(zip(RAY_KEYS, tl[:4])),
                "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": ms2_total / e2e_steps,
                        "h2d_bytes_per_step": C.sizeof(_abi.RtRenderJob), "d2h_bytes_per_step": W * H * 3 * 4,
-                       "what": "frame rendered through the C ABI and copied to pinned HOST memory every step as float32 (scene resident: "
-                               "uploaded once like the reference's load_scene)"},
+                       "what": "frame rendered through the C ABI into pinned HOST memory every step as float32 (N = 1: rt_render_host, the frame leaves in chunks "
+                               "as batches finish; N > 1: rank 0 copies the shared frame; scene resident: uploaded once like the reference's load_scene)"},
                "e2e_u8": {"value": rays_frame * e2e_steps / (ms3_total * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": ms3_total / e2e_steps,
                           "d2h_bytes_per_step": W * H * 3,
                           "what": "same, but main.py:31-33 (rot90, *255 truncation) done on the device and the uint8 PNG array copied"},

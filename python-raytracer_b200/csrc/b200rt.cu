@@ -120,6 +120,9 @@ struct RtScene {
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     cudaEvent_t ev_l0[2] = {nullptr, nullptr}, ev_deep[2] = {nullptr, nullptr};   // pipeline mode: level 0 of a set done / its deeper levels + resolve done
     bool serial_only = false;                  // rt_render_static: one set (the static array), one stream
+    // rt_render_host with a PINNED destination: the part of the frame a batch completes is copied while the next batches render
+    float* sink_host = nullptr; long long sink_done = 0;
+    cudaStream_t copy_stream = nullptr; cudaEvent_t ev_copy = nullptr;
     RtCounters* d_counters = nullptr;
     SceneView* d_view = nullptr;               // the scene as the general kernels read it (ViewArg<true>): one copy in global memory
     SceneView h_view_dev{};                    // what d_view holds
@@ -256,6 +259,8 @@ extern "C" int rt_scene_destroy(RtScene* sc) {
     }
     if (sc->ev_fork) cudaEventDestroy(sc->ev_fork);
     if (sc->ev_join) cudaEventDestroy(sc->ev_join);
+    if (sc->ev_copy) cudaEventDestroy(sc->ev_copy);
+    if (sc->copy_stream) cudaStreamDestroy(sc->copy_stream);
     for (int k = 0; k < 2; k++) { if (sc->ev_l0[k]) cudaEventDestroy(sc->ev_l0[k]); if (sc->ev_deep[k]) cudaEventDestroy(sc->ev_deep[k]); }
     if (sc->side) cudaStreamDestroy(sc->side);
     if (sc->d_stage) cudaFree(sc->d_stage);
@@ -656,6 +661,22 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
         }
         (*launches)++;
         if (pipe) CU(cudaEventRecord(sc->ev_deep[bi & 1], sc->side));
+        if (sc->sink_host && (pipe || !two)) {          // (batches resolve in order on one stream)  floats of the output that are final after this batch: whole tile columns (reference layout) / the batch's slots (compact)
+            const bool last = p0 + px_per_batch >= pm.n_local_pixels;
+            long long f1;
+            if (direct) f1 = (last ? (long long)pm.ncols : std::min<long long>(pm.ncols, ((p0 + npx) / pm.tile_px) / pm.n_tile_rows * pm.tile_w)) * pm.nrows * 3;
+            else f1 = (p0 + npx) * 3;
+            if (f1 > sc->sink_done) {
+                CU(cudaEventRecord(sc->ev_copy, s));
+                CU(cudaStreamWaitEvent(sc->copy_stream, sc->ev_copy, 0));
+                CU(cudaMemcpyAsync(sc->sink_host + sc->sink_done, d_out + sc->sink_done, sizeof(float) * (size_t)(f1 - sc->sink_done), cudaMemcpyDeviceToHost, sc->copy_stream));
+                sc->sink_done = f1;
+            }
+        }
+    }
+    if (sc->sink_host) {                                 // the caller's stream continues when the last chunk has landed
+        CU(cudaEventRecord(sc->ev_copy, sc->copy_stream));
+        CU(cudaStreamWaitEvent(st, sc->ev_copy, 0));
     }
     if (two) {                                           // the caller's stream continues when the side stream's batches are done too
         CU(cudaEventRecord(sc->ev_join, sc->side));
@@ -776,13 +797,29 @@ extern "C" int rt_render_static(RtScene* sc, const RtRenderJob* job, float* d_ou
 }
 
 extern "C" int rt_render_host(RtScene* sc, const RtRenderJob* job, float* h_out, RtCounters* counters, void* stream) {
-    if (!sc || !h_out) return fail(RT_ERR_INVALID, "null argument");
+    if (!sc || !h_out || !job) return fail(RT_ERR_INVALID, "null argument");
     int64_t n_floats = 0;
     UP(rt_job_extent(job, nullptr, &n_floats));
     UP(grow(&sc->d_stage, &sc->stage_cap, std::max<long long>(n_floats, 1)));
     cudaStream_t st = (cudaStream_t)stream;
-    UP(rt_render(sc, job, sc->d_stage, nullptr, stream));
-    CU(cudaMemcpyAsync(h_out, sc->d_stage, sizeof(float) * (size_t)n_floats, cudaMemcpyDeviceToHost, st));
+    // A pinned destination (cudaHostAlloc / cudaHostRegister) takes the frame in chunks: what a wavefront batch completes is copied
+    // on a third stream while the next batches render, so only the last chunk's copy is left after the last kernel.  Pageable
+    // memory gets one copy at the end (an "async" copy to pageable memory blocks the host, which would stop the launches).
+    cudaPointerAttributes pa{};
+    const bool pinned = cudaPointerGetAttributes(&pa, h_out) == cudaSuccess && pa.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    const bool chunked = pinned && job->direct != RT_DIRECT_SHARED_FRAME;
+    if (chunked && !sc->copy_stream) {
+        DeviceGuard dg(sc->device);
+        CU(cudaStreamCreateWithFlags(&sc->copy_stream, cudaStreamNonBlocking));
+        CU(cudaEventCreateWithFlags(&sc->ev_copy, cudaEventDisableTiming));
+    }
+    if (chunked) { sc->sink_host = h_out; sc->sink_done = 0; }
+    const int rc = rt_render(sc, job, sc->d_stage, nullptr, stream);
+    const long long done = sc->sink_done;
+    sc->sink_host = nullptr; sc->sink_done = 0;
+    if (rc != RT_OK) return rc;
+    if (done < n_floats) CU(cudaMemcpyAsync(h_out + done, sc->d_stage + done, sizeof(float) * (size_t)(n_floats - done), cudaMemcpyDeviceToHost, st));
     RtCounters cls[RT_COUNTER_CLASSES];
     if (counters) CU(cudaMemcpyAsync(cls, sc->d_counters, sizeof cls, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));

@@ -108,6 +108,31 @@ def test_batch_size_does_not_change_a_bit_with_recursive_materials():
     assert np.array_equal(win, full[300:364, 200:248])
 
 
+def test_render_host_into_pinned_memory_leaves_in_chunks_and_equals_the_device_render(lib):
+    """rt_render_host with a PINNED destination copies what every wavefront batch completes while the next batches render (whole
+    tile columns of the reference layout / the batch's slots of the compact layout): same bytes as the pageable path and as the
+    device render, also when batch boundaries fall inside tiles and tile columns."""
+    import torch
+    sc = load_case("MirrorRefraction")
+    W, H = 900, 512
+    ref = sc.render_region(0, W, 0, H).copy()                      # pageable numpy destination: one copy at the end
+    h = sc.upload()
+    for direct, batch in ((True, 37_000), (True, 0), (False, 53_000)):
+        job = sc.make_job(0, W, 0, H, direct=direct, max_batch_rays=batch)
+        nt, nf = C.c_int64(), C.c_int64()
+        abi.check(lib, lib.rt_job_extent(C.byref(job), C.byref(nt), C.byref(nf)), "rt_job_extent")
+        host = torch.full((nf.value,), -1.0, dtype=torch.float32).pin_memory()
+        ctr = abi.RtCounters()
+        abi.check(lib, lib.rt_render_host(h, C.byref(job), host.data_ptr(), C.byref(ctr), None), "rt_render_host")
+        dev = torch.full((nf.value,), -2.0, dtype=torch.float32, device="cuda")
+        abi.check(lib, lib.rt_render(h, C.byref(job), dev.data_ptr(), None, None), "rt_render")
+        torch.cuda.synchronize()
+        assert torch.equal(host, dev.cpu()), (direct, batch)
+        if direct:
+            assert np.array_equal(host.numpy().reshape(W, H, 3), ref)
+        assert ctr.error_flags == 0 and ctr.rays_primary == W * H
+
+
 @pytest.mark.parametrize("world", [2, 3, 8])
 def test_tile_sharded_render_assembles_to_the_single_rank_image(world, lib):
     """Multi-GPU split emulated on one device: every rank's compact tile buffer, concatenated as the
