@@ -283,6 +283,12 @@ def run_ours(a):
             # completes is copied while the next batches render); synchronous
             _abi.check(lib, lib.rt_render_host(h, C.byref(job_all), host_img.data_ptr(), None, torch.cuda.current_stream().cuda_stream), "rt_render_host")
             return
+        if world > 1 and not u8 and sharder.fan_in == "shared":
+            # every rank copies its slice of the finished frame (rank 0's HBM, read over NVLink) to one page-locked host frame in
+            # shared memory over its OWN PCIe link; rank 0 owns the result
+            sharder.render_to_host()
+            torch.cuda.current_stream().synchronize()
+            return
         img = sharder.render()
         if rank == 0:
             if u8:   # main.py:31-33 on the device (rt_finalize_u8): a quarter of the bytes cross PCIe
@@ -325,6 +331,8 @@ def run_ours(a):
     # ---- untimed: the frame's checksum; N > 1: rank 0 also renders the whole frame alone and the two must be bit-identical
     image_sha = None
     equals_single = None
+    if world > 1 and sharder.fan_in == "shared" and rank == 0:
+        host_img = sharder.host_image                       # where the e2e frames of this run landed
     if rank == 0:
         image_sha = hashlib.sha256(host_img.numpy().tobytes()).hexdigest()
     if world > 1:
@@ -396,7 +404,8 @@ def run_ours(a):
                "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": ms2_total / e2e_steps,
                        "h2d_bytes_per_step": C.sizeof(_abi.RtRenderJob), "d2h_bytes_per_step": W * H * 3 * 4,
                        "what": "frame rendered through the C ABI into pinned HOST memory every step as float32 (N = 1: rt_render_host, the frame leaves in chunks "
-                               "as batches finish; N > 1: rank 0 copies the shared frame; scene resident: uploaded once like the reference's load_scene)"},
+                               "as batches finish; N > 1: every rank copies its 1/N slice of the shared frame to one page-locked host frame over its own PCIe link; scene "
+                               "resident: uploaded once like the reference's load_scene)"},
                "e2e_u8": {"value": rays_frame * e2e_steps / (ms3_total * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": ms3_total / e2e_steps,
                           "d2h_bytes_per_step": W * H * 3,
                           "what": "same, but main.py:31-33 (rot90, *255 truncation) done on the device and the uint8 PNG array copied"},

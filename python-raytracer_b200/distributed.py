@@ -90,7 +90,60 @@ class TileSharder:
         if self.rank == 0:
             self.image = self._images[0]
 
+    # ------------------------------------------------------------------ frame to HOST memory over every GPU's own PCIe link
+    def _init_host_frame(self):
+        """One frame in POSIX shared memory, page-locked in every rank's process (cudaHostRegister): rank 0 owns the result, every
+        rank can copy into it."""
+        from multiprocessing import shared_memory
+        nbytes = self.W * self.H * 3 * 4
+        name = [None]
+        if self.rank == 0:
+            self._shm = shared_memory.SharedMemory(create=True, size=nbytes)
+            name[0] = self._shm.name
+        dist.broadcast_object_list(name, src=0, group=self.group)
+        if self.rank != 0:
+            self._shm = shared_memory.SharedMemory(name=name[0])
+            try:                                             # rank 0 unlinks the segment: the attachers' resource trackers must not try again
+                from multiprocessing import resource_tracker
+                resource_tracker.unregister(self._shm._name, "shared_memory")
+            except Exception:
+                pass
+        self.host_image = torch.frombuffer(self._shm.buf, dtype=torch.float32, count=self.W * self.H * 3)
+        rc = torch.cuda.cudart().cudaHostRegister(self.host_image.data_ptr(), nbytes, 1)          # cudaHostRegisterPortable
+        if int(rc) != 0:
+            raise _abi.B200RTError(f"cudaHostRegister of the shared host frame failed: {rc}")
+        n = self.W * self.H * 3
+        per = (n // self.world + 63) // 64 * 64                      # contiguous slices of the reference layout, 256-byte aligned
+        self._host_slice = (min(n, self.rank * per), min(n, (self.rank + 1) * per) if self.rank < self.world - 1 else n)
+
+    def render_to_host(self):
+        """One frame, delivered to HOST memory: like render(), then every rank copies ITS slice of the finished frame (rank 0's
+        buffer, read through the NVLink peer mapping) to the shared page-locked host frame over its own PCIe link - N copies of
+        1/N of the frame in parallel instead of one copy of all of it from rank 0 (99.5 MB at 4K: 1.4 ms at PCIe 5 speed).
+        A second 4-byte all-reduce orders rank 0's reader after everybody's copy.  Returns the host tensor on rank 0 (valid once
+        the current stream is synchronised), None elsewhere.  'shared' fan-in only."""
+        assert self.fan_in == "shared"
+        if not hasattr(self, "host_image"):
+            self._init_host_frame()
+        self.render()
+        k = (self._frame_no - 1) & 1
+        f0, f1 = self._host_slice
+        if f1 > f0:
+            self.host_image[f0:f1].copy_(self._images[k][f0:f1], non_blocking=True)
+        dist.all_reduce(self._flag, group=self.group)
+        return self.host_image if self.rank == 0 else None
+
     def close(self):
+        if getattr(self, "_shm", None) is not None:
+            torch.cuda.synchronize()
+            if self.world > 1:
+                dist.barrier(group=self.group)
+            torch.cuda.cudart().cudaHostUnregister(self.host_image.data_ptr())
+            self.host_image = None
+            self._shm.close()
+            if self.rank == 0:
+                self._shm.unlink()
+            self._shm = None
         if self._shared_ptr is not None and self._shared_ptr.value:
             torch.cuda.synchronize()
             if self.world > 1:

@@ -35,6 +35,17 @@ for name, sc in scenes.items():
                 res[f"{name}/{fan_in}"] = {"bit_identical": ok and prev["bit_identical"],
                                            "max_abs_diff": max(prev["max_abs_diff"], float(np.abs(got - ref).max()))}
             dist.barrier()
+        if fan_in == "shared":               # the same frames delivered to the shared page-locked HOST frame, one slice per rank over its own PCIe link
+            for frame in range(3):
+                host = sh.render_to_host()
+                torch.cuda.synchronize()
+                if rank == 0:
+                    got = host.numpy().reshape(sc.vc.width, sc.vc.height, 3)
+                    ref = sc.render_region(0, sc.vc.width, 0, sc.vc.height)
+                    prev = res.get(f"{name}/host", {"bit_identical": True, "max_abs_diff": 0.0})
+                    res[f"{name}/host"] = {"bit_identical": bool(np.array_equal(got, ref)) and prev["bit_identical"],
+                                           "max_abs_diff": max(prev["max_abs_diff"], float(np.abs(got - ref).max()))}
+                dist.barrier()
         sh.close()
 if rank == 0:
     print(json.dumps({"world": world, "results": res}))

@@ -33,5 +33,5 @@ def test_n_rank_render_is_bit_identical_to_single_rank():
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     line = [l for l in r.stdout.splitlines() if l.startswith("{")][-1]
     out = json.loads(line)
-    assert out["world"] == n and len(out["results"]) == 4
+    assert out["world"] == n and len(out["results"]) == 6
     assert all(v["bit_identical"] for v in out["results"].values()), out
