@@ -493,9 +493,12 @@ static int sync_device_view(RtScene* sc, const SceneView& V, cudaStream_t st) {
     sc->view_dev_valid = true;
     return RT_OK;
 }
-template <bool HAS_NODES> static ViewArg<HAS_NODES> view_arg(RtScene* sc, const SceneView& V);
-template <> ViewArg<false> view_arg<false>(RtScene*, const SceneView& V) { return ViewArg<false>{V}; }
-template <> ViewArg<true> view_arg<true>(RtScene* sc, const SceneView&) { return ViewArg<true>{sc->d_view}; }
+template <int HAS_NODES> static ViewArg<(HAS_NODES != 0)> view_arg(RtScene* sc, const SceneView& V) {
+    if constexpr (HAS_NODES != 0) return ViewArg<true>{sc->d_view};
+    else return ViewArg<false>{V};
+}
+// kernel variant of a scene (rt_core.cuh): 0 lean, 1 nodes without any mesh, 2 nodes and meshes
+static int scene_variant(const RtScene* sc) { return !sc->has_nodes ? RT_V_LEAN : (sc->has_mesh ? RT_V_NODES_MESH : RT_V_NODES); }
 
 static void sum_counters(const RtCounters* cls, RtCounters* out) {
     memset(out, 0, sizeof *out);
@@ -551,7 +554,7 @@ static int grow_set(RtScene* sc, WorkSet& w, long long batch_cap, int L, bool se
     return RT_OK;
 }
 
-template <bool HAS_NODES>
+template <int HAS_NODES>
 static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, float* d_out, cudaStream_t st, unsigned long long* launches) {
     SceneView V = sc->view;
     V.mesh_mode = job->mesh_mode;
@@ -599,7 +602,7 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
     PixelMap pmk = pm;                                   // + the sample-slot divisors of this scene
     pmk.fd_N = make_fastdiv((unsigned)N); pmk.fd_T = make_fastdiv((unsigned)V.T); pmk.fd_S = make_fastdiv((unsigned)V.S);
     if (HAS_NODES) UP(sync_device_view(sc, V, st));
-    const ViewArg<HAS_NODES> VA = view_arg<HAS_NODES>(sc, V);
+    const ViewArg<(HAS_NODES != 0)> VA = view_arg<HAS_NODES>(sc, V);
     if (two) {                                           // the side stream starts after everything the caller queued before this call
         CU(cudaEventRecord(sc->ev_fork, st));
         CU(cudaStreamWaitEvent(sc->side, sc->ev_fork, 0));
@@ -699,7 +702,9 @@ extern "C" int rt_render(RtScene* sc, const RtRenderJob* job, float* d_out, RtCo
     if (!sc->l2_window_tried) { sc->l2_window_tried = true; l2_persist_nodes(sc, st); }
     CU(cudaMemsetAsync(sc->d_counters, 0, RT_COUNTER_CLASSES * sizeof(RtCounters), st));
     unsigned long long launches = 0;
-    int rc = sc->has_nodes ? render_impl<true>(sc, job, pm, d_out, st, &launches) : render_impl<false>(sc, job, pm, d_out, st, &launches);
+    const int variant = scene_variant(sc);
+    int rc = variant == RT_V_LEAN ? render_impl<RT_V_LEAN>(sc, job, pm, d_out, st, &launches)
+           : variant == RT_V_NODES ? render_impl<RT_V_NODES>(sc, job, pm, d_out, st, &launches) : render_impl<RT_V_NODES_MESH>(sc, job, pm, d_out, st, &launches);
     if (rc != RT_OK) return rc;
     sc->last_launches = launches;
     if (counters) {
@@ -777,7 +782,9 @@ extern "C" int rt_render_static(RtScene* sc, const RtRenderJob* job, float* d_ou
     int rc = RT_OK;
     cudaError_t e = cudaMemsetAsync(sc->d_counters, 0, RT_COUNTER_CLASSES * sizeof(RtCounters), st);
     if (e != cudaSuccess) rc = fail(RT_ERR_CUDA, std::string("rt_render_static: cudaMemsetAsync: ") + cudaGetErrorString(e));
-    if (rc == RT_OK) rc = sc->has_nodes ? render_impl<true>(sc, &j, pm, d_out, st, &launches) : render_impl<false>(sc, &j, pm, d_out, st, &launches);
+    const int variant = scene_variant(sc);
+    if (rc == RT_OK) rc = variant == RT_V_LEAN ? render_impl<RT_V_LEAN>(sc, &j, pm, d_out, st, &launches)
+                        : variant == RT_V_NODES ? render_impl<RT_V_NODES>(sc, &j, pm, d_out, st, &launches) : render_impl<RT_V_NODES_MESH>(sc, &j, pm, d_out, st, &launches);
     const bool intact = w.d_samples == (float4*)(base + RT_STATIC_OFF_SAMPLES) && w.d_hit == (float4*)(base + RT_STATIC_OFF_HIT) &&
                         w.d_occ == (uint8_t*)(base + RT_STATIC_OFF_OCC) && w.d_queue[0] == (float4*)(base + RT_STATIC_OFF_Q0) &&
                         w.d_queue[1] == (float4*)(base + RT_STATIC_OFF_Q1);
@@ -923,13 +930,15 @@ extern "C" int rt_trace_rays(RtScene* sc, int64_t n, const float* h_org, const f
     const size_t smem = (sc->has_mesh || sc->has_tlas) ? sizeof(int) * RT_STACK_ROWS * RT_BLOCK : 0;
     const int grid = (int)((n + RT_BLOCK - 1) / RT_BLOCK);
     CU(cudaMemsetAsync(sc->d_counters, 0, sizeof(RtCounters), st));
-    if (sc->has_nodes) {
-        if (smem) CU(cudaFuncSetAttribute(k_trace<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        UP(sync_device_view(sc, V, st));
-        k_trace<true><<<grid, RT_BLOCK, smem, st>>>(view_arg<true>(sc, V), n, org, dir, times, rgb, t, nn, pp, geom, mat, sc->d_counters);
-    } else {
-        if (smem) CU(cudaFuncSetAttribute(k_trace<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_trace<false><<<grid, RT_BLOCK, smem, st>>>(view_arg<false>(sc, V), n, org, dir, times, rgb, t, nn, pp, geom, mat, sc->d_counters);
+    switch (scene_variant(sc)) {
+#define RT_LAUNCH_TRACE(VV)                                                                                                              \
+        if (smem) CU(cudaFuncSetAttribute(k_trace<VV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));                        \
+        if (VV != RT_V_LEAN) UP(sync_device_view(sc, V, st));                                                                            \
+        k_trace<VV><<<grid, RT_BLOCK, smem, st>>>(view_arg<VV>(sc, V), n, org, dir, times, rgb, t, nn, pp, geom, mat, sc->d_counters);
+        case RT_V_LEAN: { RT_LAUNCH_TRACE(RT_V_LEAN) } break;
+        case RT_V_NODES: { RT_LAUNCH_TRACE(RT_V_NODES) } break;
+        default: { RT_LAUNCH_TRACE(RT_V_NODES_MESH) } break;
+#undef RT_LAUNCH_TRACE
     }
     CU(cudaGetLastError());
     CU(cudaStreamSynchronize(st));
@@ -956,13 +965,15 @@ extern "C" int rt_occluded(RtScene* sc, int64_t n, const float* h_org, const flo
     SceneView V = sc->view; V.mesh_mode = mesh_mode;
     const size_t smem = (sc->has_mesh || sc->has_tlas) ? sizeof(int) * RT_STACK_ROWS * RT_BLOCK : 0;
     const int grid = (int)((n + RT_BLOCK - 1) / RT_BLOCK);
-    if (sc->has_nodes) {
-        if (smem) CU(cudaFuncSetAttribute(k_occluded<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        UP(sync_device_view(sc, V, st));
-        k_occluded<true><<<grid, RT_BLOCK, smem, st>>>(view_arg<true>(sc, V), n, org, dir, times, tmax, occ, sc->d_counters);
-    } else {
-        if (smem) CU(cudaFuncSetAttribute(k_occluded<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_occluded<false><<<grid, RT_BLOCK, smem, st>>>(view_arg<false>(sc, V), n, org, dir, times, tmax, occ, sc->d_counters);
+    switch (scene_variant(sc)) {
+#define RT_LAUNCH_OCC(VV)                                                                                                                \
+        if (smem) CU(cudaFuncSetAttribute(k_occluded<VV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));                     \
+        if (VV != RT_V_LEAN) UP(sync_device_view(sc, V, st));                                                                            \
+        k_occluded<VV><<<grid, RT_BLOCK, smem, st>>>(view_arg<VV>(sc, V), n, org, dir, times, tmax, occ, sc->d_counters);
+        case RT_V_LEAN: { RT_LAUNCH_OCC(RT_V_LEAN) } break;
+        case RT_V_NODES: { RT_LAUNCH_OCC(RT_V_NODES) } break;
+        default: { RT_LAUNCH_OCC(RT_V_NODES_MESH) } break;
+#undef RT_LAUNCH_OCC
     }
     CU(cudaGetLastError());
     CU(cudaStreamSynchronize(st));

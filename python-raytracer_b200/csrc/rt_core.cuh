@@ -6,6 +6,14 @@
 #pragma once
 #include "rt_types.cuh"
 
+// Kernel variants (the HAS_NODES template argument of everything below; non-zero = the scene has CSG / transform nodes):
+//   0  lean: no nodes, everything inlined          1  nodes, and NO mesh anywhere in the scene          2  nodes and meshes
+// Variant 1 exists because the general kernels are instruction-fetch bound (ncu: 80 % of the GPC fetch bandwidth for k_hit<1,1>):
+// without the LBVH walks, triangle tests and smooth-normal code they shrink from 116 / 107 KB to 64 / 75 KB, and the bundled CSG
+// scenes (no mesh) render 24 % faster.
+#define RT_V_LEAN 0
+#define RT_V_NODES 1
+#define RT_V_NODES_MESH 2
 #define RT_EPS 1e-4f                 // geometry/__init__.py:12
 #define RT_SHADOW_EPS 1e-4f          // geometry/__init__.py:39
 #define RT_SHADOW_EPS_SPHERE 1e-3f   // simple_geometry.py:13
@@ -658,7 +666,7 @@ RT_HD bool leaf_shadow(TraceCtx& cx, int oi, const Ray& r, float tmax) {
     }
 }
 
-RT_HD_NOINLINE bool difference_shadow(TraceCtx& cx, int c0, const Ray& mr);
+template <int V> RT_HD_NOINLINE bool difference_shadow(TraceCtx& cx, int c0, const Ray& mr);
 
 // The recursions of hierarchy.py (is_inside :111-129, get_material :131-138, shadow_intersect :80-109) run as loops over
 // an explicit frame stack of RT_MAX_NEST entries: ONE copy of each function in the instruction stream (the first version
@@ -768,6 +776,7 @@ RT_HD_NOINLINE int csg_material(TraceCtx& cx, int oi, float3 p) {
 // shadow_intersect (hierarchy.py:80-109 and the leaf versions): union = any child, intersection = ALL children report
 // shadow, difference goes through intersect() and ignores t_max
 struct ShadowFrame { int obj, cursor; Ray ray; float3 inv; };
+template <int V>
 RT_HD_NOINLINE bool csg_shadow(TraceCtx& cx, int root, const Ray& r, float tmax) {
     const DevObject* objs = cx.S.objects;
     ShadowFrame st[RT_MAX_NEST];
@@ -786,7 +795,7 @@ RT_HD_NOINLINE bool csg_shadow(TraceCtx& cx, int root, const Ray& r, float tmax)
                 Ray mr; mr.o = xform_point(xf->Minv, cr.o); mr.d = xform_dir(xf->Minv, cr.d);
                 const int ar = csg_arity(o);
                 if (ar == 0) val = o->csg == RT_CSG_INTERSECTION;
-                else if (o->csg == RT_CSG_DIFFERENCE) val = difference_shadow(cx, o->first_child, mr);
+                else if (o->csg == RT_CSG_DIFFERENCE) val = difference_shadow<V>(cx, o->first_child, mr);
                 else {
                     d++;
                     cinv = csg_ray_inv(mr);
@@ -795,7 +804,7 @@ RT_HD_NOINLINE bool csg_shadow(TraceCtx& cx, int root, const Ray& r, float tmax)
                     continue;
                 }
             }
-        } else val = leaf_shadow<true>(cx, cur, cr, tmax);
+        } else val = leaf_shadow<(V != RT_V_NODES)>(cx, cur, cr, tmax);
         for (;;) {
             if (d < 0) return val;
             const DevObject* nd = objs + st[d].obj;
@@ -833,12 +842,12 @@ RT_HD_NOINLINE void mesh_leaf_hits(TraceCtx& cx, int oi, const Ray& r, Want& wan
 // Candidate hits of ONE leaf primitive for `r`, in the reference's list order; `want(t)` prunes early.  The (at most two)
 // hit times of an analytic leaf are collected first and handed to `cand` from ONE call site: `cand` is the whole climb
 // through the ancestors' CSG filters, and a copy of it per primitive kind tripled the size of the node kernels.
-template <class Want, class Cand>
+template <int V, class Want, class Cand>
 RT_HD void leaf_hits(TraceCtx& cx, int oi, const Ray& r, Want&& want, Cand&& cand) {
     const DevObject* o = cx.S.objects + oi;
     cx.tally.prims++;
     const int kind = o->kind;
-    if (kind == RT_KIND_MESH) { mesh_leaf_hits(cx, oi, r, want, cand); return; }   // out of line: rare under nodes, and large
+    if (V != RT_V_NODES && kind == RT_KIND_MESH) { mesh_leaf_hits(cx, oi, r, want, cand); return; }   // out of line: rare under nodes, and large
     float ts[2]; int nt = 0;
     float3 nrm = f3(0, 0, 0), center = f3(0, 0, 0);
     if (kind == RT_KIND_SPHERE) {                                  // simple_geometry.py:20-46: both roots with t > 0
@@ -877,7 +886,7 @@ RT_HD void leaf_hits(TraceCtx& cx, int oi, const Ray& r, Want&& want, Cand&& can
 // order == list order; boolean any).
 struct NodeFrame { int obj; int cursor; Ray ray; float3 inv; };
 
-template <class Want, class Emit>
+template <int V, class Want, class Emit>
 RT_HD void object_hits(TraceCtx& cx, int root, const Ray& r, Want&& want, Emit&& emit) {
     const DevObject* objs = cx.S.objects;
     NodeFrame fr[RT_MAX_NEST];
@@ -908,7 +917,7 @@ RT_HD void object_hits(TraceCtx& cx, int root, const Ray& r, Want&& want, Emit&&
         emit(h);
     };
     if (!child_may_hit(cx.S, root, r, csg_ray_inv(r))) return;      // (roots that are top-level objects always pass)
-    if (objs[root].kind != RT_KIND_NODE) { leaf_hits(cx, root, r, want, cand); return; }
+    if (objs[root].kind != RT_KIND_NODE) { leaf_hits<V>(cx, root, r, want, cand); return; }
     auto push = [&](int oi, const Ray& pr) {
         const DevXform* xf = cx.S.xforms + objs[oi].xform;
         depth++;
@@ -932,17 +941,18 @@ RT_HD void object_hits(TraceCtx& cx, int root, const Ray& r, Want&& want, Emit&&
             push(child, pr);
         } else {
             leaf = child;
-            leaf_hits(cx, child, fr[depth].ray, want, cand);
+            leaf_hits<V>(cx, child, fr[depth].ray, want, cand);
         }
     }
 }
 
 // Hierarchy.shadow_intersect, difference case (hierarchy.py:94-107): goes through intersect() of both
 // children, `time > shadow_epsilon`, and ignores t_max.
+template <int V>
 RT_HD_NOINLINE bool difference_shadow(TraceCtx& cx, int c0, const Ray& mr) {
     bool occ = false;
     for (int side = 0; side < 2 && !occ; side++)       // hits of c0 outside c1, then hits of c1 inside c0 (one instantiation of the walk)
-        object_hits(cx, c0 + side, mr, [&](float t) { return !occ && t > RT_SHADOW_EPS; }, [&](const Hit& h) {
+        object_hits<V>(cx, c0 + side, mr, [&](float t) { return !occ && t > RT_SHADOW_EPS; }, [&](const Hit& h) {
             if (!occ && csg_inside(cx, c0 + 1 - side, h.p) == (side == 1)) occ = true;
         });
     return occ;
@@ -952,16 +962,15 @@ RT_HD_NOINLINE bool difference_shadow(TraceCtx& cx, int c0, const Ray& mr) {
 // read it from the parameter bank: the pointer chase sep_mesh[k] -> objects[oi].mesh -> meshes[] -> nodes / triangles (four dependent
 // L1 round trips in front of every mesh walk, and the triangle array's address again at every leaf) becomes constant-bank operands.
 // Scenes with more than RT_CONST_MESH top-level meshes run on the general kernels (convert_scene).
-template <bool HAS_NODES>
+template <int HAS_NODES>
 RT_HD int top_mesh_obj(const SceneView& S, int k) { return HAS_NODES ? RT_LDG(S.sep_mesh + k) : S.c.sep_obj[k]; }
-template <bool HAS_NODES> struct TopMesh;
-template <> struct TopMesh<true> { typedef MeshG type; static RT_HD MeshG get(const SceneView& S, int, int oi) { return MeshG{S.meshes + S.objects[oi].mesh}; } };
-template <> struct TopMesh<false> { typedef MeshC type; static RT_HD MeshC get(const SceneView& S, int k, int) { return MeshC{S, k}; } };
+template <int HAS_NODES> struct TopMesh { typedef MeshG type; static RT_HD MeshG get(const SceneView& S, int, int oi) { return MeshG{S.meshes + S.objects[oi].mesh}; } };
+template <> struct TopMesh<0> { typedef MeshC type; static RT_HD MeshC get(const SceneView& S, int k, int) { return MeshC{S, k}; } };
 
 // ------------------------------------------------------------------------------------------------
 // Closest hit over the top-level objects (scene.py:85-94): min by time, ties -> first in list order.
 // Leaves are resolved lazily (only t while scanning; position/normal/material for the winner).
-template <bool HAS_NODES>
+template <int HAS_NODES>
 RT_HD bool closest_hit(TraceCtx& cx, const Ray& r, Hit& out) {
     const SceneView& S = cx.S;
     float best = RT_INF;
@@ -1011,11 +1020,12 @@ RT_HD bool closest_hit(TraceCtx& cx, const Ray& r, Hit& out) {
                 !(en > ex || en < 0.0f) && RT_BETTER(en)) { best = en; best_obj = oi; best_aux = label; }
         } else if (HAS_NODES && kind == RT_KIND_NODE) {
             // inside one node the first hit in DFS (= list) order wins equal t: strict '<' once this node holds the best
-            object_hits(cx, oi, r, [&](float t) { return RT_BETTER(t); },
+            object_hits<HAS_NODES>(cx, oi, r, [&](float t) { return RT_BETTER(t); },
                         [&](const Hit& h) { if (RT_BETTER(h.t)) { best = h.t; best_obj = oi; node_hit = h; } });
         }
     }
     cx.sbase = 0;
+    if (HAS_NODES != RT_V_NODES)
     for (int k = 0; k < S.n_sep_mesh && in_world; k++) {              // top-level meshes: all lanes of the warp enter the LBVH together
         {
             const int oi = top_mesh_obj<HAS_NODES>(S, k);
@@ -1040,13 +1050,13 @@ RT_HD bool closest_hit(TraceCtx& cx, const Ray& r, Hit& out) {
         case RT_KIND_SPHERE: out.n = normalize(out.p - moved(cx, o, f3(ld4(&o->a)))); break;
         case RT_KIND_PLANE: out.n = f3(ld4(&o->b)); out.mat = plane_material(o, out.p, cx.time); break;
         case RT_KIND_BOX: out.n = box_normal(r, best_aux); break;
-        default: out.n = tri_normal(cx, TopMesh<HAS_NODES>::get(S, best_k, best_obj), best_aux, (HAS_NODES && S.mesh_motion) ? (r.o - mesh_shift(cx, best_obj)) + r.d * best : out.p); break;
+        default: if (HAS_NODES != RT_V_NODES) out.n = tri_normal(cx, TopMesh<HAS_NODES>::get(S, best_k, best_obj), best_aux, (HAS_NODES && S.mesh_motion) ? (r.o - mesh_shift(cx, best_obj)) + r.d * best : out.p); break;
     }
     return true;
 }
 
 // shadow_intersect of ONE top-level object (the body of the loop of scene.py:160-164); A = d.d
-template <bool HAS_NODES>
+template <int HAS_NODES>
 RT_HD bool object_shadow(TraceCtx& cx, int oi, const Ray& r, float A, float tmax) {
     const DevObject* o = cx.S.objects + oi;
     const int kind = o->kind;
@@ -1059,11 +1069,12 @@ RT_HD bool object_shadow(TraceCtx& cx, int oi, const Ray& r, float A, float tmax
     }
     if (kind == RT_KIND_MESH) return false;                           // (linear test mode only) traversed after the walk
     if (kind != RT_KIND_NODE) return leaf_shadow<false>(cx, oi, r, tmax);
-    return HAS_NODES ? csg_shadow(cx, oi, r, tmax) : false;
+    if constexpr (HAS_NODES != 0) return csg_shadow<HAS_NODES>(cx, oi, r, tmax);
+    else return false;
 }
 
 // Any-hit over the top-level objects (scene.py:160-164)
-template <bool HAS_NODES>
+template <int HAS_NODES>
 RT_HD bool occluded(TraceCtx& cx, const Ray& r, float tmax) {
     const SceneView& S = cx.S;
     const float A = dot(r.d, r.d);
@@ -1090,6 +1101,7 @@ RT_HD bool occluded(TraceCtx& cx, const Ray& r, float tmax) {
         if (object_shadow<HAS_NODES>(cx, oi, r, A, tmax)) { occ = true; break; }
     }
     cx.sbase = 0;
+    if (HAS_NODES != RT_V_NODES)
     for (int k = 0; k < S.n_sep_mesh && !occ && in_world; k++) {
         cx.tally.prims++;
         const int oi = top_mesh_obj<HAS_NODES>(S, k);
@@ -1194,7 +1206,7 @@ __device__ __forceinline__ bool mesh_shadow_packet(TraceCtx& cx, const M& m, con
 }
 
 // the any-hit loop of scene.py:160-164 for a warp of rays (same answer per lane as occluded<>)
-template <bool HAS_NODES>
+template <int HAS_NODES>
 __device__ __forceinline__ bool occluded_packet(TraceCtx& cx, const Ray& r, float tmax, bool want) {
     const SceneView& S = cx.S;
     if (S.mesh_mode & RT_MODE_LINEAR_TOP) return want ? occluded<HAS_NODES>(cx, r, tmax) : false;     // test aid: the plain loops
@@ -1212,6 +1224,7 @@ __device__ __forceinline__ bool occluded_packet(TraceCtx& cx, const Ray& r, floa
         bvh4_anyhit_packet<true>(cx, S.tlas_nodes, ri, 0.0f, tmax, active, cx.tally.prims, [&](int oi, bool mine) {
             if (mine && active && object_shadow<HAS_NODES>(cx, oi, r, A, tmax)) { occ = true; active = false; }
         });
+    if (HAS_NODES != RT_V_NODES)
     for (int k = 0; k < S.n_sep_mesh && __any_sync(RT_FULL_WARP, active); k++) {
         if (active) cx.tally.prims++;
         const int oi = top_mesh_obj<HAS_NODES>(S, k);
@@ -1232,7 +1245,7 @@ RT_HD float4 light_vector(const SceneView& S, int li) { return (CONST && li < RT
 RT_HD float4 light_colour_power(const SceneView& S, int li) { return li < RT_CONST_LIGHTS ? S.c.light_colour[li] : ld4(&S.lights[li].colour_power); }
 RT_HD float4 light_dir_norm(const SceneView& S, int li) { return li < RT_CONST_LIGHTS ? S.c.light_dirn[li] : ld4(&S.lights[li].dir_norm); }
 
-template <bool HAS_NODES>
+template <int HAS_NODES>
 RT_HD bool light_occluded(TraceCtx& cx, float3 p, int li) {
     const float4 lv = light_vector<!HAS_NODES>(cx.S, li);
     const bool point = as_int(lv.w) == RT_LIGHT_POINT;
@@ -1243,7 +1256,7 @@ RT_HD bool light_occluded(TraceCtx& cx, float3 p, int li) {
 }
 #if defined(__CUDACC__)
 // the same for a warp of hit points and one light (all 32 lanes call; want: this lane has a hit point)
-template <bool HAS_NODES>
+template <int HAS_NODES>
 __device__ __forceinline__ bool light_occluded_packet(TraceCtx& cx, float3 p, int li, bool want) {
     const float4 lv = light_vector<!HAS_NODES>(cx.S, li);
     const bool point = as_int(lv.w) == RT_LIGHT_POINT;
@@ -1350,7 +1363,7 @@ RT_HD bool shade_level(TraceCtx& cx, PathState& ps, Hit& hit, Lit&& lit, float3&
 
 // One whole level in one thread (unit-test kernels and tests/hostsim; the render kernels run the three stages as
 // separate launches: k_hit, k_shadow, k_shade)
-template <bool HAS_NODES>
+template <int HAS_NODES>
 RT_HD bool trace_level(TraceCtx& cx, PathState& ps, float3& sample) {
     Hit hit;
     if (ps.depth_left <= 0 || !closest_hit<HAS_NODES>(cx, ps.ray, hit)) { sample = fold_eval(ps.fold, f3(0, 0, 0)); return false; }

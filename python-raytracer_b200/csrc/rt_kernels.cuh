@@ -159,8 +159,8 @@ __device__ __forceinline__ PrimaryIndex primary_index(const SceneView& S, const 
 // ---- stage 1: closest hit ------------------------------------------------------------------------------
 // PRIMARY: ray i of the batch is generated here: pixel = pixel_begin + i / N, slot = i % N = (d*S + s)*T + t (loop
 // order of scene.py:57-67).  Otherwise ray i is entry i of the compacted queue `qin` (count on the device).
-template <bool HAS_NODES, bool PRIMARY>
-__global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_HIT_CSG : RT_MIN_BLOCKS_HIT) k_hit(const ViewArg<HAS_NODES> SA, PixelMap pm, long long pixel_begin, long long n_rays,
+template <int HAS_NODES, bool PRIMARY>
+__global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_HIT_CSG : RT_MIN_BLOCKS_HIT) k_hit(const ViewArg<(HAS_NODES != 0)> SA, PixelMap pm, long long pixel_begin, long long n_rays,
                                                                      RayQueue qin, const unsigned long long* qin_count,
                                                                      HitPlanes H, RtCounters* counters) {
     const SceneView& S = SA.get();
@@ -216,8 +216,8 @@ enum { SHADOW_PER_RAY = 0, SHADOW_ROWS = 1, SHADOW_PACKET = 2 };
 #ifndef RT_PACKET_SHADOW
 #define RT_PACKET_SHADOW 0
 #endif
-template <bool HAS_NODES, int MODE>
-__global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_SHADOW_CSG : RT_MIN_BLOCKS_SHADOW) k_shadow(const ViewArg<HAS_NODES> SA, long long n_rays, const unsigned long long* n_dev,
+template <int HAS_NODES, int MODE>
+__global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_SHADOW_CSG : RT_MIN_BLOCKS_SHADOW) k_shadow(const ViewArg<(HAS_NODES != 0)> SA, long long n_rays, const unsigned long long* n_dev,
                                                                            HitPlanes H, uint8_t* __restrict__ occ, RtCounters* counters) {
     const SceneView& S = SA.get();
     Tally tally = tally_zero();
@@ -320,8 +320,8 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS_SHADE) k_shade(SceneVi
 // longest of the warp's 32 paths was done (ncu: 9 of 32 lanes active).  Here every lane runs ONE level of whatever path it holds
 // per iteration, and a lane whose path has ended fetches the next queued path right away (warp-aggregated atomic on `next`, a
 // zeroed counter): the lanes of a warp stay together at the granularity of a level.
-template <bool HAS_NODES>
-__global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_HIT_CSG : RT_MIN_BLOCKS_TAIL) k_tail(const ViewArg<HAS_NODES> SA, RayQueue qin, const unsigned long long* qin_count,
+template <int HAS_NODES>
+__global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_HIT_CSG : RT_MIN_BLOCKS_TAIL) k_tail(const ViewArg<(HAS_NODES != 0)> SA, RayQueue qin, const unsigned long long* qin_count,
                                                                                           unsigned long long* next, float4* __restrict__ samples, RtCounters* counters) {
     const SceneView& S = SA.get();
     Tally tally = tally_zero();
@@ -405,8 +405,8 @@ __global__ void k_finalize_u8(const float* __restrict__ img, int ncols, int nrow
 }
 
 // ---- unit-test aids: explicit rays through the same device functions ---------------------------------------
-template <bool HAS_NODES>
-__global__ void __launch_bounds__(RT_BLOCK) k_trace(const ViewArg<HAS_NODES> SA, long long n, const float* __restrict__ org, const float* __restrict__ dir,
+template <int HAS_NODES>
+__global__ void __launch_bounds__(RT_BLOCK) k_trace(const ViewArg<(HAS_NODES != 0)> SA, long long n, const float* __restrict__ org, const float* __restrict__ dir,
                                                      const float* __restrict__ times, float* rgb, float* hit_t, float* hit_n, float* hit_p,
                                                      int* hit_geom, int* hit_mat, RtCounters* counters) {
     const SceneView& S = SA.get();
@@ -435,8 +435,8 @@ __global__ void __launch_bounds__(RT_BLOCK) k_trace(const ViewArg<HAS_NODES> SA,
     tally_flush(tally, 0, 0, counters);
 }
 
-template <bool HAS_NODES>
-__global__ void __launch_bounds__(RT_BLOCK) k_occluded(const ViewArg<HAS_NODES> SA, long long n, const float* __restrict__ org, const float* __restrict__ dir,
+template <int HAS_NODES>
+__global__ void __launch_bounds__(RT_BLOCK) k_occluded(const ViewArg<(HAS_NODES != 0)> SA, long long n, const float* __restrict__ org, const float* __restrict__ dir,
                                                         const float* __restrict__ times, const float* __restrict__ tmax, int* occ,
                                                         RtCounters* counters) {
     const SceneView& S = SA.get();

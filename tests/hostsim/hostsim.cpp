@@ -140,7 +140,7 @@ static void add_tally(RtCounters* c, const Tally& t, uint64_t primary) {
     c->mesh_hits_smooth += t.smooth; c->error_flags |= t.err;
 }
 
-template <bool HN>
+template <int HN>
 static void render_px(const Sim& sim, const SceneView& V, const int32_t* cols, const int32_t* rows, int64_t n, float* out, RtCounters* ctr) {
 #pragma omp parallel
     {
@@ -176,7 +176,7 @@ extern "C" int hostsim_render_pixels(const RtSceneDesc* d, const int32_t* cols, 
     if (rc) return rc;
     if (ctr) *ctr = RtCounters{};
     SceneView V = sim.V; V.mesh_mode = mesh_mode;
-    if (sim.hs.has_nodes) render_px<true>(sim, V, cols, rows, n, out, ctr); else render_px<false>(sim, V, cols, rows, n, out, ctr);
+    if (sim.hs.has_nodes) render_px<RT_V_NODES_MESH>(sim, V, cols, rows, n, out, ctr); else render_px<RT_V_LEAN>(sim, V, cols, rows, n, out, ctr);
     return 0;
 }
 
@@ -205,12 +205,12 @@ extern "C" int hostsim_trace_rays(const RtSceneDesc* d, int64_t n, const float* 
         ps.ray.o = f3(org[3 * i], org[3 * i + 1], org[3 * i + 2]); ps.ray.d = f3(dir[3 * i], dir[3 * i + 1], dir[3 * i + 2]);
         TraceCtx cx{V, (float)times[i], tally, stack, 1, spill};
         Hit h;
-        const bool hit = sim.hs.has_nodes ? closest_hit<true>(cx, ps.ray, h) : closest_hit<false>(cx, ps.ray, h);
+        const bool hit = sim.hs.has_nodes ? closest_hit<RT_V_NODES_MESH>(cx, ps.ray, h) : closest_hit<RT_V_LEAN>(cx, ps.ray, h);
         hit_t[i] = hit ? h.t : INFINITY; hit_geom[i] = hit ? h.geom : -1;
         if (hit_np && hit) { float* q = hit_np + 7 * i; q[0] = h.n.x; q[1] = h.n.y; q[2] = h.n.z; q[3] = h.p.x; q[4] = h.p.y; q[5] = h.p.z; q[6] = (float)h.mat; }
         ps.fold = fold_identity(); ps.depth_left = V.max_depth; ps.in_shape = 0;
         float3 sample;
-        while (sim.hs.has_nodes ? trace_level<true>(cx, ps, sample) : trace_level<false>(cx, ps, sample)) {}
+        while (sim.hs.has_nodes ? trace_level<RT_V_NODES_MESH>(cx, ps, sample) : trace_level<RT_V_LEAN>(cx, ps, sample)) {}
         rgb[3 * i] = sample.x; rgb[3 * i + 1] = sample.y; rgb[3 * i + 2] = sample.z;
     }
     return 0;
@@ -228,7 +228,7 @@ extern "C" int hostsim_occluded(const RtSceneDesc* d, int64_t n, const float* or
         Tally tally{};
         Ray r; r.o = f3(org[3 * i], org[3 * i + 1], org[3 * i + 2]); r.d = f3(dir[3 * i], dir[3 * i + 1], dir[3 * i + 2]);
         TraceCtx cx{V, (float)times[i], tally, stack, 1, spill};
-        occ[i] = (sim.hs.has_nodes ? occluded<true>(cx, r, (float)tmax[i]) : occluded<false>(cx, r, (float)tmax[i])) ? 1 : 0;
+        occ[i] = (sim.hs.has_nodes ? occluded<RT_V_NODES_MESH>(cx, r, (float)tmax[i]) : occluded<RT_V_LEAN>(cx, r, (float)tmax[i])) ? 1 : 0;
     }
     return 0;
 }
@@ -250,7 +250,7 @@ extern "C" int hostsim_node_counts(const RtSceneDesc* d, const int32_t* cols, co
             PathState ps; ps.ray = generate_ray(V, cols[i], rows[i], dd, s); ps.fold = fold_identity(); ps.depth_left = V.max_depth; ps.in_shape = 0;
             TraceCtx cx{V, V.times[t], tally, stack, 1, spill};
             float3 sample;
-            if (sim.hs.has_nodes) trace_level<true>(cx, ps, sample); else trace_level<false>(cx, ps, sample);
+            if (sim.hs.has_nodes) trace_level<RT_V_NODES_MESH>(cx, ps, sample); else trace_level<RT_V_LEAN>(cx, ps, sample);
             out[i * N + slot] = tally.nodes;
         }
     }
@@ -274,14 +274,14 @@ extern "C" int hostsim_shadow_stats(const RtSceneDesc* d, const int32_t* cols, c
             Ray ray = generate_ray(V, cols[i], rows[i], dd, s);
             TraceCtx cx{V, V.times[t], tally, stack, 1, spill};
             Hit h;
-            const bool hit = sim.hs.has_nodes ? closest_hit<true>(cx, ray, h) : closest_hit<false>(cx, ray, h);
+            const bool hit = sim.hs.has_nodes ? closest_hit<RT_V_NODES_MESH>(cx, ray, h) : closest_hit<RT_V_LEAN>(cx, ray, h);
             for (int li = 0; li < L; li++) {
                 int32_t* o = out + ((i * N + slot) * L + li) * 5;
                 o[0] = hit ? V.objects[h.geom].kind : -1; o[1] = o[2] = o[3] = o[4] = 0;
                 if (!hit) continue;
                 Tally t2{};
                 TraceCtx c2{V, V.times[t], t2, stack, 1, spill};
-                o[1] = (sim.hs.has_nodes ? light_occluded<true>(c2, h.p, li) : light_occluded<false>(c2, h.p, li)) ? 1 : 0;
+                o[1] = (sim.hs.has_nodes ? light_occluded<RT_V_NODES_MESH>(c2, h.p, li) : light_occluded<RT_V_LEAN>(c2, h.p, li)) ? 1 : 0;
                 o[2] = (int)t2.nodes; o[3] = (int)t2.tris; o[4] = (int)t2.prims;
             }
         }
