@@ -133,6 +133,26 @@ def test_render_host_into_pinned_memory_leaves_in_chunks_and_equals_the_device_r
         assert ctr.error_flags == 0 and ctr.rays_primary == W * H
 
 
+@pytest.mark.parametrize("case,over", [("MirrorRefraction", {"resolution": [96, 64]}), ("TorusMesh_smooth", {"resolution": [64, 64]}),
+                                       ("NovelScene1_small", {"resolution": [64, 32]}), ("MeshInNode", {"resolution": [64, 48]})])
+def test_every_kernel_variant_in_many_small_batches_on_two_streams(case, over, lib):
+    """The three kernel variants (lean / nodes without a mesh / nodes and meshes) with the frame cut into dozens of wavefront
+    batches: both work-buffer sets, level 0 on the caller's stream and the deeper levels on the side stream, the chunked copy
+    into pinned host memory - all must give the bytes of the one-batch render."""
+    import torch
+    sc = load_case(case, over)
+    W, H = sc.vc.width, sc.vc.height
+    ref = sc.render_region(0, W, 0, H).copy()
+    h = sc.upload()
+    for batch in (1500, 7000):
+        job = sc.make_job(0, W, 0, H, max_batch_rays=batch)
+        host = torch.full((W * H * 3,), -1.0, dtype=torch.float32).pin_memory()
+        ctr = abi.RtCounters()
+        abi.check(lib, lib.rt_render_host(h, C.byref(job), host.data_ptr(), C.byref(ctr), None), "rt_render_host")
+        assert np.array_equal(host.numpy().reshape(W, H, 3), ref), (case, batch)
+        assert ctr.error_flags == 0 and ctr.kernel_launches > 20
+
+
 @pytest.mark.parametrize("world", [2, 3, 8])
 def test_tile_sharded_render_assembles_to_the_single_rank_image(world, lib):
     """Multi-GPU split emulated on one device: every rank's compact tile buffer, concatenated as the
