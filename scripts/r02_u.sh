@@ -1,2 +1,2 @@
-for v in _l1 "" _l3 _l4; do B200RT_LIB=$PWD/python-raytracer_b200/csrc/libb200rt$v.so python bench.py --steps 6 --warmup 3 --no-cpu-baseline 2>/dev/null | python -c "
-import json,sys; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); k=d['kernel_ms_per_frame']; print('$v', round(d['ms_per_step'],2), round(k['k_hit'],2), round(k['k_shadow'],2), d['tallies_rank0_per_frame']['k_shadow']['bvh_nodes'], d['tallies_rank0_per_frame']['k_shadow']['tri_tests'], round(d['setup_ms']['lbvh_build'],1), d['image_sha256'][:8])"; done
+for v in "" _xldg; do B200RT_LIB=$PWD/python-raytracer_b200/csrc/libb200rt$v.so python bench.py --steps 6 --warmup 3 --no-cpu-baseline 2>/dev/null | python -c "
+import json,sys; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); k=d['kernel_ms_per_frame']; print('$v', round(d['ms_per_step'],2), round(k['k_hit'],2), round(k['k_shadow'],2), d['image_sha256'][:8])"; done
