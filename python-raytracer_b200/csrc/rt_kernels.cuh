@@ -16,7 +16,7 @@
 
 // resident blocks per SM each kernel's register allocation is held to (tuned on B200)
 #ifndef RT_MIN_BLOCKS_HIT
-#define RT_MIN_BLOCKS_HIT 6
+#define RT_MIN_BLOCKS_HIT 7
 #endif
 #ifndef RT_MIN_BLOCKS_SHADOW
 #define RT_MIN_BLOCKS_SHADOW 8
