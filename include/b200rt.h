@@ -172,8 +172,7 @@ typedef struct RtRenderJob {
     int32_t direct;          /* 0 = compact tile buffer; 1 = reference layout (world must be 1); RT_DIRECT_SHARED_FRAME = reference
                               * layout of the WHOLE region with world > 1: every rank writes its own tiles into one shared frame */
     int32_t mesh_mode;       /* test aids, bit field: 0 = accelerated; bit 0 = brute force over all faces (mesh.py:77);
-                              * bit 1 = plain in-order loop over the top-level objects (scene.py:87,160) instead of the object BVH;
-                              * bit 2 (rt_occluded only) = the warp-packet any-hit walks the level-0 shadow kernel uses */
+                              * bit 1 = plain in-order loop over the top-level objects (scene.py:87,160) instead of the object BVH */
     int64_t max_batch_rays;  /* 0 = default */
 } RtRenderJob;
 

@@ -585,7 +585,7 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
     if (smem) {
         CU(cudaFuncSetAttribute(k_hit<HAS_NODES, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         CU(cudaFuncSetAttribute(k_hit<HAS_NODES, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        CU(cudaFuncSetAttribute(k_shadow<HAS_NODES, SHADOW_PACKET>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CU(cudaFuncSetAttribute(k_shadow<HAS_NODES, SHADOW_PER_RAY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         CU(cudaFuncSetAttribute(k_shadow<HAS_NODES, SHADOW_ROWS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     }
     // direct: k_resolve writes the reference layout (ncols, nrows, 3) instead of the compact tile buffer.  With world > 1 only for
@@ -624,9 +624,7 @@ static int render_impl(RtScene* sc, const RtRenderJob* job, const PixelMap& pm, 
             { ProfScope ps_(sc, PC_HIT0, s);
               k_hit<HAS_NODES, true><<<(int)std::min<long long>(need, g_hit0), RT_BLOCK, smem, s>>>(VA, pmk, p0, n_rays, q0, nullptr, H, sc->d_counters + 0); }
             if (V.n_lights > 0) { ProfScope ps_(sc, PC_SHADOW0, s);
-              // the packet walk needs the shared stack area (scenes with a BVH to walk); without one there is nothing to walk per warp
-              if (RT_PACKET_SHADOW && smem) k_shadow<HAS_NODES, SHADOW_PACKET><<<(int)std::min<long long>(need, g_shadow0), RT_BLOCK, smem, s>>>(VA, n_rays, nullptr, H, w.d_occ, sc->d_counters + 1);
-              else k_shadow<HAS_NODES, SHADOW_PER_RAY><<<(int)std::min<long long>(need, g_shadow0), RT_BLOCK, smem, s>>>(VA, n_rays, nullptr, H, w.d_occ, sc->d_counters + 1);
+              k_shadow<HAS_NODES, SHADOW_PER_RAY><<<(int)std::min<long long>(need, g_shadow0), RT_BLOCK, smem, s>>>(VA, n_rays, nullptr, H, w.d_occ, sc->d_counters + 1);
               (*launches)++; }
             { ProfScope ps_(sc, PC_SHADE0, s);
               k_shade<true><<<(int)std::min<long long>(need, g_shade0), RT_BLOCK, 0, s>>>(V, pmk, p0, n_rays, q0, nullptr, H, w.d_occ, w.d_samples, q0, w.d_qcount, sc->d_counters + 2); }

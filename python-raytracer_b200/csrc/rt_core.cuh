@@ -1112,130 +1112,6 @@ RT_HD bool occluded(TraceCtx& cx, const Ray& r, float tmax) {
     return occ;
 }
 
-#if defined(__CUDACC__)
-// ------------------------------------------------------------------------------------------------
-// PACKET any-hit walks (device only).  The 32 rays of a warp at level 0 are the samples of one pixel (or of neighbouring
-// pixels of a tile) towards ONE light: nearly the same ray.  Walked lane by lane they still drift apart - a lane whose ray
-// misses one child box pops a different node than its neighbours - and from then on every lane tests ITS leaves at its own
-// step (ncu: 5.4 of 32 lanes active in the triangle tests).  Here the WARP walks the tree: one node per step for all lanes,
-// every lane tests its own ray against the four child boxes, a child is entered when ANY lane's ray touches it (one REDUX),
-// the stack is one warp-uniform stack in shared memory, and a leaf's triangles are tested once per warp with all interested
-// lanes at the same time.  Any-hit results do not depend on the visiting order, and the boxes only prune (a ray that hits a
-// triangle touches every box around it), so every lane gets exactly the answer its own walk would have given.
-// All 32 lanes of the warp must call these functions together; `active`: this lane still wants an answer.
-#define RT_FULL_WARP 0xffffffffu
-__device__ __forceinline__ unsigned ws_addr(unsigned wbase, int e) { return wbase + (unsigned)(RT_STACK_DEPTH + (e >> 5)) * RT_STACK_PITCH + (unsigned)(e & 31) * 4u; }
-__device__ __forceinline__ void ws_push(TraceCtx& cx, unsigned wbase, int& sp, int v) {
-    if (sp >= RT_PACKET_ROWS * 32) { cx.tally.err |= 1u << RT_ERR_LIMIT; return; }
-    asm volatile("st.shared.b32 [%0], %1;" :: "r"(ws_addr(wbase, sp)), "r"(v) : "memory");
-    sp++;
-}
-__device__ __forceinline__ int ws_pop(unsigned wbase, int& sp) {
-    --sp;
-    int v;
-    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(ws_addr(wbase, sp)) : "memory");
-    return v;
-}
-
-// onLeaf(leaf_code, mine): called by all lanes for every leaf some active lane's ray touches (mine: this lane's does);
-// it may clear `active`.  FLAGS: children flagged RT_TLAS_NO_TMAX are tested without the tmax bound (object BVH).
-template <bool FLAGS, class OnLeaf>
-__device__ __forceinline__ void bvh4_anyhit_packet(TraceCtx& cx, const BvhNode4* __restrict__ nodes, const RayInv& ri, const float tmin,
-                                                   const float tmax, bool& active, unsigned& visits, OnLeaf&& onLeaf) {
-#if defined(__CUDA_ARCH__)
-    const unsigned wbase = cx.saddr - (threadIdx.x & 31u) * 4u;       // lane 0's column of the block's shared stack area
-#else
-    const unsigned wbase = 0;                                          // (host pass of nvcc: never executed)
-#endif
-    int sp = 0, cur = 0;
-    for (;;) {
-        if (cur == RT_LINK_NONE) {
-            if (sp == 0) return;
-            cur = ws_pop(wbase, sp);
-        }
-        const BvhNode4* np = nodes + cur;
-        RT_LOAD_NODE4(np)
-        float t0 = tmax, t1 = tmax, t2 = tmax, t3 = tmax;
-        if (FLAGS && cx.S.tlas_flagged) {
-            const int4 fl = RT_LDG(&np->flags);
-            if (fl.x & RT_TLAS_NO_TMAX) t0 = RT_INF;
-            if (fl.y & RT_TLAS_NO_TMAX) t1 = RT_INF;
-            if (fl.z & RT_TLAS_NO_TMAX) t2 = RT_INF;
-            if (fl.w & RT_TLAS_NO_TMAX) t3 = RT_INF;
-        }
-        const Slab4 sl = slab4<true>(pnx, pny, pnz, pfx, pfy, pfz, ri.inv, ri.oinv, tmin, t0, t1, t2, t3);
-        const bool h0 = sl.h0, h1 = sl.h1, h2 = sl.h2, h3 = sl.h3;
-        const unsigned mine = active ? ((unsigned)h0 | (unsigned)h1 << 1 | (unsigned)h2 << 2 | (unsigned)h3 << 3) : 0u;
-        const unsigned any4 = __reduce_or_sync(RT_FULL_WARP, mine);
-        visits += active ? 1u : 0u;
-        int nxt = RT_LINK_NONE;
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            if (!((any4 >> k) & 1u)) continue;
-            const int l = k == 0 ? link.x : k == 1 ? link.y : k == 2 ? link.z : link.w;
-            if (l < 0) onLeaf(~l, ((mine >> k) & 1u) != 0u);
-            else if (nxt == RT_LINK_NONE) nxt = l;
-            else ws_push(cx, wbase, sp, l);
-        }
-        if (!__any_sync(RT_FULL_WARP, active)) return;
-        cur = nxt;
-    }
-}
-
-// Mesh.shadow_intersect for a warp of rays and ONE mesh (same answer per lane as mesh_shadow)
-template <class M>
-__device__ __forceinline__ bool mesh_shadow_packet(TraceCtx& cx, const M& m, const Ray& r, const RayInv& ri, bool want) {
-    bool active = want && mesh_gate_rcp(m, r, ri);
-    const int n = m.n_tris();
-    if (n <= 0 || !__any_sync(RT_FULL_WARP, active)) return false;
-    bool occ = false;
-    auto test = [&](int s, bool mine) {
-        float3 v0, v1, v2; int face;
-        tri_load(m, s, v0, v1, v2, face);                                   // one address for the whole warp
-        if (mine && active) { cx.tally.tris++; if (tri_shadow(v0, v1, v2, r)) { occ = true; active = false; } }
-    };
-    if ((cx.S.mesh_mode & RT_MODE_BRUTE_MESH) || n == 1) {
-        for (int s = 0; s < n && __any_sync(RT_FULL_WARP, active); s++) test(s, true);
-        return occ;
-    }
-    bvh4_anyhit_packet<false>(cx, m.nodes(), ri, RT_SHADOW_EPS * 0.5f, RT_INF, active, cx.tally.nodes, [&](int code, bool mine) {
-        const int first = code & ((1 << RT_LEAF_SLOT_BITS) - 1), last = first + (code >> RT_LEAF_SLOT_BITS);
-        for (int s = first; s <= last; s++) test(s, mine);
-    });
-    return occ;
-}
-
-// the any-hit loop of scene.py:160-164 for a warp of rays (same answer per lane as occluded<>)
-template <int HAS_NODES>
-__device__ __forceinline__ bool occluded_packet(TraceCtx& cx, const Ray& r, float tmax, bool want) {
-    const SceneView& S = cx.S;
-    if (S.mesh_mode & RT_MODE_LINEAR_TOP) return want ? occluded<HAS_NODES>(cx, r, tmax) : false;     // test aid: the plain loops
-    const float A = dot(r.d, r.d);
-    const RayInv ri = ray_inv(r);
-    bool occ = false, active = want;
-    cx.sbase = 0;
-    for (int k = 0; k < S.n_lin; k++) {                                      // unbounded objects: every lane, scene order
-        const int oi = RT_LDG(S.lin_objs + k);
-        if (active && object_shadow<HAS_NODES>(cx, oi, r, A, tmax)) { occ = true; active = false; }
-    }
-    active = active && (!S.has_world || touches_world(S, ri, RT_INF));       // lanes whose ray misses everything bounded are done
-    if (!__any_sync(RT_FULL_WARP, active)) return occ;
-    if (S.tlas_nodes != nullptr)
-        bvh4_anyhit_packet<true>(cx, S.tlas_nodes, ri, 0.0f, tmax, active, cx.tally.prims, [&](int oi, bool mine) {
-            if (mine && active && object_shadow<HAS_NODES>(cx, oi, r, A, tmax)) { occ = true; active = false; }
-        });
-    if (HAS_NODES != RT_V_NODES)
-    for (int k = 0; k < S.n_sep_mesh && __any_sync(RT_FULL_WARP, active); k++) {
-        if (active) cx.tally.prims++;
-        const int oi = top_mesh_obj<HAS_NODES>(S, k);
-        Ray mr = r; RayInv mri = ri;
-        if (HAS_NODES && S.mesh_motion) { mr.o = r.o - mesh_shift(cx, oi); mri = ray_inv_moved(ri, mr.o); }
-        if (mesh_shadow_packet(cx, TopMesh<HAS_NODES>::get(S, k, oi), mr, mri, active)) { occ = true; active = false; }
-    }
-    return occ;
-}
-#endif
-
 // ------------------------------------------------------------------------------------------------
 // Shadow ray of light `li` from hit point p (scene.py:148-167): un-offset origin, un-normalised direction (Q12)
 // DevLight fields of light `li`: the first RT_CONST_LIGHTS from the parameter bank (SceneConst)
@@ -1254,19 +1130,6 @@ RT_HD bool light_occluded(TraceCtx& cx, float3 p, int li) {
     cx.tally.shadow++;
     return occluded<HAS_NODES>(cx, sr, point ? 1.0f : RT_INF);
 }
-#if defined(__CUDACC__)
-// the same for a warp of hit points and one light (all 32 lanes call; want: this lane has a hit point)
-template <int HAS_NODES>
-__device__ __forceinline__ bool light_occluded_packet(TraceCtx& cx, float3 p, int li, bool want) {
-    const float4 lv = light_vector<!HAS_NODES>(cx.S, li);
-    const bool point = as_int(lv.w) == RT_LIGHT_POINT;
-    Ray sr; sr.o = p;
-    sr.d = point ? f3(lv) - p : -f3(lv);
-    if (want) cx.tally.shadow++;
-    return occluded_packet<HAS_NODES>(cx, sr, point ? 1.0f : RT_INF, want);
-}
-#endif
-
 // Blinn-Phong's two normalisations and its power per light (scene.py:170-181) on the device: MUFU.RSQ instead of IEEE sqrt + divide
 // (2 ulp), and x ** y as exp2(y * log2(x)) with the MUFU approximations (relative error about y * 2e-7: 1e-5 at hardness 64, two
 // orders below 1/255) with Python's corner cases kept exact (x ** 0 == 1, also for x == 0; 0 ** y == 0).  They feed only the

@@ -4,7 +4,7 @@
 // in the SM's instruction caches (a single fused kernel measured 94 % of the GPC instruction-fetch bandwidth and
 // a third of its issue slots stalled on "no instruction"):
 //   k_hit     : raygen (level 0) or queue load, closest hit over the scene -> hit record planes
-//   k_shadow  : any-hit shadow rays -> one occlusion byte per (light, ray); level 0 walks the BVHs warp by warp (packets)
+//   k_shadow  : any-hit shadow rays -> one occlusion bit (level 0) / byte (queued levels) per (light, ray)
 //   k_shade   : Blinn-Phong with those flags, per-level clamp fold; finished samples go to the sample buffer,
 //               reflection/refraction rays are compacted (warp ballot + prefix popcount + one atomic per warp)
 //               into the next level's ray queue (replaces the recursion of scene.py:102,203,208)
@@ -206,16 +206,10 @@ __global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_HIT_CSG : 
 //   SHADOW_PER_RAY : a thread walks the lights of its ray one after the other (big level-0 batches: the 16-B hit position is read once
 //                    instead of once per light; measured 3 ms/frame faster than sweeping the rays once per light)
 //   SHADOW_ROWS    : gridDim.y = lights (small queues of the deeper levels: every (light, ray) pair gets its own thread)
-//   SHADOW_PACKET  : like PER_RAY, but the BVHs are walked warp by warp (occluded_packet, rt_core.cuh): at level 0 the 32 lanes of a
-//                    warp hold samples of one pixel / neighbouring pixels and share the light, so their shadow rays are nearly the same.
-//                    Built, verified (rt_occluded mesh_mode bit 2, tests) and MEASURED at 4K x 64: the same 19.3 G warp instructions per
-//                    heavy launch as the per-ray walk (30.4 instead of 25.8 lanes per instruction, L1 data pipe 54 % instead of 84 %,
-//                    but the larger kernel is instruction-fetch bound: 98 % of the GPC fetch bandwidth) and 63.3 ms instead of 62.7
-//                    per frame: not the default (-DRT_PACKET_SHADOW=1 selects it).
-enum { SHADOW_PER_RAY = 0, SHADOW_ROWS = 1, SHADOW_PACKET = 2 };
-#ifndef RT_PACKET_SHADOW
-#define RT_PACKET_SHADOW 0
-#endif
+// (A third mode walked the BVHs warp by warp - the 32 samples of a pixel as one packet with a warp-uniform stack - and was verified
+// lane for lane against the per-ray walk: the same warp instructions per launch, 98 % of the GPC's instruction-fetch bandwidth, 63.3
+// instead of 62.7 ms.  Removed; DESIGN.md keeps the measurement.)
+enum { SHADOW_PER_RAY = 0, SHADOW_ROWS = 1 };
 template <int HAS_NODES, int MODE>
 __global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_SHADOW_CSG : RT_MIN_BLOCKS_SHADOW) k_shadow(const ViewArg<(HAS_NODES != 0)> SA, long long n_rays, const unsigned long long* n_dev,
                                                                            HitPlanes H, uint8_t* __restrict__ occ, RtCounters* counters) {
@@ -224,20 +218,7 @@ __global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_SHADOW_CSG
     int spill[RT_STACK_SPILL];       // overflow of the shared-memory traversal stack (thread-local memory)
     const long long n = n_dev ? (long long)*n_dev : n_rays;
     const long long stride = (long long)gridDim.x * blockDim.x;
-    if (MODE == SHADOW_PACKET) {
-        for (long long base = (long long)blockIdx.x * blockDim.x; base < n; base += stride) {     // whole warps stay together
-            const long long i = base + threadIdx.x;
-            const float4 h0 = i < n ? RT_LD_REC(&H.planes[0 * H.cap + i]) : f4(0.0f, 0.0f, 0.0f, as_float(0x7fc00000));
-            const bool live = !(h0.w != h0.w);                            // no hit: no shadow rays
-            if (!__any_sync(0xffffffffu, live)) continue;
-            TraceCtx cx{S, h0.w, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill};
-            unsigned bits = 0;
-            for (int li = 0; li < S.n_lights; li++) {
-                bits |= (light_occluded_packet<HAS_NODES>(cx, f3(h0), li, live) ? 1u : 0u) << (li & 7);
-                if ((li & 7) == 7 || li == S.n_lights - 1) { if (live) RT_ST_REC(&occ[(long long)(li >> 3) * H.cap + i], (uint8_t)bits); bits = 0; }
-            }
-        }
-    } else {
+    {
         const int li0 = MODE == SHADOW_ROWS ? (int)blockIdx.y : 0, li1 = MODE == SHADOW_ROWS ? li0 + 1 : S.n_lights;
         for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
             const float4 h0 = RT_LD_REC(&H.planes[0 * H.cap + i]);
@@ -258,7 +239,7 @@ __global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_SHADOW_CSG
 }
 
 // ---- stage 3: shading, fold, next ray ----------------------------------------------------------------------
-// PRIMARY (level 0): the occlusion flags are one BIT per (light, ray) (k_shadow SHADOW_PER_RAY / SHADOW_PACKET), the ray direction is
+// PRIMARY (level 0): the occlusion flags are one BIT per (light, ray) (k_shadow SHADOW_PER_RAY), the ray direction is
 // recomputed from the pixel; queued levels: one byte per (light, ray) (SHADOW_ROWS), direction from the queue entry.
 template <bool PRIMARY>
 __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS_SHADE) k_shade(SceneView S, PixelMap pm, long long pixel_begin, long long n_rays, RayQueue qin, const unsigned long long* qin_count,
@@ -448,8 +429,7 @@ __global__ void __launch_bounds__(RT_BLOCK) k_occluded(const ViewArg<(HAS_NODES 
     Ray r; r.o = f3(org[3 * j], org[3 * j + 1], org[3 * j + 2]); r.d = f3(dir[3 * j], dir[3 * j + 1], dir[3 * j + 2]);
     TraceCtx cx{S, times[j], tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill};
     bool o;
-    if ((S.mesh_mode & RT_MODE_PACKET_TEST) && rt_smem_stack_present(S)) o = occluded_packet<HAS_NODES>(cx, r, tmax[j], valid);   // the warp walks
-    else o = valid && occluded<HAS_NODES>(cx, r, tmax[j]);
+    o = valid && occluded<HAS_NODES>(cx, r, tmax[j]);
     if (valid) occ[i] = o ? 1 : 0;
     tally_flush(tally, 0, 0, counters);
 }

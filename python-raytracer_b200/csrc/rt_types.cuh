@@ -8,10 +8,7 @@
 #ifndef RT_STACK_DEPTH
 #define RT_STACK_DEPTH 32    // BVH traversal stack entries per ray held in shared memory (object BVH + mesh LBVH share it)
 #endif
-// further rows of the block's shared stack area that belong to the WARP as a whole: the warp-uniform stack of the packet
-// walks (bvh4_anyhit_packet), RT_PACKET_ROWS * 32 entries per warp
-#define RT_PACKET_ROWS 8
-#define RT_STACK_ROWS (RT_STACK_DEPTH + RT_PACKET_ROWS)
+#define RT_STACK_ROWS RT_STACK_DEPTH
 #ifndef RT_STACK_SPILL
 #define RT_STACK_SPILL 88
 #endif
@@ -19,7 +16,6 @@
 #define RT_TLAS_NO_TMAX 1    // object-BVH child flag
 #define RT_MODE_BRUTE_MESH 1
 #define RT_MODE_LINEAR_TOP 2
-#define RT_MODE_PACKET_TEST 4   // rt_occluded only: answer through the warp-packet walks (occluded_packet) instead of the per-lane ones
 
 // One geometry object, 16-byte aligned so fields load as 128-bit vectors (warp-uniform index
 // -> one broadcast transaction).  Meaning of a/b per kind as in RtObject (include/b200rt.h).

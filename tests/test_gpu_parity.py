@@ -527,27 +527,6 @@ def test_gpu_lbvh_equals_host_restatement_on_a_large_mesh_with_equal_keys(lib):
     assert sc.last_counters["error_flags"] == 0 and img.max() > 0
 
 
-@pytest.mark.parametrize("case,centre", [("TwoSpheresPlane", (0, 1, -0.5)), ("TorusMesh_flat", (0, 0, 0)), ("TorusMesh_smooth", (0, 0, 0)),
-                                         ("MeshInNode", (0, 1, 0)), ("NovelScene2_small", (0, 1, 0)), ("Fuzz12", (0, 1, 0))])
-def test_packet_any_hit_walk_equals_per_ray_walk(case, centre):
-    """The level-0 shadow kernel walks the object BVH and the mesh LBVHs WARP by warp (occluded_packet: one node per step for
-    all 32 lanes, a child is entered when any lane's ray touches it, leaves are tested once per warp).  Any-hit answers do not
-    depend on the visiting order, so every ray must get exactly the answer of its own walk - also for rays that have nothing
-    in common (random rays here; in the renderer the 32 rays of a warp are nearly the same ray)."""
-    sc = load_case(case)
-    rng = np.random.default_rng(77)
-    n = 30000 + 17                                                     # a ragged last warp
-    o, d = _random_rays(rng, n, np.array(centre, dtype=np.float64))
-    tmax = np.where(rng.random(n) < 0.5, 1.0, np.inf).astype(np.float32)
-    times = rng.choice(np.asarray(sc.vc.motion_times, dtype=np.float64), size=n).astype(np.float32)
-    per_ray = sc.occluded(o, d, tmax, times)
-    packet = sc.occluded(o, d, tmax, times, mesh_mode=4)
-    assert np.array_equal(per_ray, packet)
-    assert 0 < per_ray.sum() < n
-    if sc.flatten().desc.n_meshes:                                     # and with the brute-force face loop inside the packet walk
-        assert np.array_equal(per_ray, sc.occluded(o, d, tmax, times, mesh_mode=5))
-
-
 def test_ref_instances_share_one_lbvh_and_moving_meshes_extension():
     """SURVEY 8f rank 3 on the device: (a) the three instances of a `ref`-copied node share ONE RtMesh / LBVH and render exactly
     like real deep copies; (b) with "mesh_motion": true the meshes translate by speed * time (ray taken into the mesh's rest
