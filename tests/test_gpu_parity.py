@@ -150,7 +150,7 @@ def test_every_kernel_variant_in_many_small_batches_on_two_streams(case, over, l
         ctr = abi.RtCounters()
         abi.check(lib, lib.rt_render_host(h, C.byref(job), host.data_ptr(), C.byref(ctr), None), "rt_render_host")
         assert np.array_equal(host.numpy().reshape(W, H, 3), ref), (case, batch)
-        assert ctr.error_flags == 0 and (batch > 1500 or ctr.kernel_launches > 20)
+        assert ctr.error_flags == 0 and (batch > 1500 or ctr.kernel_launches >= 8)      # several batches
 
 
 @pytest.mark.parametrize("world", [2, 3, 8])
