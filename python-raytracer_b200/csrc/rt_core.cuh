@@ -886,7 +886,9 @@ RT_HD void leaf_hits(TraceCtx& cx, int oi, const Ray& r, Want&& want, Cand&& can
 // order == list order; boolean any).
 struct NodeFrame { int obj; int cursor; Ray ray; float3 inv; };
 
-template <int V, class Want, class Emit>
+// ROOT_IS_NODE: the caller knows that `root` is a node (closest_hit): the leaf-root branch - a second copy of leaf_hits and of the
+// whole climb - is not compiled (the node kernels are instruction-fetch bound)
+template <int V, bool ROOT_IS_NODE = false, class Want, class Emit>
 RT_HD void object_hits(TraceCtx& cx, int root, const Ray& r, Want&& want, Emit&& emit) {
     const DevObject* objs = cx.S.objects;
     NodeFrame fr[RT_MAX_NEST];
@@ -917,7 +919,7 @@ RT_HD void object_hits(TraceCtx& cx, int root, const Ray& r, Want&& want, Emit&&
         emit(h);
     };
     if (!child_may_hit(cx.S, root, r, csg_ray_inv(r))) return;      // (roots that are top-level objects always pass)
-    if (objs[root].kind != RT_KIND_NODE) { leaf_hits<V>(cx, root, r, want, cand); return; }
+    if (!ROOT_IS_NODE && objs[root].kind != RT_KIND_NODE) { leaf_hits<V>(cx, root, r, want, cand); return; }
     auto push = [&](int oi, const Ray& pr) {
         const DevXform* xf = cx.S.xforms + objs[oi].xform;
         depth++;
@@ -1020,7 +1022,7 @@ RT_HD bool closest_hit(TraceCtx& cx, const Ray& r, Hit& out) {
                 !(en > ex || en < 0.0f) && RT_BETTER(en)) { best = en; best_obj = oi; best_aux = label; }
         } else if (HAS_NODES && kind == RT_KIND_NODE) {
             // inside one node the first hit in DFS (= list) order wins equal t: strict '<' once this node holds the best
-            object_hits<HAS_NODES>(cx, oi, r, [&](float t) { return RT_BETTER(t); },
+            object_hits<HAS_NODES, true>(cx, oi, r, [&](float t) { return RT_BETTER(t); },
                         [&](const Hit& h) { if (RT_BETTER(h.t)) { best = h.t; best_obj = oi; node_hit = h; } });
         }
     }
