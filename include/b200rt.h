@@ -236,11 +236,15 @@ int rt_scene_build_bvh(RtScene* scene, void* stream);
  * counters may be NULL; when given, the call synchronises the stream before returning.
  * The job rectangle must lie inside the frame (RT_ERR_INVALID otherwise).  ONE render call may be in flight per scene
  * handle: the wavefront buffers (samples, hit records, ray queues, counters) belong to the handle and are re-used and
- * re-grown by every call; use one handle per stream for concurrent renders.  The caller's current device is preserved. */
+ * re-grown by every call; use one handle per stream for concurrent renders.  The caller's current device is preserved.
+ * Frames of more than one wavefront batch (64 Mi rays) are worked on two streams inside the call - level 0 of every batch on
+ * `stream`, the deeper levels of the batch before it on a high-priority side stream of the handle - and joined before the call
+ * returns its work to `stream`: to the caller the call is ordered on `stream` like a single kernel. */
 int rt_render(RtScene* scene, const RtRenderJob* job, float* d_out, RtCounters* counters, void* stream);
 
 /* Same, HOST output buffer (pageable or pinned): device staging + D2H copy inside the call;
- * synchronous.  This is the end-to-end call Scene.render() uses. */
+ * synchronous.  This is the end-to-end call Scene.render() uses.  A page-locked destination (cudaHostAlloc / cudaHostRegister)
+ * receives the part of the frame every batch completes while the later batches still render. */
 int rt_render_host(RtScene* scene, const RtRenderJob* job, float* h_out, RtCounters* counters, void* stream);
 
 /* rt_render for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
