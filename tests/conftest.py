@@ -182,3 +182,15 @@ def morton63_keys(verts_f32, faces):
             u = (u | u << np.uint64(sh)) & np.uint64(mask)
         return u
     return (expand(q[:, 0]) << np.uint64(2)) | (expand(q[:, 1]) << np.uint64(1)) | expand(q[:, 2])
+
+
+def many_meshes_scene(n=11, resolution=(96, 72)):
+    """TorusMesh with `n` top-level torus meshes (flat and smooth alternating) on a ring: more than the RT_CONST_MESH = 8 headers the
+    lean kernels keep in the parameter bank, so the scene runs on the general kernels (rt_scene_build.hpp convert_scene)."""
+    import math
+    objs = [{"materials": [1, 0], "name": "plane", "normal": [0.0, 1.0, 0.0], "position": [0.0, -1.0, 0.0], "type": "plane"}]
+    for k in range(n):
+        a = 2 * math.pi * k / n
+        objs.append({"filepath": "./meshes/torus.obj", "flat_shaded": k % 2 == 0, "materials": [2], "name": f"torus{k}",
+                     "position": [1.6 * math.cos(a), 0.3 * math.sin(3 * a), 1.6 * math.sin(a)], "scale": 0.35, "type": "mesh"})
+    return load_case("TorusMesh_flat", {"objects": objs, "resolution": list(resolution)})

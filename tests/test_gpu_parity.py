@@ -527,6 +527,26 @@ def test_gpu_lbvh_equals_host_restatement_on_a_large_mesh_with_equal_keys(lib):
     assert sc.last_counters["error_flags"] == 0 and img.max() > 0
 
 
+def test_more_top_level_meshes_than_the_parameter_bank_holds():
+    """11 top-level meshes (> RT_CONST_MESH = 8): the scene runs on the general kernels (variant 2), mesh headers from global
+    memory; against the oracle, BVH == brute force, several batches == one."""
+    from conftest import many_meshes_scene
+    sc = many_meshes_scene()
+    W, H = sc.vc.width, sc.vc.height
+    img = sc.render_region(0, W, 0, H).copy()
+    ref, c_ref = oracle.render(sc.flatten(), abi)
+    frac, dmax, _ = parity_stats(to_png_array(img), to_png_array(ref))
+    assert frac >= PARITY_FRACTION, (frac, dmax)
+    c = sc.last_counters
+    assert c["error_flags"] == 0 and c["rays_primary"] == c_ref["rays_primary"] and c["tri_tests"] > 0
+    assert np.array_equal(sc.render_region(0, W, 0, H, mesh_mode=3), img)
+    h = sc.upload()
+    out = np.empty((W, H, 3), np.float32)
+    job = sc.make_job(0, W, 0, H, max_batch_rays=1000)
+    abi.check(sc._lib, sc._lib.rt_render_host(h, C.byref(job), out.ctypes.data, None, None), "rt_render_host")
+    assert np.array_equal(out, img)
+
+
 def test_ref_instances_share_one_lbvh_and_moving_meshes_extension():
     """SURVEY 8f rank 3 on the device: (a) the three instances of a `ref`-copied node share ONE RtMesh / LBVH and render exactly
     like real deep copies; (b) with "mesh_motion": true the meshes translate by speed * time (ray taken into the mesh's rest

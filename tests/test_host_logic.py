@@ -189,6 +189,22 @@ def test_device_functions_on_host_match_oracle(case):
     assert c_sim["error_flags"] == 0
 
 
+def test_more_top_level_meshes_than_the_parameter_bank_holds():
+    """11 top-level meshes: convert_scene routes the scene to the general kernels (the lean ones read at most RT_CONST_MESH = 8 mesh
+    headers from the parameter bank); host twin against the oracle, and the BVHs only prune."""
+    from conftest import many_meshes_scene
+    sc = many_meshes_scene()
+    fs = sc.flatten()
+    assert fs.desc.n_meshes >= 1 and sum(1 for o in sc.objects if type(o).__name__ == "Mesh") == 11
+    ref, c_ref = oracle.render(fs, abi)
+    img, c_sim = hostsim.render(fs, abi)
+    frac, dmax, _ = parity_stats(to_png_array(ref), to_png_array(img))
+    assert frac >= 0.999, (frac, dmax)
+    assert c_sim["error_flags"] == 0 and c_sim["tri_tests"] > 0
+    plain, _ = hostsim.render(fs, abi, mesh_mode=3)
+    assert np.array_equal(img, plain)
+
+
 @pytest.mark.parametrize("seed", FUZZ_HOST_SEEDS)
 def test_device_functions_on_host_match_oracle_on_random_scenes(seed):
     """Fresh random scenes (nested CSG, `ref` copies, meshes in nodes, moving objects, textures, DOF / motion / jitter):
