@@ -494,8 +494,8 @@ static int sync_device_view(RtScene* sc, const SceneView& V, cudaStream_t st) {
     return RT_OK;
 }
 template <int HAS_NODES> static ViewArg<(HAS_NODES != 0)> view_arg(RtScene* sc, const SceneView& V) {
-    if constexpr (HAS_NODES != 0) return ViewArg<true>{sc->d_view};
-    else return ViewArg<false>{V};
+    if constexpr (HAS_NODES != 0) return ViewArg<true>{V, sc->d_view};
+    else return ViewArg<false>{V, nullptr};
 }
 // kernel variant of a scene (rt_core.cuh): 0 lean, 1 nodes without any mesh, 2 nodes and meshes
 static int scene_variant(const RtScene* sc) { return !sc->has_nodes ? RT_V_LEAN : (sc->has_mesh ? RT_V_NODES_MESH : RT_V_NODES); }

@@ -42,15 +42,24 @@ struct TraceCtx {
     int sbase;           // entries below sbase belong to the object-BVH walk in progress (top_next)
     int* spill;          // entries RT_STACK_DEPTH.. of the stack: RT_STACK_SPILL ints of thread-local memory owned by the kernel,
                          // touched only by unusually deep walks (kept OUT of this struct so its scalars stay in registers)
+    // General kernels: S above is the kernel's by-value parameter (constant bank) for everything that is inlined into the kernel;
+    // the out-of-line node functions get a context whose S is the one copy in global memory (global()), because a reference to
+    // the parameter that reaches a real call makes the compiler copy the whole parameter into every thread's stack frame.  So: a
+    // context bound to the parameter must never be passed to an RT_HD_NOINLINE function - pass cx.global().  Sg == nullptr (lean
+    // kernels, host twin): there is no such function on the path / no such distinction.
+    const SceneView* Sg;
 #if defined(__CUDA_ARCH__)
-    __device__ __forceinline__ TraceCtx(const SceneView& S_, float time_, Tally& tally_, int* stack_, int /*stride: RT_BLOCK*/, int* spill_)
-        : S(S_), time(time_), tally(tally_), sbase(0), spill(spill_) {
+    __device__ __forceinline__ TraceCtx(const SceneView& S_, float time_, Tally& tally_, int* stack_, int /*stride: RT_BLOCK*/, int* spill_, const SceneView* Sg_ = nullptr)
+        : S(S_), time(time_), tally(tally_), sbase(0), spill(spill_), Sg(Sg_) {
         // the volatile move keeps the address in a register: left to itself the compiler re-derives it (two S2R, LEA, ...) at every use
         asm volatile("mov.u32 %0, %1;" : "=r"(saddr) : "r"(stack_ ? (unsigned)__cvta_generic_to_shared(stack_) : 0u));
     }
+    __device__ __forceinline__ TraceCtx(const SceneView& S_, const TraceCtx& o) : S(S_), time(o.time), tally(o.tally), saddr(o.saddr), sbase(o.sbase), spill(o.spill), Sg(o.Sg) {}
+    __device__ __forceinline__ TraceCtx global() const { return TraceCtx(*Sg, *this); }      // (only the general kernels call it: Sg is set)
 #else
-    TraceCtx(const SceneView& S_, float time_, Tally& tally_, int* stack_, int stride_, int* spill_)
-        : S(S_), time(time_), tally(tally_), stack(stack_), stack_stride(stride_), sbase(0), spill(spill_) {}
+    TraceCtx(const SceneView& S_, float time_, Tally& tally_, int* stack_, int stride_, int* spill_, const SceneView* Sg_ = nullptr)
+        : S(S_), time(time_), tally(tally_), stack(stack_), stack_stride(stride_), sbase(0), spill(spill_), Sg(Sg_) {}
+    TraceCtx global() const { return *this; }
 #endif
 };
 #define RT_STACK_PITCH (4 * RT_BLOCK)    // bytes between consecutive entries of one thread's stack (entries of a warp's lanes are adjacent words)
@@ -847,7 +856,7 @@ RT_HD void leaf_hits(TraceCtx& cx, int oi, const Ray& r, Want&& want, Cand&& can
     const DevObject* o = cx.S.objects + oi;
     cx.tally.prims++;
     const int kind = o->kind;
-    if (V != RT_V_NODES && kind == RT_KIND_MESH) { mesh_leaf_hits(cx, oi, r, want, cand); return; }   // out of line: rare under nodes, and large
+    if (V != RT_V_NODES && kind == RT_KIND_MESH) { TraceCtx gx = cx.global(); mesh_leaf_hits(gx, oi, r, want, cand); return; }   // out of line: rare under nodes, and large
     float ts[2]; int nt = 0;
     float3 nrm = f3(0, 0, 0), center = f3(0, 0, 0);
     if (kind == RT_KIND_SPHERE) {                                  // simple_geometry.py:20-46: both roots with t > 0
@@ -894,6 +903,7 @@ RT_HD void object_hits(TraceCtx& cx, int root, const Ray& r, Want&& want, Emit&&
     NodeFrame fr[RT_MAX_NEST];
     int depth = -1;
     int leaf = root;
+    TraceCtx gx = cx.global();                         // for the out-of-line is_inside / get_material calls of the climb
     auto cand = [&](Hit h) {
         int child = leaf;
         for (int lv = depth; lv >= 0; lv--) {
@@ -901,17 +911,17 @@ RT_HD void object_hits(TraceCtx& cx, int root, const Ray& r, Want&& want, Emit&&
             const int c0 = nd->first_child, nc = nd->n_children;
             if (nd->csg == RT_CSG_INTERSECTION) {                  // hierarchy.py:52-57: every OTHER child contains it
                 for (int j = 0; j < nc; j++)
-                    if (c0 + j != child && !csg_inside(cx, c0 + j, h.p)) return;
+                    if (c0 + j != child && !csg_inside(gx, c0 + j, h.p)) return;
             } else if (nd->csg == RT_CSG_DIFFERENCE) {             // hierarchy.py:58-70
-                if (child == c0) { if (csg_inside(cx, c0 + 1, h.p)) return; }
+                if (child == c0) { if (csg_inside(gx, c0 + 1, h.p)) return; }
                 else {
-                    if (!csg_inside(cx, c0, h.p)) return;
-                    h.mat = csg_material(cx, c0, h.p);
+                    if (!csg_inside(gx, c0, h.p)) return;
+                    h.mat = csg_material(gx, c0, h.p);
                     h.n = -h.n;
                 }
             }
             if (h.mat == -1) h.mat = nd->n_mats > 0 ? nd->mat0 : -2;    // hierarchy.py:73-74
-            const DevXform* xf = cx.S.xforms + nd->xform;
+            const DevXform* xf = gx.S.xforms + nd->xform;      // (gx, not cx: this closure travels to the out-of-line mesh_leaf_hits)
             h.p = xform_point(xf->M, h.p);                          // hierarchy.py:75
             h.n = xform_normal(xf->Minv, h.n);                      // hierarchy.py:76
             child = fr[lv].obj;
@@ -1071,7 +1081,7 @@ RT_HD bool object_shadow(TraceCtx& cx, int oi, const Ray& r, float A, float tmax
     }
     if (kind == RT_KIND_MESH) return false;                           // (linear test mode only) traversed after the walk
     if (kind != RT_KIND_NODE) return leaf_shadow<false>(cx, oi, r, tmax);
-    if constexpr (HAS_NODES != 0) return csg_shadow<HAS_NODES>(cx, oi, r, tmax);
+    if constexpr (HAS_NODES != 0) { TraceCtx gx = cx.global(); return csg_shadow<HAS_NODES>(gx, oi, r, tmax); }
     else return false;
 }
 

@@ -117,14 +117,14 @@ __device__ __forceinline__ void tally_flush(const Tally& t, unsigned long long p
 
 __device__ __forceinline__ Tally tally_zero() { Tally t; t.shadow = t.reflect = t.refract = t.nodes = t.tris = t.prims = t.shaded = t.smooth = t.err = 0; return t; }
 
-// How a kernel receives the scene.  Lean kernels (no CSG / transform nodes): SceneView BY VALUE in the parameter bank - everything
-// is inlined, every field is a constant-bank operand.  General kernels: a pointer to ONE copy in global memory.  Their out-of-line
-// node functions (csg_inside, csg_shadow, ...) take the scene by reference; for a by-value parameter that made every THREAD copy the
-// whole SceneView into its local-memory stack frame at kernel entry and read it back from there (ptxas: 2.0 - 3.2 KB frames,
-// 512 threads per SM): one shared read-only copy stays in L1 instead.
+// How a kernel receives the scene: SceneView BY VALUE in the parameter bank (every field a constant-bank operand for the code inlined
+// into the kernel) and, for the general kernels, also a pointer to ONE copy in global memory for their out-of-line node functions
+// (csg_inside, csg_shadow, ...), which take the scene by reference (TraceCtx::global()): a reference to the by-value parameter that
+// reaches a real call made every THREAD copy the whole SceneView into its local-memory stack frame at kernel entry and read it back
+// from there (ptxas: 2.0 - 3.2 KB frames, 512 threads per SM).
 template <bool GLOBAL> struct ViewArg;
-template <> struct ViewArg<false> { SceneView v; __device__ __forceinline__ const SceneView& get() const { return v; } };
-template <> struct ViewArg<true> { const SceneView* __restrict__ p; __device__ __forceinline__ const SceneView& get() const { return *p; } };
+template <> struct ViewArg<false> { SceneView v; const SceneView* p; __device__ __forceinline__ const SceneView& get() const { return v; } };
+template <> struct ViewArg<true> { SceneView v; const SceneView* __restrict__ p; __device__ __forceinline__ const SceneView& get() const { return v; } };
 
 extern __shared__ int rt_smem_stack[];   // RT_STACK_ROWS * blockDim.x ints when the scene has a mesh or an object BVH
 // the launches allocate the shared stack area only for scenes with something to walk (b200rt.cu: has_mesh || has_tlas)
@@ -184,7 +184,7 @@ __global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_HIT_CSG : 
         }
         Hit hit;
         if (live) {
-            TraceCtx cx{S, time, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill};
+            TraceCtx cx{S, time, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill, SA.p};
             live = closest_hit<HAS_NODES>(cx, ray, hit);
         }
         if (live) {
@@ -223,7 +223,7 @@ __global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_SHADOW_CSG
         for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
             const float4 h0 = RT_LD_REC(&H.planes[0 * H.cap + i]);
             if (h0.w != h0.w) continue;                                       // no hit: no shadow rays
-            TraceCtx cx{S, h0.w, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill};
+            TraceCtx cx{S, h0.w, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill, SA.p};
             if (MODE == SHADOW_ROWS) {                                        // one byte per (light, ray)
                 RT_ST_REC(&occ[(long long)li0 * H.cap + i], (uint8_t)(light_occluded<HAS_NODES>(cx, f3(h0), li0) ? 1 : 0));
             } else {                                                          // one BIT per (light, ray): byte plane li / 8; the lanes of a warp still work on ONE light at a time
@@ -327,7 +327,7 @@ __global__ void __launch_bounds__(RT_BLOCK, HAS_NODES ? RT_MIN_BLOCKS_HIT_CSG : 
         }
         if (!__any_sync(0xffffffffu, have)) break;
         if (have) {
-            TraceCtx cx{S, time, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill};
+            TraceCtx cx{S, time, tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill, SA.p};
             float3 sample;
             if (trace_level<HAS_NODES>(cx, ps, sample)) n_queued++;      // counted like the rays the wavefront levels would have queued
             else { samples[slot] = f4(sample.x, sample.y, sample.z, 0.0f); have = false; }
@@ -398,7 +398,7 @@ __global__ void __launch_bounds__(RT_BLOCK) k_trace(const ViewArg<(HAS_NODES != 
         PathState ps;
         ps.ray.o = f3(org[3 * i], org[3 * i + 1], org[3 * i + 2]);
         ps.ray.d = f3(dir[3 * i], dir[3 * i + 1], dir[3 * i + 2]);
-        TraceCtx cx{S, times[i], tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill};
+        TraceCtx cx{S, times[i], tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill, SA.p};
         Hit h;
         if (closest_hit<HAS_NODES>(cx, ps.ray, h)) {
             hit_t[i] = h.t; hit_geom[i] = h.geom; hit_mat[i] = h.mat;
@@ -427,7 +427,7 @@ __global__ void __launch_bounds__(RT_BLOCK) k_occluded(const ViewArg<(HAS_NODES 
     const bool valid = i < n;
     const long long j = valid ? i : 0;
     Ray r; r.o = f3(org[3 * j], org[3 * j + 1], org[3 * j + 2]); r.d = f3(dir[3 * j], dir[3 * j + 1], dir[3 * j + 2]);
-    TraceCtx cx{S, times[j], tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill};
+    TraceCtx cx{S, times[j], tally, rt_smem_stack + threadIdx.x, (int)blockDim.x, spill, SA.p};
     bool o;
     o = valid && occluded<HAS_NODES>(cx, r, tmax[j]);
     if (valid) occ[i] = o ? 1 : 0;
